@@ -1,0 +1,156 @@
+// Shared device/host helpers for the sm_100a ETL kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <math.h>
+
+#include "../../include/etl_b200.h"
+
+namespace etl {
+
+// ---------------------------------------------------------------- host side
+
+void set_error(const char* fmt, ...);
+
+struct Handle {
+    int device = -1;
+    int sm_count = 0;
+    void* scratch = nullptr;       // general arena (partials, tables); contents undefined between calls
+    size_t scratch_bytes = 0;
+    uint64_t* tile_state = nullptr;  // look-back words only; zeroed when (re)allocated or on epoch wrap
+    size_t tile_words = 0;
+    uint32_t epoch = 0;            // tag of the last scan launch; 0 is never a live tag
+    unsigned int* counters = nullptr;  // 64 "last block done" tickets; zero between launches
+    // staging for the *_host entry points
+    void* stage = nullptr;
+    size_t stage_bytes = 0;
+    cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t events[12] = {};
+};
+
+// make the general arena at least `bytes` (cudaMalloc + device sync when it grows)
+int arena_reserve(Handle* h, size_t bytes);
+// make room for `words` tile-state words and hand out the tag for one scan launch
+int tile_state_acquire(Handle* h, size_t words, cudaStream_t stream, uint32_t* epoch);
+
+#define ETL_CUDA(call)                                                              \
+    do {                                                                            \
+        cudaError_t e__ = (call);                                                   \
+        if (e__ != cudaSuccess) {                                                   \
+            etl::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                           __FILE__, __LINE__);                                     \
+            return ETL_ECUDA;                                                       \
+        }                                                                           \
+    } while (0)
+
+#define ETL_REQUIRE(cond, ...)            \
+    do {                                  \
+        if (!(cond)) {                    \
+            etl::set_error(__VA_ARGS__);  \
+            return ETL_EINVAL;            \
+        }                                 \
+    } while (0)
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static inline bool aligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3) == 0; }
+static inline size_t dtype_size(int dt) { return (dt == ETL_F64 || dt == ETL_I64) ? 8 : 4; }
+
+// -------------------------------------------------------------- device side
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+// streaming 128-bit loads: read once, keep out of L1
+__device__ __forceinline__ int4 ld_stream_v4(const void* p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ double2 ld_stream_d2(const void* p) {
+    double2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    return r;
+}
+
+// tile-state word traffic for the decoupled look-back scans (one 64-bit word
+// carries tag + flag + value, so relaxed gpu-scope accesses are enough)
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ unsigned lanemask_lt() {
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// Tile-state word: [63:42] epoch (22 bits) | [41:40] flag | [39:0] value.
+constexpr int TS_VALUE_BITS = 40;
+constexpr uint64_t TS_VALUE_MASK = (1ull << TS_VALUE_BITS) - 1;
+constexpr uint64_t TS_FLAG_AGG = 1ull << TS_VALUE_BITS;
+constexpr uint64_t TS_FLAG_INCL = 2ull << TS_VALUE_BITS;
+constexpr uint64_t TS_FLAG_MASK = 3ull << TS_VALUE_BITS;
+constexpr int TS_EPOCH_SHIFT = 42;
+constexpr uint32_t TS_EPOCH_MAX = (1u << 22) - 1;
+
+// Decoupled look-back, run by ONE full warp of tile `tile`: publishes the
+// tile's aggregate, walks back over predecessors' states until it meets an
+// inclusive prefix, publishes its own inclusive prefix and returns the
+// exclusive prefix (same value in every lane).  Tiles must be dispatched in
+// index order (blockIdx order), as in any single-pass chained scan.
+__device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* state, uint32_t epoch, int64_t tile,
+                                                       uint64_t aggregate) {
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t tag = (uint64_t)epoch << TS_EPOCH_SHIFT;
+    if (tile == 0) {
+        if (lane == 0) st_relaxed_u64(state, tag | TS_FLAG_INCL | aggregate);
+        return 0;
+    }
+    if (lane == 0) st_relaxed_u64(state + tile, tag | TS_FLAG_AGG | aggregate);
+    uint64_t excl = 0;
+    int64_t j = tile - 1;
+    while (true) {
+        const int64_t idx = j - lane;
+        uint64_t s;
+        if (idx >= 0) {
+            do {
+                s = ld_relaxed_u64(state + idx);
+            } while ((s >> TS_EPOCH_SHIFT) != epoch || (s & TS_FLAG_MASK) == 0);
+        } else {
+            s = TS_FLAG_INCL;  // virtual predecessor of tile 0: inclusive prefix 0
+        }
+        const unsigned incl = __ballot_sync(0xffffffffu, (s & TS_FLAG_MASK) == TS_FLAG_INCL);
+        uint64_t v = s & TS_VALUE_MASK;
+        if (incl) {
+            const unsigned first = __ffs(incl) - 1;  // nearest predecessor holding a prefix
+            if (lane > first) v = 0;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (incl) break;
+        j -= 32;
+    }
+    if (lane == 0) st_relaxed_u64(state + tile, tag | TS_FLAG_INCL | (excl + aggregate));
+    return excl;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace etl

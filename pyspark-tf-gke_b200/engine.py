@@ -1,0 +1,185 @@
+"""Per-GPU engine: owns the C-ABI handle and wraps each entry point for torch
+device buffers.  torch is used for device memory and streams only; all compute
+is in libetl_b200.so.  No CPU path exists here: every method needs CUDA."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import ETL_F32, ETL_F64, ETL_I32, ETL_I64, F64x3, I32x3, VP3
+
+_DTYPE_CODE = {torch.float64: ETL_F64, torch.float32: ETL_F32, torch.int32: ETL_I32, torch.int64: ETL_I64}
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def words_for(n: int) -> int:
+    return (n + 31) // 32
+
+
+@dataclass
+class Column:
+    """A device column: `data` (1-D tensor) + optional validity bitmap (`valid`,
+    int32 words, Arrow bit order, 1 = non-null)."""
+
+    data: torch.Tensor
+    valid: Optional[torch.Tensor] = None
+
+    def __len__(self):
+        return self.data.shape[0]
+
+    @property
+    def dtype_code(self) -> int:
+        return _DTYPE_CODE[self.data.dtype]
+
+    @staticmethod
+    def from_host(values: np.ndarray, valid: Optional[np.ndarray], device) -> "Column":
+        data = torch.from_numpy(np.ascontiguousarray(values)).to(device)
+        bitmap = None
+        if valid is not None:
+            bitmap = torch.from_numpy(pack_validity_host(valid).view(np.int32)).to(device)
+        return Column(data, bitmap)
+
+    def valid_host(self) -> np.ndarray:
+        n = len(self)
+        if self.valid is None:
+            return np.ones(n, dtype=bool)
+        w = self.valid.cpu().numpy().view(np.uint8)
+        return np.unpackbits(w, bitorder="little")[:n].astype(bool)
+
+
+def pack_validity_host(valid: np.ndarray) -> np.ndarray:
+    valid = np.asarray(valid, dtype=bool)
+    n = valid.shape[0]
+    padded = np.zeros(words_for(n) * 32, dtype=np.uint8)
+    padded[:n] = valid
+    return np.packbits(padded, bitorder="little").view(np.uint32).copy()
+
+
+class Engine:
+    """One per GPU (replaces the per-executor SparkSession state,
+    spark_session.py:37-88)."""
+
+    def __init__(self, device: Optional[int] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("pyspark_tf_gke_b200 needs a CUDA device: there is no CPU fallback")
+        self.lib = _lib.load()
+        self.device_index = torch.cuda.current_device() if device is None else int(device)
+        self.device = torch.device("cuda", self.device_index)
+        h = C.c_void_p()
+        _lib.check(self.lib.etl_create(self.device_index, C.byref(h)))
+        self._h = h
+        self.launches = 0  # kernels of ours launched through this engine
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.etl_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def reserve(self, nbytes: int):
+        _lib.check(self.lib.etl_reserve(self._h, nbytes))
+
+    def empty(self, n: int, dtype) -> torch.Tensor:
+        return torch.empty(n, dtype=dtype, device=self.device)
+
+    # ---------------------------------------------------------------- a2
+    def null_count(self, col: Column, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """filter(col.isNull()).count() (k_means.py:23) -> device int64 scalar."""
+        out = self.empty(1, torch.int64) if out is None else out
+        _lib.check(self.lib.etl_null_count(self._h, _ptr(col.valid), len(col), out.data_ptr(), self._stream()))
+        self.launches += 1 if col.valid is not None and len(col) else 0
+        return out
+
+    # ---------------------------------------------------------------- a4
+    def sum_count(self, cols: Sequence[Column], row_valid: Optional[torch.Tensor] = None,
+                  out_sum: Optional[torch.Tensor] = None, out_count: Optional[torch.Tensor] = None):
+        """(sum, count) over ~isnan & isNotNull for up to 3 columns
+        (k_means.py:45-48) -> device tensors f64[ncols], i64[ncols]."""
+        nc = len(cols)
+        n = len(cols[0])
+        out_sum = self.empty(3, torch.float64) if out_sum is None else out_sum
+        out_count = self.empty(3, torch.int64) if out_count is None else out_count
+        val = VP3(*[_ptr(c.data) for c in cols], *([None] * (3 - nc)))
+        vv = VP3(*[_ptr(c.valid) for c in cols], *([None] * (3 - nc)))
+        dt = I32x3(*[c.dtype_code for c in cols], *([0] * (3 - nc)))
+        _lib.check(self.lib.etl_column_sum_count(self._h, nc, C.byref(val), C.byref(vv), C.byref(dt), _ptr(row_valid),
+                                                 n, out_sum.data_ptr(), out_count.data_ptr(), self._stream()))
+        self.launches += 1
+        return out_sum[:nc], out_count[:nc]
+
+    # ------------------------------------------------------------- a3/a5
+    def project_filter_impute(self, key: Column, vals: Sequence[Column], fill: Sequence[float],
+                              out_code: Optional[torch.Tensor] = None,
+                              out_vals: Optional[Sequence[torch.Tensor]] = None,
+                              out_rows: Optional[torch.Tensor] = None):
+        """filter(key.isNotNull()) + 3x when(isNull|isnan, mean).otherwise(c) as
+        double, compacted in input order (k_means.py:27-28,49-51).  Returns
+        (out_code i32[n], [3 x f64[n]], rows i64[1]) - the first `rows` entries
+        of each output are the kept rows."""
+        n = len(key)
+        assert len(vals) == 3 and len(fill) == 3
+        out_code = self.empty(n, torch.int32) if out_code is None else out_code
+        out_vals = [self.empty(n, torch.float64) for _ in range(3)] if out_vals is None else list(out_vals)
+        out_rows = self.empty(1, torch.int64) if out_rows is None else out_rows
+        val = VP3(*[_ptr(c.data) for c in vals])
+        vv = VP3(*[_ptr(c.valid) for c in vals])
+        dt = I32x3(*[c.dtype_code for c in vals])
+        fl = F64x3(*[float(f) for f in fill])
+        ov = VP3(*[t.data_ptr() for t in out_vals])
+        _lib.check(self.lib.etl_project_filter_impute(self._h, _ptr(key.data), _ptr(key.valid), C.byref(val),
+                                                      C.byref(vv), C.byref(dt), C.byref(fl), n, out_code.data_ptr(),
+                                                      C.byref(ov), out_rows.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return out_code, out_vals, out_rows
+
+    def project_filter_impute_host(self, key_code: np.ndarray, key_valid: Optional[np.ndarray],
+                                   vals: Sequence[np.ndarray], vals_valid: Sequence[Optional[np.ndarray]],
+                                   fill: Sequence[float], out_code: np.ndarray, out_vals: Sequence[np.ndarray]) -> int:
+        """Host-buffer entry (numpy arrays; bitmaps as uint32 words).  Returns the
+        kept-row count; outputs are written into the given host arrays."""
+        n = key_code.shape[0]
+        np_code = {np.dtype(np.float64): ETL_F64, np.dtype(np.float32): ETL_F32, np.dtype(np.int32): ETL_I32}
+
+        def hp(a):
+            return None if a is None else a.ctypes.data
+
+        val = VP3(*[hp(v) for v in vals])
+        vv = VP3(*[hp(v) for v in vals_valid])
+        dt = I32x3(*[np_code[v.dtype] for v in vals])
+        fl = F64x3(*[float(f) for f in fill])
+        ov = VP3(*[hp(v) for v in out_vals])
+        rows = C.c_int64(0)
+        _lib.check(self.lib.etl_project_filter_impute_host(self._h, hp(key_code), hp(key_valid), C.byref(val),
+                                                           C.byref(vv), C.byref(dt), C.byref(fl), n, hp(out_code),
+                                                           C.byref(ov), C.byref(rows)))
+        chunk = 1 << 20
+        self.launches += (n + chunk - 1) // chunk
+        return rows.value
+
+    # ------------------------------------------------------------ synth
+    def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,
+                     null_rate: float = 0.0, nan_rate: float = 0.0, with_valid: bool = True) -> Column:
+        dtype = {0: torch.float64, 1: torch.float64, 2: torch.int32, 3: torch.int64}[kind]
+        data = self.empty(n, dtype)
+        valid = torch.zeros(words_for(n), dtype=torch.int32, device=self.device) if with_valid else None
+        _lib.check(self.lib.etl_synth_column(self._h, seed, stream_id, kind, modulus, null_rate, nan_rate, row0, n,
+                                             data.data_ptr(), _ptr(valid), self._stream()))
+        self.launches += 1 if n else 0
+        return Column(data, valid)

@@ -1,0 +1,50 @@
+"""The C-ABI library loads and exports every symbol include/etl_b200.h declares
+(no compute calls: this runs without a GPU)."""
+import ctypes
+import os
+import re
+
+import pyspark_tf_gke_b200 as pkg
+from tests.conftest import ROOT
+
+
+def _declared():
+    with open(os.path.join(ROOT, "include", "etl_b200.h")) as fh:
+        text = fh.read()
+    return sorted(set(re.findall(r"ETL_API\s+[\w\s\*]+?\b(etl_\w+)\s*\(", text)))
+
+
+def test_header_declares_entry_points():
+    names = _declared()
+    assert "etl_create" in names and "etl_project_filter_impute" in names
+    assert len(names) >= 9
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(pkg._lib.LIB_PATH)
+    for name in _declared():
+        assert hasattr(lib, name), f"{name} declared in etl_b200.h but not exported"
+
+
+def test_binding_covers_every_declared_symbol():
+    assert sorted(pkg._lib.exported_names()) == _declared()
+    lib = pkg._lib.load()
+    assert lib.etl_abi_version() >= 1
+    assert lib.etl_last_error() is not None
+
+
+def test_product_does_not_import_oracle():
+    pkg_dir = os.path.join(ROOT, "pyspark-tf-gke_b200")
+    for dirpath, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                with open(os.path.join(dirpath, f)) as fh:
+                    src = fh.read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+                assert "liboracle" not in src, f
+
+
+def test_bad_arguments_are_rejected_without_a_gpu():
+    lib = pkg._lib.load()
+    assert lib.etl_reserve(None, 0) == -1
+    assert b"NULL" in lib.etl_last_error()
