@@ -1,21 +1,35 @@
 // Fused map-side projection: isNotNull filter + mean-impute + cast-to-double +
 // order-preserving compaction, one pass over the rows (k_means.py:27-28,49-51).
 //
-// One CTA = one tile of 1024 rows, 256 threads x 4 consecutive rows.  Every
-// thread issues all of its 128-bit loads first (1 x int4 of key codes and, for
-// fp64 columns, 2 x double2 per column: 7 independent 16-byte requests in
-// flight per thread), then the keep bits are ranked with warp ballots, the tile
-// total goes through a single-pass decoupled look-back (one 64-bit state word
-// per tile), kept rows are staged in shared memory in output order and leave as
-// fully coalesced stores.  HBM traffic = the algorithmic bytes: each input byte
-// is read once and each output byte written once.
+// Persistent, warp-specialised kernel.  A CTA owns a contiguous range of
+// 1024-row tiles and runs three roles over a ring of shared-memory stages:
+//   loader warp   one lane issues the tile's column slices as 1-D bulk async
+//                 copies (TMA engine, cp.async.bulk) onto the stage's `full`
+//                 mbarrier, PROJ_STAGES tiles ahead - the bytes in flight live
+//                 in shared memory, not in registers;
+//   scanner warp  once, at start: popcount of the key bitmap over the CTA's whole
+//                 row range, published as one 64-bit word per CTA; the sum of
+//                 the lower CTAs' words is this CTA's first output row (the
+//                 keep predicate depends on the bitmap alone, so the cross-CTA
+//                 scan needs no chained look-back).  Then per tile, as soon as
+//                 it has landed: popcount of its 32 key-validity words (a
+//                 validity bitmap is a stored warp ballot) + warp scan ->
+//                 per-32-row segment offsets and the tile's base row;
+//   8 consumer warps  rank = base + segment offset + popc(word & lanemask_lt),
+//                 impute / cast, and store: kept lanes of a warp write
+//                 consecutive rows, so stores are coalesced without staging.
+// No __syncthreads in the steady state; roles meet only on mbarriers.  HBM
+// traffic = the algorithmic bytes: every input byte is read once, every output
+// byte written once.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace etl {
 
-constexpr int PROJ_THREADS = 256;
-constexpr int PROJ_RPT = 4;  // rows per thread
-constexpr int PROJ_TILE = PROJ_THREADS * PROJ_RPT;
+constexpr int PROJ_TILE = 1024;
+constexpr int PROJ_CONSUMER_WARPS = 8;
+constexpr int PROJ_THREADS = (PROJ_CONSUMER_WARPS + 2) * 32;  // + loader + scanner
+constexpr int PROJ_MAX_STAGES = 6;
 
 struct ProjParams {
     const int32_t* key_code;
@@ -28,127 +42,198 @@ struct ProjParams {
     int32_t* out_code;
     double* out_val[3];
     int64_t* out_rows;
-    uint64_t* tile_state;
+    uint64_t* cta_state;  // one tagged word per CTA: kept rows of its range
     uint32_t epoch;
+    int stages;
+    int64_t tiles_per_cta;
 };
 
-// 4 consecutive values of one column as doubles (the implicit cast of the
-// when/otherwise expression).  Full tiles take the 128-bit path.
-__device__ __forceinline__ void load4_full(const void* base, int dtype, int64_t row, double v[4]) {
-    if (dtype == ETL_F64) {
-        const double2 a = ld_stream_d2(static_cast<const double*>(base) + row);
-        const double2 b = ld_stream_d2(static_cast<const double*>(base) + row + 2);
-        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-    } else {
-        const int4 q = ld_stream_v4(static_cast<const int32_t*>(base) + row);
-        if (dtype == ETL_F32) {
-            v[0] = (double)__int_as_float(q.x); v[1] = (double)__int_as_float(q.y);
-            v[2] = (double)__int_as_float(q.z); v[3] = (double)__int_as_float(q.w);
-        } else {
-            v[0] = (double)q.x; v[1] = (double)q.y; v[2] = (double)q.z; v[3] = (double)q.w;
-        }
-    }
+struct __align__(128) ProjStage {
+    double val[3][PROJ_TILE];  // raw column slices; 4-byte dtypes use the first half of a slot
+    int32_t code[PROJ_TILE];
+    uint32_t valid[4][32];     // key, val0, val1, val2 bitmap words of the tile
+};
+
+__device__ __forceinline__ uint32_t seg_mask(int seg, int rows) {
+    const int left = rows - seg * 32;
+    return left >= 32 ? 0xffffffffu : (left <= 0 ? 0u : ((1u << left) - 1));
 }
 
-__device__ __forceinline__ double load1(const void* base, int dtype, int64_t row) {
-    if (dtype == ETL_F64) return static_cast<const double*>(base)[row];
-    if (dtype == ETL_F32) return (double)static_cast<const float*>(base)[row];
-    return (double)static_cast<const int32_t*>(base)[row];
+__device__ __forceinline__ double stage_value(const ProjStage& st, int c, int dtype, int r) {
+    if (dtype == ETL_F64) return st.val[c][r];
+    if (dtype == ETL_F32) return (double)reinterpret_cast<const float*>(st.val[c])[r];
+    return (double)reinterpret_cast<const int32_t*>(st.val[c])[r];
 }
 
-// the 4 validity bits of rows [row, row+4), row % 4 == 0; rows >= n read as 0
-__device__ __forceinline__ unsigned valid_nibble(const uint32_t* bitmap, int64_t row, int64_t n) {
-    unsigned nib = 0xF;
-    if (bitmap) nib = (__ldg(bitmap + (row >> 5)) >> (row & 31)) & 0xF;
-    const int64_t left = n - row;
-    if (left < 4) nib &= left <= 0 ? 0u : ((1u << left) - 1);
-    return nib;
+// tail tile only (rows < 1024, sizes not multiples of 16 bytes): plain copies by the loader warp
+__device__ __forceinline__ void warp_copy_words(void* dst, const void* src, int words, int lane) {
+    for (int i = lane; i < words; i += 32) static_cast<uint32_t*>(dst)[i] = static_cast<const uint32_t*>(src)[i];
 }
 
 __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(const ProjParams p) {
-    __shared__ int32_t s_code[PROJ_TILE];
-    __shared__ double s_val[3][PROJ_TILE];
-    __shared__ uint32_t s_warp_count[PROJ_THREADS / 32];
-    __shared__ uint64_t s_tile_base;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ProjStage* stages = reinterpret_cast<ProjStage*>(smem_raw);
+    __shared__ uint64_t full_bar[PROJ_MAX_STAGES], scan_bar[PROJ_MAX_STAGES], empty_bar[PROJ_MAX_STAGES];
+    __shared__ uint32_t s_seg_off[PROJ_MAX_STAGES][32];
+    __shared__ uint64_t s_base[PROJ_MAX_STAGES];
 
-    const int tid = threadIdx.x;
-    const int lane = tid & 31, warp = tid >> 5;
-    const int64_t tile = blockIdx.x;
-    const int64_t row = tile * PROJ_TILE + (int64_t)tid * PROJ_RPT;
-    const bool full = (tile + 1) * PROJ_TILE <= p.n;
-
-    // ---- loads first: everything below until the staging step depends only on
-    // the validity nibbles, so the wide loads stay in flight across the scan
-    int32_t code[4];
-    double v[3][4];
-    if (full) {
-        const int4 q = ld_stream_v4(p.key_code + row);
-        code[0] = q.x; code[1] = q.y; code[2] = q.z; code[3] = q.w;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) load4_full(p.val[c], p.val_dtype[c], row, v[c]);
-    } else {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const bool in = row + j < p.n;
-            code[j] = in ? p.key_code[row + j] : 0;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) v[c][j] = in ? load1(p.val[c], p.val_dtype[c], row + j) : 0.0;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = p.stages;
+    const int64_t tiles = (p.n + PROJ_TILE - 1) / PROJ_TILE;
+    const int64_t t_begin = (int64_t)blockIdx.x * p.tiles_per_cta;
+    const int64_t t_end = t_begin + p.tiles_per_cta < tiles ? t_begin + p.tiles_per_cta : tiles;
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&scan_bar[s], 1);
+            mbar_init(&empty_bar[s], PROJ_CONSUMER_WARPS);
         }
+        mbar_init_fence();
     }
-    const unsigned keep = valid_nibble(p.key_valid, row, p.n);
-    unsigned vnib[3];
-#pragma unroll
-    for (int c = 0; c < 3; ++c) vnib[c] = valid_nibble(p.val_valid[c], row, p.n);
-
-    // ---- rank kept rows: 4 ballots (one per row slot), rows ordered lane-major
-    const unsigned lt = lanemask_lt();
-    unsigned below = 0, warp_total = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const unsigned b = __ballot_sync(0xffffffffu, (keep >> j) & 1u);
-        below += __popc(b & lt);
-        warp_total += __popc(b);
-    }
-    if (lane == 0) s_warp_count[warp] = warp_total;
     __syncthreads();
-    unsigned warp_base = 0, tile_total = 0;
-#pragma unroll
-    for (int w = 0; w < PROJ_THREADS / 32; ++w) {
-        const unsigned cnt = s_warp_count[w];
-        if (w < warp) warp_base += cnt;
-        tile_total += cnt;
-    }
-    if (warp == 0) {
-        const uint64_t excl = lookback_exclusive(p.tile_state, p.epoch, tile, tile_total);
-        if (lane == 0) {
-            s_tile_base = excl;
-            if (tile == gridDim.x - 1) *p.out_rows = (int64_t)(excl + tile_total);
-        }
-    }
 
-    // ---- impute + stage in output order
-    unsigned pos = warp_base + below;
+    if (warp == PROJ_CONSUMER_WARPS) {
+        // ------------------------------------------------------------ loader
+        int k = 0;
+        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+            const int s = k % S;
+            if (k >= S) mbar_wait(&empty_bar[s], ((k / S) - 1) & 1);
+            ProjStage& st = stages[s];
+            const int64_t row0 = t * PROJ_TILE;
+            const int64_t left = p.n - row0;
+            if (left >= PROJ_TILE) {
+                if (lane == 0) {
+                    unsigned bytes = PROJ_TILE * 4;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        if ((keep >> j) & 1u) {
-            s_code[pos] = code[j];
+                    for (int c = 0; c < 3; ++c) bytes += PROJ_TILE * (p.val_dtype[c] == ETL_F64 ? 8 : 4);
+                    bytes += p.key_valid ? 128 : 0;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const double x = v[c][j];
-                const bool bad = !((vnib[c] >> j) & 1u) || (x != x);
-                s_val[c][pos] = bad ? p.fill[c] : x;
+                    for (int c = 0; c < 3; ++c) bytes += p.val_valid[c] ? 128 : 0;
+                    mbar_arrive_expect_tx(&full_bar[s], bytes);
+                    if (p.key_valid) bulk_load(st.valid[0], p.key_valid + (row0 >> 5), 128, &full_bar[s]);
+                    bulk_load(st.code, p.key_code + row0, PROJ_TILE * 4, &full_bar[s]);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const unsigned es = p.val_dtype[c] == ETL_F64 ? 8 : 4;
+                        bulk_load(st.val[c], static_cast<const char*>(p.val[c]) + row0 * es, PROJ_TILE * es,
+                                  &full_bar[s]);
+                        if (p.val_valid[c])
+                            bulk_load(st.valid[1 + c], p.val_valid[c] + (row0 >> 5), 128, &full_bar[s]);
+                    }
+                }
+            } else {
+                const int rows = (int)left, words = (rows + 31) >> 5;
+                warp_copy_words(st.code, p.key_code + row0, rows, lane);
+                if (p.key_valid) warp_copy_words(st.valid[0], p.key_valid + (row0 >> 5), words, lane);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const int w = p.val_dtype[c] == ETL_F64 ? 2 : 1;
+                    warp_copy_words(st.val[c], static_cast<const uint32_t*>(p.val[c]) + row0 * w, rows * w, lane);
+                    if (p.val_valid[c]) warp_copy_words(st.valid[1 + c], p.val_valid[c] + (row0 >> 5), words, lane);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full_bar[s]);
             }
-            ++pos;
+        }
+    } else if (warp == PROJ_CONSUMER_WARPS + 1) {
+        // ----------------------------------------------------------- scanner
+        // kept rows of this CTA's whole range -> cross-CTA exclusive sum
+        uint64_t running = 0;
+        if (p.key_valid) {
+            const int64_t row_end = t_end * PROJ_TILE < p.n ? t_end * PROJ_TILE : p.n;
+            const int64_t w_begin = (t_begin * PROJ_TILE) >> 5, w_end = (row_end + 31) >> 5;
+            uint64_t mine = 0;
+            for (int64_t w = w_begin + lane; w < w_end; w += 32) {
+                uint32_t bits = __ldg(p.key_valid + w);
+                if (w == w_end - 1 && (row_end & 31)) bits &= (1u << (row_end & 31)) - 1;
+                mine += __popc(bits);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+            const uint64_t tag = (uint64_t)p.epoch << TS_EPOCH_SHIFT;
+            if (lane == 0) st_relaxed_u64(p.cta_state + blockIdx.x, tag | TS_FLAG_AGG | mine);
+            uint64_t below = 0;
+            for (int i = lane; i < (int)blockIdx.x; i += 32) {
+                uint64_t sw;
+                do {
+                    sw = ld_relaxed_u64(p.cta_state + i);
+                } while ((sw >> TS_EPOCH_SHIFT) != p.epoch);
+                below += sw & TS_VALUE_MASK;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
+            running = below;
+            if (blockIdx.x == gridDim.x - 1 && lane == 0) *p.out_rows = (int64_t)(below + mine);
+        } else {
+            running = (uint64_t)t_begin * PROJ_TILE;
+            if (blockIdx.x == gridDim.x - 1 && lane == 0) *p.out_rows = p.n;
+        }
+        int k = 0;
+        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+            const int s = k % S;
+            mbar_wait(&full_bar[s], (k / S) & 1);
+            const int64_t left = p.n - t * PROJ_TILE;
+            const int rows = left >= PROJ_TILE ? PROJ_TILE : (int)left;
+            const uint32_t kw = (p.key_valid ? stages[s].valid[0][lane] : 0xffffffffu) & seg_mask(lane, rows);
+            const unsigned cnt = __popc(kw);
+            unsigned incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += up;
+            }
+            s_seg_off[s][lane] = incl - cnt;
+            if (lane == 0) s_base[s] = running;
+            running += __shfl_sync(0xffffffffu, incl, 31);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&scan_bar[s]);
+        }
+    } else {
+        // --------------------------------------------------------- consumers
+        const unsigned lt = lanemask_lt();
+        int k = 0;
+        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+            const int s = k % S;
+            const unsigned ph = (k / S) & 1;
+            mbar_wait(&full_bar[s], ph);
+            mbar_wait(&scan_bar[s], ph);
+            const ProjStage& st = stages[s];
+            const int64_t left = p.n - t * PROJ_TILE;
+            const int rows = left >= PROJ_TILE ? PROJ_TILE : (int)left;
+            const uint64_t base = s_base[s];
+            int32_t code[4];
+            double x[3][4];
+            uint64_t pos[4];
+            bool keep[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int g = j * PROJ_CONSUMER_WARPS + warp;  // 32-row segment = bitmap word
+                const int r = g * 32 + lane;
+                const uint32_t m = seg_mask(g, rows);
+                const uint32_t kw = (p.key_valid ? st.valid[0][g] : 0xffffffffu) & m;
+                keep[j] = (kw >> lane) & 1u;
+                pos[j] = base + s_seg_off[s][g] + __popc(kw & lt);
+                code[j] = st.code[r];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const uint32_t vw = p.val_valid[c] ? st.valid[1 + c][g] : 0xffffffffu;
+                    const double v = stage_value(st, c, p.val_dtype[c], r);
+                    const bool bad = !((vw >> lane) & 1u) || (v != v);
+                    x[c][j] = bad ? p.fill[c] : v;
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);  // stage may be refilled while we store
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (keep[j]) {
+                    p.out_code[pos[j]] = code[j];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) p.out_val[c][pos[j]] = x[c][j];
+                }
+            }
         }
     }
-    __syncthreads();
-
-    // ---- coalesced copy-out of the tile's kept rows
-    const uint64_t base = s_tile_base;
-    for (unsigned i = tid; i < tile_total; i += PROJ_THREADS) p.out_code[base + i] = s_code[i];
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-        for (unsigned i = tid; i < tile_total; i += PROJ_THREADS) p.out_val[c][base + i] = s_val[c][i];
 }
 
 static int check_project_args(const int32_t* key_code, const void* const val[3], const uint32_t* key_valid,
@@ -190,10 +275,38 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
     p.n = n;
     p.out_code = out_code;
     p.out_rows = d_out_rows;
-    int rc = tile_state_acquire(h, (size_t)tiles, stream, &p.epoch);
+    // persistent grid: every CTA must be resident (a CTA waits for the lower CTAs' counts)
+    static int s_stages = 0, s_ctas_per_sm = 0;
+    if (s_stages == 0) {
+        int stages = 3;
+        if (const char* e = getenv("ETL_PROJ_STAGES")) stages = atoi(e);
+        if (stages < 2) stages = 2;
+        if (stages > PROJ_MAX_STAGES) stages = PROJ_MAX_STAGES;
+        const size_t dyn = (size_t)stages * sizeof(ProjStage);
+        ETL_CUDA(cudaFuncSetAttribute(project_filter_impute_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)dyn));
+        int occ = 0;
+        ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, project_filter_impute_kernel, PROJ_THREADS, dyn));
+        if (occ < 1) {
+            set_error("project: kernel does not fit on an SM with %d stages", stages);
+            return ETL_ECUDA;
+        }
+        if (const char* e = getenv("ETL_PROJ_CTAS_PER_SM")) {
+            const int want = atoi(e);
+            if (want >= 1 && want < occ) occ = want;
+        }
+        s_ctas_per_sm = occ;
+        s_stages = stages;
+    }
+    p.stages = s_stages;
+    int64_t grid = (int64_t)h->sm_count * s_ctas_per_sm;
+    if (grid > tiles) grid = tiles;
+    p.tiles_per_cta = (tiles + grid - 1) / grid;
+    grid = (tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;  // no empty CTAs
+    int rc = tile_state_acquire(h, (size_t)grid, stream, &p.epoch);
     if (rc != ETL_OK) return rc;
-    p.tile_state = h->tile_state;
-    project_filter_impute_kernel<<<(unsigned)tiles, PROJ_THREADS, 0, stream>>>(p);
+    p.cta_state = h->tile_state;
+    project_filter_impute_kernel<<<(unsigned)grid, PROJ_THREADS, (size_t)s_stages * sizeof(ProjStage), stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }
