@@ -80,7 +80,7 @@ ETL_API int etl_reserve(etl_handle* h, size_t bytes);
  * replaced by fill[c].  val_dtype[c] is the input dtype of column c (ETL_F64 /
  * ETL_F32 / ETL_I32; an integer column cannot hold NaN).  out_* must hold n
  * rows.  *d_out_rows (device int64) receives the kept-row count.
- * Scratch: one 8-byte word per CTA of the persistent grid, from the handle. */
+ * Scratch: one 8-byte word per chunk (<= 65536 chunks), from the handle. */
 ETL_API int etl_project_filter_impute(etl_handle* h,
                               const int32_t* key_code, const uint32_t* key_valid,
                               const void* const val[3], const uint32_t* const val_valid[3],

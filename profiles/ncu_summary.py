@@ -1,0 +1,27 @@
+#!/usr/bin/env python
+"""Summarise an .ncu-rep (read here, no GPU needed): python profiles/ncu_summary.py file.ncu-rep"""
+import csv, io, subprocess, sys
+WANT = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum',
+        'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed', 'dram__throughput.avg.pct_of_peak_sustained_elapsed',
+        'sm__warps_active.avg.pct_of_peak_sustained_active', 'launch__registers_per_thread', 'launch__grid_size',
+        'launch__block_size', 'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem',
+        'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__throughput.avg.pct_of_peak_sustained_elapsed',
+        'lts__throughput.avg.pct_of_peak_sustained_elapsed', 'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+        'l1tex__data_pipe_lsu_wavefronts_mem_shared.sum', 'smsp__inst_executed.sum', 'sm__inst_executed_pipe_lsu.sum',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'lts__t_sector_hit_rate.pct',
+        'lts__t_sectors_srcunit_tex_op_write.sum', 'lts__t_sectors_srcunit_tex_op_read.sum', 'lts__t_sectors_op_red.sum',
+        'lts__t_sectors_op_atom.sum']
+def main(path):
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units = rows[0], rows[1]
+    for r in rows[2:]:
+        print('==', r[hdr.index('Kernel Name')][:80], 'grid', r[hdr.index('Grid Size')] if 'Grid Size' in hdr else '')
+        for w in WANT:
+            if w in hdr:
+                i = hdr.index(w); print(f'  {w:70s} {r[i]} {units[i]}')
+        stalls = [(float(r[i] or 0), h) for i, h in enumerate(hdr) if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct') and r[i]]
+        for v, h in sorted(stalls, reverse=True)[:6]:
+            print(f'  stall {h.split("stalled_")[1][:-20]:40s} {v:.1f} %')
+if __name__ == '__main__':
+    main(sys.argv[1])

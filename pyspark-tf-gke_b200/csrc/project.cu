@@ -1,26 +1,28 @@
 // Fused map-side projection: isNotNull filter + mean-impute + cast-to-double +
 // order-preserving compaction, one pass over the rows (k_means.py:27-28,49-51).
 //
-// Persistent, warp-specialised kernel.  A CTA owns a contiguous range of
-// 1024-row tiles and runs three roles over a ring of shared-memory stages:
-//   loader warp   one lane issues the tile's column slices as 1-D bulk async
-//                 copies (TMA engine, cp.async.bulk) onto the stage's `full`
-//                 mbarrier, PROJ_STAGES tiles ahead - the bytes in flight live
-//                 in shared memory, not in registers;
-//   scanner warp  once, at start: popcount of the key bitmap over the CTA's whole
-//                 row range, published as one 64-bit word per CTA; the sum of
-//                 the lower CTAs' words is this CTA's first output row (the
-//                 keep predicate depends on the bitmap alone, so the cross-CTA
-//                 scan needs no chained look-back).  Then per tile, as soon as
-//                 it has landed: popcount of its 32 key-validity words (a
-//                 validity bitmap is a stored warp ballot) + warp scan ->
-//                 per-32-row segment offsets and the tile's base row;
+// Persistent, warp-specialised kernel.  Rows are cut into 1024-row tiles and
+// tiles into chunks (1 tile each unless the table is huge); CTAs claim chunks
+// dynamically (first one static, then an atomic ticket) so no SM idles at the
+// tail.  Three roles meet only on mbarriers, over a ring of shared-memory
+// stages - no __syncthreads in the steady state:
+//   loader warp   claims chunks; one lane issues each tile's column slices as
+//                 1-D bulk async copies (TMA engine, cp.async.bulk) onto the
+//                 stage's `full` mbarrier, PROJ_STAGES tiles ahead - the bytes
+//                 in flight live in shared memory, not in registers;
+//   scanner warp  the keep predicate depends on the key bitmap alone, so at start
+//                 the CTA popcounts the bitmap of its share of the chunks into
+//                 one tagged 64-bit word per chunk in scratch, and a chunk's
+//                 first output row is just the sum of the lower chunks' words -
+//                 no chained look-back; the scanner keeps that sum incrementally
+//                 from chunk to chunk.  Per tile, once it has landed: popcount of its 32 key
+//                 validity words (a validity bitmap is a stored warp ballot) +
+//                 warp scan -> per-32-row segment offsets and the tile's base;
 //   8 consumer warps  rank = base + segment offset + popc(word & lanemask_lt),
 //                 impute / cast, and store: kept lanes of a warp write
 //                 consecutive rows, so stores are coalesced without staging.
-// No __syncthreads in the steady state; roles meet only on mbarriers.  HBM
-// traffic = the algorithmic bytes: every input byte is read once, every output
-// byte written once.
+// HBM traffic = the algorithmic bytes: every input byte is read once, every
+// output byte written once (plus 4 B of bitmap per 32 rows read twice).
 #include "common.cuh"
 #include <stdlib.h>
 
@@ -30,6 +32,7 @@ constexpr int PROJ_TILE = 1024;
 constexpr int PROJ_CONSUMER_WARPS = 8;
 constexpr int PROJ_THREADS = (PROJ_CONSUMER_WARPS + 2) * 32;  // + loader + scanner
 constexpr int PROJ_MAX_STAGES = 6;
+constexpr int64_t PROJ_MAX_CHUNKS = 1 << 16;
 
 struct ProjParams {
     const int32_t* key_code;
@@ -42,10 +45,12 @@ struct ProjParams {
     int32_t* out_code;
     double* out_val[3];
     int64_t* out_rows;
-    uint64_t* cta_state;  // one tagged word per CTA: kept rows of its range
+    uint64_t* chunk_state;   // one tagged word per chunk: kept rows of the chunk
+    unsigned int* ticket;    // [0] next chunk to claim, [1] CTAs finished; both 0 between launches
     uint32_t epoch;
     int stages;
-    int64_t tiles_per_cta;
+    int chunk_tiles;
+    int64_t chunks;
 };
 
 struct __align__(128) ProjStage {
@@ -76,12 +81,11 @@ __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(con
     __shared__ uint64_t full_bar[PROJ_MAX_STAGES], scan_bar[PROJ_MAX_STAGES], empty_bar[PROJ_MAX_STAGES];
     __shared__ uint32_t s_seg_off[PROJ_MAX_STAGES][32];
     __shared__ uint64_t s_base[PROJ_MAX_STAGES];
+    __shared__ int64_t s_tile[PROJ_MAX_STAGES];  // tile in the stage, -1 = no more work
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = p.stages;
     const int64_t tiles = (p.n + PROJ_TILE - 1) / PROJ_TILE;
-    const int64_t t_begin = (int64_t)blockIdx.x * p.tiles_per_cta;
-    const int64_t t_end = t_begin + p.tiles_per_cta < tiles ? t_begin + p.tiles_per_cta : tiles;
     if (tid == 0) {
         for (int s = 0; s < S; ++s) {
             mbar_init(&full_bar[s], 1);
@@ -92,17 +96,63 @@ __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(con
     }
     __syncthreads();
 
+    if (warp != PROJ_CONSUMER_WARPS && p.key_valid) {
+        // Every warp but the loader: kept rows of this CTA's share of the chunks
+        // (blockIdx.x, + gridDim.x, ...; lowest first - they are needed first),
+        // published as tagged words.  Nobody waits here; readers spin on the tag.
+        const uint64_t tag = (uint64_t)p.epoch << TS_EPOCH_SHIFT;
+        const int64_t chunk_rows = (int64_t)p.chunk_tiles * PROJ_TILE;
+        const int cw = warp < PROJ_CONSUMER_WARPS ? warp : PROJ_CONSUMER_WARPS;  // 0..8
+        for (int64_t c = blockIdx.x + (int64_t)cw * gridDim.x; c < p.chunks;
+             c += (int64_t)(PROJ_CONSUMER_WARPS + 1) * gridDim.x) {
+            const int64_t r0 = c * chunk_rows;
+            const int64_t r1 = r0 + chunk_rows < p.n ? r0 + chunk_rows : p.n;
+            const int64_t w0 = r0 >> 5, w1 = (r1 + 31) >> 5;
+            uint64_t mine = 0;
+            for (int64_t w = w0 + lane; w < w1; w += 32 * 4) {
+                uint32_t bits[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) bits[u] = w + 32 * u < w1 ? __ldg(p.key_valid + w + 32 * u) : 0u;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (w + 32 * u == w1 - 1 && (r1 & 31)) bits[u] &= (1u << (r1 & 31)) - 1;
+                    mine += __popc(bits[u]);
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+            if (lane == 0) st_relaxed_u64(p.chunk_state + c, tag | TS_FLAG_AGG | mine);
+        }
+    }
+
     if (warp == PROJ_CONSUMER_WARPS) {
         // ------------------------------------------------------------ loader
-        int k = 0;
-        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+        int64_t chunk = blockIdx.x;  // first chunk is static, the rest come from the ticket
+        int in_chunk = 0;
+        for (int k = 0;; ++k) {
             const int s = k % S;
             if (k >= S) mbar_wait(&empty_bar[s], ((k / S) - 1) & 1);
+            if (in_chunk == p.chunk_tiles || chunk * p.chunk_tiles + in_chunk >= tiles) {
+                unsigned next = 0;
+                if (lane == 0) next = atomicAdd(p.ticket, 1u);
+                chunk = (int64_t)gridDim.x + __shfl_sync(0xffffffffu, next, 0);
+                in_chunk = 0;
+            }
+            const int64_t t = chunk * p.chunk_tiles + in_chunk;
+            ++in_chunk;
+            if (chunk >= p.chunks) {  // out of work: tell the other roles and leave
+                if (lane == 0) {
+                    s_tile[s] = -1;
+                    mbar_arrive(&full_bar[s]);
+                }
+                break;
+            }
             ProjStage& st = stages[s];
             const int64_t row0 = t * PROJ_TILE;
             const int64_t left = p.n - row0;
             if (left >= PROJ_TILE) {
                 if (lane == 0) {
+                    s_tile[s] = t;
                     unsigned bytes = PROJ_TILE * 4;
 #pragma unroll
                     for (int c = 0; c < 3; ++c) bytes += PROJ_TILE * (p.val_dtype[c] == ETL_F64 ? 8 : 4);
@@ -132,46 +182,53 @@ __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(con
                     if (p.val_valid[c]) warp_copy_words(st.valid[1 + c], p.val_valid[c] + (row0 >> 5), words, lane);
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&full_bar[s]);
+                if (lane == 0) {
+                    s_tile[s] = t;
+                    mbar_arrive(&full_bar[s]);
+                }
+            }
+        }
+        // last CTA out re-arms the ticket for the next launch
+        if (lane == 0) {
+            if (atomicAdd(p.ticket + 1, 1u) == gridDim.x - 1) {
+                p.ticket[0] = 0;
+                p.ticket[1] = 0;
             }
         }
     } else if (warp == PROJ_CONSUMER_WARPS + 1) {
         // ----------------------------------------------------------- scanner
-        // kept rows of this CTA's whole range -> cross-CTA exclusive sum
-        uint64_t running = 0;
-        if (p.key_valid) {
-            const int64_t row_end = t_end * PROJ_TILE < p.n ? t_end * PROJ_TILE : p.n;
-            const int64_t w_begin = (t_begin * PROJ_TILE) >> 5, w_end = (row_end + 31) >> 5;
-            uint64_t mine = 0;
-            for (int64_t w = w_begin + lane; w < w_end; w += 32) {
-                uint32_t bits = __ldg(p.key_valid + w);
-                if (w == w_end - 1 && (row_end & 31)) bits &= (1u << (row_end & 31)) - 1;
-                mine += __popc(bits);
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-            const uint64_t tag = (uint64_t)p.epoch << TS_EPOCH_SHIFT;
-            if (lane == 0) st_relaxed_u64(p.cta_state + blockIdx.x, tag | TS_FLAG_AGG | mine);
-            uint64_t below = 0;
-            for (int i = lane; i < (int)blockIdx.x; i += 32) {
-                uint64_t sw;
-                do {
-                    sw = ld_relaxed_u64(p.cta_state + i);
-                } while ((sw >> TS_EPOCH_SHIFT) != p.epoch);
-                below += sw & TS_VALUE_MASK;
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) below += __shfl_xor_sync(0xffffffffu, below, o);
-            running = below;
-            if (blockIdx.x == gridDim.x - 1 && lane == 0) *p.out_rows = (int64_t)(below + mine);
-        } else {
-            running = (uint64_t)t_begin * PROJ_TILE;
-            if (blockIdx.x == gridDim.x - 1 && lane == 0) *p.out_rows = p.n;
-        }
-        int k = 0;
-        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+        const uint64_t tag = (uint64_t)p.epoch << TS_EPOCH_SHIFT;
+        const int64_t chunk_rows = (int64_t)p.chunk_tiles * PROJ_TILE;
+        uint64_t running = 0;     // first output row of the next tile if it continues the current chunk
+        int64_t next_chunk = 0;   // `running` = kept rows of chunks [0, next_chunk) when a chunk starts
+        for (int k = 0;; ++k) {
             const int s = k % S;
             mbar_wait(&full_bar[s], (k / S) & 1);
+            const int64_t t = s_tile[s];
+            if (t < 0) break;
+            const int64_t chunk = t / p.chunk_tiles;
+            if (t == chunk * p.chunk_tiles) {  // a new chunk starts: add the chunks skipped since the last one
+                if (p.key_valid) {
+                    uint64_t add = 0;
+                    for (int64_t c = next_chunk + lane; c < chunk; c += 32 * 8) {
+                        uint64_t sw[8];  // 8 independent loads in flight per lane
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            sw[u] = c + 32 * u < chunk ? ld_relaxed_u64(p.chunk_state + c + 32 * u) : tag;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            while ((sw[u] >> TS_EPOCH_SHIFT) != p.epoch) sw[u] = ld_relaxed_u64(p.chunk_state + c + 32 * u);
+                            add += sw[u] & TS_VALUE_MASK;
+                        }
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) add += __shfl_xor_sync(0xffffffffu, add, o);
+                    running += add;
+                } else {
+                    running = (uint64_t)chunk * chunk_rows;
+                }
+                next_chunk = chunk;
+            }
             const int64_t left = p.n - t * PROJ_TILE;
             const int rows = left >= PROJ_TILE ? PROJ_TILE : (int)left;
             const uint32_t kw = (p.key_valid ? stages[s].valid[0][lane] : 0xffffffffu) & seg_mask(lane, rows);
@@ -185,17 +242,21 @@ __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(con
             s_seg_off[s][lane] = incl - cnt;
             if (lane == 0) s_base[s] = running;
             running += __shfl_sync(0xffffffffu, incl, 31);
+            if (t == tiles - 1 && lane == 0) *p.out_rows = (int64_t)running;
+            // `running` now covers chunks [0, chunk] once the chunk's last tile is done
+            if (t + 1 == (chunk + 1) * p.chunk_tiles || t == tiles - 1) next_chunk = chunk + 1;
             __syncwarp();
             if (lane == 0) mbar_arrive(&scan_bar[s]);
         }
     } else {
         // --------------------------------------------------------- consumers
         const unsigned lt = lanemask_lt();
-        int k = 0;
-        for (int64_t t = t_begin; t < t_end; ++t, ++k) {
+        for (int k = 0;; ++k) {
             const int s = k % S;
             const unsigned ph = (k / S) & 1;
             mbar_wait(&full_bar[s], ph);
+            const int64_t t = s_tile[s];
+            if (t < 0) break;
             mbar_wait(&scan_bar[s], ph);
             const ProjStage& st = stages[s];
             const int64_t left = p.n - t * PROJ_TILE;
@@ -275,7 +336,7 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
     p.n = n;
     p.out_code = out_code;
     p.out_rows = d_out_rows;
-    // persistent grid: every CTA must be resident (a CTA waits for the lower CTAs' counts)
+    // persistent grid: every CTA must be resident (a scanner waits for other CTAs' chunk counts)
     static int s_stages = 0, s_ctas_per_sm = 0;
     if (s_stages == 0) {
         int stages = 3;
@@ -301,11 +362,24 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
     p.stages = s_stages;
     int64_t grid = (int64_t)h->sm_count * s_ctas_per_sm;
     if (grid > tiles) grid = tiles;
-    p.tiles_per_cta = (tiles + grid - 1) / grid;
-    grid = (tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;  // no empty CTAs
-    int rc = tile_state_acquire(h, (size_t)grid, stream, &p.epoch);
+    // chunk = unit of dynamic scheduling: ~8+ chunks per CTA, at most 4 tiles (measured best on
+    // config 2: fewer claims and state sums per tile, still fine-grained at the tail), more only
+    // when the table is so large that the chunk-state array would pass PROJ_MAX_CHUNKS words
+    int64_t ct = tiles / (grid * 8);
+    ct = ct < 1 ? 1 : (ct > 4 ? 4 : ct);
+    const int64_t ct_min = (tiles + PROJ_MAX_CHUNKS - 1) / PROJ_MAX_CHUNKS;
+    if (ct < ct_min) ct = ct_min;
+    if (const char* e = getenv("ETL_PROJ_CHUNK_TILES")) {
+        const int want = atoi(e);
+        if (want >= ct_min) ct = want;
+    }
+    p.chunk_tiles = (int)ct;
+    p.chunks = (tiles + p.chunk_tiles - 1) / p.chunk_tiles;
+    if (grid > p.chunks) grid = p.chunks;
+    int rc = tile_state_acquire(h, (size_t)p.chunks, stream, &p.epoch);
     if (rc != ETL_OK) return rc;
-    p.cta_state = h->tile_state;
+    p.chunk_state = h->tile_state;
+    p.ticket = h->counters + 2;
     project_filter_impute_kernel<<<(unsigned)grid, PROJ_THREADS, (size_t)s_stages * sizeof(ProjStage), stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
