@@ -99,6 +99,27 @@ ETL_API int etl_project_filter_impute_host(etl_handle* h,
                                    const int32_t val_dtype[3], const double fill[3], int64_t n,
                                    int32_t* out_code, double* const out_val[3], int64_t* out_rows);
 
+/* No counterpart in the reference (it never manages device memory): the same
+ * projection as etl_project_filter_impute for callers that must not trigger a
+ * device allocation - e.g. a process whose GPU memory is wholly owned by a pool
+ * allocator, or a latency-critical loop that cannot take cudaMalloc's device
+ * synchronisation.  Needs no handle and calls no cudaMalloc / cudaFree or
+ * allocating library routine: the kernel's scratch is a fixed 131,328-byte
+ * __device__ array that each GPU loading the library holds until exit.
+ *   - runs on the CURRENT device; buffers as for etl_project_filter_impute;
+ *   - n > ETL_NOALLOC_MAX_ROWS returns ETL_ECAPACITY (nothing is launched);
+ *   - the first call on a device resolves the array's device address and sizes
+ *     the grid: make it before starting any stream capture;
+ *   - all calls on a device share the scratch (it keeps the last call's words;
+ *     each call re-arms what it needs on `stream`): calls ordered on one stream
+ *     are fine, calls that overlap on the GPU race and corrupt each other. */
+#define ETL_NOALLOC_MAX_ROWS (((int64_t)1) << 31)
+ETL_API int etl_project_filter_impute_noalloc(const int32_t* key_code, const uint32_t* key_valid,
+                                      const void* const val[3], const uint32_t* const val_valid[3],
+                                      const int32_t val_dtype[3], const double fill[3], int64_t n,
+                                      int32_t* out_code, double* const out_val[3],
+                                      int64_t* d_out_rows, void* stream);
+
 /* ---- a2: null count ---------------------------------------------------- */
 
 /* Replaces input_df.filter(col("measure_name").isNull()).count()

@@ -553,3 +553,154 @@ extern "C" int etl_project_filter_impute_host(etl_handle* hh, const int32_t* key
     ETL_CUDA(cudaSetDevice(h->device));
     return etl::project_host(h, key_code, key_valid, val, val_valid, val_dtype, fill, n, out_code, out_val, out_rows);
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free entry point.
+//
+// Who needs it: a caller whose device memory is already spoken for.  Typical
+// cases are a host process that gave the whole GPU to a pool allocator (a torch
+// or RMM arena sized to the card: a raw cudaMalloc from inside this library
+// would fail, or succeed only by taking memory the pool thinks it owns), and a
+// latency-sensitive loop that cannot afford the implicit device-wide
+// synchronisation of cudaMalloc / cudaFree.  Such callers cannot use
+// etl_create(), because a handle allocates its scratch.
+//
+// What it does instead: the projection kernel's scratch (one tagged 64-bit word
+// per chunk plus the two ticket words) lives in a file-scope __device__ array
+// that every GPU loading this library carries until the process exits
+// (NOALLOC_SCRATCH_BYTES = 131,328 bytes).  Nothing is allocated, here or in
+// any library routine; inputs and outputs are still the caller's buffers.
+//
+// Rules that follow from the shared, fixed-size scratch:
+//   * n is limited to ETL_NOALLOC_MAX_ROWS (2^31 rows); larger tables are
+//     rejected with ETL_ECAPACITY before anything touches the GPU;
+//   * the first call on each device looks the array's device address up
+//     (cudaGetSymbolAddress - in host code the array's name is only a handle,
+//     not a pointer a kernel can use), reads the SM count and sizes the grid.
+//     Make that first call before starting any stream capture;
+//   * every call on a device uses the same words.  Each call re-zeroes the
+//     ticket words and tags the chunk words with a fresh epoch on the caller's
+//     stream, so calls issued one after another on one stream are independent;
+//     two calls that overlap on the GPU (different streams, no ordering) race
+//     on the scratch and produce garbage.
+// ---------------------------------------------------------------------------
+#include <mutex>
+
+namespace etl {
+
+constexpr int64_t NOALLOC_MAX_CHUNKS = 16384;
+constexpr int64_t NOALLOC_TICKET_WORDS = 32;  // 256 bytes: keeps the ticket on its own lines
+constexpr int64_t NOALLOC_MAX_ROWS = (int64_t)1 << 31;
+constexpr size_t NOALLOC_SCRATCH_BYTES = (NOALLOC_MAX_CHUNKS + NOALLOC_TICKET_WORDS) * sizeof(uint64_t);
+constexpr int NOALLOC_STAGES = 3;
+constexpr int NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) uint64_t g_noalloc_scratch[NOALLOC_MAX_CHUNKS + NOALLOC_TICKET_WORDS];
+static_assert(sizeof(g_noalloc_scratch) == NOALLOC_SCRATCH_BYTES && NOALLOC_SCRATCH_BYTES == 131328,
+              "the documented scratch size is part of the interface");
+
+struct NoAllocDevice {
+    bool ready = false;
+    uint64_t* scratch = nullptr;  // device address of g_noalloc_scratch on this GPU
+    int sm_count = 0;
+    int ctas_per_sm = 0;
+    uint32_t epoch = 0;
+};
+static NoAllocDevice g_noalloc_dev[NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mutex;
+
+// one-time set-up for the current device (caller holds the mutex)
+static int noalloc_setup(int dev, NoAllocDevice* d) {
+    uint64_t* ptr = nullptr;
+    ETL_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    if (ptr == nullptr) {
+        set_error("project_noalloc: cudaGetSymbolAddress returned a null address on device %d", dev);
+        return ETL_ECUDA;
+    }
+    ETL_CUDA(cudaDeviceGetAttribute(&d->sm_count, cudaDevAttrMultiProcessorCount, dev));
+    const size_t dyn = (size_t)NOALLOC_STAGES * sizeof(ProjStage);
+    // raise the opt-in limit to the largest ring any path uses, so neither path undercuts the other
+    ETL_CUDA(cudaFuncSetAttribute(project_filter_impute_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(PROJ_MAX_STAGES * sizeof(ProjStage))));
+    int occ = 0;
+    ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, project_filter_impute_kernel, PROJ_THREADS, dyn));
+    if (occ < 1) {
+        set_error("project_noalloc: kernel does not fit on an SM of device %d", dev);
+        return ETL_ECUDA;
+    }
+    d->ctas_per_sm = occ;
+    d->scratch = ptr;
+    d->epoch = 0;  // the array is zero at module load; 0 is never a live tag
+    d->ready = true;
+    return ETL_OK;
+}
+
+}  // namespace etl
+
+extern "C" int etl_project_filter_impute_noalloc(const int32_t* key_code, const uint32_t* key_valid,
+                                                 const void* const val[3], const uint32_t* const val_valid[3],
+                                                 const int32_t val_dtype[3], const double fill[3], int64_t n,
+                                                 int32_t* out_code, double* const out_val[3], int64_t* d_out_rows,
+                                                 void* stream_) {
+    using namespace etl;
+    ETL_REQUIRE(fill != nullptr && d_out_rows != nullptr, "project_noalloc: fill/d_out_rows is NULL");
+    if (n > NOALLOC_MAX_ROWS) {
+        set_error("project_noalloc: n=%lld exceeds the fixed scratch (max %lld rows); use etl_project_filter_impute",
+                  (long long)n, (long long)NOALLOC_MAX_ROWS);
+        return ETL_ECAPACITY;
+    }
+    int rc = check_project_args(key_code, val, key_valid, val_valid, val_dtype, n, out_code, out_val);
+    if (rc != ETL_OK) return rc;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    int dev = -1;
+    ETL_CUDA(cudaGetDevice(&dev));
+    ETL_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "project_noalloc: device ordinal %d unsupported", dev);
+
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    NoAllocDevice* d = &g_noalloc_dev[dev];
+    if (!d->ready) {
+        rc = noalloc_setup(dev, d);
+        if (rc != ETL_OK) return rc;
+    }
+    if (n == 0) {
+        ETL_CUDA(cudaMemsetAsync(d_out_rows, 0, sizeof(int64_t), stream));
+        return ETL_OK;
+    }
+    const int64_t tiles = (n + PROJ_TILE - 1) / PROJ_TILE;
+    ProjParams p;
+    p.key_code = key_code;
+    p.key_valid = key_valid;
+    for (int c = 0; c < 3; ++c) {
+        p.val[c] = val[c];
+        p.val_valid[c] = val_valid[c];
+        p.val_dtype[c] = val_dtype[c];
+        p.fill[c] = fill[c];
+        p.out_val[c] = out_val[c];
+    }
+    p.n = n;
+    p.out_code = out_code;
+    p.out_rows = d_out_rows;
+    p.stages = NOALLOC_STAGES;
+    int64_t grid = (int64_t)d->sm_count * d->ctas_per_sm;
+    if (grid > tiles) grid = tiles;
+    int64_t ct = tiles / (grid * 8);
+    ct = ct < 1 ? 1 : (ct > 4 ? 4 : ct);
+    const int64_t ct_min = (tiles + NOALLOC_MAX_CHUNKS - 1) / NOALLOC_MAX_CHUNKS;
+    if (ct < ct_min) ct = ct_min;
+    p.chunk_tiles = (int)ct;
+    p.chunks = (tiles + ct - 1) / ct;  // <= NOALLOC_MAX_CHUNKS by construction
+    if (grid > p.chunks) grid = p.chunks;
+    p.chunk_state = d->scratch;
+    p.ticket = reinterpret_cast<unsigned int*>(d->scratch + NOALLOC_MAX_CHUNKS);
+    // the array still holds the previous call's words: a fresh tag retires the chunk words
+    // (wiped outright when the 22-bit tag wraps), and the ticket pair must start at zero
+    if (d->epoch >= TS_EPOCH_MAX) {
+        ETL_CUDA(cudaMemsetAsync(d->scratch, 0, NOALLOC_MAX_CHUNKS * sizeof(uint64_t), stream));
+        d->epoch = 0;
+    }
+    p.epoch = ++d->epoch;
+    ETL_CUDA(cudaMemsetAsync(p.ticket, 0, 2 * sizeof(unsigned int), stream));
+    project_filter_impute_kernel<<<(unsigned)grid, PROJ_THREADS, (size_t)NOALLOC_STAGES * sizeof(ProjStage), stream>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}

@@ -183,3 +183,26 @@ class Engine:
                                              data.data_ptr(), _ptr(valid), self._stream()))
         self.launches += 1 if n else 0
         return Column(data, valid)
+
+
+def project_filter_impute_noalloc(key: Column, vals: Sequence[Column], fill: Sequence[float], out_code: torch.Tensor,
+                                  out_vals: Sequence[torch.Tensor], out_rows: torch.Tensor) -> None:
+    """The projection for callers that must not allocate device memory (for
+    instance because a pool allocator owns the whole GPU, or because the
+    device-wide sync inside cudaMalloc is unaffordable): no Engine / handle is
+    involved and every buffer, outputs included, is passed in.  Runs on torch's
+    current device and stream.  Limits and sharing rules are those of
+    etl_project_filter_impute_noalloc in include/etl_b200.h: at most 2^31 rows,
+    first call per device outside stream capture, calls that overlap on the GPU
+    corrupt each other because they share one fixed scratch array."""
+    lib = _lib.load()
+    n = len(key)
+    val = VP3(*[_ptr(c.data) for c in vals])
+    vv = VP3(*[_ptr(c.valid) for c in vals])
+    dt = I32x3(*[c.dtype_code for c in vals])
+    fl = F64x3(*[float(f) for f in fill])
+    ov = VP3(*[t.data_ptr() for t in out_vals])
+    stream = torch.cuda.current_stream(key.data.device).cuda_stream
+    _lib.check(lib.etl_project_filter_impute_noalloc(_ptr(key.data), _ptr(key.valid), C.byref(val), C.byref(vv),
+                                                     C.byref(dt), C.byref(fl), n, out_code.data_ptr(), C.byref(ov),
+                                                     out_rows.data_ptr(), stream))
