@@ -141,6 +141,118 @@ ETL_API int etl_column_sum_count(etl_handle* h, int32_t ncols,
                          const int32_t val_dtype[], const uint32_t* row_valid, int64_t n,
                          double* d_sum, int64_t* d_count, void* stream);
 
+/* ---- a1: CSV text -> columnar device buffers ----------------------------- */
+
+/* Together these replace spark.read.csv(path, header=True, inferSchema=True)
+ * (spark_checks/python_checks/spark_workload_to_cloud_k8s.py:48) and the
+ * csv.DictReader loop of load_csv (workloads/raw-tf/train_tf_ps.py:114-137) for
+ * the columns the ETL stage uses.  `text` is the whole file in device memory,
+ * 16-byte aligned, readable up to the next multiple of 8 past nbytes.  RFC-4180
+ * quoting (quoted fields may hold commas and newlines, "" is an escaped quote);
+ * blank lines are dropped, as Spark and csv.reader do.
+ *
+ * etl_csv_index_rows:  *d_rows (device int64) = number of records, header line
+ *                      included.  Leaves per-block state in the handle's arena.
+ * etl_csv_row_offsets: row_start[r] (device int64[rows]) = byte offset of record
+ *                      r.  Must directly follow etl_csv_index_rows on the same
+ *                      text (it reads that state). */
+ETL_API int etl_csv_index_rows(etl_handle* h, const uint8_t* text, int64_t nbytes, int64_t* d_rows, void* stream);
+ETL_API int etl_csv_row_offsets(etl_handle* h, const uint8_t* text, int64_t nbytes, int64_t* row_start, void* stream);
+
+/* Decode up to 8 columns of records [first_row, first_row + rows).  field[s] =
+ * position of column s in a record (0-based, < 256); kind[s]: 0 = numeric ->
+ * out[s] is double[rows], 1 = string -> out[s] is int32[rows] holding the slot
+ * of the string in the column's dictionary (-1 where null).  valid[s] =
+ * ceil(rows/32) bitmap words, fully written.  An empty cell, a cell missing from
+ * a short record and (numeric) an unparsable cell are null.  Numerals are
+ * converted correctly rounded (as Double.parseDouble / float() do) for <= 19
+ * significant digits and |decimal exponent| <= 19 (<= 22 when the digits fit
+ * 2^53); a numeral outside that domain is never approximated: it is counted in
+ * d_status[0] and the caller must treat the decode as failed.
+ * Dictionaries (string columns): dict_hash[s] / dict_rep[s] = uint64[capacity]
+ * device arrays zeroed by the caller before the first call (they persist across
+ * calls, so several calls share one dictionary); capacity = power of two.  A slot
+ * s is used iff dict_hash[s][slot] != 0; dict_rep[s][slot] = (byte offset << 24)
+ * | (quoted << 23) | length of one occurrence of the string in `text`.
+ * flags: ETL_CSV_TRIM_STRINGS strips ASCII whitespace around string cells
+ * (load_csv, train_tf_ps.py:120); ETL_CSV_NAN_IS_NULL makes a NaN literal null
+ * (load_csv drops such rows, train_tf_ps.py:129) instead of a NaN value (Spark).
+ * d_status (device int32[4], zeroed by the caller): [0] numerals outside the
+ * exact domain, [1] dictionary-full events, [2] bit s set = column s held a
+ * non-integer numeral (inferSchema: double rather than int), [3] unparsable
+ * numerals.  *d_first_bad_row (device int64, caller sets it to INT64_MAX) = the
+ * lowest record with a [0] or [1] event. */
+#define ETL_CSV_TRIM_STRINGS 1
+#define ETL_CSV_NAN_IS_NULL 2
+ETL_API int etl_csv_parse_columns(etl_handle* h, const uint8_t* text, int64_t nbytes, const int64_t* row_start,
+                          int64_t first_row, int64_t rows, int32_t ncols, const int32_t* field,
+                          const int32_t* kind, void* const* out, uint32_t* const* valid,
+                          uint64_t* const* dict_hash, uint64_t* const* dict_rep,
+                          const int32_t* dict_capacity, int32_t flags, int32_t* d_status,
+                          int64_t* d_first_bad_row, void* stream);
+
+/* a7: StringIndexerModel.transform (k_means.py:74) on dictionary codes, in place:
+ * codes[i] = table[codes[i]] if 0 <= codes[i] < table_size else `missing`
+ * (handleInvalid="keep" maps unseen / null to numLabels). */
+ETL_API int etl_remap_codes(etl_handle* h, int32_t* codes, int64_t n, const int32_t* table, int32_t table_size,
+                    int32_t missing, void* stream);
+
+/* ---- a6: StringIndexer.fit's group-by-count ------------------------------ */
+
+/* Replaces the aggregation inside StringIndexer(handleInvalid="keep").fit
+ * (k_means.py:34,73): d_counts[b] (device int64[bins]) = number of valid rows
+ * whose code is b; codes outside [0, bins) are counted in *d_out_of_range.  The
+ * caller orders labels by (count desc, label asc) on the host - at most a few
+ * thousand pairs - as Spark does on the driver. */
+ETL_API int etl_code_histogram(etl_handle* h, const int32_t* codes, const uint32_t* valid, int64_t n, int32_t bins,
+                       int64_t* d_counts, int64_t* d_out_of_range, void* stream);
+
+/* ---- a8-a10: OneHotEncoder + VectorAssembler -> `features` ---------------- */
+
+/* Replaces OneHotEncoder (dropLast) + VectorAssembler([vec] * repeats + numeric
+ * cols) + select("features") (k_means.py:38,64-68,74-77).  index[i] in
+ * [0, num_labels]: num_labels (or any value outside [0, num_labels)) is the
+ * "unknown" category whose one-hot block is all zeros.  Row i of the output is
+ * [onehot(index[i])] * repeats ++ [(num[c][i] - shift[c]) * scale[c], c = 0..2];
+ * shift / scale may be NULL (0 / 1).  Dense: out = [n, repeats * num_labels + 3]
+ * row-major, out_dtype ETL_F64 (Spark's DenseVector) or ETL_F32 (the trainer's
+ * dtype).  Sparse: ELL form of Spark's SparseVector - out_index / out_value =
+ * [n, repeats + 3], ascending indices, index -1 = unused slot. */
+ETL_API int etl_assemble_features_dense(etl_handle* h, const int32_t* index, const double* const num[3],
+                                const double* shift, const double* scale, int64_t n, int32_t num_labels,
+                                int32_t repeats, int32_t out_dtype, void* out, void* stream);
+ETL_API int etl_assemble_features_sparse(etl_handle* h, const int32_t* index, const double* const num[3],
+                                 const double* shift, const double* scale, int64_t n, int32_t num_labels,
+                                 int32_t repeats, int32_t* out_index, double* out_value, void* stream);
+
+/* ---- a11/a12: the layout the Keras trainer reads -------------------------- */
+
+/* Replaces the row filter and array building of load_csv
+ * (workloads/raw-tf/train_tf_ps.py:120-149): keep a row iff its label and all
+ * three numerics are non-null (NaN cells must already be null: decode with
+ * ETL_CSV_NAN_IS_NULL or call etl_nan_to_null), in input order;
+ * X[k] = float32((num[c] - shift[c]) * scale[c]), y[k] = remap[label] (remap NULL:
+ * the label code itself).  X = float32[n * 3] row-major, y = int32[n]; the first
+ * *d_out_rows rows are written - the arrays from_tensor_slices consumes
+ * (train_tf_ps.py:597,664). */
+ETL_API int etl_pack_tf_features(etl_handle* h, const int32_t* label, const uint32_t* label_valid,
+                         const double* const num[3], const uint32_t* const num_valid[3], const double* shift,
+                         const double* scale, const int32_t* remap, int32_t remap_size, int64_t n, float* X,
+                         int32_t* y, int64_t* d_out_rows, void* stream);
+/* valid[i] &= !isnan(val[i]) (the `v.lower() == "nan"` rule of load_csv for
+ * columns that did not come from the CSV decoder). */
+ETL_API int etl_nan_to_null(etl_handle* h, const double* val, uint32_t* valid, int64_t n, void* stream);
+
+/* ---- north-star extension: bucketing (no reference site) ------------------ */
+
+/* Spark ML Bucketizer(handleInvalid="keep"): out[i] = b with splits[b] <= x <
+ * splits[b+1] (the last bucket also takes x == splits[last]); null or NaN ->
+ * nsplits - 1 (the extra bucket); x outside [splits[0], splits[last]] -> -1 and
+ * counted in *d_out_of_range (Spark raises).  d_splits: device double[nsplits],
+ * strictly increasing, 3 <= nsplits <= 4096. */
+ETL_API int etl_bucketize(etl_handle* h, const double* val, const uint32_t* valid, int64_t n, const double* d_splits,
+                  int32_t nsplits, int32_t* out, int64_t* d_out_of_range, void* stream);
+
 /* ---- synthetic tables (bench / test infrastructure) -------------------- */
 
 /* Counter-based generator, identical to pyspark_tf_gke_b200.synth on the host:

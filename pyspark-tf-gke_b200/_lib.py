@@ -45,6 +45,24 @@ _PROTOS = {
     "etl_null_count": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "etl_column_sum_count": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(VP3), C.POINTER(VP3), C.POINTER(I32x3),
                                        C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "etl_csv_index_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "etl_csv_row_offsets": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "etl_csv_parse_columns": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "etl_remap_codes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "etl_code_histogram": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p]),
+    "etl_assemble_features_dense": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_void_p, C.c_int64,
+                                              C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "etl_assemble_features_sparse": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_void_p,
+                                               C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "etl_pack_tf_features": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(VP3), C.POINTER(VP3), C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p]),
+    "etl_nan_to_null": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "etl_bucketize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
+                                C.c_void_p, C.c_void_p]),
     "etl_synth_column": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_uint64, C.c_double,
                                    C.c_double, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

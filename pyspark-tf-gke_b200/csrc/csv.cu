@@ -1,0 +1,593 @@
+// CSV text -> device-resident columnar buffers.
+// Replaces spark.read.csv(path, header=True, inferSchema=True)
+// (spark_workload_to_cloud_k8s.py:48) and the csv.DictReader loop of load_csv
+// (train_tf_ps.py:114-137) for the columns the ETL stage uses.
+//
+// Quoting is RFC 4180 (quote ", doubled-quote escape; a quoted field may hold
+// commas and newlines); backslash escapes are outside the documented domain.
+//
+// Three steps, all byte-parallel until the field parse:
+//   1. csv_block_summary_kernel  per 16 KiB block: parity of the quote count and
+//      the number of record starts assuming the block begins outside / inside
+//      quotes (a record start = the byte after a newline that is outside quotes,
+//      unless the line it opens is blank - Spark and csv.reader drop blank lines)
+//   2. csv_block_scan_kernel     one CTA composes the block summaries in order
+//      -> every block's true starting quote state and first row number
+//   3. csv_row_offsets_kernel    re-derives the masks with the true state and
+//      writes row_start[row] (int64 byte offsets)
+//   4. csv_parse_rows_kernel     one warp per 32 rows: the warp tokenises a row
+//      cooperatively (8 bytes per lane, quote parity by ballot, comma ranks by
+//      shuffle scan), then lane s converts requested column s: numerals through
+//      dec_parse (correctly rounded), strings through an open-addressing
+//      dictionary in global memory keyed by a 64-bit hash with a byte-compare
+//      collision check.  Results of 32 rows are staged in shared memory so each
+//      column leaves as one coalesced store and one validity word per 32 rows.
+#include "common.cuh"
+#include "decimal.cuh"
+
+namespace etl {
+
+constexpr int CSV_THREADS = 256;
+constexpr int CSV_BYTES_PER_THREAD = 64;
+constexpr int CSV_BLOCK_BYTES = CSV_THREADS * CSV_BYTES_PER_THREAD;  // 16 KiB
+constexpr int CSV_MAX_COLS = 8;      // requested columns per parse call
+constexpr int CSV_MAX_FIELDS = 256;  // field positions that can be requested
+
+struct CsvBlockSummary {
+    uint32_t parity;  // quote count of the block & 1
+    uint32_t pad;
+    uint64_t starts_if_outside;  // record starts if the block begins outside quotes
+    uint64_t starts_if_inside;
+    uint64_t reserved;
+};
+struct CsvBlockStart {
+    uint64_t first_row;
+    uint32_t inside;  // 1 = block begins inside a quoted field
+    uint32_t pad;
+};
+
+// 4-bit mask of the bytes of w equal to the byte replicated in `pat`
+__device__ __forceinline__ unsigned eq4(uint32_t w, uint32_t pat) {
+    const uint32_t r = __vcmpeq4(w, pat) & 0x08040201u;
+    return (r * 0x01010101u) >> 24;  // distinct bits per byte: the byte sum is the mask
+}
+
+// Masks over the 64 bytes [base, base + 64) of the text: quotes, newlines, and
+// `opens` = the byte FOLLOWING position i exists and opens a non-blank line.
+__device__ __forceinline__ void csv_masks64(const uint8_t* __restrict__ text, int64_t base, int64_t n, uint64_t* quotes,
+                                            uint64_t* newlines, uint64_t* opens) {
+    uint64_t q = 0, nl = 0, cr = 0;
+    if (base + 64 <= n) {
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            const int4 x = ld_stream_v4(text + base + 16 * v);
+            const uint32_t w[4] = {(uint32_t)x.x, (uint32_t)x.y, (uint32_t)x.z, (uint32_t)x.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int sh = 16 * v + 4 * k;
+                q |= (uint64_t)eq4(w[k], 0x22222222u) << sh;
+                nl |= (uint64_t)eq4(w[k], 0x0a0a0a0au) << sh;
+                cr |= (uint64_t)eq4(w[k], 0x0d0d0d0du) << sh;
+            }
+        }
+    } else {
+        for (int i = 0; i < 64 && base + i < n; ++i) {
+            const uint8_t c = text[base + i];
+            q |= (uint64_t)(c == '"') << i;
+            nl |= (uint64_t)(c == '\n') << i;
+            cr |= (uint64_t)(c == '\r') << i;
+        }
+    }
+    // the two bytes after the window decide whether positions 62/63 open a non-blank line
+    const uint8_t a = base + 64 < n ? text[base + 64] : 0, b = base + 65 < n ? text[base + 65] : 0;
+    const uint64_t nl1 = (nl >> 1) | ((uint64_t)(a == '\n') << 63);
+    const uint64_t cr1 = (cr >> 1) | ((uint64_t)(a == '\r') << 63);
+    const uint64_t nl2 = (nl >> 2) | ((uint64_t)(a == '\n') << 62) | ((uint64_t)(b == '\n') << 63);
+    // in1 / in2: byte i+1 / i+2 is inside the text
+    const int64_t left = n - base;  // bytes of the text from `base`
+    const uint64_t in1 = left >= 65 ? ~0ull : (left <= 1 ? 0ull : ((1ull << (left - 1)) - 1));
+    const uint64_t in2 = left >= 66 ? ~0ull : (left <= 2 ? 0ull : ((1ull << (left - 2)) - 1));
+    // next byte exists, is not '\n', and is not a '\r' that ends the text or precedes '\n'
+    *opens = in1 & ~nl1 & ~(cr1 & (~in2 | nl2));
+    *quotes = q;
+    *newlines = nl;
+}
+
+// bit i = parity of the quotes strictly before position i (window-relative)
+__device__ __forceinline__ uint64_t inside_mask(uint64_t q) {
+    uint64_t x = q;
+    x ^= x << 1; x ^= x << 2; x ^= x << 4; x ^= x << 8; x ^= x << 16; x ^= x << 32;
+    return x << 1;
+}
+
+// does byte 0 of the text open a non-blank line?
+__device__ __forceinline__ bool csv_first_line_nonblank(const uint8_t* text, int64_t n) {
+    if (n <= 0) return false;
+    const uint8_t c = text[0];
+    if (c == '\n') return false;
+    if (c == '\r' && (n == 1 || text[1] == '\n')) return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const uint8_t* __restrict__ text, int64_t n,
+                                                                        CsvBlockSummary* __restrict__ out) {
+    __shared__ uint32_t s_par[CSV_THREADS / 32];
+    __shared__ uint32_t s_out[CSV_THREADS / 32], s_in[CSV_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
+    uint64_t q, nl, opens;
+    csv_masks64(text, base, n, &q, &nl, &opens);
+    const uint64_t ins = inside_mask(q);
+    unsigned c_out = __popcll(nl & ~ins & opens), c_in = __popcll(nl & ins & opens);  // thread starts outside / inside
+    const unsigned tp = __popcll(q) & 1;
+    // thread's starting state relative to the block start
+    const unsigned wb = __ballot_sync(0xffffffffu, tp);
+    const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
+    if (lane == 0) s_par[warp] = __popc(wb) & 1;
+    __syncthreads();
+    unsigned warp_state = 0, block_par = 0;
+#pragma unroll
+    for (int w = 0; w < CSV_THREADS / 32; ++w) {
+        if (w < warp) warp_state ^= s_par[w];
+        block_par ^= s_par[w];
+    }
+    const unsigned st = lane_state ^ warp_state;
+    unsigned a = st ? c_in : c_out;   // starts if the block begins outside quotes
+    unsigned b = st ? c_out : c_in;   // ... inside quotes
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if (lane == 0) { s_out[warp] = a; s_in[warp] = b; }
+    __syncthreads();
+    if (tid == 0) {
+        uint64_t ta = 0, tb = 0;
+#pragma unroll
+        for (int w = 0; w < CSV_THREADS / 32; ++w) { ta += s_out[w]; tb += s_in[w]; }
+        if (blockIdx.x == 0 && csv_first_line_nonblank(text, n)) { ta += 1; tb += 1; }  // row 0 starts at byte 0
+        CsvBlockSummary r;
+        r.parity = block_par; r.pad = 0; r.starts_if_outside = ta; r.starts_if_inside = tb; r.reserved = 0;
+        out[blockIdx.x] = r;
+    }
+}
+
+// Single CTA: ordered composition of the block summaries.
+__global__ void __launch_bounds__(1024) csv_block_scan_kernel(const CsvBlockSummary* __restrict__ sum, int64_t blocks,
+                                                              CsvBlockStart* __restrict__ start, int64_t* total_rows) {
+    __shared__ uint32_t s_par[1024];
+    __shared__ uint64_t s_a[1024], s_b[1024];   // rows if the thread's span begins outside / inside
+    __shared__ uint32_t s_state[1024];
+    __shared__ uint64_t s_row[1024];
+    const int tid = threadIdx.x;
+    const int64_t per = (blocks + 1023) / 1024;
+    const int64_t lo = tid * per, hi = lo + per < blocks ? lo + per : blocks;
+    uint32_t par = 0;
+    uint64_t a = 0, b = 0;
+    for (int64_t i = lo; i < hi; ++i) {
+        const CsvBlockSummary s = sum[i];
+        a += par ? s.starts_if_inside : s.starts_if_outside;
+        b += par ? s.starts_if_outside : s.starts_if_inside;
+        par ^= s.parity;
+    }
+    s_par[tid] = par; s_a[tid] = a; s_b[tid] = b;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t st = 0;
+        uint64_t row = 0;
+        for (int t = 0; t < 1024; ++t) {
+            s_state[t] = st; s_row[t] = row;
+            row += st ? s_b[t] : s_a[t];
+            st ^= s_par[t];
+        }
+        *total_rows = (int64_t)row;
+    }
+    __syncthreads();
+    uint32_t st = s_state[tid];
+    uint64_t row = s_row[tid];
+    for (int64_t i = lo; i < hi; ++i) {
+        const CsvBlockSummary s = sum[i];
+        CsvBlockStart o;
+        o.first_row = row; o.inside = st; o.pad = 0;
+        start[i] = o;
+        row += st ? s.starts_if_inside : s.starts_if_outside;
+        st ^= s.parity;
+    }
+}
+
+__global__ void __launch_bounds__(CSV_THREADS) csv_row_offsets_kernel(const uint8_t* __restrict__ text, int64_t n,
+                                                                      const CsvBlockStart* __restrict__ start,
+                                                                      int64_t* __restrict__ row_start) {
+    __shared__ uint32_t s_par[CSV_THREADS / 32];
+    __shared__ uint32_t s_cnt[CSV_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
+    uint64_t q, nl, opens;
+    csv_masks64(text, base, n, &q, &nl, &opens);
+    const CsvBlockStart bs = start[blockIdx.x];
+    const unsigned tp = __popcll(q) & 1;
+    const unsigned wb = __ballot_sync(0xffffffffu, tp);
+    const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
+    if (lane == 0) s_par[warp] = __popc(wb) & 1;
+    __syncthreads();
+    unsigned st = lane_state ^ bs.inside;
+#pragma unroll
+    for (int w = 0; w < CSV_THREADS / 32; ++w)
+        if (w < warp) st ^= s_par[w];
+    uint64_t ins = inside_mask(q);
+    if (st) ins = ~ins;
+    uint64_t ev = nl & ~ins & opens;  // newlines outside quotes whose next byte opens a non-blank line
+    const bool virt = blockIdx.x == 0 && tid == 0 && csv_first_line_nonblank(text, n);
+    unsigned cnt = __popcll(ev) + (virt ? 1 : 0);
+    unsigned incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    if (lane == 31) s_cnt[warp] = incl;
+    __syncthreads();
+    uint64_t row = bs.first_row + (incl - cnt);
+#pragma unroll
+    for (int w = 0; w < CSV_THREADS / 32; ++w)
+        if (w < warp) row += s_cnt[w];
+    if (virt) row_start[row++] = 0;
+    while (ev) {
+        const int i = __ffsll((long long)ev) - 1;
+        ev &= ev - 1;
+        row_start[row++] = base + i + 1;
+    }
+}
+
+// ------------------------------------------------------------------ field parse
+
+struct CsvParseParams {
+    const uint8_t* text;
+    int64_t n;
+    const int64_t* row_start;
+    int64_t first_row;   // first row to decode (1 skips the header)
+    int64_t rows;        // rows to decode
+    int ncols;
+    int32_t field[CSV_MAX_COLS];   // field position of column s in a row
+    int32_t kind[CSV_MAX_COLS];    // 0 = numeric -> double, 1 = string -> dictionary slot (int32)
+    void* out[CSV_MAX_COLS];
+    uint32_t* valid[CSV_MAX_COLS];
+    uint64_t* dict_hash[CSV_MAX_COLS];  // string columns: capacity words, 0 = empty
+    uint64_t* dict_rep[CSV_MAX_COLS];   // representative field of the slot (packed offset / length / quoted)
+    uint32_t dict_mask[CSV_MAX_COLS];   // capacity - 1 (capacity is a power of two)
+    int flags;                          // CSV_TRIM_STRINGS | CSV_NAN_IS_NULL
+    int32_t* status;                    // [0] numerals outside the exact domain, [1] dictionary overflows,
+                                        // [2] bit s set: column s saw a non-integer numeral, [3] unparsable numerals
+    int64_t* first_bad_row;             // smallest row (file order) with a status[0] / status[1] event
+};
+constexpr int CSV_TRIM_STRINGS = 1;  // load_csv strips the label cell (train_tf_ps.py:120)
+constexpr int CSV_NAN_IS_NULL = 2;   // load_csv drops rows whose numeric text is "nan" (train_tf_ps.py:129)
+
+constexpr uint64_t REP_LEN_BITS = 23;
+constexpr uint64_t REP_QUOTED = 1ull << REP_LEN_BITS;
+__device__ __forceinline__ uint64_t rep_pack(int64_t off, int len, bool quoted) {
+    return ((uint64_t)off << (REP_LEN_BITS + 1)) | (quoted ? REP_QUOTED : 0) | (uint64_t)len;
+}
+
+// canonical bytes of a field: a quoted field's content with "" read as one "
+struct FieldCursor {
+    const uint8_t* p;
+    int len, i;
+    bool quoted;
+    __device__ __forceinline__ FieldCursor(const uint8_t* p_, int len_, bool q) : p(p_), len(len_), i(0), quoted(q) {}
+    __device__ __forceinline__ int next() {  // -1 at the end
+        if (i >= len) return -1;
+        const uint8_t c = p[i++];
+        if (quoted && c == '"' && i < len && p[i] == '"') ++i;
+        return c;
+    }
+};
+
+__device__ __forceinline__ uint64_t field_hash(const uint8_t* p, int len, bool quoted) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    FieldCursor cur(p, len, quoted);
+    for (int c = cur.next(); c >= 0; c = cur.next()) h = (h ^ (uint64_t)c) * 0x100000001b3ull;
+    h = mix64(h);
+    return h ? h : 1;
+}
+
+__device__ __forceinline__ bool field_equal(const uint8_t* text, uint64_t ra, uint64_t rb) {
+    FieldCursor a(text + (ra >> (REP_LEN_BITS + 1)), (int)(ra & (REP_QUOTED - 1)), (ra & REP_QUOTED) != 0);
+    FieldCursor b(text + (rb >> (REP_LEN_BITS + 1)), (int)(rb & (REP_QUOTED - 1)), (rb & REP_QUOTED) != 0);
+    while (true) {
+        const int x = a.next(), y = b.next();
+        if (x != y) return false;
+        if (x < 0) return true;
+    }
+}
+
+// returns the slot of the field's string, inserting it if new; -1 if the table is full
+__device__ __forceinline__ int dict_find_or_insert(uint64_t* hash_tab, uint64_t* rep_tab, uint32_t mask,
+                                                   const uint8_t* text, uint64_t h, uint64_t rep) {
+    uint32_t slot = (uint32_t)(h >> 24) & mask;
+    for (uint32_t probe = 0; probe <= mask; ++probe) {
+        uint64_t cur = ld_relaxed_u64(hash_tab + slot);
+        if (cur == 0) {
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(hash_tab + slot), 0ull, (unsigned long long)h);
+            if (cur == 0) {  // we own the slot: publish its representative
+                st_relaxed_u64(rep_tab + slot, rep);
+                return (int)slot;
+            }
+        }
+        if (cur == h) {
+            uint64_t r;
+            do { r = ld_relaxed_u64(rep_tab + slot); } while (r == 0);
+            if (field_equal(text, r, rep)) return (int)slot;
+        }
+        slot = (slot + 1) & mask;
+    }
+    return -1;
+}
+
+// 8-bit mask of the bytes of w equal to c
+__device__ __forceinline__ unsigned eq8(uint64_t w, uint32_t pat) {
+    return eq4((uint32_t)w, pat) | (eq4((uint32_t)(w >> 32), pat) << 4);
+}
+
+constexpr int PARSE_WARPS = 4;
+
+__global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const CsvParseParams p) {
+    __shared__ int64_t s_fstart[PARSE_WARPS][CSV_MAX_COLS], s_fend[PARSE_WARPS][CSV_MAX_COLS];
+    __shared__ int8_t s_slot_of_field[CSV_MAX_FIELDS];
+    __shared__ uint64_t s_val[PARSE_WARPS][CSV_MAX_COLS][32];  // double bits or dictionary slot per row of the group
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < CSV_MAX_FIELDS; i += blockDim.x) s_slot_of_field[i] = -1;
+    __syncthreads();
+    if (tid < p.ncols) s_slot_of_field[p.field[tid]] = (int8_t)tid;
+    __syncthreads();
+    const unsigned lt = lanemask_lt();
+    const int64_t groups = (p.rows + 31) / 32;
+    for (int64_t g = (int64_t)blockIdx.x * PARSE_WARPS + warp; g < groups; g += (int64_t)gridDim.x * PARSE_WARPS) {
+        const int64_t r0 = g * 32;
+        const int in_group = p.rows - r0 < 32 ? (int)(p.rows - r0) : 32;
+        uint32_t my_valid = 0;  // lane s: validity word of column s over the group's rows
+        for (int rr = 0; rr < in_group; ++rr) {
+            const int64_t row = p.first_row + r0 + rr;
+            const int64_t start = p.row_start[row];
+            // ---- tokenise: the warp walks the row in 256-byte windows
+            if (lane < p.ncols) { s_fstart[warp][lane] = -1; s_fend[warp][lane] = -1; }
+            __syncwarp();
+            if (lane == 0 && s_slot_of_field[0] >= 0) s_fstart[warp][s_slot_of_field[0]] = start;
+            int64_t abase = start & ~(int64_t)7;
+            unsigned inside = 0, ncomma = 0;
+            int64_t row_end = -1;
+            while (true) {
+                const int64_t wpos = abase + 8 * lane;
+                uint64_t w = 0;
+                if (wpos < p.n) w = *reinterpret_cast<const uint64_t*>(p.text + wpos);  // buffer is padded to 8 bytes
+                // bytes of this word that belong to the row so far and to the text
+                unsigned vm = 0xff;
+                if (wpos < start) vm &= start - wpos >= 8 ? 0u : (0xffu << (start - wpos));
+                if (wpos + 8 > p.n) vm &= p.n <= wpos ? 0u : (0xffu >> (8 - (p.n - wpos)));
+                const unsigned q8 = eq8(w, 0x22222222u) & vm;
+                const unsigned c8 = eq8(w, 0x2c2c2c2cu) & vm;
+                const unsigned n8 = eq8(w, 0x0a0a0a0au) & vm;
+                const unsigned pb = __ballot_sync(0xffffffffu, __popc(q8) & 1);
+                const unsigned st = (inside ^ __popc(pb & lt)) & 1;
+                unsigned ins = q8;  // prefix parity over the 8 bytes
+                ins ^= ins << 1; ins ^= ins << 2; ins ^= ins << 4;
+                ins = (ins << 1) & 0xff;
+                if (st) ins ^= 0xff;
+                unsigned end8 = n8 & ~ins;  // record-ending newlines
+                const unsigned eb = __ballot_sync(0xffffffffu, end8 != 0);
+                unsigned keep = 0xff;       // bytes before the record end
+                int end_lane = 32;
+                if (eb) {
+                    end_lane = __ffs(eb) - 1;
+                    const unsigned e_first = __shfl_sync(0xffffffffu, end8, end_lane);
+                    const int ebit = __ffs(e_first) - 1;
+                    row_end = abase + 8 * end_lane + ebit;
+                    keep = lane < end_lane ? 0xffu : (lane == end_lane ? ((1u << ebit) - 1) : 0u);
+                }
+                unsigned oc = c8 & ~ins & keep;  // field separators
+                const unsigned cnt = __popc(oc);
+                unsigned incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += up;
+                }
+                unsigned fi = ncomma + incl - cnt;  // index of the field this lane's first separator closes
+                while (oc) {
+                    const int b = __ffs(oc) - 1;
+                    oc &= oc - 1;
+                    const int64_t pos = wpos + b;
+                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fend[warp][s_slot_of_field[fi]] = pos;
+                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0)
+                        s_fstart[warp][s_slot_of_field[fi + 1]] = pos + 1;
+                    ++fi;
+                }
+                ncomma += __shfl_sync(0xffffffffu, incl, 31);
+                inside = (inside ^ __popc(pb)) & 1;
+                if (eb) break;
+                abase += 256;
+                if (abase >= p.n) { row_end = p.n; break; }
+            }
+            __syncwarp();
+            // ---- convert: lane s handles requested column s
+            bool ok = false;
+            uint64_t bits = 0;
+            if (lane < p.ncols) {
+                int64_t fs = s_fstart[warp][lane], fe = s_fend[warp][lane];
+                if (fs >= 0) {  // the row has this field; an open end = the row's last field
+                    if (fe < 0) fe = row_end;
+                    if (fe > fs && p.text[fe - 1] == '\r' && fe == row_end) --fe;  // CRLF line end
+                    const uint8_t* f = p.text + fs;
+                    int len = (int)(fe - fs);
+                    const bool numeric = p.kind[lane] == 0;
+                    if (numeric || (p.flags & CSV_TRIM_STRINGS)) {
+                        while (len > 0 && dec_is_space(f[0])) { ++f; --len; }
+                        while (len > 0 && dec_is_space(f[len - 1])) --len;
+                    }
+                    bool quoted = false;
+                    if (len >= 2 && f[0] == '"' && f[len - 1] == '"') {
+                        quoted = true; ++f; len -= 2;
+                        if (numeric || (p.flags & CSV_TRIM_STRINGS)) {  // csv yields the inner text, then .strip()
+                            while (len > 0 && dec_is_space(f[0])) { ++f; --len; }
+                            while (len > 0 && dec_is_space(f[len - 1])) --len;
+                        }
+                    }
+                    if (numeric) {
+                        double v = 0.0;
+                        int fl = 0;
+                        const int st = dec_parse(f, len, &v, &fl);
+                        if (st == DEC_OK) {
+                            ok = !((fl & DEC_FLAG_NAN) && (p.flags & CSV_NAN_IS_NULL));
+                            bits = (uint64_t)__double_as_longlong(v);
+                            if ((fl & DEC_FLAG_NONINT) && !(p.status[2] & (1 << lane))) atomicOr(p.status + 2, 1 << lane);
+                        } else if (st == DEC_INEXACT) {
+                            atomicAdd(p.status + 0, 1);
+                            atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
+                        } else if (st == DEC_INVALID) {
+                            atomicAdd(p.status + 3, 1);
+                        }
+                    } else if (len > 0) {
+                        const uint64_t h = field_hash(f, len, quoted);
+                        const int slot = dict_find_or_insert(p.dict_hash[lane], p.dict_rep[lane], p.dict_mask[lane],
+                                                             p.text, h, rep_pack(f - p.text, len, quoted));
+                        if (slot >= 0) {
+                            ok = true;
+                            bits = (uint64_t)(uint32_t)slot;
+                        } else {
+                            atomicAdd(p.status + 1, 1);
+                            atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
+                        }
+                    }
+                }
+                s_val[warp][lane][rr] = bits;
+                my_valid |= (ok ? 1u : 0u) << rr;
+            }
+            __syncwarp();
+        }
+        // ---- coalesced write-out of the group: 32 rows per column
+        for (int s = 0; s < p.ncols; ++s) {
+            const uint32_t vw = __shfl_sync(0xffffffffu, my_valid, s);
+            if (lane < in_group) {
+                const uint64_t b = s_val[warp][s][lane];
+                if (p.kind[s] == 0) static_cast<double*>(p.out[s])[r0 + lane] = __longlong_as_double((long long)b);
+                else static_cast<int32_t*>(p.out[s])[r0 + lane] = ((vw >> lane) & 1u) ? (int32_t)b : -1;
+            }
+            if (lane == 0) p.valid[s][g] = vw;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) remap_codes_kernel(int32_t* __restrict__ codes, int64_t n,
+                                                          const int32_t* __restrict__ table, int32_t table_size,
+                                                          int32_t missing) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t c = codes[i];
+        codes[i] = (c >= 0 && c < table_size) ? __ldg(table + c) : missing;
+    }
+}
+
+}  // namespace etl
+
+using etl::Handle;
+
+extern "C" int etl_csv_index_rows(etl_handle* hh, const uint8_t* text, int64_t nbytes, int64_t* d_rows,
+                                  void* stream_) {
+    ETL_REQUIRE(hh && d_rows, "csv_index_rows: NULL handle or output");
+    ETL_REQUIRE(nbytes >= 0, "csv_index_rows: nbytes < 0");
+    ETL_REQUIRE(nbytes == 0 || (text && etl::aligned16(text)), "csv_index_rows: text must be 16-byte aligned");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    if (nbytes == 0) {
+        ETL_CUDA(cudaMemsetAsync(d_rows, 0, sizeof(int64_t), stream));
+        return ETL_OK;
+    }
+    const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
+    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
+    int rc = etl::arena_reserve(h, need);
+    if (rc != ETL_OK) return rc;
+    auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
+    auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
+    etl::csv_block_summary_kernel<<<(unsigned)blocks, etl::CSV_THREADS, 0, stream>>>(text, nbytes, sum);
+    etl::csv_block_scan_kernel<<<1, 1024, 0, stream>>>(sum, blocks, start, d_rows);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_csv_row_offsets(etl_handle* hh, const uint8_t* text, int64_t nbytes, int64_t* row_start,
+                                   void* stream_) {
+    ETL_REQUIRE(hh, "csv_row_offsets: NULL handle");
+    ETL_REQUIRE(nbytes >= 0, "csv_row_offsets: nbytes < 0");
+    if (nbytes == 0) return ETL_OK;
+    ETL_REQUIRE(text && etl::aligned16(text) && row_start, "csv_row_offsets: NULL or misaligned argument");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
+    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
+    ETL_REQUIRE(h->scratch_bytes >= need, "csv_row_offsets: call etl_csv_index_rows on the same text first");
+    auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
+    auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
+    etl::csv_row_offsets_kernel<<<(unsigned)blocks, etl::CSV_THREADS, 0, stream>>>(text, nbytes, start, row_start);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_csv_parse_columns(etl_handle* hh, const uint8_t* text, int64_t nbytes, const int64_t* row_start,
+                                     int64_t first_row, int64_t rows, int32_t ncols, const int32_t* field,
+                                     const int32_t* kind, void* const* out, uint32_t* const* valid,
+                                     uint64_t* const* dict_hash, uint64_t* const* dict_rep,
+                                     const int32_t* dict_capacity, int32_t flags, int32_t* d_status,
+                                     int64_t* d_first_bad_row, void* stream_) {
+    ETL_REQUIRE(hh && field && kind && out && valid && d_status && d_first_bad_row, "csv_parse_columns: NULL argument");
+    ETL_REQUIRE(ncols >= 1 && ncols <= etl::CSV_MAX_COLS, "csv_parse_columns: ncols=%d not in 1..%d", ncols,
+                etl::CSV_MAX_COLS);
+    ETL_REQUIRE(rows >= 0 && first_row >= 0, "csv_parse_columns: negative row range");
+    if (rows == 0) return ETL_OK;
+    ETL_REQUIRE(text && row_start && nbytes > 0, "csv_parse_columns: NULL text / row_start");
+    ETL_REQUIRE((reinterpret_cast<uintptr_t>(text) & 7) == 0, "csv_parse_columns: text must be 8-byte aligned");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    etl::CsvParseParams p{};
+    p.text = text; p.n = nbytes; p.row_start = row_start; p.first_row = first_row; p.rows = rows; p.ncols = ncols;
+    p.flags = flags; p.status = d_status; p.first_bad_row = d_first_bad_row;
+    for (int s = 0; s < ncols; ++s) {
+        ETL_REQUIRE(field[s] >= 0 && field[s] < etl::CSV_MAX_FIELDS, "csv_parse_columns: field[%d]=%d out of range", s,
+                    field[s]);
+        for (int t = 0; t < s; ++t) ETL_REQUIRE(field[t] != field[s], "csv_parse_columns: field %d requested twice", field[s]);
+        ETL_REQUIRE(kind[s] == 0 || kind[s] == 1, "csv_parse_columns: kind[%d]=%d", s, kind[s]);
+        ETL_REQUIRE(out[s] && valid[s], "csv_parse_columns: out[%d]/valid[%d] is NULL", s, s);
+        p.field[s] = field[s]; p.kind[s] = kind[s]; p.out[s] = out[s]; p.valid[s] = valid[s];
+        if (kind[s] == 1) {
+            ETL_REQUIRE(dict_hash && dict_rep && dict_capacity && dict_hash[s] && dict_rep[s],
+                        "csv_parse_columns: string column %d needs a dictionary", s);
+            const int32_t cap = dict_capacity[s];
+            ETL_REQUIRE(cap >= 2 && (cap & (cap - 1)) == 0, "csv_parse_columns: dict_capacity[%d]=%d is not a power of two",
+                        s, cap);
+            p.dict_hash[s] = dict_hash[s]; p.dict_rep[s] = dict_rep[s]; p.dict_mask[s] = (uint32_t)cap - 1;
+        }
+    }
+    ETL_CUDA(cudaSetDevice(h->device));
+    const int64_t groups = (rows + 31) / 32;
+    int64_t blocks = (groups + etl::PARSE_WARPS - 1) / etl::PARSE_WARPS;
+    const int64_t cap = (int64_t)h->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    etl::csv_parse_rows_kernel<<<(unsigned)blocks, etl::PARSE_WARPS * 32, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_remap_codes(etl_handle* hh, int32_t* codes, int64_t n, const int32_t* table, int32_t table_size,
+                               int32_t missing, void* stream_) {
+    ETL_REQUIRE(hh && (n == 0 || (codes && table)), "remap_codes: NULL argument");
+    ETL_REQUIRE(n >= 0 && table_size >= 0, "remap_codes: negative size");
+    if (n == 0) return ETL_OK;
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > (int64_t)h->sm_count * 16) blocks = (int64_t)h->sm_count * 16;
+    etl::remap_codes_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(codes, n, table, table_size,
+                                                                                             missing);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}

@@ -173,6 +173,128 @@ class Engine:
         self.launches += (n + chunk - 1) // chunk
         return rows.value
 
+    # -------------------------------------------------------------- a1 csv
+    def csv_index_rows(self, text: torch.Tensor, nbytes: int) -> torch.Tensor:
+        out = self.empty(1, torch.int64)
+        _lib.check(self.lib.etl_csv_index_rows(self._h, text.data_ptr(), nbytes, out.data_ptr(), self._stream()))
+        self.launches += 2 if nbytes else 0
+        return out
+
+    def csv_row_offsets(self, text: torch.Tensor, nbytes: int, rows: int) -> torch.Tensor:
+        row_start = self.empty(max(rows, 1), torch.int64)
+        _lib.check(self.lib.etl_csv_row_offsets(self._h, text.data_ptr(), nbytes, row_start.data_ptr(), self._stream()))
+        self.launches += 1 if nbytes else 0
+        return row_start[:rows]
+
+    def csv_parse_columns(self, text: torch.Tensor, nbytes: int, row_start: torch.Tensor, first_row: int, rows: int,
+                          fields: Sequence[int], kinds: Sequence[int], dicts: Sequence[Optional[Tuple[torch.Tensor, torch.Tensor]]],
+                          flags: int = 0):
+        """-> (columns, status int32[4] on host, first_bad_row).  kinds: 0 numeric
+        (f64), 1 string (int32 dictionary slot).  dicts[s] = (hash, rep) uint64
+        tables (as int64 tensors, power-of-two length) for string columns."""
+        nc = len(fields)
+        outs, valids = [], []
+        for k in kinds:
+            outs.append(self.empty(rows, torch.float64 if k == 0 else torch.int32))
+            valids.append(torch.zeros(words_for(rows), dtype=torch.int32, device=self.device))
+        status = torch.zeros(4, dtype=torch.int32, device=self.device)
+        first_bad = torch.full((1,), torch.iinfo(torch.int64).max, dtype=torch.int64, device=self.device)
+        I = C.c_int32 * nc
+        P = C.c_void_p * nc
+        dh = P(*[(d[0].data_ptr() if d is not None else None) for d in dicts])
+        dr = P(*[(d[1].data_ptr() if d is not None else None) for d in dicts])
+        dc = I(*[(d[0].shape[0] if d is not None else 0) for d in dicts])
+        _lib.check(self.lib.etl_csv_parse_columns(
+            self._h, text.data_ptr(), nbytes, _ptr(row_start), first_row, rows, nc, I(*fields), I(*kinds),
+            P(*[t.data_ptr() for t in outs]), P(*[t.data_ptr() for t in valids]), dh, dr, dc, flags,
+            status.data_ptr(), first_bad.data_ptr(), self._stream()))
+        self.launches += 1 if rows else 0
+        cols = [Column(o, v) for o, v in zip(outs, valids)]
+        return cols, status, first_bad
+
+    def remap_codes(self, codes: torch.Tensor, table: torch.Tensor, missing: int) -> torch.Tensor:
+        """StringIndexerModel.transform on codes, in place (k_means.py:74)."""
+        _lib.check(self.lib.etl_remap_codes(self._h, codes.data_ptr(), codes.shape[0], table.data_ptr(), table.shape[0],
+                                            missing, self._stream()))
+        self.launches += 1 if codes.shape[0] else 0
+        return codes
+
+    # ---------------------------------------------------------------- a6
+    def code_histogram(self, col: Column, bins: int):
+        """group-by-count of StringIndexer.fit (k_means.py:34,73) -> (int64[bins], out_of_range int64[1])."""
+        counts = self.empty(bins, torch.int64)
+        oor = self.empty(1, torch.int64)
+        _lib.check(self.lib.etl_code_histogram(self._h, _ptr(col.data), _ptr(col.valid), len(col), bins,
+                                               counts.data_ptr(), oor.data_ptr(), self._stream()))
+        self.launches += 1 if len(col) else 0
+        return counts, oor
+
+    # ------------------------------------------------------------ a8-a10
+    def assemble_dense(self, index: torch.Tensor, nums: Sequence[torch.Tensor], num_labels: int, repeats: int,
+                       dtype=torch.float64, shift=None, scale=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        n = index.shape[0]
+        D = repeats * num_labels + 3
+        out = torch.empty((n, D), dtype=dtype, device=self.device) if out is None else out
+        sh = F64x3(*shift) if shift is not None else None
+        sc = F64x3(*scale) if scale is not None else None
+        _lib.check(self.lib.etl_assemble_features_dense(
+            self._h, index.data_ptr(), C.byref(VP3(*[t.data_ptr() for t in nums])),
+            C.cast(sh, C.c_void_p) if sh is not None else None, C.cast(sc, C.c_void_p) if sc is not None else None,
+            n, num_labels, repeats, _DTYPE_CODE[dtype], out.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return out
+
+    def assemble_sparse(self, index: torch.Tensor, nums: Sequence[torch.Tensor], num_labels: int, repeats: int,
+                        shift=None, scale=None):
+        n = index.shape[0]
+        W = repeats + 3
+        oi = torch.empty((n, W), dtype=torch.int32, device=self.device)
+        ov = torch.empty((n, W), dtype=torch.float64, device=self.device)
+        sh = F64x3(*shift) if shift is not None else None
+        sc = F64x3(*scale) if scale is not None else None
+        _lib.check(self.lib.etl_assemble_features_sparse(
+            self._h, index.data_ptr(), C.byref(VP3(*[t.data_ptr() for t in nums])),
+            C.cast(sh, C.c_void_p) if sh is not None else None, C.cast(sc, C.c_void_p) if sc is not None else None,
+            n, num_labels, repeats, oi.data_ptr(), ov.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return oi, ov
+
+    # ----------------------------------------------------------- a11/a12
+    def pack_tf(self, label: Column, nums: Sequence[Column], remap: Optional[torch.Tensor] = None, shift=None,
+                scale=None):
+        """Row filter + X float32[N,3] / y int32[N] of load_csv (train_tf_ps.py:120-149)."""
+        n = len(label)
+        X = torch.empty((n, 3), dtype=torch.float32, device=self.device)
+        y = self.empty(n, torch.int32)
+        rows = self.empty(1, torch.int64)
+        sh = F64x3(*shift) if shift is not None else None
+        sc = F64x3(*scale) if scale is not None else None
+        _lib.check(self.lib.etl_pack_tf_features(
+            self._h, _ptr(label.data), _ptr(label.valid), C.byref(VP3(*[_ptr(c.data) for c in nums])),
+            C.byref(VP3(*[_ptr(c.valid) for c in nums])), C.cast(sh, C.c_void_p) if sh is not None else None,
+            C.cast(sc, C.c_void_p) if sc is not None else None, _ptr(remap), 0 if remap is None else remap.shape[0], n,
+            X.data_ptr(), y.data_ptr(), rows.data_ptr(), self._stream()))
+        self.launches += 3 if n else 0
+        return X, y, rows
+
+    def nan_to_null(self, col: Column) -> Column:
+        n = len(col)
+        if col.valid is None:
+            col.valid = torch.full((words_for(n),), -1, dtype=torch.int32, device=self.device)
+        _lib.check(self.lib.etl_nan_to_null(self._h, _ptr(col.data), _ptr(col.valid), n, self._stream()))
+        self.launches += 1 if n else 0
+        return col
+
+    def bucketize(self, col: Column, splits: Sequence[float]):
+        n = len(col)
+        d_splits = torch.tensor(list(splits), dtype=torch.float64, device=self.device)
+        out = self.empty(n, torch.int32)
+        oor = self.empty(1, torch.int64)
+        _lib.check(self.lib.etl_bucketize(self._h, _ptr(col.data), _ptr(col.valid), n, d_splits.data_ptr(),
+                                          d_splits.shape[0], out.data_ptr(), oor.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return out, oor
+
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,
                      null_rate: float = 0.0, nan_rate: float = 0.0, with_valid: bool = True) -> Column:

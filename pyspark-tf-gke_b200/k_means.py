@@ -1,0 +1,161 @@
+"""Drop-in for the ETL stage of workloads/raw-spark/k_means.py.
+
+`KMeansWorkload.k_means(input_df)` keeps the reference's signature, log lines,
+MEASURE_NAME_WEIGHT handling and error behaviour (log, then re-raise,
+k_means.py:108-110); `input_df` is a DeviceTable instead of a Spark DataFrame
+and every operation of lines 22-77 runs as a CUDA kernel through the C ABI.
+The stage ends where the reference's does: `dataset = select("features")`
+(k_means.py:77).  KMeans.fit (k_means.py:83-87) is the next component
+(SURVEY.md §8f), so `model` is None for now and the feature matrix is exposed on
+the returned pipeline model."""
+from __future__ import annotations
+
+import logging
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from .engine import Column, Engine
+from .table import DeviceTable, read_csv
+
+NUMERIC_COLS = ["value", "lower_ci", "upper_ci"]
+KEY_COL = "measure_name"
+
+
+def string_indexer_order(labels: Sequence[str], counts: Sequence[int]) -> List[int]:
+    """StringIndexer's default stringOrderType="frequencyDesc": by count
+    descending, ties by label ascending (Spark >= 3.0).  Labels compare as Java
+    strings; for BMP text that equals Python's code-point order."""
+    return sorted(range(len(labels)), key=lambda i: (-int(counts[i]), labels[i]))
+
+
+@dataclass
+class EtlPipelineModel:
+    """What Pipeline.fit(...) produced (k_means.py:71-73): the StringIndexer
+    labels, the imputation means and the assembler layout; transform() applies
+    them to a table (k_means.py:74,77)."""
+
+    engine: Engine
+    labels: List[str]           # StringIndexerModel.labels, index order
+    label_counts: List[int]
+    means: List[Optional[float]]
+    repeats: int
+    null_key_count: int = 0
+    rows_after_filter: int = 0
+    # results of transforming the training table
+    index: Optional[torch.Tensor] = None        # int32[n] label index per kept row
+    numerics: Optional[List[torch.Tensor]] = None  # 3 x f64[n], imputed
+    features_dim: int = 0
+
+    def _index_table(self, table_labels: Sequence[str]) -> torch.Tensor:
+        pos = {s: i for i, s in enumerate(self.labels)}
+        L = len(self.labels)
+        return torch.tensor([pos.get(s, L) for s in table_labels] or [L], dtype=torch.int32, device=self.engine.device)
+
+    def transform(self, table: DeviceTable):
+        """filter(isNotNull) + impute + index (unseen label -> numLabels) on a new
+        table -> (index int32[n], numerics)."""
+        eng = self.engine
+        key = table.strings[KEY_COL]
+        vals = [table.numeric[c] for c in NUMERIC_COLS]
+        fill = [m if m is not None else float("nan") for m in self.means]
+        code, nums, rows = eng.project_filter_impute(key.column, vals, fill)
+        r = int(rows.item())
+        code, nums = code[:r], [v[:r] for v in nums]
+        eng.remap_codes(code, self._index_table(key.labels), len(self.labels))
+        return code, nums
+
+    def features(self, dtype=torch.float64, index=None, numerics=None) -> torch.Tensor:
+        """Dense `features` matrix [n, repeats * L + 3] (DenseVector rows)."""
+        index = self.index if index is None else index
+        numerics = self.numerics if numerics is None else numerics
+        return self.engine.assemble_dense(index, numerics, len(self.labels), self.repeats, dtype=dtype)
+
+    def features_sparse(self, index=None, numerics=None):
+        """ELL form of the SparseVector rows: (indices int32[n, repeats+3], values f64[n, repeats+3])."""
+        index = self.index if index is None else index
+        numerics = self.numerics if numerics is None else numerics
+        return self.engine.assemble_sparse(index, numerics, len(self.labels), self.repeats)
+
+
+class KMeansWorkload:
+    DB_CONFIG = None
+    pipeline_model = None
+    kmeans_model = None
+
+    def __init__(self, engine: Optional[Engine] = None):
+        self.logger = logging.getLogger("KMeansWorkload")
+        self.engine = engine
+
+    def k_means(self, input_df: DeviceTable):
+        try:
+            eng = self.engine or input_df.engine
+            key = input_df.strings[KEY_COL]
+            self.logger.info("Checking for missing values in 'measure_name'...")
+            null_measure_name_count = int(eng.null_count(key.column).item())              # k_means.py:23
+            self.logger.info(f"Column 'measure_name' has {null_measure_name_count} missing values")
+            rows_after = input_df.rows - null_measure_name_count                          # k_means.py:27-28
+            self.logger.info(f"Rows after filtering out missing 'measure_name' values: {rows_after}")
+
+            numeric_cols = [c for c in NUMERIC_COLS if c in input_df.numeric]
+            if len(numeric_cols) != 3:
+                raise KeyError(f"input needs the numeric columns {NUMERIC_COLS}")
+            vals = [input_df.numeric[c] for c in numeric_cols]
+            # k_means.py:45-48: three avg jobs -> one pass; the isNotNull filter of :27 is still in the plan
+            sums, counts = eng.sum_count(vals, row_valid=key.column.valid)
+            sums, counts = sums.cpu().tolist(), counts.cpu().tolist()
+            means = [s / c if c else None for s, c in zip(sums, counts)]
+
+            try:
+                repeats = int(os.environ.get("MEASURE_NAME_WEIGHT", "5"))                 # k_means.py:56-61
+            except Exception:
+                repeats = 5
+            if repeats < 1:
+                repeats = 1
+            self.logger.info(f"Applying measure_name weight by repeating measure_name_vec {repeats} time(s)")
+            self.logger.info("Applying feature engineering pipeline...")
+
+            # k_means.py:27 + :49-51: filter, impute, cast - one kernel
+            fill = [m if m is not None else float("nan") for m in means]
+            code, nums, rows = eng.project_filter_impute(key.column, vals, fill)
+            r = int(rows.item())
+            assert r == rows_after
+            code, nums = code[:r], [v[:r] for v in nums]
+
+            # StringIndexer.fit (k_means.py:34,73): group-by-count, then order on the host
+            L0 = max(len(key.labels), 1)
+            hist, oor = eng.code_histogram(Column(code), L0)
+            hist = hist.cpu().tolist()
+            seen = [i for i in range(len(key.labels)) if hist[i] > 0]
+            order = string_indexer_order([key.labels[i] for i in seen], [hist[i] for i in seen])
+            labels = [key.labels[seen[i]] for i in order]
+            label_counts = [hist[seen[i]] for i in order]
+            model = EtlPipelineModel(eng, labels, label_counts, means, repeats, null_measure_name_count, r)
+            # StringIndexerModel.transform (k_means.py:74): code -> index
+            eng.remap_codes(code, model._index_table(key.labels), len(labels))
+            model.index, model.numerics = code, nums
+            model.features_dim = repeats * len(labels) + 3
+            return model, None
+        except Exception as e:
+            self.logger.error(f"Error training K-Means model: {e}")
+            raise
+
+    @classmethod
+    def main(cls, source: Optional[str] = None):
+        """`python k_means.py` (k_means.py:164-212): the reference reads the table
+        over JDBC; here the same table is read from the CSV it was loaded from
+        (infra/local/mysql-database/load_csv.py:30,76).  Errors are logged, not
+        raised (k_means.py:197-198)."""
+        logging.basicConfig(level=logging.INFO)
+        instance = cls()
+        try:
+            eng = Engine()
+            instance.engine = eng
+            src = source or os.environ.get("HEALTH_CSV", "health.csv")
+            table = read_csv(eng, src, NUMERIC_COLS, [KEY_COL])
+            cls.pipeline_model, cls.kmeans_model = instance.k_means(table)
+        except Exception as e:
+            instance.logger.error(f"An error occurred: {e}")
+        return instance

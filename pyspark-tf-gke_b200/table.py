@@ -1,0 +1,172 @@
+"""DeviceTable: the columnar, device-resident stand-in for the Spark DataFrame
+the ETL stage receives (`input_df` of KMeansWorkload.k_means, k_means.py:17).
+
+read_csv replaces spark.read.csv(path, header=True, inferSchema=True)
+(spark_workload_to_cloud_k8s.py:48) / the JDBC read of the same table
+(google_health_SQL.py:26-37): the file is copied to the GPU once and decoded
+there; only the header line and the (small) string dictionaries come back to
+the host."""
+from __future__ import annotations
+
+import csv
+import io
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+from urllib.request import urlopen
+
+import numpy as np
+import torch
+
+from ._lib import EtlError
+from .engine import Column, Engine
+
+CSV_TRIM_STRINGS = 1
+CSV_NAN_IS_NULL = 2
+
+
+@dataclass
+class StringColumn:
+    """Dictionary-encoded string column: `codes` index into `labels`
+    (ascending by code point, the order Java/Python compare strings in), -1 / a
+    cleared validity bit = null."""
+
+    column: Column
+    labels: List[str]
+
+
+@dataclass
+class DeviceTable:
+    engine: Engine
+    rows: int
+    numeric: Dict[str, Column] = field(default_factory=dict)
+    strings: Dict[str, StringColumn] = field(default_factory=dict)
+    inferred_types: Dict[str, str] = field(default_factory=dict)
+    header: List[str] = field(default_factory=list)
+
+    @property
+    def columns(self) -> List[str]:
+        return list(self.header) if self.header else list(self.strings) + list(self.numeric)
+
+    def count(self) -> int:
+        return self.rows
+
+
+def read_bytes(source) -> bytes:
+    """Path, http(s) URL (open_text, train_tf_ps.py:53-72) or bytes."""
+    if isinstance(source, (bytes, bytearray, memoryview)):
+        return bytes(source)
+    if source.startswith("http://") or source.startswith("https://"):
+        return urlopen(source).read()
+    with open(source, "rb") as fh:
+        return fh.read()
+
+
+def upload_text(eng: Engine, raw: bytes) -> torch.Tensor:
+    """File bytes -> device uint8 tensor, zero padded to a multiple of 64 (+64)
+    so the decoder's 8-byte window loads never leave the allocation."""
+    n = len(raw)
+    padded = (n + 127) // 64 * 64
+    host = torch.zeros(padded, dtype=torch.uint8).pin_memory()
+    if n:
+        host[:n] = torch.frombuffer(bytearray(raw), dtype=torch.uint8)
+    return host.to(eng.device, non_blocking=True)
+
+
+def _dictionary_labels(text: torch.Tensor, hash_tab: torch.Tensor, rep_tab: torch.Tensor):
+    """Used slots of a decode dictionary and their strings (one small gather)."""
+    h = hash_tab.cpu().numpy().view(np.uint64)
+    used = np.nonzero(h)[0]
+    rep = rep_tab.cpu().numpy().view(np.uint64)[used]
+    off = (rep >> np.uint64(24)).astype(np.int64)
+    quoted = ((rep >> np.uint64(23)) & np.uint64(1)).astype(bool)
+    length = (rep & np.uint64((1 << 23) - 1)).astype(np.int64)
+    if used.size == 0:
+        return used, []
+    idx = np.concatenate([np.arange(o, o + l) for o, l in zip(off, length)])
+    blob = text[torch.from_numpy(idx).to(text.device)].cpu().numpy().tobytes()
+    labels, pos = [], 0
+    for l, q in zip(length, quoted):
+        s = blob[pos:pos + l].decode("utf-8")
+        pos += l
+        labels.append(s.replace('""', '"') if q else s)
+    return used, labels
+
+
+def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str], trim_strings: bool = False,
+             nan_is_null: bool = False, dict_capacity: int = 1 << 16) -> DeviceTable:
+    raw = read_bytes(source)
+    n = len(raw)
+    text = upload_text(eng, raw)
+    rows_total = int(eng.csv_index_rows(text, n).item())
+    if rows_total == 0:
+        return DeviceTable(eng, 0)
+    row_start = eng.csv_row_offsets(text, n, rows_total)
+    # header line -> field positions (DictReader: a repeated name keeps its last position)
+    hdr_end = int(row_start[1].item()) if rows_total > 1 else n
+    header = next(csv.reader(io.StringIO(raw[:hdr_end].decode("utf-8"), newline="")))
+    pos = {name: j for j, name in enumerate(header)}
+    rows = rows_total - 1
+    table = DeviceTable(eng, rows, header=header)
+    wanted = [(c, 0) for c in numeric] + [(c, 1) for c in strings]
+    present = [(c, k) for c, k in wanted if c in pos]
+    if len(present) > 8:
+        raise ValueError("read_csv: at most 8 columns per call")
+    flags = (CSV_TRIM_STRINGS if trim_strings else 0) | (CSV_NAN_IS_NULL if nan_is_null else 0)
+    dicts = [None if k == 0 else (torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device),
+                                  torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device)) for _, k in present]
+    if present and rows:
+        cols, status, first_bad = eng.csv_parse_columns(text, n, row_start, 1, rows, [pos[c] for c, _ in present],
+                                                        [k for _, k in present], dicts, flags)
+        st = status.cpu().numpy()
+        if st[0]:
+            raise EtlError(-4, f"{int(st[0])} numeral(s) outside the exactly-converted domain (<=19 significant digits, "
+                               f"|exp10|<=19); first at CSV record {int(first_bad.item())}")
+        if st[1]:
+            raise EtlError(-5, f"string dictionary full (capacity {dict_capacity}); first at CSV record "
+                               f"{int(first_bad.item())}")
+    else:
+        cols, st = [], np.zeros(4, dtype=np.int32)
+    for s, ((name, kind), col) in enumerate(zip(present, cols)):
+        if kind == 0:
+            table.numeric[name] = col
+            if rows:
+                table.inferred_types[name] = "double" if (int(st[2]) >> s) & 1 else "int"
+        else:
+            used, labels = _dictionary_labels(text, *dicts[s])
+            order = sorted(range(len(labels)), key=lambda i: labels[i])
+            remap = torch.full((dict_capacity,), -1, dtype=torch.int32)
+            remap[torch.from_numpy(used[order].astype(np.int64))] = torch.arange(len(order), dtype=torch.int32)
+            eng.remap_codes(col.data, remap.to(eng.device), -1)
+            table.strings[name] = StringColumn(col, [labels[i] for i in order])
+    # a requested column that the header lacks is all null (row.get(c, "") in load_csv)
+    for name, kind in wanted:
+        if name not in pos:
+            from .engine import words_for
+
+            nullmap = torch.zeros(words_for(rows), dtype=torch.int32, device=eng.device)
+            if kind == 0:
+                table.numeric[name] = Column(torch.zeros(rows, dtype=torch.float64, device=eng.device), nullmap)
+            else:
+                table.strings[name] = StringColumn(Column(torch.full((rows,), -1, dtype=torch.int32, device=eng.device),
+                                                          nullmap), [])
+    return table
+
+
+def from_host_columns(eng: Engine, key: Sequence[Optional[str]], numerics: Dict[str, np.ndarray],
+                      key_name: str = "measure_name") -> DeviceTable:
+    """A table from already-decoded host columns (the JDBC path,
+    google_health_SQL.py:26-37: numerics arrive as FLOAT with SQL NULLs).  NaN in
+    a float array is a value; pass a numpy masked array to mark nulls."""
+    labels = sorted({s for s in key if s is not None})
+    code_of = {s: i for i, s in enumerate(labels)}
+    codes = np.array([code_of[s] if s is not None else -1 for s in key], dtype=np.int32)
+    kvalid = np.array([s is not None for s in key], dtype=bool)
+    t = DeviceTable(eng, len(key))
+    t.strings[key_name] = StringColumn(Column.from_host(codes, kvalid, eng.device), labels)
+    for name, arr in numerics.items():
+        if isinstance(arr, np.ma.MaskedArray):
+            t.numeric[name] = Column.from_host(np.ascontiguousarray(arr.filled(0)), ~np.ma.getmaskarray(arr), eng.device)
+        else:
+            t.numeric[name] = Column.from_host(np.ascontiguousarray(arr), None, eng.device)
+        t.inferred_types[name] = {"float64": "double", "float32": "float", "int32": "int"}[str(t.numeric[name].data.dtype).split(".")[-1]]
+    return t

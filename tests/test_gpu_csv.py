@@ -1,0 +1,262 @@
+"""Config 1 (BASELINE.json configs[0]): the default input end to end, plus the
+CSV decoder's edge cases - CUDA path against the golden vectors captured from
+the reference's own load_csv and against the oracle's restatement of the Spark
+stage.  Everything is compared bit for bit (integer / byte / index work, and
+fp64 values that are parsed, copied or imputed; the means are exact on this
+input because every sum is an integer < 2^53)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import pyspark_tf_gke_b200 as pkg
+from oracle import etl_oracle as O
+from tests.conftest import GOLDEN, health_text
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = pkg.Engine(0)
+    yield e
+    e.close()
+
+
+def _cases():
+    with open(os.path.join(GOLDEN, "load_csv_cases.json")) as fh:
+        return json.load(fh)
+
+
+@pytest.mark.parametrize("which", ["workloads", "infra"])
+def test_load_csv_health_matches_reference_golden(eng, which):
+    g = np.load(os.path.join(GOLDEN, "load_csv_health.npz"))
+    X, y, vocab = pkg.load_csv(health_text(which).encode())
+    assert X.dtype == np.float32 and y.dtype == np.int32 and X.flags["C_CONTIGUOUS"]
+    assert X.shape == (15355, 3) and y.shape == (15355,)
+    assert X.tobytes() == g["X"].tobytes()
+    assert y.tobytes() == g["y"].tobytes()
+    assert vocab == [str(s) for s in g["vocab"]]
+    assert np.bincount(y).tolist() == [1133, 1015, 1225, 1040, 1196, 1040, 1301, 1040, 1196, 521, 1075, 475, 707, 1040, 1351]
+
+
+@pytest.mark.parametrize("name", sorted(_cases()))
+def test_load_csv_cases_match_reference_golden(eng, name):
+    case = _cases()[name]
+    raw = case["text"].encode()
+    if name == "big_and_small":
+        # 3.4e38 is outside the exactly-converted numeral domain: loud failure, never an approximation
+        with pytest.raises(pkg.EtlError, match="outside the exactly-converted domain"):
+            pkg.load_csv(raw)
+        return
+    if "raises" in case:
+        with pytest.raises(RuntimeError, match="No valid rows"):
+            pkg.load_csv(raw)
+        return
+    X, y, vocab = pkg.load_csv(raw)
+    assert [[float(v).hex() for v in row] for row in X] == case["X_hex"]
+    assert y.tolist() == case["y"]
+    assert vocab == case["vocab"]
+
+
+def test_load_csv_numerals_inside_the_exact_domain(eng):
+    text = ("subpopulation,value,lower_ci,upper_ci\n"
+            "A,123456789012345,0.1,1e-5\nB,16777217,9007199254740993,1e22\n"
+            "C,0.30000000000000004,12345678901234567890,-0\nD,1234567890123456789e-19,.5,5.\n")
+    X, y, vocab = pkg.load_csv(text.encode())
+    eX, ey, ev = O.load_csv(text)
+    assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev
+
+
+def test_load_csv_other_columns_and_label_map(eng, tmp_path):
+    text = health_text("workloads")
+    X, y, vocab = pkg.load_csv(text.encode(), ["upper_ci", "value", "lower_ci"], "state_name")
+    eX, ey, ev = O.load_csv(text, ["upper_ci", "value", "lower_ci"], "state_name")
+    assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev and len(vocab) == 52
+    path = tmp_path / "label_map.json"
+    pkg.write_label_map(vocab, str(path))
+    with open(path) as fh:
+        raw = fh.read()
+    assert json.loads(raw) == {str(i): s for i, s in enumerate(vocab)}
+    assert raw.startswith('{\n  "0": "Alabama"')  # indent=2, int keys (train_tf_ps.py:582-583)
+
+
+@pytest.mark.parametrize("which", ["workloads", "infra"])
+@pytest.mark.parametrize("repeats", [5, 1])
+def test_k_means_etl_matches_oracle(eng, which, repeats, monkeypatch):
+    text = health_text(which)
+    monkeypatch.setenv("MEASURE_NAME_WEIGHT", str(repeats))
+    table = pkg.read_csv(eng, text.encode(), ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    assert table.rows == 18155
+    assert table.inferred_types["value"] == ("int" if which == "workloads" else "double")
+    model, kmeans = pkg.KMeansWorkload(eng).k_means(table)
+    exp = O.k_means_etl(text, repeats=repeats)
+    assert model.null_key_count == exp["null_measure_name"] == 0
+    assert model.rows_after_filter == exp["rows_after_filter"] == 18155
+    assert [float(m).hex() for m in model.means] == [float(exp["means"][c]).hex() for c in ("value", "lower_ci", "upper_ci")]
+    assert model.means == [1738.2895095771808, 1724.1278848441589, 1762.6607185343803]
+    assert model.labels == exp["labels"] and model.label_counts == exp["label_counts"]
+    assert model.index.cpu().numpy().tolist() == exp["index"].astype(np.int32).tolist()
+    for a, b in zip(model.numerics, exp["numerics"]):
+        assert a.cpu().numpy().tobytes() == b.tobytes()
+    F = model.features().cpu().numpy()
+    assert F.shape == (18155, repeats * 30 + 3) == exp["features"].shape
+    assert F.tobytes() == exp["features"].tobytes()
+    F32 = model.features(torch.float32).cpu().numpy()
+    assert F32.tobytes() == exp["features"].astype(np.float32).tobytes()
+    # the SparseVector view
+    oi, ov = (t.cpu().numpy() for t in model.features_sparse())
+    sparse = O.assemble_features_sparse(exp["index"], 30, exp["numerics"], repeats)
+    for i in (0, 1, 17, 9000, 18154):
+        ind = [int(k) for k, v in zip(oi[i], ov[i]) if k >= 0 and v != 0.0]
+        val = [float(v) for k, v in zip(oi[i], ov[i]) if k >= 0 and v != 0.0]
+        assert (ind, val) == sparse[i]
+
+
+def test_k_means_logs_and_reraises(eng, caplog):
+    wl = pkg.KMeansWorkload(eng)
+    table = pkg.read_csv(eng, b"measure_name,value\nA,1\n", ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    del table.numeric["lower_ci"]
+    with caplog.at_level("ERROR"):
+        with pytest.raises(KeyError):
+            wl.k_means(table)
+    assert "Error training K-Means model" in caplog.text
+
+
+def test_unseen_and_null_keys_go_to_the_unknown_index(eng):
+    train = b"measure_name,value,lower_ci,upper_ci\nb,1,2,3\na,4,5,6\nb,7,,9\n,1,1,1\n"
+    table = pkg.read_csv(eng, train, ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    model, _ = pkg.KMeansWorkload(eng).k_means(table)
+    assert model.null_key_count == 1 and model.rows_after_filter == 3
+    assert model.labels == ["b", "a"] and model.label_counts == [2, 1]
+    assert model.means == [4.0, 3.5, 6.0]
+    assert model.numerics[1].cpu().tolist() == [2.0, 5.0, 3.5]
+    other = pkg.read_csv(eng, b"measure_name,value,lower_ci,upper_ci\nzzz,1,2,3\na,,5,6\n", ["value", "lower_ci", "upper_ci"],
+                         ["measure_name"])
+    index, nums = model.transform(other)
+    assert index.cpu().tolist() == [2, 1]          # unseen -> numLabels (handleInvalid="keep")
+    assert nums[0].cpu().tolist() == [1.0, 4.0]    # imputed with the training mean
+    F = model.features(index=index, numerics=nums).cpu().numpy()
+    assert F.shape == (2, 5 * 2 + 3) and F[0, :10].sum() == 0 and F[1, :10].tolist() == [0, 1] * 5
+
+
+def _synthetic_csv(rows, seed):
+    rng = np.random.default_rng(seed)
+    names = ["alpha", "be,ta", 'ga"mma', "delta\nline", "  eps  ", ""]
+    lines = ["id,measure_name,filler,value,lower_ci,upper_ci"]
+    for i in range(rows):
+        k = names[rng.integers(len(names))]
+        if any(ch in k for ch in ',"\n') or rng.random() < 0.1:
+            k = '"' + k.replace('"', '""') + '"'
+        filler = "x" * int(rng.integers(0, 400)) if rng.random() < 0.05 else "f"
+        cells = []
+        for _ in range(3):
+            u = rng.random()
+            cells.append("" if u < 0.07 else ("NaN" if u < 0.09 else (str(int(rng.integers(0, 100000))) if u < 0.6
+                                                                       else repr(float(np.round(rng.random() * 1e5, 3))))))
+        eol = "\r\n" if rng.random() < 0.1 else "\n"
+        lines.append(f"{i},{k},{filler},{','.join(cells)}" + ("\n" if rng.random() < 0.02 else "") + eol.rstrip("\n"))
+    return "\n".join(lines) + "\n"
+
+
+@pytest.mark.parametrize("rows,seed", [(1, 0), (37, 1), (5000, 2), (120_000, 3)])
+def test_decoder_on_synthetic_csv_with_quotes_newlines_and_nulls(eng, rows, seed):
+    text = _synthetic_csv(rows, seed)
+    table = pkg.read_csv(eng, text.encode(), ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    header, cols = O.read_csv_columns(text)
+    assert table.rows == len(cols["value"])
+    for c in ("value", "lower_ci", "upper_ci"):
+        v, vv = O.to_numeric_column(cols[c])
+        got = table.numeric[c]
+        assert (got.valid_host() == vv).all()
+        g = got.data.cpu().numpy()
+        assert g[vv].tobytes() == v[vv].tobytes()  # NaN text -> NaN value, same bits
+    key = table.strings["measure_name"]
+    exp_keys = cols["measure_name"]
+    kv = key.column.valid_host()
+    assert (kv == np.array([k is not None for k in exp_keys])).all()
+    codes = key.column.data.cpu().numpy()
+    assert [key.labels[c] if ok else None for c, ok in zip(codes, kv)] == exp_keys
+    # and the TF-side reader on the same text
+    try:
+        eX, ey, ev = O.load_csv(text, label_col="measure_name")
+    except RuntimeError:
+        with pytest.raises(RuntimeError):
+            pkg.load_csv(text.encode(), label_col="measure_name")
+        return
+    X, y, vocab = pkg.load_csv(text.encode(), label_col="measure_name")
+    assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev
+
+
+def test_row_index_across_block_boundaries(eng):
+    # quoted fields with newlines and commas straddling the 16 KiB scan blocks
+    parts = ["a,b"]
+    for i in range(300):
+        parts.append(f'{i},"' + ("line\n" * (i % 50)) + ',"",' + "z" * (i * 7 % 997) + '"')
+        if i % 17 == 0:
+            parts.append("")  # blank line
+    text = "\r\n".join(parts)
+    raw = text.encode()
+    t = pkg.table.upload_text(eng, raw)
+    rows = int(eng.csv_index_rows(t, len(raw)).item())
+    import csv, io
+    exp = [r for r in csv.reader(io.StringIO(text, newline="")) if r]
+    assert rows == len(exp) == 301
+    starts = eng.csv_row_offsets(t, len(raw), rows).cpu().numpy()
+    assert starts[0] == 0
+    for r in (1, 2, 51, 299, 300):
+        assert raw[starts[r]:].decode().startswith(f"{r - 1},\"")
+
+
+def test_empty_and_header_only_inputs(eng):
+    assert pkg.read_csv(eng, b"", ["value"], ["measure_name"]).rows == 0
+    t = pkg.read_csv(eng, b"measure_name,value\n", ["value"], ["measure_name"])
+    assert t.rows == 0
+    t = pkg.read_csv(eng, b"\n\n\r\n", ["value"], ["measure_name"])
+    assert t.rows == 0
+
+
+def test_bucketize_standardise_and_histogram(eng):
+    rng = np.random.default_rng(5)
+    n = 100_001
+    x = rng.random(n) * 10
+    x[::97] = np.nan
+    valid = rng.random(n) > 0.05
+    col = pkg.Column.from_host(x, valid, eng.device)
+    splits = [0.0, 1.0, 2.5, 5.0, 10.0]
+    out, oor = eng.bucketize(col, splits)
+    exp = O.bucketize(np.where(valid, x, np.nan), splits)
+    assert out.cpu().numpy().tolist() == exp.astype(np.int32).tolist() and int(oor.item()) == 0
+    out, oor = eng.bucketize(pkg.Column.from_host(np.array([-1.0, 0.0, 10.0, 11.0]), None, eng.device), splits)
+    assert out.cpu().tolist() == [-1, 0, 3, -1] and int(oor.item()) == 2
+    # histogram: shared-memory path and the global path (bins > 8192)
+    for bins in (30, 20_000):
+        codes = rng.integers(0, bins, n).astype(np.int32)
+        counts, bad = eng.code_histogram(pkg.Column.from_host(codes, valid, eng.device), bins)
+        assert counts.cpu().numpy().tolist() == np.bincount(codes[valid], minlength=bins).tolist() and int(bad.item()) == 0
+    # standardised numerics in the TF layout: (x - mean) * (1 / std), float32
+    nums = [rng.random(n) * 100 for _ in range(3)]
+    stats = [O.column_stats(v) for v in nums]
+    lab = pkg.Column.from_host(rng.integers(0, 7, n).astype(np.int32), valid, eng.device)
+    cols = [pkg.Column.from_host(v, None, eng.device) for v in nums]
+    X, y, rows = eng.pack_tf(lab, cols, shift=[m for m, _ in stats], scale=[1.0 / s for _, s in stats])
+    r = int(rows.item())
+    assert r == int(valid.sum())
+    expX = np.stack([O.standardize(v[valid], m, s, with_mean=True) for v, (m, s) in zip(nums, stats)], axis=1)
+    np.testing.assert_allclose(X[:r].cpu().numpy(), expX.astype(np.float32), rtol=1e-6, atol=0)
+    assert y[:r].cpu().numpy().tolist() == lab.data.cpu().numpy()[valid].tolist()
+
+
+def test_nan_to_null_then_pack(eng):
+    n = 5000
+    rng = np.random.default_rng(9)
+    nums = [rng.random(n) for _ in range(3)]
+    nums[1][::13] = np.nan
+    lab = pkg.Column.from_host(rng.integers(0, 3, n).astype(np.int32), None, eng.device)
+    cols = [eng.nan_to_null(pkg.Column.from_host(v, None, eng.device)) for v in nums]
+    X, y, rows = eng.pack_tf(lab, cols)
+    keep = ~np.isnan(nums[1])
+    assert int(rows.item()) == int(keep.sum())
+    assert X[:int(rows.item())].cpu().numpy().tobytes() == np.stack([v[keep] for v in nums], axis=1).astype(np.float32).tobytes()
