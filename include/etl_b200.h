@@ -243,6 +243,54 @@ ETL_API int etl_pack_tf_features(etl_handle* h, const int32_t* label, const uint
  * columns that did not come from the CSV decoder). */
 ETL_API int etl_nan_to_null(etl_handle* h, const double* val, uint32_t* valid, int64_t n, void* stream);
 
+/* ---- north-star extension: explicit groupBy aggregates (no reference site) - */
+
+/* df.groupBy(key).agg(count(*), count(c), sum(c), avg(c), min(c), max(c)) for up
+ * to 3 double columns; the reference's only groupBy is the count inside
+ * StringIndexer.fit (k_means.py:34,73).  Spark semantics: a null key is its own
+ * group; count(c) counts non-null cells; sum/min/max skip nulls; NaN propagates
+ * through sum and is the largest value for min/max.
+ * The result lives in a caller-owned open-addressing table of
+ * etl_groupby_table_words(...) uint64 words: `capacity` (power of two, >= 2 x
+ * the number of groups) entries plus one for the null-key group; entry layout
+ * {key, rows, (count_c, sum_c) x ncols [, (min_c, max_c) x ncols]}.  Key value
+ * INT64_MIN is reserved.  Usage: init once, accumulate any number of batches
+ * (also partial tables received from other ranks), compact.
+ * etl_groupby_accumulate: keys int32/int64 with element stride key_stride; val[c]
+ * double with element stride val_stride[c] (NULL = 1) - strides let it read the
+ * 16-byte {key, value} records of the exchange directly.  groups_hint <= 2048
+ * (0 = unknown -> 1024) selects the shared-memory kernel (per-CTA table, one
+ * flush), larger the direct global-table kernel.  d_status (device int64[2],
+ * zeroed by the caller): [0] rows dropped because the table was full, [1] rows
+ * carrying the reserved key - both must be 0 for a valid result.
+ * etl_groupby_compact: used entries -> out_keys/out_rows int64[out_capacity],
+ * out_count int64 / out_sum,out_min,out_max double [ncols][out_capacity]
+ * (column-major), in table order (sort by key to compare); *d_groups = groups
+ * found (may exceed out_capacity: then only the first out_capacity were
+ * written).  An all-null group has count 0, sum 0 and NaN min/max. */
+ETL_API int etl_groupby_table_words(int32_t ncols, int32_t minmax, int64_t capacity, int64_t* words);
+ETL_API int etl_groupby_init(etl_handle* h, uint64_t* table, int64_t capacity, int32_t ncols, int32_t minmax,
+                     void* stream);
+ETL_API int etl_groupby_accumulate(etl_handle* h, const void* keys, int32_t key_dtype, int64_t key_stride,
+                           const uint32_t* key_valid, int32_t ncols, const double* const val[],
+                           const int64_t val_stride[], const uint32_t* const val_valid[], int64_t n,
+                           uint64_t* table, int64_t capacity, int32_t minmax, int64_t groups_hint,
+                           int64_t* d_status, void* stream);
+ETL_API int etl_groupby_compact(etl_handle* h, const uint64_t* table, int64_t capacity, int32_t ncols, int32_t minmax,
+                        int64_t out_capacity, int64_t* out_keys, int64_t* out_rows, int64_t* out_count,
+                        double* out_sum, double* out_min, double* out_max, int64_t* d_groups, void* stream);
+
+/* The map side of Spark's shuffle exchange (the Exchange hashpartitioning node
+ * under every aggregate of k_means.py:23-48; north-star item 4): rows (key int64,
+ * value double) are grouped by destination rank dest = (hi32(mix64(key)) * parts)
+ * >> 32 into one buffer of 16-byte records {key, value bits}; destination d
+ * occupies records [d_part_base[d], d_part_base[d] + d_part_counts[d]).  That
+ * buffer is the send side of an all-to-all (NCCL, torch.distributed); the
+ * receiver feeds its records to etl_groupby_accumulate with strides of 2.
+ * out_records: int64[2 * n], 16-byte aligned.  parts <= 64. */
+ETL_API int etl_hash_partition(etl_handle* h, const int64_t* keys, const double* vals, int64_t n, int32_t parts,
+                       int64_t* d_part_counts, int64_t* d_part_base, int64_t* out_records, void* stream);
+
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 
 /* Spark ML Bucketizer(handleInvalid="keep"): out[i] = b with splits[b] <= x <

@@ -63,6 +63,15 @@ _PROTOS = {
     "etl_nan_to_null": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "etl_bucketize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
                                 C.c_void_p, C.c_void_p]),
+    "etl_groupby_table_words": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_int64)]),
+    "etl_groupby_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
+    "etl_groupby_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                         C.c_void_p, C.c_void_p]),
+    "etl_groupby_compact": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "etl_hash_partition": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
     "etl_synth_column": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_uint64, C.c_double,
                                    C.c_double, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

@@ -1,0 +1,486 @@
+// groupBy(key).agg(count, sum, mean, min, max) - hash aggregation.
+// North-star extension: the reference's only groupBy is the count hidden inside
+// StringIndexer.fit (k_means.py:34,73); Spark semantics are restated in
+// oracle/etl_oracle.py::groupby_agg.
+//
+// One global open-addressing table (array of fixed-stride entries, key + row
+// count + per-column count / sum [/ min / max]) is the result AND the spill
+// target.  Two kernels fill it:
+//   groupby_smem_kernel    low cardinality: every CTA aggregates into its own
+//        shared-memory open-addressing table (64-bit CAS on the key slot,
+//        32-bit native shared atomics for counts, CAS-loop shared atomics for
+//        fp64 sums) and flushes it once at the end; a row whose key finds no
+//        shared slot within the probe limit spills straight to the global table;
+//   groupby_global_kernel  high cardinality: every row goes to the global table
+//        (one 32-byte entry = one sector for a single value column).
+// Then groupby_compact_kernel turns used entries into dense columnar output.
+// Hash = splitmix64 finaliser; the same function picks the destination rank of
+// the exchange (hash_partition), so a key's rank and its slot are independent
+// bits of one hash.
+#include "common.cuh"
+
+namespace etl {
+
+constexpr uint64_t GB_EMPTY = 0x8000000000000000ull;  // INT64_MIN: reserved, cannot be a key
+constexpr int GB_THREADS = 256;
+constexpr int GB_MAX_PROBES_SMEM = 32;
+
+struct GroupByParams {
+    const void* keys;
+    int32_t key_dtype;      // ETL_I32 / ETL_I64
+    int64_t key_stride;     // in elements (1 = contiguous)
+    const uint32_t* key_valid;
+    const double* val[3];
+    int64_t val_stride[3];
+    const uint32_t* val_valid[3];
+    int32_t ncols;
+    int32_t minmax;
+    int64_t n;
+    uint64_t* table;        // [capacity + 1] entries of `stride` words; entry `capacity` = the null-key group
+    uint64_t mask;          // capacity - 1
+    int32_t stride;         // words per entry: 2 + 2 * ncols (+ 2 * ncols with min/max)
+    int32_t smem_slots;     // power of two
+    unsigned long long* status;  // [0] rows that found no global slot (table full), [1] rows with the reserved key
+};
+
+__device__ __forceinline__ uint64_t dbl_sortable(double x) {
+    if (x != x) return 0xfff8000000000000ull;  // every NaN -> one value above +inf (Spark: NaN is largest)
+    const uint64_t b = (uint64_t)__double_as_longlong(x);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dbl_from_sortable(uint64_t e) {
+    const uint64_t b = (e >> 63) ? (e & 0x7fffffffffffffffull) : ~e;
+    return __longlong_as_double((long long)b);
+}
+
+__device__ __forceinline__ int64_t gb_load_key(const GroupByParams& p, int64_t i) {
+    if (p.key_dtype == ETL_I64) return static_cast<const int64_t*>(p.keys)[i * p.key_stride];
+    return (int64_t)static_cast<const int32_t*>(p.keys)[i * p.key_stride];
+}
+__device__ __forceinline__ bool gb_bit(const uint32_t* bm, int64_t i) {
+    return !bm || ((__ldg(bm + (i >> 5)) >> (i & 31)) & 1u);
+}
+
+// add one row's (or one flushed partial's) contribution to a global entry
+__device__ __forceinline__ void gb_global_add(uint64_t* e, const GroupByParams& p, unsigned long long rows,
+                                              const unsigned long long cnt[3], const double sum[3],
+                                              const uint64_t mn[3], const uint64_t mx[3]) {
+    atomicAdd(reinterpret_cast<unsigned long long*>(e + 1), rows);
+    for (int c = 0; c < p.ncols; ++c) {
+        if (!cnt[c]) continue;
+        atomicAdd(reinterpret_cast<unsigned long long*>(e + 2 + 2 * c), cnt[c]);
+        atomicAdd(reinterpret_cast<double*>(e + 3 + 2 * c), sum[c]);
+        if (p.minmax) {
+            atomicMin(reinterpret_cast<unsigned long long*>(e + 2 + 2 * p.ncols + 2 * c), (unsigned long long)mn[c]);
+            atomicMax(reinterpret_cast<unsigned long long*>(e + 3 + 2 * p.ncols + 2 * c), (unsigned long long)mx[c]);
+        }
+    }
+}
+
+// entry of `key` in the global table (inserting it), or nullptr when the table is full
+__device__ __forceinline__ uint64_t* gb_global_slot(const GroupByParams& p, uint64_t key) {
+    uint64_t slot = (mix64(key) >> 20) & p.mask;
+    for (uint64_t probe = 0; probe <= p.mask; ++probe) {
+        uint64_t* e = p.table + slot * p.stride;
+        uint64_t cur = ld_relaxed_u64(e);
+        if (cur == GB_EMPTY)
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(e), (unsigned long long)GB_EMPTY, (unsigned long long)key);
+        if (cur == GB_EMPTY || cur == key) return e;
+        slot = (slot + 1) & p.mask;
+    }
+    return nullptr;
+}
+
+__device__ __forceinline__ void gb_row_to_global(const GroupByParams& p, uint64_t key, bool key_null, const bool ok[3],
+                                                 const double v[3]) {
+    uint64_t* e = key_null ? p.table + (p.mask + 1) * p.stride : gb_global_slot(p, key);
+    if (!e) {
+        atomicAdd(p.status, 1ull);
+        return;
+    }
+    unsigned long long cnt[3];
+    uint64_t mn[3], mx[3];
+    double sum[3];
+    for (int c = 0; c < 3; ++c) {
+        cnt[c] = ok[c] ? 1 : 0;
+        sum[c] = v[c];
+        mn[c] = mx[c] = dbl_sortable(v[c]);
+    }
+    gb_global_add(e, p, 1, cnt, sum, mn, mx);
+}
+
+__global__ void __launch_bounds__(GB_THREADS) groupby_global_kernel(const GroupByParams p) {
+    for (int64_t i = (int64_t)blockIdx.x * GB_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * GB_THREADS) {
+        const bool key_null = !gb_bit(p.key_valid, i);
+        const uint64_t key = (uint64_t)gb_load_key(p, i);
+        if (!key_null && key == GB_EMPTY) {
+            atomicAdd(p.status + 1, 1ull);
+            continue;
+        }
+        bool ok[3] = {false, false, false};
+        double v[3] = {0.0, 0.0, 0.0};
+        for (int c = 0; c < p.ncols; ++c) {
+            ok[c] = gb_bit(p.val_valid[c], i);
+            if (ok[c]) v[c] = p.val[c][i * p.val_stride[c]];
+        }
+        gb_row_to_global(p, key, key_null, ok, v);
+    }
+}
+
+// shared table layout (dynamic smem): keys u64[S] | sum f64[3][S] | min u64[3][S] | max u64[3][S] (if minmax)
+//                                     | rows u32[S] | cnt u32[3][S]
+template <bool MINMAX>
+__global__ void __launch_bounds__(GB_THREADS) groupby_smem_kernel(const GroupByParams p) {
+    extern __shared__ __align__(16) unsigned char gb_smem[];
+    const int S = p.smem_slots;
+    const int V = p.ncols;
+    uint64_t* skeys = reinterpret_cast<uint64_t*>(gb_smem);
+    double* ssum = reinterpret_cast<double*>(skeys + S);
+    uint64_t* smin = reinterpret_cast<uint64_t*>(ssum + (size_t)V * S);
+    uint64_t* smax = smin + (MINMAX ? (size_t)V * S : 0);
+    uint32_t* srows = reinterpret_cast<uint32_t*>(smax + (MINMAX ? (size_t)V * S : 0));
+    uint32_t* scnt = srows + S;
+    for (int i = threadIdx.x; i < S; i += GB_THREADS) {
+        skeys[i] = GB_EMPTY;
+        srows[i] = 0;
+        for (int c = 0; c < V; ++c) {
+            ssum[c * S + i] = 0.0;
+            scnt[c * S + i] = 0;
+            if (MINMAX) { smin[c * S + i] = ~0ull; smax[c * S + i] = 0ull; }
+        }
+    }
+    __syncthreads();
+    const uint32_t smask = (uint32_t)S - 1;
+    for (int64_t i = (int64_t)blockIdx.x * GB_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * GB_THREADS) {
+        const bool key_null = !gb_bit(p.key_valid, i);
+        const uint64_t key = (uint64_t)gb_load_key(p, i);
+        if (!key_null && key == GB_EMPTY) {
+            atomicAdd(p.status + 1, 1ull);
+            continue;
+        }
+        bool ok[3] = {false, false, false};
+        double v[3] = {0.0, 0.0, 0.0};
+        for (int c = 0; c < V; ++c) {
+            ok[c] = gb_bit(p.val_valid[c], i);
+            if (ok[c]) v[c] = p.val[c][i * p.val_stride[c]];
+        }
+        int slot = -1;
+        if (!key_null) {
+            uint32_t s = (uint32_t)(mix64(key) >> 40) & smask;
+            for (int probe = 0; probe < GB_MAX_PROBES_SMEM; ++probe) {
+                uint64_t cur = skeys[s];
+                if (cur == GB_EMPTY)
+                    cur = atomicCAS(reinterpret_cast<unsigned long long*>(skeys + s), (unsigned long long)GB_EMPTY,
+                                    (unsigned long long)key);
+                if (cur == GB_EMPTY || cur == key) { slot = (int)s; break; }
+                s = (s + 1) & smask;
+            }
+        }
+        if (slot < 0) {  // null key, or no shared slot within the probe limit: spill to the global table
+            gb_row_to_global(p, key, key_null, ok, v);
+            continue;
+        }
+        atomicAdd(srows + slot, 1u);
+        for (int c = 0; c < V; ++c) {
+            if (!ok[c]) continue;
+            atomicAdd(scnt + c * S + slot, 1u);
+            atomicAdd(ssum + c * S + slot, v[c]);
+            if (MINMAX) {
+                const uint64_t e = dbl_sortable(v[c]);
+                atomicMin(reinterpret_cast<unsigned long long*>(smin + c * S + slot), (unsigned long long)e);
+                atomicMax(reinterpret_cast<unsigned long long*>(smax + c * S + slot), (unsigned long long)e);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < S; i += GB_THREADS) {
+        const uint64_t key = skeys[i];
+        if (key == GB_EMPTY) continue;
+        uint64_t* e = gb_global_slot(p, key);
+        if (!e) {
+            atomicAdd(p.status, (unsigned long long)srows[i]);
+            continue;
+        }
+        unsigned long long cnt[3] = {0, 0, 0};
+        double sum[3] = {0, 0, 0};
+        uint64_t mn[3] = {~0ull, ~0ull, ~0ull}, mx[3] = {0, 0, 0};
+        for (int c = 0; c < V; ++c) {
+            cnt[c] = scnt[c * S + i];
+            sum[c] = ssum[c * S + i];
+            if (MINMAX) { mn[c] = smin[c * S + i]; mx[c] = smax[c * S + i]; }
+        }
+        gb_global_add(e, p, srows[i], cnt, sum, mn, mx);
+    }
+}
+
+__global__ void __launch_bounds__(256) groupby_init_kernel(uint64_t* table, int64_t entries, int32_t stride,
+                                                           int32_t ncols, int32_t minmax) {
+    const int64_t total = entries * stride;
+    for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(w % stride);
+        uint64_t v = 0;
+        if (f == 0) v = GB_EMPTY;
+        else if (minmax && f >= 2 + 2 * ncols) v = ((f - 2 - 2 * ncols) & 1) ? 0ull : ~0ull;  // min slot / max slot
+        table[w] = v;
+    }
+}
+
+// used entries -> dense columnar arrays (order = slot order; callers sort by key)
+__global__ void __launch_bounds__(256) groupby_compact_kernel(const uint64_t* __restrict__ table, int64_t capacity,
+                                                              int32_t stride, int32_t ncols, int32_t minmax,
+                                                              int64_t* out_keys, int64_t* out_rows, int64_t* out_cnt,
+                                                              double* out_sum, double* out_min, double* out_max,
+                                                              int64_t out_capacity, unsigned long long* d_groups) {
+    for (int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; s < capacity; s += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t* e = table + s * stride;
+        if (e[0] == GB_EMPTY) continue;
+        // warp-aggregated append
+        const unsigned active = __activemask();
+        const int leader = __ffs(active) - 1;
+        unsigned long long base = 0;
+        if ((threadIdx.x & 31) == leader) base = atomicAdd(d_groups, (unsigned long long)__popc(active));
+        base = __shfl_sync(active, base, leader);
+        const int64_t g = (int64_t)base + __popc(active & lanemask_lt());
+        if (g >= out_capacity) continue;
+        out_keys[g] = (int64_t)e[0];
+        out_rows[g] = (int64_t)e[1];
+        for (int c = 0; c < ncols; ++c) {
+            out_cnt[c * out_capacity + g] = (int64_t)e[2 + 2 * c];
+            out_sum[c * out_capacity + g] = __longlong_as_double((long long)e[3 + 2 * c]);
+            if (minmax) {
+                const bool any = e[2 + 2 * c] != 0;
+                const double nanv = __longlong_as_double(0x7ff8000000000000ll);
+                out_min[c * out_capacity + g] = any ? dbl_from_sortable(e[2 + 2 * ncols + 2 * c]) : nanv;
+                out_max[c * out_capacity + g] = any ? dbl_from_sortable(e[3 + 2 * ncols + 2 * c]) : nanv;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- exchange
+// Hash partition of (key, value) rows into P destination ranges of one output
+// buffer of 16-byte records {key, value bits} - the send buffer of the
+// all-to-all.  dest = (hi32(mix64(key)) * P) >> 32.
+constexpr int PART_TILE = 2048;
+constexpr int PART_THREADS = 256;
+constexpr int PART_MAX = 64;
+
+__device__ __forceinline__ int part_dest(uint64_t key, int parts) {
+    return (int)__umulhi((unsigned)(mix64(key) >> 32), (unsigned)parts);  // Lemire range reduction, < parts
+}
+
+__global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int64_t* __restrict__ keys, int64_t n,
+                                                                       int parts, unsigned long long* counts) {
+    __shared__ unsigned int s_cnt[PART_MAX];
+    if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * PART_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * PART_THREADS) {
+        const int d = part_dest((uint64_t)keys[i], parts);
+        atomicAdd(&s_cnt[d & (PART_MAX - 1)], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < parts && s_cnt[threadIdx.x]) atomicAdd(counts + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+}
+
+// exclusive scan of the <= 64 destination counts
+__global__ void partition_scan_kernel(const int64_t* counts, int64_t* base, int parts) {
+    int64_t run = 0;
+    for (int d = 0; d < parts; ++d) { base[d] = run; run += counts[d]; }
+}
+
+__global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const int64_t* __restrict__ keys,
+                                                                         const double* __restrict__ vals, int64_t n,
+                                                                         int parts, const int64_t* __restrict__ part_base,
+                                                                         unsigned long long* cursor, int64_t* out_records) {
+    __shared__ unsigned int s_cnt[PART_MAX], s_off[PART_MAX];
+    __shared__ unsigned long long s_gbase[PART_MAX];
+    __shared__ int64_t s_key[PART_TILE];
+    __shared__ double s_val[PART_TILE];
+    __shared__ uint8_t s_dest[PART_TILE];
+    const int64_t tiles = (n + PART_TILE - 1) / PART_TILE;
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        __syncthreads();
+        if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        const int64_t row0 = t * PART_TILE;
+        const int rows = n - row0 < PART_TILE ? (int)(n - row0) : PART_TILE;
+        // pass 1: destination and rank within (tile, destination)
+        unsigned rank[PART_TILE / PART_THREADS];
+        int dest[PART_TILE / PART_THREADS];
+        int64_t k[PART_TILE / PART_THREADS];
+        double v[PART_TILE / PART_THREADS];
+#pragma unroll
+        for (int j = 0; j < PART_TILE / PART_THREADS; ++j) {
+            const int r = j * PART_THREADS + threadIdx.x;
+            dest[j] = -1;
+            if (r < rows) {
+                k[j] = keys[row0 + r];
+                v[j] = vals[row0 + r];
+                dest[j] = part_dest((uint64_t)k[j], parts);
+                rank[j] = atomicAdd(&s_cnt[dest[j]], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned run = 0;
+            for (int d = 0; d < parts; ++d) { s_off[d] = run; run += s_cnt[d]; }
+        }
+        if (threadIdx.x < parts && s_cnt[threadIdx.x])
+            s_gbase[threadIdx.x] = atomicAdd(cursor + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+        __syncthreads();
+        // pass 2: stage by destination, then write each destination's run contiguously
+#pragma unroll
+        for (int j = 0; j < PART_TILE / PART_THREADS; ++j) {
+            if (dest[j] < 0) continue;
+            const unsigned pos = s_off[dest[j]] + rank[j];
+            s_key[pos] = k[j];
+            s_val[pos] = v[j];
+            s_dest[pos] = (uint8_t)dest[j];
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < rows; i += PART_THREADS) {
+            const int d = s_dest[i];
+            const int64_t g = part_base[d] + (int64_t)s_gbase[d] + (i - (int)s_off[d]);
+            longlong2 rec;
+            rec.x = s_key[i];
+            rec.y = __double_as_longlong(s_val[i]);
+            *reinterpret_cast<longlong2*>(out_records + 2 * g) = rec;
+        }
+    }
+}
+
+}  // namespace etl
+
+using etl::Handle;
+
+static inline int gb_stride(int ncols, int minmax) { return 2 + 2 * ncols + (minmax ? 2 * ncols : 0); }
+
+extern "C" int etl_groupby_table_words(int32_t ncols, int32_t minmax, int64_t capacity, int64_t* words) {
+    ETL_REQUIRE(words && ncols >= 0 && ncols <= 3 && capacity >= 2 && (capacity & (capacity - 1)) == 0,
+                "groupby_table_words: ncols in 0..3 and a power-of-two capacity required");
+    *words = (capacity + 1) * gb_stride(ncols, minmax);
+    return ETL_OK;
+}
+
+extern "C" int etl_groupby_init(etl_handle* hh, uint64_t* table, int64_t capacity, int32_t ncols, int32_t minmax,
+                                void* stream_) {
+    ETL_REQUIRE(hh && table, "groupby_init: NULL argument");
+    ETL_REQUIRE(ncols >= 0 && ncols <= 3 && capacity >= 2 && (capacity & (capacity - 1)) == 0,
+                "groupby_init: ncols in 0..3 and a power-of-two capacity required");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    const int64_t total = (capacity + 1) * gb_stride(ncols, minmax);
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > (int64_t)h->sm_count * 16) blocks = (int64_t)h->sm_count * 16;
+    etl::groupby_init_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(table, capacity + 1,
+                                                                                             gb_stride(ncols, minmax),
+                                                                                             ncols, minmax);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_groupby_accumulate(etl_handle* hh, const void* keys, int32_t key_dtype, int64_t key_stride,
+                                      const uint32_t* key_valid, int32_t ncols, const double* const val[],
+                                      const int64_t val_stride[], const uint32_t* const val_valid[], int64_t n,
+                                      uint64_t* table, int64_t capacity, int32_t minmax, int64_t groups_hint,
+                                      int64_t* d_status, void* stream_) {
+    ETL_REQUIRE(hh && table && d_status, "groupby_accumulate: NULL argument");
+    ETL_REQUIRE(ncols >= 0 && ncols <= 3, "groupby_accumulate: ncols=%d not in 0..3", ncols);
+    ETL_REQUIRE(key_dtype == ETL_I32 || key_dtype == ETL_I64, "groupby_accumulate: key_dtype=%d", key_dtype);
+    ETL_REQUIRE(capacity >= 2 && (capacity & (capacity - 1)) == 0, "groupby_accumulate: capacity must be a power of two");
+    ETL_REQUIRE(n >= 0 && key_stride >= 1, "groupby_accumulate: bad n / key_stride");
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(keys != nullptr, "groupby_accumulate: keys is NULL");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    etl::GroupByParams p{};
+    p.keys = keys; p.key_dtype = key_dtype; p.key_stride = key_stride; p.key_valid = key_valid;
+    p.ncols = ncols; p.minmax = minmax ? 1 : 0; p.n = n; p.table = table; p.mask = (uint64_t)capacity - 1;
+    p.stride = gb_stride(ncols, minmax);
+    p.status = reinterpret_cast<unsigned long long*>(d_status);
+    for (int c = 0; c < ncols; ++c) {
+        ETL_REQUIRE(val && val[c], "groupby_accumulate: val[%d] is NULL", c);
+        p.val[c] = val[c];
+        p.val_stride[c] = val_stride ? val_stride[c] : 1;
+        p.val_valid[c] = val_valid ? val_valid[c] : nullptr;
+    }
+    ETL_CUDA(cudaSetDevice(h->device));
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int64_t want = (n + etl::GB_THREADS - 1) / etl::GB_THREADS;
+    // shared-memory path when the groups (at load <= 0.5) fit a per-CTA table of at most 4096 slots
+    int slots = 256;
+    const int64_t hint = groups_hint > 0 ? groups_hint : 1024;
+    while (slots < 2 * hint && slots < 8192) slots *= 2;
+    const size_t per_slot = 8 + 4 + (size_t)ncols * (8 + 4) + (minmax ? (size_t)ncols * 16 : 0);
+    const bool use_smem = hint <= 2048 && slots * per_slot <= 200 * 1024;
+    if (use_smem) {
+        p.smem_slots = slots;
+        const size_t smem = slots * per_slot;
+        auto kern = minmax ? etl::groupby_smem_kernel<true> : etl::groupby_smem_kernel<false>;
+        ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, etl::GB_THREADS, smem));
+        if (occ < 1) occ = 1;
+        int64_t blocks = (int64_t)h->sm_count * occ;
+        if (blocks > want) blocks = want;
+        kern<<<(unsigned)blocks, etl::GB_THREADS, smem, stream>>>(p);
+    } else {
+        int64_t blocks = (int64_t)h->sm_count * 8;
+        if (blocks > want) blocks = want;
+        etl::groupby_global_kernel<<<(unsigned)blocks, etl::GB_THREADS, 0, stream>>>(p);
+    }
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_groupby_compact(etl_handle* hh, const uint64_t* table, int64_t capacity, int32_t ncols,
+                                   int32_t minmax, int64_t out_capacity, int64_t* out_keys, int64_t* out_rows,
+                                   int64_t* out_count, double* out_sum, double* out_min, double* out_max,
+                                   int64_t* d_groups, void* stream_) {
+    ETL_REQUIRE(hh && table && out_keys && out_rows && d_groups, "groupby_compact: NULL argument");
+    ETL_REQUIRE(ncols == 0 || (out_count && out_sum), "groupby_compact: out_count/out_sum is NULL");
+    ETL_REQUIRE(!minmax || ncols == 0 || (out_min && out_max), "groupby_compact: out_min/out_max is NULL");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    ETL_CUDA(cudaMemsetAsync(d_groups, 0, sizeof(int64_t), stream));
+    int64_t blocks = (capacity + 255) / 256;
+    if (blocks > (int64_t)h->sm_count * 16) blocks = (int64_t)h->sm_count * 16;
+    etl::groupby_compact_kernel<<<(unsigned)blocks, 256, 0, stream>>>(
+        table, capacity, gb_stride(ncols, minmax), ncols, minmax ? 1 : 0, out_keys, out_rows, out_count, out_sum, out_min,
+        out_max, out_capacity, reinterpret_cast<unsigned long long*>(d_groups));
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, const double* vals, int64_t n, int32_t parts,
+                                  int64_t* d_part_counts, int64_t* d_part_base, int64_t* out_records, void* stream_) {
+    ETL_REQUIRE(hh && d_part_counts && d_part_base, "hash_partition: NULL argument");
+    ETL_REQUIRE(parts >= 1 && parts <= etl::PART_MAX, "hash_partition: parts=%d not in 1..%d", parts, etl::PART_MAX);
+    ETL_REQUIRE(n >= 0, "hash_partition: n < 0");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    ETL_CUDA(cudaMemsetAsync(d_part_counts, 0, sizeof(int64_t) * parts, stream));
+    if (n == 0) {
+        ETL_CUDA(cudaMemsetAsync(d_part_base, 0, sizeof(int64_t) * parts, stream));
+        return ETL_OK;
+    }
+    ETL_REQUIRE(keys && vals && out_records && etl::aligned16(out_records), "hash_partition: NULL or misaligned buffer");
+    int rc = etl::arena_reserve(h, sizeof(unsigned long long) * etl::PART_MAX);
+    if (rc != ETL_OK) return rc;
+    unsigned long long* cursor = static_cast<unsigned long long*>(h->scratch);
+    ETL_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * etl::PART_MAX, stream));
+    int64_t blocks = (n + etl::PART_THREADS * 8 - 1) / (etl::PART_THREADS * 8);
+    if (blocks > (int64_t)h->sm_count * 8) blocks = (int64_t)h->sm_count * 8;
+    etl::partition_count_kernel<<<(unsigned)blocks, etl::PART_THREADS, 0, stream>>>(
+        keys, n, parts, reinterpret_cast<unsigned long long*>(d_part_counts));
+    ETL_CUDA(cudaGetLastError());
+    etl::partition_scan_kernel<<<1, 1, 0, stream>>>(d_part_counts, d_part_base, parts);
+    ETL_CUDA(cudaGetLastError());
+    const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
+    int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
+    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(keys, vals, n, parts, d_part_base,
+                                                                                      cursor, out_records);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}

@@ -63,6 +63,17 @@ def pack_validity_host(valid: np.ndarray) -> np.ndarray:
     return np.packbits(padded, bitorder="little").view(np.uint32).copy()
 
 
+@dataclass
+class GroupTable:
+    """Caller-owned hash-aggregation table (see etl_groupby_* in etl_b200.h)."""
+
+    table: torch.Tensor
+    capacity: int
+    ncols: int
+    minmax: bool
+    status: torch.Tensor
+
+
 class Engine:
     """One per GPU (replaces the per-executor SparkSession state,
     spark_session.py:37-88)."""
@@ -294,6 +305,82 @@ class Engine:
                                           d_splits.shape[0], out.data_ptr(), oor.data_ptr(), self._stream()))
         self.launches += 1 if n else 0
         return out, oor
+
+    # ------------------------------------------------- groupBy (extension)
+    def groupby_new(self, capacity: int, ncols: int, minmax: bool = False) -> "GroupTable":
+        words = C.c_int64()
+        _lib.check(self.lib.etl_groupby_table_words(ncols, int(minmax), capacity, C.byref(words)))
+        table = self.empty(words.value, torch.int64)
+        _lib.check(self.lib.etl_groupby_init(self._h, table.data_ptr(), capacity, ncols, int(minmax), self._stream()))
+        self.launches += 1
+        status = torch.zeros(2, dtype=torch.int64, device=self.device)
+        return GroupTable(table, capacity, ncols, bool(minmax), status)
+
+    def groupby_accumulate(self, gt: "GroupTable", keys: torch.Tensor, key_valid: Optional[torch.Tensor],
+                           vals: Sequence[torch.Tensor], vals_valid: Sequence[Optional[torch.Tensor]] = (),
+                           groups_hint: int = 0, n: Optional[int] = None, key_stride: int = 1,
+                           val_strides: Optional[Sequence[int]] = None) -> None:
+        """One batch of rows into the table.  keys int32/int64; vals f64.  With
+        strides it reads the {key, value} records of the exchange in place."""
+        nc = gt.ncols
+        assert len(vals) == nc
+        n = keys.shape[0] if n is None else n
+        P = C.c_void_p * max(nc, 1)
+        L = C.c_int64 * max(nc, 1)
+        vv = list(vals_valid) + [None] * (nc - len(vals_valid))
+        strides = list(val_strides) if val_strides is not None else [1] * nc
+        _lib.check(self.lib.etl_groupby_accumulate(
+            self._h, keys.data_ptr(), _DTYPE_CODE[keys.dtype], key_stride, _ptr(key_valid), nc,
+            P(*[v.data_ptr() for v in vals]) if nc else None, L(*strides) if nc else None,
+            P(*[_ptr(v) for v in vv]) if nc else None, n, gt.table.data_ptr(), gt.capacity, int(gt.minmax),
+            groups_hint, gt.status.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+
+    def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None) -> dict:
+        """Dense result sorted by key: keys, rows, per column count/sum/mean[/min/max]
+        (device tensors), plus the null-key group.  Raises if rows were dropped."""
+        cap = gt.capacity if max_groups is None else max_groups
+        nc = gt.ncols
+        keys = self.empty(cap, torch.int64)
+        rows = self.empty(cap, torch.int64)
+        cnt = torch.empty((max(nc, 1), cap), dtype=torch.int64, device=self.device)
+        sm = torch.empty((max(nc, 1), cap), dtype=torch.float64, device=self.device)
+        mn = torch.empty((max(nc, 1), cap), dtype=torch.float64, device=self.device) if gt.minmax else None
+        mx = torch.empty((max(nc, 1), cap), dtype=torch.float64, device=self.device) if gt.minmax else None
+        groups = self.empty(1, torch.int64)
+        _lib.check(self.lib.etl_groupby_compact(self._h, gt.table.data_ptr(), gt.capacity, nc, int(gt.minmax), cap,
+                                                keys.data_ptr(), rows.data_ptr(), cnt.data_ptr(), sm.data_ptr(),
+                                                _ptr(mn), _ptr(mx), groups.data_ptr(), self._stream()))
+        self.launches += 1
+        st = gt.status.cpu().tolist()
+        if st[0] or st[1]:
+            raise _lib.EtlError(-5, f"groupBy: {st[0]} row(s) dropped (table full), {st[1]} row(s) with the reserved key")
+        g = int(groups.item())
+        if g > cap:
+            raise _lib.EtlError(-5, f"groupBy: {g} groups exceed the output capacity {cap}")
+        order = torch.argsort(keys[:g])
+        out = {"keys": keys[:g][order], "rows": rows[:g][order], "cols": []}
+        for c in range(nc):
+            col = {"count": cnt[c, :g][order], "sum": sm[c, :g][order]}
+            col["mean"] = col["sum"] / col["count"].to(torch.float64)
+            if gt.minmax:
+                col["min"], col["max"] = mn[c, :g][order], mx[c, :g][order]
+            out["cols"].append(col)
+        stride = 2 + 2 * nc + (2 * nc if gt.minmax else 0)
+        null_entry = gt.table[gt.capacity * stride:(gt.capacity + 1) * stride].cpu()
+        out["null_group_rows"] = int(null_entry[1].item())
+        return out
+
+    def hash_partition(self, keys: torch.Tensor, vals: torch.Tensor, parts: int):
+        """Map side of the exchange -> (records int64[n, 2], counts int64[parts], base int64[parts])."""
+        n = keys.shape[0]
+        rec = torch.empty((max(n, 1), 2), dtype=torch.int64, device=self.device)
+        counts = self.empty(parts, torch.int64)
+        base = self.empty(parts, torch.int64)
+        _lib.check(self.lib.etl_hash_partition(self._h, _ptr(keys), _ptr(vals), n, parts, counts.data_ptr(),
+                                               base.data_ptr(), rec.data_ptr(), self._stream()))
+        self.launches += 3 if n else 0
+        return rec[:n], counts, base
 
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,

@@ -1,0 +1,141 @@
+"""groupBy aggregates and the hash partition of the exchange against the oracle.
+Keys, row counts and counts are exact; sums are exact on integer-valued data and
+within 1e-6 relative otherwise (atomic accumulation order is not fixed);
+min / max are exact."""
+import numpy as np
+import pytest
+import torch
+
+import pyspark_tf_gke_b200 as pkg
+import pyspark_tf_gke_b200.synth as S
+from oracle import etl_oracle as O
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = pkg.Engine(0)
+    yield e
+    e.close()
+
+
+def _check(res, exp, exact_sums, minmax):
+    assert res["keys"].cpu().numpy().tolist() == exp["keys"].tolist()
+    assert res["rows"].cpu().numpy().tolist() == exp["rows"].tolist()
+    assert res["null_group_rows"] == exp.get("null_group_rows", 0)
+    for got, want in zip(res["cols"], exp["cols"]):
+        assert got["count"].cpu().numpy().tolist() == want["count"].tolist()
+        gs, ws = got["sum"].cpu().numpy(), want["sum"]
+        if exact_sums:
+            assert gs.tobytes() == ws.tobytes()
+        else:
+            np.testing.assert_allclose(gs, ws, rtol=REL_TOL, atol=0, equal_nan=True)
+            np.testing.assert_allclose(got["mean"].cpu().numpy(), want["mean"], rtol=REL_TOL, atol=0, equal_nan=True)
+        if minmax:
+            assert np.array_equal(got["min"].cpu().numpy(), want["min"], equal_nan=True)
+            assert np.array_equal(got["max"].cpu().numpy(), want["max"], equal_nan=True)
+
+
+@pytest.mark.parametrize("n,groups,hint", [(0, 5, 0), (1, 1, 0), (1000, 7, 0), (200_003, 1000, 1000), (200_003, 30, 30),
+                                           (300_000, 5000, 5000), (300_000, 5000, 100)])
+@pytest.mark.parametrize("key_dtype", [np.int32, np.int64])
+def test_groupby_matches_oracle(eng, n, groups, hint, key_dtype):
+    keys, kv = S.host_column(5, 0, S.KIND_KEY64, n, modulus=groups, null_rate=0.02)
+    keys = (keys - groups // 2).astype(key_dtype)  # negative keys too
+    vals, valid = [], []
+    for c in range(3):
+        v, vv = S.host_column(5, 1 + c, S.KIND_REAL, n, null_rate=0.07, nan_rate=0.001 if c == 2 else 0.0)
+        vals.append(v - 5e4)
+        valid.append(vv)
+    gt = eng.groupby_new(1 << 14, 3, minmax=True)
+    kcol = pkg.Column.from_host(keys, kv, eng.device)
+    cols = [pkg.Column.from_host(v, vv, eng.device) for v, vv in zip(vals, valid)]
+    eng.groupby_accumulate(gt, kcol.data, kcol.valid, [c.data for c in cols], [c.valid for c in cols], groups_hint=hint)
+    res = eng.groupby_result(gt)
+    exp = O.groupby_agg(keys, kv, vals, valid)
+    _check(res, exp, exact_sums=False, minmax=True)
+
+
+def test_groupby_exact_sums_on_integer_valued_data_in_batches(eng):
+    n, groups = 500_000, 1000
+    keys, _ = S.host_column(2, 0, S.KIND_KEY32, n, modulus=groups)
+    vals, valid = [], []
+    for c in range(3):
+        v, vv = S.host_column(2, 1 + c, S.KIND_EXACT, n, null_rate=0.07)
+        vals.append(v)
+        valid.append(vv)
+    gt = eng.groupby_new(4096, 3)
+    half = (n // 2) // 32 * 32
+    for lo, hi in ((0, half), (half, n)):  # two batches into one table
+        k = pkg.Column.from_host(keys[lo:hi], None, eng.device)
+        cols = [pkg.Column.from_host(v[lo:hi], vv[lo:hi], eng.device) for v, vv in zip(vals, valid)]
+        eng.groupby_accumulate(gt, k.data, None, [c.data for c in cols], [c.valid for c in cols], groups_hint=groups)
+    res = eng.groupby_result(gt)
+    exp = O.groupby_agg(keys, None, vals, valid)
+    _check(res, exp, exact_sums=True, minmax=False)
+
+
+def test_groupby_all_null_group_and_full_table(eng):
+    keys = np.array([1, 1, 2, 3], dtype=np.int64)
+    v = np.array([1.0, 2.0, 5.0, 7.0])
+    vv = np.array([True, True, False, True])
+    gt = eng.groupby_new(8, 1, minmax=True)
+    c = pkg.Column.from_host(v, vv, eng.device)
+    eng.groupby_accumulate(gt, torch.from_numpy(keys).to(eng.device), None, [c.data], [c.valid])
+    res = eng.groupby_result(gt)
+    assert res["keys"].cpu().tolist() == [1, 2, 3] and res["rows"].cpu().tolist() == [2, 1, 1]
+    col = res["cols"][0]
+    assert col["count"].cpu().tolist() == [2, 0, 1] and col["sum"].cpu().tolist() == [3.0, 0.0, 7.0]
+    assert np.array_equal(col["min"].cpu().numpy(), np.array([1.0, np.nan, 7.0]), equal_nan=True)
+    assert np.isnan(col["mean"].cpu().numpy()[1])
+    # 100 distinct keys cannot fit 8 slots: loud failure, not a silent drop
+    gt = eng.groupby_new(8, 0)
+    eng.groupby_accumulate(gt, torch.arange(100, dtype=torch.int64, device=eng.device), None, [], groups_hint=4096)
+    with pytest.raises(pkg.EtlError, match="dropped"):
+        eng.groupby_result(gt)
+
+
+@pytest.mark.parametrize("parts", [1, 2, 8])
+def test_hash_partition_matches_oracle_destinations(eng, parts):
+    n = 300_007
+    keys, _ = S.host_column(3, 0, S.KIND_KEY64, n, modulus=10**8)
+    vals, _ = S.host_column(3, 1, S.KIND_REAL, n)
+    rec, counts, base = eng.hash_partition(torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device), parts)
+    rec = rec.cpu().numpy()
+    dest = O.partition_dest(keys, parts)
+    assert counts.cpu().numpy().tolist() == np.bincount(dest, minlength=parts).tolist()
+    assert base.cpu().numpy().tolist() == np.concatenate([[0], np.cumsum(np.bincount(dest, minlength=parts))[:-1]]).tolist()
+    # every destination range holds exactly its rows (as a multiset of records)
+    b = base.cpu().numpy().tolist() + [n]
+    for d in range(parts):
+        got = rec[b[d]:b[d + 1]]
+        assert (O.partition_dest(got[:, 0], parts) == d).all()
+        want = np.stack([keys[dest == d], vals[dest == d].view(np.int64)], axis=1)
+        assert np.array_equal(got[np.lexsort((got[:, 1], got[:, 0]))], want[np.lexsort((want[:, 1], want[:, 0]))])
+
+
+def test_partition_then_strided_merge_equals_direct_groupby(eng):
+    # single-process emulation of the exchange: every destination range is merged
+    # into its own table; together they must equal the direct aggregation
+    n, groups, parts = 400_000, 50_000, 4
+    keys, _ = S.host_column(9, 0, S.KIND_KEY64, n, modulus=groups)
+    vals, _ = S.host_column(9, 1, S.KIND_EXACT, n)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    rec, counts, base = eng.hash_partition(dk, dv, parts)
+    b = base.cpu().tolist() + [n]
+    all_keys, all_sums, all_rows = [], [], []
+    for d in range(parts):
+        part = rec[b[d]:b[d + 1]].contiguous().view(-1)
+        gt = eng.groupby_new(1 << 17, 1)
+        eng.groupby_accumulate(gt, part, None, [part[1:].view(torch.float64)], groups_hint=groups, n=b[d + 1] - b[d],
+                               key_stride=2, val_strides=[2])
+        r = eng.groupby_result(gt)
+        all_keys.append(r["keys"]); all_sums.append(r["cols"][0]["sum"]); all_rows.append(r["rows"])
+    k = torch.cat(all_keys).cpu().numpy()
+    order = np.argsort(k)
+    exp = O.groupby_agg_fast(keys, [vals], [None])
+    assert k[order].tolist() == exp["keys"].tolist()  # disjoint ownership: no key on two ranks
+    assert torch.cat(all_rows).cpu().numpy()[order].tolist() == exp["rows"].tolist()
+    assert torch.cat(all_sums).cpu().numpy()[order].tobytes() == exp["cols"][0]["sum"].tobytes()
