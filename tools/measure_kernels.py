@@ -1,0 +1,260 @@
+#!/usr/bin/env python
+"""Per-kernel roofline measurements for every row of SURVEY.md §8 (one GPU).
+
+    python tools/measure_kernels.py [--out profiles/r01_kernels.json] [--only name,...] [--full]
+
+For each kernel: synthetic input of the BASELINE.json shape resident in HBM,
+>= 3 warm-up launches, K timed launches bracketed by CUDA events on the launching
+stream (inputs are larger than L2 everywhere), algorithmic bytes per launch
+ / mean launch time = achieved GB/s, against the measured copy peak
+of MEASURED_PEAKS.json.  A CPU figure for the same operation (NumPy / pyarrow /
+the compiled oracle, bounded sample, thread count stated) is taken beside it.
+These are kernel numbers; the headline line stays with bench.py."""
+from __future__ import annotations
+
+import argparse
+import gzip
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+import pyspark_tf_gke_b200 as pkg  # noqa: E402
+import pyspark_tf_gke_b200.synth as S  # noqa: E402
+
+
+def peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def timed(fn, steps=20, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ev[0].record()
+    for i in range(steps):
+        fn()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ts = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
+    return sum(ts) / len(ts), min(ts)
+
+
+def cpu_time(fn, reps=3):
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        fn()
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def entry(name, rows, alg_bytes, mean_ms, min_ms, cpu=None, note=""):
+    p, src = peak()
+    gbs = alg_bytes / (mean_ms * 1e-3) / 1e9
+    e = {"kernel": name, "rows": rows, "algorithmic_bytes": alg_bytes, "mean_ms": mean_ms, "min_ms": min_ms,
+         "rows_per_s": rows / (mean_ms * 1e-3), "achieved_gbs": gbs, "peak_gbs": p, "peak_source": src, "frac": gbs / p,
+         "note": note}
+    if cpu:
+        e["cpu"] = cpu
+    print(json.dumps(e), flush=True)
+    return e
+
+
+def table2(eng, n, seed=1, kind=S.KIND_EXACT):
+    cfg = S.CONFIG2
+    key = eng.synth_column(seed, 0, S.KIND_KEY32, n, modulus=cfg["categories"], null_rate=cfg["key_null"])
+    cols = [eng.synth_column(seed, 1 + c, kind, n, null_rate=cfg["val_null"][c]) for c in range(3)]
+    return key, cols
+
+
+def m_null_count(eng, args):
+    n = 100_000_000
+    key, _ = table2(eng, n)
+    out = eng.empty(1, torch.int64)
+    mean, mn = timed(lambda: eng.null_count(key, out))
+    host = key.valid.cpu().numpy().view(np.uint8)
+    t = cpu_time(lambda: n - int(np.unpackbits(host[: n // 8]).sum()))
+    return entry("null_count_kernel (k_means.py:23)", n, n // 8, mean, mn,
+                 {"rows_per_s": n / t, "impl": "numpy unpackbits+sum", "cores": 1}, "1 bit per row; launch-latency bound")
+
+
+def m_sum_count(eng, args):
+    n = 100_000_000
+    key, cols = table2(eng, n)
+    s, c = eng.empty(3, torch.float64), eng.empty(3, torch.int64)
+    mean, mn = timed(lambda: eng.sum_count(cols, row_valid=key.valid, out_sum=s, out_count=c))
+    m = 10_000_000
+    hv = [col.data[:m].cpu().numpy() for col in cols]
+    hm = [np.unpackbits(col.valid[: m // 32].cpu().numpy().view(np.uint8), bitorder="little").astype(bool) for col in cols]
+    t = cpu_time(lambda: [float(v[k].sum()) for v, k in zip(hv, hm)])
+    return entry("column_sum_count_kernel x3 (k_means.py:45-48)", n, n * 24 + 4 * (n // 8), mean, mn,
+                 {"rows_per_s": m / t, "impl": "numpy masked sum, 10M-row sample", "cores": 1})
+
+
+def m_histogram(eng, args):
+    n = 100_000_000
+    out = []
+    for bins in (30, 1000):
+        codes = eng.synth_column(2, 0, S.KIND_KEY32, n, modulus=bins, null_rate=0.01)
+        mean, mn = timed(lambda: eng.code_histogram(codes, bins))
+        m = 10_000_000
+        hc = codes.data[:m].cpu().numpy()
+        t = cpu_time(lambda: np.bincount(hc, minlength=bins))
+        out.append(entry(f"code_histogram_kernel bins={bins} (StringIndexer.fit, k_means.py:34,73)", n, n * 4 + n // 8, mean,
+                         mn, {"rows_per_s": m / t, "impl": "numpy bincount, 10M-row sample", "cores": 1}))
+    return out
+
+
+def m_groupby3(eng, args):
+    cfg = S.CONFIG3
+    n = cfg["rows"]
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY32, n, modulus=cfg["groups"], with_valid=False)
+    cols = [eng.synth_column(cfg["seed"], 1 + c, S.KIND_EXACT, n, null_rate=cfg["val_null"][c]) for c in range(3)]
+    gt = eng.groupby_new(4096, 3)
+
+    def run():
+        eng.groupby_accumulate(gt, key.data, None, [c.data for c in cols], [c.valid for c in cols], groups_hint=cfg["groups"])
+
+    mean, mn = timed(run, steps=10)
+    m = 10_000_000
+    import pyarrow as pa
+    import pyarrow.compute  # noqa: F401
+
+    tbl = pa.table({"k": key.data[:m].cpu().numpy(), **{f"v{c}": cols[c].data[:m].cpu().numpy() for c in range(3)}})
+    t = cpu_time(lambda: tbl.group_by("k").aggregate([(f"v{c}", a) for c in range(3) for a in ("sum", "count")]))
+    return entry("groupby_smem_kernel config3: 100M rows, 1K groups, 3x sum/count", n, n * 28 + 3 * (n // 8), mean, mn,
+                 {"rows_per_s": m / t, "impl": "pyarrow Table.group_by, 10M-row sample", "cores": pa.cpu_count()})
+
+
+def m_groupby4(eng, args):
+    cfg = S.CONFIG4
+    n = cfg["rows"] if args.full else cfg["rows"] // 4
+    groups = cfg["groups"] if args.full else cfg["groups"] // 4
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=groups, with_valid=False)
+    val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False)
+    cap = 1 << int(np.ceil(np.log2(groups * 2)))
+    gt = eng.groupby_new(cap, 1)
+    torch.cuda.synchronize()
+
+    def run():
+        eng.groupby_accumulate(gt, key.data, None, [val.data], groups_hint=groups)
+
+    mean, mn = timed(run, steps=3, warmup=1)
+    return entry(f"groupby_global_kernel config4 (1 GPU): {n} rows, {groups} groups, sum/count", n, int(n * 18.5), mean, mn,
+                 None, "random 32-byte table entries: sector traffic >> algorithmic bytes")
+
+
+def m_partition(eng, args):
+    n = 125_000_000
+    key = eng.synth_column(3, 0, S.KIND_KEY64, n, modulus=10**8, with_valid=False)
+    val = eng.synth_column(3, 1, S.KIND_EXACT, n, with_valid=False)
+    mean, mn = timed(lambda: eng.hash_partition(key.data, val.data, 8), steps=10)
+    return entry("hash_partition (count + scatter) P=8, 125M rows (config 4 map side)", n, n * (8 + 16 + 16), mean, mn, None,
+                 "count pass reads keys (8 B), scatter pass reads 16 B and writes 16 B per row")
+
+
+def health_like_text(target_rows):
+    with gzip.open(os.path.join(ROOT, "tests", "golden", "health_workloads.csv.gz"), "rb") as fh:
+        raw = fh.read()
+    head, body = raw.split(b"\n", 1)
+    reps = max(1, target_rows // 18155)
+    return head + b"\n" + body * reps, 18155 * reps
+
+
+def m_csv(eng, args):
+    raw, rows = health_like_text(10_000_000)
+    n = len(raw)
+    text = pkg.table.upload_text(eng, raw)
+    torch.cuda.synchronize()
+    res = []
+    mean, mn = timed(lambda: eng.csv_index_rows(text, n), steps=10)
+    res.append(entry("csv_block_summary + csv_block_scan (row index, pass 1)", rows, n, mean, mn))
+    total = int(eng.csv_index_rows(text, n).item())
+    assert total == rows + 1
+    mean, mn = timed(lambda: eng.csv_row_offsets(text, n, total), steps=10)
+    res.append(entry("csv_row_offsets_kernel (pass 2)", rows, n + 8 * total, mean, mn))
+    row_start = eng.csv_row_offsets(text, n, total)
+    cap = 1 << 16
+
+    def parse():
+        d = (torch.zeros(cap, dtype=torch.int64, device=eng.device), torch.zeros(cap, dtype=torch.int64, device=eng.device))
+        return eng.csv_parse_columns(text, n, row_start, 1, rows, [5, 6, 7, 2], [0, 0, 0, 1], [None, None, None, d])
+
+    mean, mn = timed(parse, steps=5)
+    import io
+
+    import pyarrow as pa
+    import pyarrow.csv as pacsv
+
+    sample = raw[: n // 10]
+    sample = sample[: sample.rfind(b"\n") + 1]
+    t = cpu_time(lambda: pacsv.read_csv(io.BytesIO(sample), convert_options=pacsv.ConvertOptions(
+        include_columns=["measure_name", "value", "lower_ci", "upper_ci"])), reps=2)
+    res.append(entry("csv_parse_rows_kernel (4 columns: 3 numeric + dictionary key)", rows, n + rows * 28.5, mean, mn,
+                     {"rows_per_s": (rows / 10) / t, "bytes_per_s": len(sample) / t,
+                      "impl": "pyarrow.csv.read_csv, 1/10 sample", "cores": pa.cpu_count()},
+                     "instruction-issue bound (byte-level tokenising + numeral conversion), not HBM bound"))
+    return res
+
+
+def m_features(eng, args):
+    n = 10_000_000
+    idx = eng.synth_column(1, 0, S.KIND_KEY32, n, modulus=31, with_valid=False).data
+    nums = [eng.synth_column(1, 1 + c, S.KIND_EXACT, n, with_valid=False).data for c in range(3)]
+    res = []
+    for dtype, es in ((torch.float64, 8), (torch.float32, 4)):
+        out = torch.empty((n, 153), dtype=dtype, device=eng.device)
+        mean, mn = timed(lambda: eng.assemble_dense(idx, nums, 30, 5, dtype=dtype, out=out), steps=5)
+        res.append(entry(f"assemble_dense_kernel D=153 {str(dtype).split('.')[-1]} (k_means.py:38,64-77)", n,
+                         n * (28 + 153 * es), mean, mn, None, "write bound"))
+        del out
+    mean, mn = timed(lambda: eng.assemble_sparse(idx, nums, 30, 5), steps=5)
+    res.append(entry("assemble_sparse_kernel (ELL, 8 slots)", n, n * (28 + 8 * 12), mean, mn))
+    lab = eng.synth_column(4, 0, S.KIND_KEY32, n, modulus=15, null_rate=0.083)
+    cols = [eng.synth_column(4, 1 + c, S.KIND_EXACT, n, null_rate=0.074) for c in range(3)]
+    X, y, r = eng.pack_tf(lab, cols)
+    kept = int(r.item())
+    mean, mn = timed(lambda: eng.pack_tf(lab, cols), steps=10)
+    res.append(entry("tf_tile_count + tf_tile_scan + tf_pack (load_csv layout, train_tf_ps.py:120-149)", n,
+                     n * 28 + 8 * (n // 8) + kept * 16, mean, mn, None,
+                     "includes the torch allocation of X/y each call; bitmaps are read twice"))
+    return res
+
+
+ALL = {"null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
+       "groupby4": m_groupby4, "partition": m_partition, "csv": m_csv, "features": m_features}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--only", default="")
+    ap.add_argument("--full", action="store_true", help="config 4 at the full 1B rows / 100M groups")
+    args = ap.parse_args()
+    eng = pkg.Engine(0)
+    names = [s for s in args.only.split(",") if s] or list(ALL)
+    results = []
+    for name in names:
+        r = ALL[name](eng, args)
+        results.extend(r if isinstance(r, list) else [r])
+        torch.cuda.empty_cache()
+    if args.out:
+        with open(args.out, "w") as fh:
+            json.dump({"gpu": torch.cuda.get_device_name(0), "results": results}, fh, indent=1)
+
+
+if __name__ == "__main__":
+    main()
