@@ -260,7 +260,11 @@ ETL_API int etl_nan_to_null(etl_handle* h, const double* val, uint32_t* valid, i
  * double with element stride val_stride[c] (NULL = 1) - strides let it read the
  * 16-byte {key, value} records of the exchange directly.  groups_hint <= 2048
  * (0 = unknown -> 1024) selects the shared-memory kernel (per-CTA table, one
- * flush), larger the direct global-table kernel.  d_status (device int64[2],
+ * flush), larger the direct global-table kernel.  key_range > 0 promises int32
+ * keys in [0, key_range) (dictionary codes, bucket ids; <= 8192, contiguous
+ * columns, no min/max): the shared table is then indexed by the key itself; a key
+ * outside the promise is still aggregated correctly, through the global table.
+ * d_status (device int64[2],
  * zeroed by the caller): [0] rows dropped because the table was full, [1] rows
  * carrying the reserved key - both must be 0 for a valid result.
  * etl_groupby_compact: used entries -> out_keys/out_rows int64[out_capacity],
@@ -275,7 +279,7 @@ ETL_API int etl_groupby_accumulate(etl_handle* h, const void* keys, int32_t key_
                            const uint32_t* key_valid, int32_t ncols, const double* const val[],
                            const int64_t val_stride[], const uint32_t* const val_valid[], int64_t n,
                            uint64_t* table, int64_t capacity, int32_t minmax, int64_t groups_hint,
-                           int64_t* d_status, void* stream);
+                           int32_t key_range, int64_t* d_status, void* stream);
 ETL_API int etl_groupby_compact(etl_handle* h, const uint64_t* table, int64_t capacity, int32_t ncols, int32_t minmax,
                         int64_t out_capacity, int64_t* out_keys, int64_t* out_rows, int64_t* out_count,
                         double* out_sum, double* out_min, double* out_max, int64_t* d_groups, void* stream);

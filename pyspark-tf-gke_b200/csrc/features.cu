@@ -66,36 +66,62 @@ struct AssembleParams {
 };
 
 constexpr int ASM_THREADS = 256;
+constexpr int ASM_MAXJ = 8;  // columns per lane held in registers: D <= 256 takes the fast kernel
 
 // One warp per row: lane l writes columns l, l + 32, ... so every store
 // instruction of the warp covers 32 consecutive elements of the row-major
-// output (no index division anywhere; the one-hot test is `repeats` compares).
+// output.  A lane's columns are the same for every row, so what each of them
+// means - which label a one-hot column stands for, or which numeric it carries -
+// is worked out once per thread; per row and element only a compare, a select
+// and the store remain.
 template <typename T>
 __global__ void __launch_bounds__(ASM_THREADS) assemble_dense_kernel(const AssembleParams p) {
+    const int lane = threadIdx.x & 31;
+    const int D = p.repeats * p.num_labels + 3;
+    const int onehot = p.repeats * p.num_labels;
+    int label_of[ASM_MAXJ];  // >= 0: one-hot column of that label; -1..-3: numeric 0..2; -4: past the row
+#pragma unroll
+    for (int j = 0; j < ASM_MAXJ; ++j) {
+        const int col = lane + 32 * j;
+        label_of[j] = col >= D ? -4 : (col >= onehot ? -1 - (col - onehot) : col % p.num_labels);
+    }
+    T* out = static_cast<T*>(p.out);
+    const int64_t warps = (int64_t)gridDim.x * (ASM_THREADS / 32);
+    for (int64_t r = (int64_t)blockIdx.x * (ASM_THREADS / 32) + (threadIdx.x >> 5); r < p.n; r += warps) {
+        int32_t idx = __ldg(p.index + r);
+        if (idx < 0 || idx >= p.num_labels) idx = -100;  // unknown label: matches no column
+        const T x0 = (T)((__ldg(p.num[0] + r) - p.shift[0]) * p.scale[0]);
+        const T x1 = (T)((__ldg(p.num[1] + r) - p.shift[1]) * p.scale[1]);
+        const T x2 = (T)((__ldg(p.num[2] + r) - p.shift[2]) * p.scale[2]);
+        T* row = out + r * D + lane;
+#pragma unroll
+        for (int j = 0; j < ASM_MAXJ; ++j) {
+            const int l = label_of[j];
+            if (l == -4) break;
+            const T v = l >= 0 ? (T)(l == idx ? 1 : 0) : (l == -1 ? x0 : (l == -2 ? x1 : x2));
+            row[32 * j] = v;
+        }
+    }
+}
+
+// any feature dimension (D > 256): same mapping, column meaning recomputed per element
+template <typename T>
+__global__ void __launch_bounds__(ASM_THREADS) assemble_dense_wide_kernel(const AssembleParams p) {
     const int lane = threadIdx.x & 31;
     const int D = p.repeats * p.num_labels + 3;
     const int onehot = p.repeats * p.num_labels;
     T* out = static_cast<T*>(p.out);
     const int64_t warps = (int64_t)gridDim.x * (ASM_THREADS / 32);
     for (int64_t r = (int64_t)blockIdx.x * (ASM_THREADS / 32) + (threadIdx.x >> 5); r < p.n; r += warps) {
-        const int32_t idx = __ldg(p.index + r);
-        const bool known = idx >= 0 && idx < p.num_labels;
-        double x = 0.0;
-        if (lane < 3) x = (__ldg(p.num[lane] + r) - p.shift[lane]) * p.scale[lane];
-        const double x0 = __shfl_sync(0xffffffffu, x, 0), x1 = __shfl_sync(0xffffffffu, x, 1),
-                     x2 = __shfl_sync(0xffffffffu, x, 2);
+        int32_t idx = __ldg(p.index + r);
+        if (idx < 0 || idx >= p.num_labels) idx = -100;
+        const T x0 = (T)((__ldg(p.num[0] + r) - p.shift[0]) * p.scale[0]);
+        const T x1 = (T)((__ldg(p.num[1] + r) - p.shift[1]) * p.scale[1]);
+        const T x2 = (T)((__ldg(p.num[2] + r) - p.shift[2]) * p.scale[2]);
         T* row = out + r * D;
         for (int col = lane; col < D; col += 32) {
-            T v;
-            if (col >= onehot) {
-                const int c = col - onehot;
-                v = (T)(c == 0 ? x0 : (c == 1 ? x1 : x2));
-            } else {
-                bool one = false;
-                for (int rep = 0; rep < p.repeats; ++rep) one |= col == rep * p.num_labels + idx;
-                v = (T)((one && known) ? 1 : 0);
-            }
-            row[col] = v;
+            const int c = col - onehot;
+            row[col] = c < 0 ? (T)(col % p.num_labels == idx ? 1 : 0) : (c == 0 ? x0 : (c == 1 ? x1 : x2));
         }
     }
 }
@@ -337,8 +363,14 @@ extern "C" int etl_assemble_features_dense(etl_handle* hh, const int32_t* index,
     p.out = out;
     const int64_t blocks = capped_blocks(h, (n + 7) / 8, 8);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-    if (out_dtype == ETL_F64) etl::assemble_dense_kernel<double><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
-    else etl::assemble_dense_kernel<float><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
+    const bool narrow = (int64_t)repeats * num_labels + 3 <= 32 * etl::ASM_MAXJ && num_labels > 0;
+    if (out_dtype == ETL_F64) {
+        if (narrow) etl::assemble_dense_kernel<double><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
+        else etl::assemble_dense_wide_kernel<double><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
+    } else {
+        if (narrow) etl::assemble_dense_kernel<float><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
+        else etl::assemble_dense_wide_kernel<float><<<(unsigned)blocks, etl::ASM_THREADS, 0, stream>>>(p);
+    }
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

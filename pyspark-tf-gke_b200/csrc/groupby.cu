@@ -40,6 +40,7 @@ struct GroupByParams {
     uint64_t mask;          // capacity - 1
     int32_t stride;         // words per entry: 2 + 2 * ncols (+ 2 * ncols with min/max)
     int32_t smem_slots;     // power of two
+    int32_t key_range;      // > 0: keys are known to lie in [0, key_range) -> direct-indexed shared table
     unsigned long long* status;  // [0] rows that found no global slot (table full), [1] rows with the reserved key
 };
 
@@ -213,6 +214,100 @@ __global__ void __launch_bounds__(GB_THREADS) groupby_smem_kernel(const GroupByP
     }
 }
 
+// Low cardinality with a known small key range (dictionary codes, bucket ids,
+// config 3's keys): the shared table is indexed by the key itself - no hashing,
+// no probing, no key compare.  Per row: one native 32-bit shared atomic for the
+// row count and, per value column, one fp64 shared atomic add (or, for a null
+// cell, a native 32-bit add to the column's null counter: count = rows - nulls).
+// 256 threads x 4 rows per tile with 128-bit loads; slot R collects null keys.
+template <int NC>
+__global__ void __launch_bounds__(GB_THREADS) groupby_dense_kernel(const GroupByParams p) {
+    extern __shared__ __align__(16) unsigned char gb_smem[];
+    const int R = p.key_range;          // slots 0..R-1 = keys, slot R = null key
+    const int S = R + 1;
+    double* ssum = reinterpret_cast<double*>(gb_smem);
+    uint32_t* srows = reinterpret_cast<uint32_t*>(ssum + (size_t)NC * S);
+    uint32_t* snull = srows + S;
+    for (int i = threadIdx.x; i < S; i += GB_THREADS) {
+        srows[i] = 0;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { ssum[c * S + i] = 0.0; snull[c * S + i] = 0; }
+    }
+    __syncthreads();
+    const int32_t* keys = static_cast<const int32_t*>(p.keys);
+    const int64_t tiles = (p.n + GB_THREADS * 4 - 1) / (GB_THREADS * 4);
+    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int64_t row = t * GB_THREADS * 4 + (int64_t)threadIdx.x * 4;
+        if (row >= p.n) continue;
+        const bool full = row + 4 <= p.n;
+        int32_t k[4];
+        double v[NC][4];
+        unsigned vn[NC];
+        if (full) {
+            const int4 q = ld_stream_v4(keys + row);
+            k[0] = q.x; k[1] = q.y; k[2] = q.z; k[3] = q.w;
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                const double2 a = ld_stream_d2(p.val[c] + row), b = ld_stream_d2(p.val[c] + row + 2);
+                v[c][0] = a.x; v[c][1] = a.y; v[c][2] = b.x; v[c][3] = b.y;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool in = row + j < p.n;
+                k[j] = in ? keys[row + j] : 0;
+#pragma unroll
+                for (int c = 0; c < NC; ++c) v[c][j] = in ? p.val[c][row + j] : 0.0;
+            }
+        }
+        const int left = p.n - row < 4 ? (int)(p.n - row) : 4;
+        const unsigned in_mask = (1u << left) - 1;
+        unsigned kn = 0xF;
+        if (p.key_valid) kn = (__ldg(p.key_valid + (row >> 5)) >> (row & 31)) & 0xF;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            vn[c] = 0xF;
+            if (p.val_valid[c]) vn[c] = (__ldg(p.val_valid[c] + (row >> 5)) >> (row & 31)) & 0xF;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (!((in_mask >> j) & 1u)) continue;
+            const bool key_null = !((kn >> j) & 1u);
+            if (!key_null && (k[j] < 0 || k[j] >= R)) {  // outside the promised range: straight to the global table
+                bool ok[3] = {false, false, false};
+                double x[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+                for (int c = 0; c < NC; ++c) { ok[c] = (vn[c] >> j) & 1u; x[c] = v[c][j]; }
+                gb_row_to_global(p, (uint64_t)(int64_t)k[j], false, ok, x);
+                continue;
+            }
+            const int slot = key_null ? R : k[j];
+            atomicAdd(srows + slot, 1u);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                if ((vn[c] >> j) & 1u) atomicAdd(ssum + c * S + slot, v[c][j]);
+                else atomicAdd(snull + c * S + slot, 1u);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < S; i += GB_THREADS) {
+        const uint32_t rows = srows[i];
+        if (!rows) continue;
+        uint64_t* e = i == R ? p.table + (p.mask + 1) * p.stride : gb_global_slot(p, (uint64_t)(int64_t)i);
+        if (!e) {
+            atomicAdd(p.status, (unsigned long long)rows);
+            continue;
+        }
+        unsigned long long cnt[3] = {0, 0, 0};
+        double sum[3] = {0, 0, 0};
+        const uint64_t mn[3] = {~0ull, ~0ull, ~0ull}, mx[3] = {0, 0, 0};
+#pragma unroll
+        for (int c = 0; c < NC; ++c) { cnt[c] = rows - snull[c * S + i]; sum[c] = ssum[c * S + i]; }
+        gb_global_add(e, p, rows, cnt, sum, mn, mx);
+    }
+}
+
 __global__ void __launch_bounds__(256) groupby_init_kernel(uint64_t* table, int64_t entries, int32_t stride,
                                                            int32_t ncols, int32_t minmax) {
     const int64_t total = entries * stride;
@@ -383,7 +478,7 @@ extern "C" int etl_groupby_accumulate(etl_handle* hh, const void* keys, int32_t 
                                       const uint32_t* key_valid, int32_t ncols, const double* const val[],
                                       const int64_t val_stride[], const uint32_t* const val_valid[], int64_t n,
                                       uint64_t* table, int64_t capacity, int32_t minmax, int64_t groups_hint,
-                                      int64_t* d_status, void* stream_) {
+                                      int32_t key_range, int64_t* d_status, void* stream_) {
     ETL_REQUIRE(hh && table && d_status, "groupby_accumulate: NULL argument");
     ETL_REQUIRE(ncols >= 0 && ncols <= 3, "groupby_accumulate: ncols=%d not in 0..3", ncols);
     ETL_REQUIRE(key_dtype == ETL_I32 || key_dtype == ETL_I64, "groupby_accumulate: key_dtype=%d", key_dtype);
@@ -412,7 +507,22 @@ extern "C" int etl_groupby_accumulate(etl_handle* hh, const void* keys, int32_t 
     while (slots < 2 * hint && slots < 8192) slots *= 2;
     const size_t per_slot = 8 + 4 + (size_t)ncols * (8 + 4) + (minmax ? (size_t)ncols * 16 : 0);
     const bool use_smem = hint <= 2048 && slots * per_slot <= 200 * 1024;
-    if (use_smem) {
+    bool dense_ok = key_range > 0 && key_range <= 8192 && key_dtype == ETL_I32 && key_stride == 1 && !minmax && ncols >= 1 &&
+                    etl::aligned16(keys);
+    for (int c = 0; c < ncols && dense_ok; ++c) dense_ok = p.val_stride[c] == 1 && etl::aligned16(p.val[c]);
+    const size_t dense_smem = ((size_t)key_range + 1) * (4 + (size_t)ncols * 12);
+    if (dense_ok && dense_smem <= 100 * 1024) {
+        p.key_range = key_range;
+        auto kern = ncols == 1 ? etl::groupby_dense_kernel<1> : (ncols == 2 ? etl::groupby_dense_kernel<2> : etl::groupby_dense_kernel<3>);
+        ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dense_smem));
+        int occ = 0;
+        ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, etl::GB_THREADS, dense_smem));
+        if (occ < 1) occ = 1;
+        const int64_t tiles = (n + etl::GB_THREADS * 4 - 1) / (etl::GB_THREADS * 4);
+        int64_t blocks = (int64_t)h->sm_count * occ;
+        if (blocks > tiles) blocks = tiles;
+        kern<<<(unsigned)blocks, etl::GB_THREADS, dense_smem, stream>>>(p);
+    } else if (use_smem) {
         p.smem_slots = slots;
         const size_t smem = slots * per_slot;
         auto kern = minmax ? etl::groupby_smem_kernel<true> : etl::groupby_smem_kernel<false>;

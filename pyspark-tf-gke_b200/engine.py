@@ -319,7 +319,7 @@ class Engine:
     def groupby_accumulate(self, gt: "GroupTable", keys: torch.Tensor, key_valid: Optional[torch.Tensor],
                            vals: Sequence[torch.Tensor], vals_valid: Sequence[Optional[torch.Tensor]] = (),
                            groups_hint: int = 0, n: Optional[int] = None, key_stride: int = 1,
-                           val_strides: Optional[Sequence[int]] = None) -> None:
+                           val_strides: Optional[Sequence[int]] = None, key_range: int = 0) -> None:
         """One batch of rows into the table.  keys int32/int64; vals f64.  With
         strides it reads the {key, value} records of the exchange in place."""
         nc = gt.ncols
@@ -333,7 +333,7 @@ class Engine:
             self._h, keys.data_ptr(), _DTYPE_CODE[keys.dtype], key_stride, _ptr(key_valid), nc,
             P(*[v.data_ptr() for v in vals]) if nc else None, L(*strides) if nc else None,
             P(*[_ptr(v) for v in vv]) if nc else None, n, gt.table.data_ptr(), gt.capacity, int(gt.minmax),
-            groups_hint, gt.status.data_ptr(), self._stream()))
+            groups_hint, key_range, gt.status.data_ptr(), self._stream()))
         self.launches += 1 if n else 0
 
     def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None) -> dict:

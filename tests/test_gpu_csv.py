@@ -142,6 +142,18 @@ def test_unseen_and_null_keys_go_to_the_unknown_index(eng):
     assert F.shape == (2, 5 * 2 + 3) and F[0, :10].sum() == 0 and F[1, :10].tolist() == [0, 1] * 5
 
 
+def test_dense_features_wide_and_edge_dimensions(eng):
+    rng = np.random.default_rng(3)
+    n = 5003
+    nums = [rng.random(n) * 100 for _ in range(3)]
+    dn = [torch.from_numpy(v).to(eng.device) for v in nums]
+    for L, repeats in [(1, 1), (29, 1), (30, 5), (84, 3), (85, 3), (300, 2), (7, 40)]:
+        idx = rng.integers(0, L + 1, n).astype(np.int32)  # L itself = unknown label
+        F = eng.assemble_dense(torch.from_numpy(idx).to(eng.device), dn, L, repeats).cpu().numpy()
+        exp = O.assemble_features_dense(idx.astype(np.float64), L, nums, repeats)
+        assert F.shape == exp.shape and F.tobytes() == exp.tobytes(), (L, repeats)
+
+
 def _synthetic_csv(rows, seed):
     rng = np.random.default_rng(seed)
     names = ["alpha", "be,ta", 'ga"mma', "delta\nline", "  eps  ", ""]

@@ -77,6 +77,30 @@ def test_groupby_exact_sums_on_integer_valued_data_in_batches(eng):
     _check(res, exp, exact_sums=True, minmax=False)
 
 
+@pytest.mark.parametrize("ncols", [1, 2, 3])
+def test_groupby_direct_indexed_path(eng, ncols):
+    # key_range promises int32 keys in [0, range): direct-indexed shared table; keys
+    # outside the promise and null keys must still come out right
+    n, groups = 300_001, 1000
+    keys, kv = S.host_column(8, 0, S.KIND_KEY32, n, modulus=groups, null_rate=0.01)
+    keys = keys.copy()
+    keys[::5003] = 5000 + (np.arange(len(keys[::5003])) % 7)   # beyond the promised range
+    keys[7::9001] = -3
+    vals, valid = [], []
+    for c in range(ncols):
+        v, vv = S.host_column(8, 1 + c, S.KIND_EXACT, n, null_rate=0.07, nan_rate=0.0)
+        vals.append(v)
+        valid.append(vv)
+    gt = eng.groupby_new(4096, ncols)
+    k = pkg.Column.from_host(keys, kv, eng.device)
+    cols = [pkg.Column.from_host(v, vv, eng.device) for v, vv in zip(vals, valid)]
+    eng.groupby_accumulate(gt, k.data, k.valid, [c.data for c in cols], [c.valid for c in cols], groups_hint=groups,
+                           key_range=groups)
+    res = eng.groupby_result(gt)
+    exp = O.groupby_agg(keys, kv, vals, valid)
+    _check(res, exp, exact_sums=True, minmax=False)
+
+
 def test_groupby_all_null_group_and_full_table(eng):
     keys = np.array([1, 1, 2, 3], dtype=np.int64)
     v = np.array([1.0, 2.0, 5.0, 7.0])
