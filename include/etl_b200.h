@@ -79,7 +79,8 @@ ETL_API int etl_reserve(etl_handle* h, size_t bytes);
  * write the key code and the three numerics cast to double, a null or NaN cell
  * replaced by fill[c].  val_dtype[c] is the input dtype of column c (ETL_F64 /
  * ETL_F32 / ETL_I32; an integer column cannot hold NaN).  out_* must hold n
- * rows.  *d_out_rows (device int64) receives the kept-row count.
+ * rows.  *d_out_rows (device int64) receives the kept-row count.  For this entry
+ * the bitmaps, too, must be 16-byte aligned (they are fetched by bulk copies).
  * Scratch: one 8-byte word per chunk (<= 65536 chunks), from the handle. */
 ETL_API int etl_project_filter_impute(etl_handle* h,
                               const int32_t* key_code, const uint32_t* key_valid,
@@ -98,6 +99,9 @@ ETL_API int etl_project_filter_impute_host(etl_handle* h,
                                    const void* const val[3], const uint32_t* const val_valid[3],
                                    const int32_t val_dtype[3], const double fill[3], int64_t n,
                                    int32_t* out_code, double* const out_val[3], int64_t* out_rows);
+
+/* Number of kernel launches (= row chunks) the host-buffer entry makes for n rows. */
+ETL_API int64_t etl_project_filter_impute_host_launches(int64_t n);
 
 /* No counterpart in the reference (it never manages device memory): the same
  * projection as etl_project_filter_impute for callers that must not trigger a

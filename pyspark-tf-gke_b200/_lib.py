@@ -39,6 +39,7 @@ _PROTOS = {
     "etl_project_filter_impute_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(VP3), C.POINTER(VP3),
                                                  C.POINTER(I32x3), C.POINTER(F64x3), C.c_int64, C.c_void_p,
                                                  C.POINTER(VP3), C.POINTER(C.c_int64)]),
+    "etl_project_filter_impute_host_launches": (C.c_int64, [C.c_int64]),
     "etl_project_filter_impute_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.POINTER(VP3),
                                                     C.POINTER(I32x3), C.POINTER(F64x3), C.c_int64, C.c_void_p,
                                                     C.POINTER(VP3), C.c_void_p, C.c_void_p]),

@@ -25,6 +25,7 @@
 // output byte written once (plus 4 B of bitmap per 32 rows read twice).
 #include "common.cuh"
 #include <stdlib.h>
+#include <vector>
 
 namespace etl {
 
@@ -299,17 +300,20 @@ __global__ void __launch_bounds__(PROJ_THREADS) project_filter_impute_kernel(con
 
 static int check_project_args(const int32_t* key_code, const void* const val[3], const uint32_t* key_valid,
                               const uint32_t* const val_valid[3], const int32_t val_dtype[3], int64_t n,
-                              const int32_t* out_code, double* const out_val[3]) {
+                              const int32_t* out_code, double* const out_val[3], bool device_bitmaps = true) {
     ETL_REQUIRE(n >= 0 && n < ((int64_t)1 << 39), "project: n=%lld out of range", (long long)n);
     ETL_REQUIRE(val && val_valid && val_dtype && out_val, "project: NULL argument array");
     if (n == 0) return ETL_OK;
     ETL_REQUIRE(key_code && out_code, "project: key_code/out_code is NULL");
-    ETL_REQUIRE(aligned16(key_code) && aligned4(key_valid), "project: key buffers misaligned");
+    // device bitmaps are fetched by 16-byte-granular bulk copies; host bitmaps get re-staged
+    ETL_REQUIRE(aligned16(key_code) && (device_bitmaps ? aligned16(key_valid) : aligned4(key_valid)),
+                "project: key buffers misaligned");
     for (int c = 0; c < 3; ++c) {
         ETL_REQUIRE(val[c] && out_val[c], "project: val[%d]/out_val[%d] is NULL", c, c);
         ETL_REQUIRE(val_dtype[c] == ETL_F64 || val_dtype[c] == ETL_F32 || val_dtype[c] == ETL_I32,
                     "project: val_dtype[%d]=%d unsupported", c, val_dtype[c]);
-        ETL_REQUIRE(aligned16(val[c]) && aligned4(val_valid[c]), "project: val[%d] buffers misaligned", c);
+        ETL_REQUIRE(aligned16(val[c]) && (device_bitmaps ? aligned16(val_valid[c]) : aligned4(val_valid[c])),
+                    "project: val[%d] buffers misaligned", c);
     }
     return ETL_OK;
 }
@@ -393,6 +397,22 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
 constexpr int64_t HOST_CHUNK_ROWS = (int64_t)1 << 20;
 constexpr int HOST_SLOTS = 3;
 
+// Chunk sizes of the host pipeline: uniform 1 Mi-row chunks (a ramp of smaller
+// chunks at the head and tail, to shorten the un-overlapped first copy-in and
+// last copy-out, measured slightly slower: more, smaller copies).  Every chunk
+// but the last is a multiple of 1024 rows.  Returns the largest size.
+static int64_t host_chunk_schedule(int64_t n, std::vector<int64_t>* sizes) {
+    int64_t big = HOST_CHUNK_ROWS;
+    if (const char* e = getenv("ETL_HOST_CHUNK_ROWS")) {
+        const long long want = atoll(e);
+        if (want >= 1024) big = (want + 1023) & ~(long long)1023;
+    }
+    sizes->clear();
+    for (int64_t left = n; left > 0; left -= big) sizes->push_back(left < big ? left : big);
+    const int64_t mx = n < big ? n : big;
+    return (mx + 1023) & ~(int64_t)1023;
+}
+
 static int64_t host_popcount_bits(const uint32_t* bitmap, int64_t row0, int64_t rows) {
     if (!bitmap) return rows;
     int64_t cnt = 0;
@@ -442,13 +462,12 @@ static size_t carve_slot(char* base, int64_t chunk, StageSlot* s) {
         off += (bytes + 255) & ~(size_t)255;
         return p;
     };
-    const size_t words = (size_t)((chunk + 31) >> 5) * 4;
     StageSlot t;
     t.code = (int32_t*)take(chunk * 4);
-    t.key_valid = (uint32_t*)take(words);
+    t.key_valid = nullptr;  // bitmaps are staged whole, once (they are 1/64 of the data)
     for (int c = 0; c < 3; ++c) {
         t.val[c] = take(chunk * 8);
-        t.val_valid[c] = (uint32_t*)take(words);
+        t.val_valid[c] = nullptr;
     }
     t.out_code = (int32_t*)take(chunk * 4);
     for (int c = 0; c < 3; ++c) t.out_val[c] = (double*)take(chunk * 8);
@@ -462,47 +481,51 @@ int project_host(Handle* h, const int32_t* key_code, const uint32_t* key_valid, 
                  int32_t* out_code, double* const out_val[3], int64_t* out_rows) {
     *out_rows = 0;
     if (n == 0) return ETL_OK;
-    const int64_t chunk = n < HOST_CHUNK_ROWS ? ((n + 1023) & ~(int64_t)1023) : HOST_CHUNK_ROWS;
+    std::vector<int64_t> sizes;
+    const int64_t chunk = host_chunk_schedule(n, &sizes);
     const size_t slot_bytes = carve_slot(nullptr, chunk, nullptr);
-    int rc = ensure_host_pipeline(h, slot_bytes * HOST_SLOTS);
+    const size_t bitmap_bytes = ((size_t)((n + 31) >> 5) * 4 + 255) & ~(size_t)255;
+    int rc = ensure_host_pipeline(h, slot_bytes * HOST_SLOTS + 4 * bitmap_bytes);
     if (rc != ETL_OK) return rc;
     StageSlot slot[HOST_SLOTS];
     for (int s = 0; s < HOST_SLOTS; ++s) carve_slot(static_cast<char*>(h->stage) + s * slot_bytes, chunk, &slot[s]);
+    uint32_t* d_bitmap[4];
+    for (int b = 0; b < 4; ++b)
+        d_bitmap[b] = reinterpret_cast<uint32_t*>(static_cast<char*>(h->stage) + slot_bytes * HOST_SLOTS + b * bitmap_bytes);
     cudaStream_t s_in = h->streams[0], s_k = h->streams[1], s_out = h->streams[2];
     cudaEvent_t* in_ready = h->events;            // [slot]
     cudaEvent_t* k_done = h->events + HOST_SLOTS; // [slot]
     cudaEvent_t* out_done = h->events + 2 * HOST_SLOTS;
 
-    int64_t written = 0;
-    const int64_t chunks = (n + chunk - 1) / chunk;
-    for (int64_t i = 0; i < chunks; ++i) {
+    // all four validity bitmaps first: 4 copies instead of 4 per chunk
+    const uint32_t* h_bitmap[4] = {key_valid, val_valid[0], val_valid[1], val_valid[2]};
+    for (int b = 0; b < 4; ++b)
+        if (h_bitmap[b])
+            ETL_CUDA(cudaMemcpyAsync(d_bitmap[b], h_bitmap[b], (size_t)((n + 31) >> 5) * 4, cudaMemcpyHostToDevice, s_in));
+    int64_t written = 0, row0 = 0;
+    const int64_t chunks = (int64_t)sizes.size();
+    for (int64_t i = 0; i < chunks; row0 += sizes[i], ++i) {
         const int s = (int)(i % HOST_SLOTS);
-        const int64_t row0 = i * chunk;
-        const int64_t rows = n - row0 < chunk ? n - row0 : chunk;
-        const size_t words = (size_t)((rows + 31) >> 5);
+        const int64_t rows = sizes[i];
         const int64_t kept = host_popcount_bits(key_valid, row0, rows);
         StageSlot& st = slot[s];
         // copy-in (after the kernel that last read this slot's inputs)
         if (i >= HOST_SLOTS) ETL_CUDA(cudaStreamWaitEvent(s_in, k_done[s], 0));
         ETL_CUDA(cudaMemcpyAsync(st.code, key_code + row0, rows * 4, cudaMemcpyHostToDevice, s_in));
-        if (key_valid)
-            ETL_CUDA(cudaMemcpyAsync(st.key_valid, key_valid + (row0 >> 5), words * 4, cudaMemcpyHostToDevice, s_in));
         for (int c = 0; c < 3; ++c) {
             const size_t es = dtype_size(val_dtype[c]);
             ETL_CUDA(cudaMemcpyAsync(st.val[c], static_cast<const char*>(val[c]) + row0 * es, rows * es,
                                      cudaMemcpyHostToDevice, s_in));
-            if (val_valid[c])
-                ETL_CUDA(cudaMemcpyAsync(st.val_valid[c], val_valid[c] + (row0 >> 5), words * 4,
-                                         cudaMemcpyHostToDevice, s_in));
         }
         ETL_CUDA(cudaEventRecord(in_ready[s], s_in));
         // kernel (after the copy-out that last read this slot's outputs)
         ETL_CUDA(cudaStreamWaitEvent(s_k, in_ready[s], 0));
         if (i >= HOST_SLOTS) ETL_CUDA(cudaStreamWaitEvent(s_k, out_done[s], 0));
         const void* dval[3] = {st.val[0], st.val[1], st.val[2]};
-        const uint32_t* dvalid[3] = {val_valid[0] ? st.val_valid[0] : nullptr, val_valid[1] ? st.val_valid[1] : nullptr,
-                                     val_valid[2] ? st.val_valid[2] : nullptr};
-        rc = launch_project(h, st.code, key_valid ? st.key_valid : nullptr, dval, dvalid, val_dtype, fill, rows,
+        const uint32_t* dvalid[3] = {val_valid[0] ? d_bitmap[1] + (row0 >> 5) : nullptr,
+                                     val_valid[1] ? d_bitmap[2] + (row0 >> 5) : nullptr,
+                                     val_valid[2] ? d_bitmap[3] + (row0 >> 5) : nullptr};
+        rc = launch_project(h, st.code, key_valid ? d_bitmap[0] + (row0 >> 5) : nullptr, dval, dvalid, val_dtype, fill, rows,
                             st.out_code, st.out_val, st.out_rows, s_k);
         if (rc != ETL_OK) return rc;
         ETL_CUDA(cudaEventRecord(k_done[s], s_k));
@@ -548,7 +571,7 @@ extern "C" int etl_project_filter_impute_host(etl_handle* hh, const int32_t* key
     ETL_REQUIRE(hh != nullptr, "project_host: handle is NULL");
     ETL_REQUIRE(fill != nullptr && out_rows != nullptr, "project_host: fill/out_rows is NULL");
     Handle* h = reinterpret_cast<Handle*>(hh);
-    int rc = etl::check_project_args(key_code, val, key_valid, val_valid, val_dtype, n, out_code, out_val);
+    int rc = etl::check_project_args(key_code, val, key_valid, val_valid, val_dtype, n, out_code, out_val, false);
     if (rc != ETL_OK) return rc;
     ETL_CUDA(cudaSetDevice(h->device));
     return etl::project_host(h, key_code, key_valid, val, val_valid, val_dtype, fill, n, out_code, out_val, out_rows);
@@ -703,4 +726,11 @@ extern "C" int etl_project_filter_impute_noalloc(const int32_t* key_code, const 
     project_filter_impute_kernel<<<(unsigned)grid, PROJ_THREADS, (size_t)NOALLOC_STAGES * sizeof(ProjStage), stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
+}
+
+extern "C" int64_t etl_project_filter_impute_host_launches(int64_t n) {
+    if (n <= 0) return 0;
+    std::vector<int64_t> sizes;
+    etl::host_chunk_schedule(n, &sizes);
+    return (int64_t)sizes.size();
 }

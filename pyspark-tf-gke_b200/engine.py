@@ -180,8 +180,7 @@ class Engine:
         _lib.check(self.lib.etl_project_filter_impute_host(self._h, hp(key_code), hp(key_valid), C.byref(val),
                                                            C.byref(vv), C.byref(dt), C.byref(fl), n, hp(out_code),
                                                            C.byref(ov), C.byref(rows)))
-        chunk = 1 << 20
-        self.launches += (n + chunk - 1) // chunk
+        self.launches += int(self.lib.etl_project_filter_impute_host_launches(n))
         return rows.value
 
     # -------------------------------------------------------------- a1 csv
