@@ -257,7 +257,8 @@ ETL_API int etl_nan_to_null(etl_handle* h, const double* val, uint32_t* valid, i
  * The result lives in a caller-owned open-addressing table of
  * etl_groupby_table_words(...) uint64 words: `capacity` (power of two, >= 2 x
  * the number of groups) entries plus one for the null-key group; entry layout
- * {key, rows, (count_c, sum_c) x ncols [, (min_c, max_c) x ncols]}.  Key value
+ * {key, rows, (nulls_c, sum_c) x ncols [, (min_c, max_c) x ncols]}, count(c) =
+ * rows - nulls_c.  Key value
  * INT64_MIN is reserved.  Usage: init once, accumulate any number of batches
  * (also partial tables received from other ranks), compact.
  * etl_groupby_accumulate: keys int32/int64 with element stride key_stride; val[c]
@@ -290,14 +291,19 @@ ETL_API int etl_groupby_compact(etl_handle* h, const uint64_t* table, int64_t ca
 
 /* The map side of Spark's shuffle exchange (the Exchange hashpartitioning node
  * under every aggregate of k_means.py:23-48; north-star item 4): rows (key int64,
- * value double) are grouped by destination rank dest = (hi32(mix64(key)) * parts)
- * >> 32 into one buffer of 16-byte records {key, value bits}; destination d
- * occupies records [d_part_base[d], d_part_base[d] + d_part_counts[d]).  That
- * buffer is the send side of an all-to-all (NCCL, torch.distributed); the
- * receiver feeds its records to etl_groupby_accumulate with strides of 2.
- * out_records: int64[2 * n], 16-byte aligned.  parts <= 64. */
-ETL_API int etl_hash_partition(etl_handle* h, const int64_t* keys, const double* vals, int64_t n, int32_t parts,
-                       int64_t* d_part_counts, int64_t* d_part_base, int64_t* out_records, void* stream);
+ * value double, element strides key_stride / val_stride so {key, value} records
+ * can be re-partitioned in place) are grouped by destination into one buffer of
+ * 16-byte records {key, value bits}.  Two levels from one hash h = mix64(key):
+ * rank = (hi32(h) * ranks) >> 32 picks the GPU, bucket = (lo32(h) * buckets)
+ * >> 32 a 1/buckets slice of that GPU's aggregation table (etl_groupby_* place
+ * a key's home slot at (lo32(h) * capacity) >> 32).  Destination d = rank *
+ * buckets + bucket occupies records [d_part_base[d], + d_part_counts[d]).  Rank
+ * ranges are the send side of an all-to-all (NCCL, torch.distributed); feeding
+ * the receiver's table bucket by bucket keeps the slice being updated resident
+ * in L2.  out_records: int64[2 * n], 16-byte aligned; ranks * buckets <= 256. */
+ETL_API int etl_hash_partition(etl_handle* h, const int64_t* keys, int64_t key_stride, const double* vals,
+                       int64_t val_stride, int64_t n, int32_t ranks, int32_t buckets, int64_t* d_part_counts,
+                       int64_t* d_part_base, int64_t* out_records, void* stream);
 
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 

@@ -475,9 +475,12 @@ def mix64(x: np.ndarray) -> np.ndarray:
     return z ^ (z >> np.uint64(31))
 
 
-def partition_dest(keys: np.ndarray, parts: int) -> np.ndarray:
-    """Destination rank of each key in the hash exchange: the top 32 bits of
-    mix64(key), multiplied by P and shifted down 32 (Lemire's range reduction) -
-    so every rank owns a disjoint key set."""
-    h = mix64(np.asarray(keys).astype(np.int64).view(np.uint64)) >> np.uint64(32)
-    return ((h * np.uint64(parts)) >> np.uint64(32)).astype(np.int32)
+def partition_dest(keys: np.ndarray, ranks: int, buckets: int = 1) -> np.ndarray:
+    """Destination of each key in the hash exchange, two levels from one hash h =
+    mix64(key): rank = (hi32(h) * ranks) >> 32 (Lemire's range reduction) picks
+    the GPU - every rank owns a disjoint key set - and bucket = (lo32(h) * buckets)
+    >> 32 a slice of that GPU's table.  dest = rank * buckets + bucket."""
+    h = mix64(np.asarray(keys).astype(np.int64).view(np.uint64))
+    rank = ((h >> np.uint64(32)) * np.uint64(ranks)) >> np.uint64(32)
+    bucket = ((h & np.uint64(0xFFFFFFFF)) * np.uint64(buckets)) >> np.uint64(32)
+    return (rank * np.uint64(buckets) + bucket).astype(np.int32)

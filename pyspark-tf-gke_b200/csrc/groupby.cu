@@ -3,9 +3,10 @@
 // StringIndexer.fit (k_means.py:34,73); Spark semantics are restated in
 // oracle/etl_oracle.py::groupby_agg.
 //
-// One global open-addressing table (array of fixed-stride entries, key + row
-// count + per-column count / sum [/ min / max]) is the result AND the spill
-// target.  Two kernels fill it:
+// One global open-addressing table (array of fixed-stride entries: key, row
+// count, per column {null cells, sum} [, {min, max}]; count(c) = rows - nulls,
+// so a row without nulls costs one atomic per column) is the result AND the
+// spill target.  Two kernels fill it:
 //   groupby_smem_kernel    low cardinality: every CTA aggregates into its own
 //        shared-memory open-addressing table (64-bit CAS on the key slot,
 //        32-bit native shared atomics for counts, CAS-loop shared atomics for
@@ -68,8 +69,8 @@ __device__ __forceinline__ void gb_global_add(uint64_t* e, const GroupByParams& 
                                               const uint64_t mn[3], const uint64_t mx[3]) {
     atomicAdd(reinterpret_cast<unsigned long long*>(e + 1), rows);
     for (int c = 0; c < p.ncols; ++c) {
+        if (cnt[c] != rows) atomicAdd(reinterpret_cast<unsigned long long*>(e + 2 + 2 * c), rows - cnt[c]);  // nulls
         if (!cnt[c]) continue;
-        atomicAdd(reinterpret_cast<unsigned long long*>(e + 2 + 2 * c), cnt[c]);
         atomicAdd(reinterpret_cast<double*>(e + 3 + 2 * c), sum[c]);
         if (p.minmax) {
             atomicMin(reinterpret_cast<unsigned long long*>(e + 2 + 2 * p.ncols + 2 * c), (unsigned long long)mn[c]);
@@ -80,7 +81,9 @@ __device__ __forceinline__ void gb_global_add(uint64_t* e, const GroupByParams& 
 
 // entry of `key` in the global table (inserting it), or nullptr when the table is full
 __device__ __forceinline__ uint64_t* gb_global_slot(const GroupByParams& p, uint64_t key) {
-    uint64_t slot = (mix64(key) >> 20) & p.mask;
+    // home slot = top bits of the LOW hash word (range-reduced), so the keys of bucket b of B
+    // (etl_hash_partition's second level, same word) live in one contiguous 1/B of the table
+    uint64_t slot = __umulhi((unsigned)mix64(key), (unsigned)(p.mask + 1));
     for (uint64_t probe = 0; probe <= p.mask; ++probe) {
         uint64_t* e = p.table + slot * p.stride;
         uint64_t cur = ld_relaxed_u64(e);
@@ -310,13 +313,17 @@ __global__ void __launch_bounds__(GB_THREADS) groupby_dense_kernel(const GroupBy
 
 __global__ void __launch_bounds__(256) groupby_init_kernel(uint64_t* table, int64_t entries, int32_t stride,
                                                            int32_t ncols, int32_t minmax) {
-    const int64_t total = entries * stride;
-    for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
-        const int f = (int)(w % stride);
-        uint64_t v = 0;
-        if (f == 0) v = GB_EMPTY;
-        else if (minmax && f >= 2 + 2 * ncols) v = ((f - 2 - 2 * ncols) & 1) ? 0ull : ~0ull;  // min slot / max slot
-        table[w] = v;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < entries; e += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t* w = table + e * stride;
+        if (stride == 4) {  // single value column: one 32-byte entry, two 16-byte stores
+            *reinterpret_cast<ulonglong2*>(w) = make_ulonglong2(GB_EMPTY, 0ull);
+            *reinterpret_cast<ulonglong2*>(w + 2) = make_ulonglong2(0ull, 0ull);
+            continue;
+        }
+        w[0] = GB_EMPTY;
+        for (int f = 1; f < 2 + 2 * ncols; ++f) w[f] = 0;
+        if (minmax)
+            for (int c = 0; c < ncols; ++c) { w[2 + 2 * ncols + 2 * c] = ~0ull; w[3 + 2 * ncols + 2 * c] = 0ull; }
     }
 }
 
@@ -340,10 +347,10 @@ __global__ void __launch_bounds__(256) groupby_compact_kernel(const uint64_t* __
         out_keys[g] = (int64_t)e[0];
         out_rows[g] = (int64_t)e[1];
         for (int c = 0; c < ncols; ++c) {
-            out_cnt[c * out_capacity + g] = (int64_t)e[2 + 2 * c];
+            out_cnt[c * out_capacity + g] = (int64_t)(e[1] - e[2 + 2 * c]);
             out_sum[c * out_capacity + g] = __longlong_as_double((long long)e[3 + 2 * c]);
             if (minmax) {
-                const bool any = e[2 + 2 * c] != 0;
+                const bool any = e[1] != e[2 + 2 * c];
                 const double nanv = __longlong_as_double(0x7ff8000000000000ll);
                 out_min[c * out_capacity + g] = any ? dbl_from_sortable(e[2 + 2 * ncols + 2 * c]) : nanv;
                 out_max[c * out_capacity + g] = any ? dbl_from_sortable(e[3 + 2 * ncols + 2 * c]) : nanv;
@@ -358,19 +365,24 @@ __global__ void __launch_bounds__(256) groupby_compact_kernel(const uint64_t* __
 // all-to-all.  dest = (hi32(mix64(key)) * P) >> 32.
 constexpr int PART_TILE = 2048;
 constexpr int PART_THREADS = 256;
-constexpr int PART_MAX = 64;
+constexpr int PART_MAX = 256;
 
-__device__ __forceinline__ int part_dest(uint64_t key, int parts) {
-    return (int)__umulhi((unsigned)(mix64(key) >> 32), (unsigned)parts);  // Lemire range reduction, < parts
+// destination = rank * buckets + bucket: rank from the high hash word, bucket from the low one
+// (Lemire range reductions; the bucket matches the slot ranges of gb_global_slot)
+__device__ __forceinline__ int part_dest(uint64_t key, int ranks, int buckets) {
+    const uint64_t h = mix64(key);
+    return (int)(__umulhi((unsigned)(h >> 32), (unsigned)ranks) * (unsigned)buckets + __umulhi((unsigned)h, (unsigned)buckets));
 }
 
-__global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int64_t* __restrict__ keys, int64_t n,
-                                                                       int parts, unsigned long long* counts) {
+__global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int64_t* __restrict__ keys,
+                                                                       int64_t key_stride, int64_t n, int ranks,
+                                                                       int buckets, unsigned long long* counts) {
+    const int parts = ranks * buckets;
     __shared__ unsigned int s_cnt[PART_MAX];
     if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;
     __syncthreads();
     for (int64_t i = (int64_t)blockIdx.x * PART_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * PART_THREADS) {
-        const int d = part_dest((uint64_t)keys[i], parts);
+        const int d = part_dest((uint64_t)keys[i * key_stride], ranks, buckets);
         atomicAdd(&s_cnt[d & (PART_MAX - 1)], 1u);
     }
     __syncthreads();
@@ -384,9 +396,12 @@ __global__ void partition_scan_kernel(const int64_t* counts, int64_t* base, int 
 }
 
 __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const int64_t* __restrict__ keys,
-                                                                         const double* __restrict__ vals, int64_t n,
-                                                                         int parts, const int64_t* __restrict__ part_base,
+                                                                         int64_t key_stride,
+                                                                         const double* __restrict__ vals,
+                                                                         int64_t val_stride, int64_t n, int ranks,
+                                                                         int buckets, const int64_t* __restrict__ part_base,
                                                                          unsigned long long* cursor, int64_t* out_records) {
+    const int parts = ranks * buckets;
     __shared__ unsigned int s_cnt[PART_MAX], s_off[PART_MAX];
     __shared__ unsigned long long s_gbase[PART_MAX];
     __shared__ int64_t s_key[PART_TILE];
@@ -409,9 +424,9 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
             const int r = j * PART_THREADS + threadIdx.x;
             dest[j] = -1;
             if (r < rows) {
-                k[j] = keys[row0 + r];
-                v[j] = vals[row0 + r];
-                dest[j] = part_dest((uint64_t)k[j], parts);
+                k[j] = keys[(row0 + r) * key_stride];
+                v[j] = vals[(row0 + r) * val_stride];
+                dest[j] = part_dest((uint64_t)k[j], ranks, buckets);
                 rank[j] = atomicAdd(&s_cnt[dest[j]], 1u);
             }
         }
@@ -464,8 +479,8 @@ extern "C" int etl_groupby_init(etl_handle* hh, uint64_t* table, int64_t capacit
                 "groupby_init: ncols in 0..3 and a power-of-two capacity required");
     Handle* h = reinterpret_cast<Handle*>(hh);
     ETL_CUDA(cudaSetDevice(h->device));
-    const int64_t total = (capacity + 1) * gb_stride(ncols, minmax);
-    int64_t blocks = (total + 255) / 256;
+    ETL_REQUIRE(etl::aligned16(table), "groupby_init: table must be 16-byte aligned");
+    int64_t blocks = (capacity + 1 + 255) / 256;
     if (blocks > (int64_t)h->sm_count * 16) blocks = (int64_t)h->sm_count * 16;
     etl::groupby_init_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(table, capacity + 1,
                                                                                              gb_stride(ncols, minmax),
@@ -562,13 +577,16 @@ extern "C" int etl_groupby_compact(etl_handle* hh, const uint64_t* table, int64_
     return ETL_OK;
 }
 
-extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, const double* vals, int64_t n, int32_t parts,
-                                  int64_t* d_part_counts, int64_t* d_part_base, int64_t* out_records, void* stream_) {
+extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, int64_t key_stride, const double* vals,
+                                  int64_t val_stride, int64_t n, int32_t ranks, int32_t buckets, int64_t* d_part_counts,
+                                  int64_t* d_part_base, int64_t* out_records, void* stream_) {
     ETL_REQUIRE(hh && d_part_counts && d_part_base, "hash_partition: NULL argument");
-    ETL_REQUIRE(parts >= 1 && parts <= etl::PART_MAX, "hash_partition: parts=%d not in 1..%d", parts, etl::PART_MAX);
-    ETL_REQUIRE(n >= 0, "hash_partition: n < 0");
+    ETL_REQUIRE(ranks >= 1 && buckets >= 1 && (int64_t)ranks * buckets <= etl::PART_MAX,
+                "hash_partition: ranks=%d x buckets=%d must be in 1..%d", ranks, buckets, etl::PART_MAX);
+    ETL_REQUIRE(n >= 0 && key_stride >= 1 && val_stride >= 1, "hash_partition: bad n / stride");
     Handle* h = reinterpret_cast<Handle*>(hh);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const int parts = ranks * buckets;
     ETL_CUDA(cudaSetDevice(h->device));
     ETL_CUDA(cudaMemsetAsync(d_part_counts, 0, sizeof(int64_t) * parts, stream));
     if (n == 0) {
@@ -583,14 +601,14 @@ extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, const dou
     int64_t blocks = (n + etl::PART_THREADS * 8 - 1) / (etl::PART_THREADS * 8);
     if (blocks > (int64_t)h->sm_count * 8) blocks = (int64_t)h->sm_count * 8;
     etl::partition_count_kernel<<<(unsigned)blocks, etl::PART_THREADS, 0, stream>>>(
-        keys, n, parts, reinterpret_cast<unsigned long long*>(d_part_counts));
+        keys, key_stride, n, ranks, buckets, reinterpret_cast<unsigned long long*>(d_part_counts));
     ETL_CUDA(cudaGetLastError());
     etl::partition_scan_kernel<<<1, 1, 0, stream>>>(d_part_counts, d_part_base, parts);
     ETL_CUDA(cudaGetLastError());
     const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
     int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
-    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(keys, vals, n, parts, d_part_base,
-                                                                                      cursor, out_records);
+    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(
+        keys, key_stride, vals, val_stride, n, ranks, buckets, d_part_base, cursor, out_records);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

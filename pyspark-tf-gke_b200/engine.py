@@ -370,16 +370,29 @@ class Engine:
         out["null_group_rows"] = int(null_entry[1].item())
         return out
 
-    def hash_partition(self, keys: torch.Tensor, vals: torch.Tensor, parts: int):
-        """Map side of the exchange -> (records int64[n, 2], counts int64[parts], base int64[parts])."""
-        n = keys.shape[0]
+    def hash_partition(self, keys: torch.Tensor, vals: torch.Tensor, ranks: int, buckets: int = 1,
+                       n: Optional[int] = None, key_stride: int = 1, val_stride: int = 1):
+        """Map side of the exchange -> (records int64[n, 2], counts int64[ranks*buckets],
+        base int64[ranks*buckets]); destination = rank * buckets + bucket."""
+        n = keys.shape[0] if n is None else n
+        parts = ranks * buckets
         rec = torch.empty((max(n, 1), 2), dtype=torch.int64, device=self.device)
         counts = self.empty(parts, torch.int64)
         base = self.empty(parts, torch.int64)
-        _lib.check(self.lib.etl_hash_partition(self._h, _ptr(keys), _ptr(vals), n, parts, counts.data_ptr(),
-                                               base.data_ptr(), rec.data_ptr(), self._stream()))
+        _lib.check(self.lib.etl_hash_partition(self._h, _ptr(keys), key_stride, _ptr(vals), val_stride, n, ranks, buckets,
+                                               counts.data_ptr(), base.data_ptr(), rec.data_ptr(), self._stream()))
         self.launches += 3 if n else 0
         return rec[:n], counts, base
+
+    def groupby_accumulate_records(self, gt: "GroupTable", records: torch.Tensor, lo: int, hi: int,
+                                   groups_hint: int = 1 << 30) -> None:
+        """Rows [lo, hi) of a {key, value} record buffer into a 1-column table."""
+        if hi <= lo:
+            return
+        flat = records.view(-1)
+        part = flat[2 * lo:]
+        self.groupby_accumulate(gt, part, None, [part[1:].view(torch.float64)], groups_hint=groups_hint, n=hi - lo,
+                                key_stride=2, val_strides=[2])
 
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,

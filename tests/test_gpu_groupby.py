@@ -121,45 +121,64 @@ def test_groupby_all_null_group_and_full_table(eng):
         eng.groupby_result(gt)
 
 
-@pytest.mark.parametrize("parts", [1, 2, 8])
-def test_hash_partition_matches_oracle_destinations(eng, parts):
+@pytest.mark.parametrize("ranks,buckets", [(1, 1), (2, 1), (8, 1), (1, 16), (8, 32)])
+def test_hash_partition_matches_oracle_destinations(eng, ranks, buckets):
     n = 300_007
+    parts = ranks * buckets
     keys, _ = S.host_column(3, 0, S.KIND_KEY64, n, modulus=10**8)
     vals, _ = S.host_column(3, 1, S.KIND_REAL, n)
-    rec, counts, base = eng.hash_partition(torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device), parts)
+    rec, counts, base = eng.hash_partition(torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device),
+                                           ranks, buckets)
     rec = rec.cpu().numpy()
-    dest = O.partition_dest(keys, parts)
+    dest = O.partition_dest(keys, ranks, buckets)
     assert counts.cpu().numpy().tolist() == np.bincount(dest, minlength=parts).tolist()
     assert base.cpu().numpy().tolist() == np.concatenate([[0], np.cumsum(np.bincount(dest, minlength=parts))[:-1]]).tolist()
     # every destination range holds exactly its rows (as a multiset of records)
     b = base.cpu().numpy().tolist() + [n]
     for d in range(parts):
         got = rec[b[d]:b[d + 1]]
-        assert (O.partition_dest(got[:, 0], parts) == d).all()
+        assert (O.partition_dest(got[:, 0], ranks, buckets) == d).all()
         want = np.stack([keys[dest == d], vals[dest == d].view(np.int64)], axis=1)
         assert np.array_equal(got[np.lexsort((got[:, 1], got[:, 0]))], want[np.lexsort((want[:, 1], want[:, 0]))])
 
 
-def test_partition_then_strided_merge_equals_direct_groupby(eng):
-    # single-process emulation of the exchange: every destination range is merged
-    # into its own table; together they must equal the direct aggregation
-    n, groups, parts = 400_000, 50_000, 4
+@pytest.mark.parametrize("buckets", [1, 8])
+def test_partition_then_strided_merge_equals_direct_groupby(eng, buckets):
+    # single-process emulation of the exchange: every rank's range is merged into
+    # its own table (bucket by bucket); together they must equal the direct aggregation
+    n, groups, ranks = 400_000, 50_000, 4
     keys, _ = S.host_column(9, 0, S.KIND_KEY64, n, modulus=groups)
     vals, _ = S.host_column(9, 1, S.KIND_EXACT, n)
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
-    rec, counts, base = eng.hash_partition(dk, dv, parts)
+    rec, counts, base = eng.hash_partition(dk, dv, ranks, buckets)
     b = base.cpu().tolist() + [n]
     all_keys, all_sums, all_rows = [], [], []
-    for d in range(parts):
-        part = rec[b[d]:b[d + 1]].contiguous().view(-1)
+    for r in range(ranks):
         gt = eng.groupby_new(1 << 17, 1)
-        eng.groupby_accumulate(gt, part, None, [part[1:].view(torch.float64)], groups_hint=groups, n=b[d + 1] - b[d],
-                               key_stride=2, val_strides=[2])
-        r = eng.groupby_result(gt)
-        all_keys.append(r["keys"]); all_sums.append(r["cols"][0]["sum"]); all_rows.append(r["rows"])
+        for k in range(buckets):
+            d = r * buckets + k
+            eng.groupby_accumulate_records(gt, rec, b[d], b[d + 1], groups)
+        res = eng.groupby_result(gt)
+        all_keys.append(res["keys"]); all_sums.append(res["cols"][0]["sum"]); all_rows.append(res["rows"])
     k = torch.cat(all_keys).cpu().numpy()
     order = np.argsort(k)
     exp = O.groupby_agg_fast(keys, [vals], [None])
     assert k[order].tolist() == exp["keys"].tolist()  # disjoint ownership: no key on two ranks
     assert torch.cat(all_rows).cpu().numpy()[order].tolist() == exp["rows"].tolist()
     assert torch.cat(all_sums).cpu().numpy()[order].tobytes() == exp["cols"][0]["sum"].tobytes()
+
+
+def test_bucketed_single_gpu_shuffle_path(eng):
+    import pyspark_tf_gke_b200.dist as D
+
+    n, groups = 500_000, 100_000
+    keys, _ = S.host_column(4, 0, S.KIND_KEY64, n, modulus=groups)
+    vals, _ = S.host_column(4, 1, S.KIND_EXACT, n)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    exp = O.groupby_agg_fast(keys, [vals], [None])
+    for buckets in (1, 16):
+        gt = D.shuffle_groupby_sum(eng, dk, dv, 1 << 18, groups_hint=groups, buckets=buckets)
+        res = eng.groupby_result(gt)
+        assert res["keys"].cpu().numpy().tolist() == exp["keys"].tolist()
+        assert res["cols"][0]["sum"].cpu().numpy().tobytes() == exp["cols"][0]["sum"].tobytes()
+    assert D.choose_buckets(1 << 28, 1) == 256 and D.choose_buckets(1 << 25, 8) == 32 and D.choose_buckets(1 << 10, 8) == 1

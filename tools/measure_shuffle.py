@@ -1,0 +1,140 @@
+#!/usr/bin/env python
+"""Config 4 (BASELINE.json configs[3]): 1B-row groupBy on a high-cardinality key
+(100M groups), strong scaling over 1/2/4/8 GPUs: hash-partition -> NCCL
+all-to-all over NVLink -> local final merge.
+
+    python tools/measure_shuffle.py                       # 1 GPU (direct aggregation, no exchange)
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tools/measure_shuffle.py [--rows R --groups G --steps K]
+
+Total rows are fixed; rank r generates rows [r*R/N, (r+1)*R/N) of the synthetic
+table on its own GPU.  Timed with CUDA events between barriers, max over ranks;
+phases (partition / exchange / merge) are timed separately the same way.  Checks:
+row conservation, disjoint key ownership (sum of per-rank groups == distinct
+keys), and the grand total of the sums against a plain column sum."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import pyspark_tf_gke_b200 as pkg  # noqa: E402
+import pyspark_tf_gke_b200.dist as D  # noqa: E402
+import pyspark_tf_gke_b200.synth as S  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=S.CONFIG4["rows"])
+    ap.add_argument("--groups", type=int, default=S.CONFIG4["groups"])
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=1)
+    ap.add_argument("--buckets", type=int, default=-1, help="table buckets per rank (-1 = choose from the table size)")
+    args = ap.parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = pkg.Engine(local)
+    n = args.rows // world // 32 * 32
+    row0 = rank * n
+    key = eng.synth_column(S.CONFIG4["seed"], 0, S.KIND_KEY64, n, row0=row0, modulus=args.groups, with_valid=False).data
+    val = eng.synth_column(S.CONFIG4["seed"], 1, S.KIND_EXACT, n, row0=row0, with_valid=False).data
+    groups_local = args.groups // world + args.groups // (world * 4) + 1024
+    cap = 1 << int(np.ceil(np.log2(2 * groups_local)))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def ev():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def max_ms(a, b):
+        t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=eng.device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    phases = {"partition": [], "exchange": [], "merge": [], "total": []}
+    gt = None
+    sent = 0
+    for it in range(args.warmup + args.steps):
+        gt = None
+        torch.cuda.empty_cache()
+        barrier()
+        t0 = ev()
+        B = D.choose_buckets(cap, world) if args.buckets < 0 else args.buckets
+        gt = eng.groupby_new(cap, 1)
+        if world == 1 and B == 1:
+            t1 = t2 = ev()
+            eng.groupby_accumulate(gt, key, None, [val], groups_hint=args.groups)
+        else:
+            rec, counts, _ = eng.hash_partition(key, val, world, B)
+            matrix = counts.view(world, B)
+            t1 = ev()
+            if world > 1:
+                recv_matrix = torch.empty_like(matrix)
+                dist.all_to_all_single(recv_matrix.view(-1), matrix.contiguous().view(-1))
+                got = D.exchange_records(rec, matrix.sum(dim=1))
+                sent = int(matrix.sum().item()) - int(matrix[rank].sum().item())
+                recv_matrix = recv_matrix.cpu()
+            else:
+                got, recv_matrix = rec, matrix.cpu()
+            t2 = ev()
+            lengths = recv_matrix.reshape(-1)
+            starts = (torch.cumsum(lengths, 0) - lengths).view(world, B).tolist()
+            lengths = lengths.view(world, B).tolist()
+            for b in range(B):
+                for s_ in range(world):
+                    eng.groupby_accumulate_records(gt, got, starts[s_][b], starts[s_][b] + lengths[s_][b], args.groups)
+            del rec, got
+        t3 = ev()
+        torch.cuda.synchronize()
+        if it >= args.warmup:
+            phases["partition"].append(max_ms(t0, t1))
+            phases["exchange"].append(max_ms(t1, t2))
+            phases["merge"].append(max_ms(t2, t3))
+            phases["total"].append(max_ms(t0, t3))
+    # ---- checks
+    res = eng.groupby_result(gt, max_groups=cap)
+    tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
+    gsum = res["cols"][0]["sum"].sum().reshape(1)
+    s, c = eng.sum_count([pkg.Column(val)])
+    direct = s[:1].clone()
+    if world > 1:
+        dist.all_reduce(tot)
+        dist.all_reduce(gsum)
+        dist.all_reduce(direct)
+    ok_rows = int(tot[0].item()) == n * world
+    ok_sum = float(gsum.item()) == float(direct.item())  # integer-valued data: exact
+    if rank == 0:
+        mean = {k: float(np.mean(v)) for k, v in phases.items()}
+        line = {"workload": "config4 shuffle+aggregate", "n_gpus": world, "rows_total": n * world, "groups": args.groups,
+                "distinct_keys_found": int(tot[1].item()), "rows_conserved": ok_rows, "sum_matches_column_sum": ok_sum,
+                "ms": mean, "rows_per_s": n * world / (mean["total"] * 1e-3),
+                "buckets_per_rank": B, "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
+                "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
+                "steps": args.steps}
+        print(json.dumps(line), flush=True)
+    assert ok_rows and ok_sum
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
