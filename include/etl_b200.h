@@ -151,7 +151,7 @@ ETL_API int etl_column_sum_count(etl_handle* h, int32_t ncols,
  * (spark_checks/python_checks/spark_workload_to_cloud_k8s.py:48) and the
  * csv.DictReader loop of load_csv (workloads/raw-tf/train_tf_ps.py:114-137) for
  * the columns the ETL stage uses.  `text` is the whole file in device memory,
- * 16-byte aligned, readable up to the next multiple of 8 past nbytes.  RFC-4180
+ * 16-byte aligned, with at least 16 readable bytes after nbytes.  RFC-4180
  * quoting (quoted fields may hold commas and newlines, "" is an escaped quote);
  * blank lines are dropped, as Spark and csv.reader do.
  *

@@ -15,13 +15,14 @@
 //      -> every block's true starting quote state and first row number
 //   3. csv_row_offsets_kernel    re-derives the masks with the true state and
 //      writes row_start[row] (int64 byte offsets)
-//   4. csv_parse_rows_kernel     one warp per 32 rows: the warp tokenises a row
-//      cooperatively (8 bytes per lane, quote parity by ballot, comma ranks by
-//      shuffle scan), then lane s converts requested column s: numerals through
-//      dec_parse (correctly rounded), strings through an open-addressing
-//      dictionary in global memory keyed by a 64-bit hash with a byte-compare
-//      collision check.  Results of 32 rows are staged in shared memory so each
-//      column leaves as one coalesced store and one validity word per 32 rows.
+//   4. csv_parse_rows_kernel     one warp per 32 rows, two phases: (A) the warp
+//      tokenises the rows one after another (8 bytes per lane, quote parity by
+//      ballot, comma ranks by shuffle scan) and leaves every requested field's
+//      bounds in shared memory; (B) lane r converts row r, all lanes busy:
+//      numerals through dec_parse (correctly rounded), strings through an open-
+//      addressing dictionary in global memory keyed by a 64-bit hash (8 bytes per
+//      step) with a byte-exact collision check.  Each column leaves as one
+//      coalesced store plus one ballot-built validity word per 32 rows.
 #include "common.cuh"
 #include "decimal.cuh"
 
@@ -330,11 +331,122 @@ __device__ __forceinline__ unsigned eq8(uint64_t w, uint32_t pat) {
 }
 
 constexpr int PARSE_WARPS = 4;
+constexpr uint32_t F_NONE = 0xffffffffu;
 
+// 8 text bytes at an arbitrary address as a little-endian word (two aligned loads + funnel shift;
+// the text buffer is readable up to the next multiple of 8 past its end)
+__device__ __forceinline__ uint64_t load8_unaligned(const uint8_t* p) {
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint64_t* q = reinterpret_cast<const uint64_t*>(a & ~(uintptr_t)7);
+    const unsigned sh = (unsigned)(a & 7) * 8;
+    const uint64_t lo = q[0];
+    if (sh == 0) return lo;
+    return (lo >> sh) | (q[1] << (64 - sh));
+}
+
+// hash of a field's bytes, 8 at a time; `plain` = no doubled quotes inside (the common case)
+__device__ __forceinline__ uint64_t field_hash_words(const uint8_t* p, int len) {
+    uint64_t h = 0x9E3779B97F4A7C15ull ^ (uint64_t)len;
+    int i = 0;
+    for (; i + 8 <= len; i += 8) h = (h ^ load8_unaligned(p + i)) * 0xff51afd7ed558ccdull, h ^= h >> 32;
+    if (i < len) {
+        const uint64_t w = load8_unaligned(p + i) & (~0ull >> (8 * (8 - (len - i))));
+        h = (h ^ w) * 0xff51afd7ed558ccdull, h ^= h >> 32;
+    }
+    h = mix64(h);
+    return h ? h : 1;
+}
+__device__ __forceinline__ bool field_equal_words(const uint8_t* a, const uint8_t* b, int len) {
+    int i = 0;
+    for (; i + 8 <= len; i += 8)
+        if (load8_unaligned(a + i) != load8_unaligned(b + i)) return false;
+    if (i < len) {
+        const uint64_t m = ~0ull >> (8 * (8 - (len - i)));
+        if ((load8_unaligned(a + i) ^ load8_unaligned(b + i)) & m) return false;
+    }
+    return true;
+}
+// does the field hold a quote character (a doubled one inside a quoted field, or a bare one)?
+__device__ __forceinline__ bool field_has_quote(const uint8_t* p, int len) {
+    for (int i = 0; i < len; i += 8) {
+        const int take = len - i < 8 ? len - i : 8;
+        const unsigned m = eq8(load8_unaligned(p + i), 0x22222222u) & (0xffu >> (8 - take));
+        if (m) return true;
+    }
+    return false;
+}
+
+// dictionary probe with the word-wise compare for plain fields (canonical cursor compare otherwise)
+__device__ __forceinline__ int dict_find_or_insert_fast(uint64_t* hash_tab, uint64_t* rep_tab, uint32_t mask,
+                                                        const uint8_t* text, uint64_t h, const uint8_t* f, int len,
+                                                        bool quoted, bool plain) {
+    const uint64_t rep = rep_pack(f - text, len, quoted);
+    uint32_t slot = (uint32_t)(h >> 24) & mask;
+    for (uint32_t probe = 0; probe <= mask; ++probe) {
+        uint64_t cur = ld_relaxed_u64(hash_tab + slot);
+        if (cur == 0) {
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(hash_tab + slot), 0ull, (unsigned long long)h);
+            if (cur == 0) {
+                st_relaxed_u64(rep_tab + slot, rep);
+                return (int)slot;
+            }
+        }
+        if (cur == h) {
+            uint64_t r;
+            do { r = ld_relaxed_u64(rep_tab + slot); } while (r == 0);
+            const bool r_quoted = (r & REP_QUOTED) != 0;
+            const int r_len = (int)(r & (REP_QUOTED - 1));
+            const uint8_t* rp = text + (r >> (REP_LEN_BITS + 1));
+            // two plain fields are equal iff their bytes are; anything involving doubled quotes goes the slow way
+            const bool r_plain = !field_has_quote(rp, r_len);
+            (void)r_quoted;
+            if (plain && r_plain ? (r_len == len && field_equal_words(rp, f, len)) : field_equal(text, r, rep))
+                return (int)slot;
+        }
+        slot = (slot + 1) & mask;
+    }
+    return -1;
+}
+
+// [-]digits[.digits] with at most 15 significant digits: exact through one divide (Clinger);
+// returns false when the cell needs the general parser
+__device__ __forceinline__ bool dec_parse_simple(const uint8_t* p, int len, double* out, int* flags) {
+    if (len <= 0 || len > 17) return false;
+    int i = 0;
+    const bool neg = p[0] == '-';
+    if (neg) i = 1;
+    uint64_t m = 0;
+    int digits = 0, frac = 0;
+    bool dot = false;
+    for (; i < len; ++i) {
+        const unsigned c = p[i];
+        if (c - '0' <= 9u) {
+            m = m * 10 + (c - '0');
+            ++digits;
+            frac += dot ? 1 : 0;
+        } else if (c == '.' && !dot) {
+            dot = true;
+        } else {
+            return false;
+        }
+    }
+    if (digits == 0 || digits > 15) return false;
+    double r = (double)m;
+    if (frac) r /= dec_pow10(frac);
+    *out = neg ? -r : r;
+    *flags = dot ? DEC_FLAG_NONINT : 0;
+    return true;
+}
+
+// Two phases per group of 32 rows:
+//   A  the warp tokenises the rows one after another (8 bytes per lane per 256-byte window) and
+//      leaves each requested field's [start, end) in shared memory;
+//   B  lane r converts row r - all 32 lanes busy - and the group's values leave as one coalesced
+//      store per column plus one ballot-built validity word.
 __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const CsvParseParams p) {
-    __shared__ int64_t s_fstart[PARSE_WARPS][CSV_MAX_COLS], s_fend[PARSE_WARPS][CSV_MAX_COLS];
+    __shared__ uint32_t s_fs[PARSE_WARPS][CSV_MAX_COLS][32], s_fe[PARSE_WARPS][CSV_MAX_COLS][32];  // relative to the group
+    __shared__ uint32_t s_rend[PARSE_WARPS][32];
     __shared__ int8_t s_slot_of_field[CSV_MAX_FIELDS];
-    __shared__ uint64_t s_val[PARSE_WARPS][CSV_MAX_COLS][32];  // double bits or dictionary slot per row of the group
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < CSV_MAX_FIELDS; i += blockDim.x) s_slot_of_field[i] = -1;
     __syncthreads();
@@ -345,22 +457,21 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
     for (int64_t g = (int64_t)blockIdx.x * PARSE_WARPS + warp; g < groups; g += (int64_t)gridDim.x * PARSE_WARPS) {
         const int64_t r0 = g * 32;
         const int in_group = p.rows - r0 < 32 ? (int)(p.rows - r0) : 32;
-        uint32_t my_valid = 0;  // lane s: validity word of column s over the group's rows
+        const int64_t my_start = lane < in_group ? p.row_start[p.first_row + r0 + lane] : 0;
+        const int64_t gbase = __shfl_sync(0xffffffffu, my_start, 0);  // offsets below are relative to this
+        for (int s = 0; s < p.ncols; ++s) { s_fs[warp][s][lane] = F_NONE; s_fe[warp][s][lane] = F_NONE; }
+        __syncwarp();
+        // ---------------------------------------------------------------- phase A
         for (int rr = 0; rr < in_group; ++rr) {
-            const int64_t row = p.first_row + r0 + rr;
-            const int64_t start = p.row_start[row];
-            // ---- tokenise: the warp walks the row in 256-byte windows
-            if (lane < p.ncols) { s_fstart[warp][lane] = -1; s_fend[warp][lane] = -1; }
-            __syncwarp();
-            if (lane == 0 && s_slot_of_field[0] >= 0) s_fstart[warp][s_slot_of_field[0]] = start;
+            const int64_t start = __shfl_sync(0xffffffffu, my_start, rr);
+            if (lane == 0 && s_slot_of_field[0] >= 0) s_fs[warp][s_slot_of_field[0]][rr] = (uint32_t)(start - gbase);
             int64_t abase = start & ~(int64_t)7;
             unsigned inside = 0, ncomma = 0;
             int64_t row_end = -1;
             while (true) {
                 const int64_t wpos = abase + 8 * lane;
                 uint64_t w = 0;
-                if (wpos < p.n) w = *reinterpret_cast<const uint64_t*>(p.text + wpos);  // buffer is padded to 8 bytes
-                // bytes of this word that belong to the row so far and to the text
+                if (wpos < p.n) w = *reinterpret_cast<const uint64_t*>(p.text + wpos);
                 unsigned vm = 0xff;
                 if (wpos < start) vm &= start - wpos >= 8 ? 0u : (0xffu << (start - wpos));
                 if (wpos + 8 > p.n) vm &= p.n <= wpos ? 0u : (0xffu >> (8 - (p.n - wpos)));
@@ -369,22 +480,21 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                 const unsigned n8 = eq8(w, 0x0a0a0a0au) & vm;
                 const unsigned pb = __ballot_sync(0xffffffffu, __popc(q8) & 1);
                 const unsigned st = (inside ^ __popc(pb & lt)) & 1;
-                unsigned ins = q8;  // prefix parity over the 8 bytes
+                unsigned ins = q8;
                 ins ^= ins << 1; ins ^= ins << 2; ins ^= ins << 4;
                 ins = (ins << 1) & 0xff;
                 if (st) ins ^= 0xff;
-                unsigned end8 = n8 & ~ins;  // record-ending newlines
+                const unsigned end8 = n8 & ~ins;
                 const unsigned eb = __ballot_sync(0xffffffffu, end8 != 0);
-                unsigned keep = 0xff;       // bytes before the record end
-                int end_lane = 32;
+                unsigned keep = 0xff;
                 if (eb) {
-                    end_lane = __ffs(eb) - 1;
+                    const int end_lane = __ffs(eb) - 1;
                     const unsigned e_first = __shfl_sync(0xffffffffu, end8, end_lane);
                     const int ebit = __ffs(e_first) - 1;
                     row_end = abase + 8 * end_lane + ebit;
                     keep = lane < end_lane ? 0xffu : (lane == end_lane ? ((1u << ebit) - 1) : 0u);
                 }
-                unsigned oc = c8 & ~ins & keep;  // field separators
+                unsigned oc = c8 & ~ins & keep;
                 const unsigned cnt = __popc(oc);
                 unsigned incl = cnt;
 #pragma unroll
@@ -392,14 +502,13 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                     const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
                     if (lane >= o) incl += up;
                 }
-                unsigned fi = ncomma + incl - cnt;  // index of the field this lane's first separator closes
+                unsigned fi = ncomma + incl - cnt;
                 while (oc) {
                     const int b = __ffs(oc) - 1;
                     oc &= oc - 1;
-                    const int64_t pos = wpos + b;
-                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fend[warp][s_slot_of_field[fi]] = pos;
-                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0)
-                        s_fstart[warp][s_slot_of_field[fi + 1]] = pos + 1;
+                    const uint32_t pos = (uint32_t)(wpos + b - gbase);
+                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fe[warp][s_slot_of_field[fi]][rr] = pos;
+                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0) s_fs[warp][s_slot_of_field[fi + 1]][rr] = pos + 1;
                     ++fi;
                 }
                 ncomma += __shfl_sync(0xffffffffu, incl, 31);
@@ -408,69 +517,71 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                 abase += 256;
                 if (abase >= p.n) { row_end = p.n; break; }
             }
-            __syncwarp();
-            // ---- convert: lane s handles requested column s
+            if (lane == 0) s_rend[warp][rr] = (uint32_t)(row_end - gbase);
+        }
+        __syncwarp();
+        // ---------------------------------------------------------------- phase B: lane = row
+        const int64_t row = p.first_row + r0 + lane;
+        const uint32_t rend = lane < in_group ? s_rend[warp][lane] : 0;
+        for (int s = 0; s < p.ncols; ++s) {
             bool ok = false;
             uint64_t bits = 0;
-            if (lane < p.ncols) {
-                int64_t fs = s_fstart[warp][lane], fe = s_fend[warp][lane];
-                if (fs >= 0) {  // the row has this field; an open end = the row's last field
-                    if (fe < 0) fe = row_end;
-                    if (fe > fs && p.text[fe - 1] == '\r' && fe == row_end) --fe;  // CRLF line end
-                    const uint8_t* f = p.text + fs;
-                    int len = (int)(fe - fs);
-                    const bool numeric = p.kind[lane] == 0;
-                    if (numeric || (p.flags & CSV_TRIM_STRINGS)) {
+            const uint32_t fs = s_fs[warp][s][lane];
+            if (lane < in_group && fs != F_NONE) {
+                uint32_t fe = s_fe[warp][s][lane];
+                if (fe == F_NONE) fe = rend;  // the row's last field
+                const uint8_t* f = p.text + gbase + fs;
+                int len = (int)(fe - fs);
+                if (len > 0 && fe == rend && f[len - 1] == '\r') --len;  // CRLF line end
+                const bool numeric = p.kind[s] == 0;
+                const bool trim = numeric || (p.flags & CSV_TRIM_STRINGS);
+                if (trim) {
+                    while (len > 0 && dec_is_space(f[0])) { ++f; --len; }
+                    while (len > 0 && dec_is_space(f[len - 1])) --len;
+                }
+                bool quoted = false;
+                if (len >= 2 && f[0] == '"' && f[len - 1] == '"') {
+                    quoted = true; ++f; len -= 2;
+                    if (trim) {  // csv yields the inner text, then .strip()
                         while (len > 0 && dec_is_space(f[0])) { ++f; --len; }
                         while (len > 0 && dec_is_space(f[len - 1])) --len;
                     }
-                    bool quoted = false;
-                    if (len >= 2 && f[0] == '"' && f[len - 1] == '"') {
-                        quoted = true; ++f; len -= 2;
-                        if (numeric || (p.flags & CSV_TRIM_STRINGS)) {  // csv yields the inner text, then .strip()
-                            while (len > 0 && dec_is_space(f[0])) { ++f; --len; }
-                            while (len > 0 && dec_is_space(f[len - 1])) --len;
-                        }
+                }
+                if (numeric) {
+                    double v = 0.0;
+                    int fl = 0;
+                    int st = DEC_OK;
+                    if (!dec_parse_simple(f, len, &v, &fl)) st = dec_parse(f, len, &v, &fl);
+                    if (st == DEC_OK) {
+                        ok = !((fl & DEC_FLAG_NAN) && (p.flags & CSV_NAN_IS_NULL));
+                        bits = (uint64_t)__double_as_longlong(v);
+                        if ((fl & DEC_FLAG_NONINT) && !(p.status[2] & (1 << s))) atomicOr(p.status + 2, 1 << s);
+                    } else if (st == DEC_INEXACT) {
+                        atomicAdd(p.status + 0, 1);
+                        atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
+                    } else if (st == DEC_INVALID) {
+                        atomicAdd(p.status + 3, 1);
                     }
-                    if (numeric) {
-                        double v = 0.0;
-                        int fl = 0;
-                        const int st = dec_parse(f, len, &v, &fl);
-                        if (st == DEC_OK) {
-                            ok = !((fl & DEC_FLAG_NAN) && (p.flags & CSV_NAN_IS_NULL));
-                            bits = (uint64_t)__double_as_longlong(v);
-                            if ((fl & DEC_FLAG_NONINT) && !(p.status[2] & (1 << lane))) atomicOr(p.status + 2, 1 << lane);
-                        } else if (st == DEC_INEXACT) {
-                            atomicAdd(p.status + 0, 1);
-                            atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
-                        } else if (st == DEC_INVALID) {
-                            atomicAdd(p.status + 3, 1);
-                        }
-                    } else if (len > 0) {
-                        const uint64_t h = field_hash(f, len, quoted);
-                        const int slot = dict_find_or_insert(p.dict_hash[lane], p.dict_rep[lane], p.dict_mask[lane],
-                                                             p.text, h, rep_pack(f - p.text, len, quoted));
-                        if (slot >= 0) {
-                            ok = true;
-                            bits = (uint64_t)(uint32_t)slot;
-                        } else {
-                            atomicAdd(p.status + 1, 1);
-                            atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
-                        }
+                } else if (len > 0) {
+                    // "plain" = no quote character at all: such strings always take the word-wise hash, strings
+                    // holding a quote (doubled inside a quoted field, or bare) always the canonical byte-wise one
+                    const bool plain = !field_has_quote(f, len);
+                    const uint64_t h = plain ? field_hash_words(f, len) : field_hash(f, len, quoted);
+                    const int slot = dict_find_or_insert_fast(p.dict_hash[s], p.dict_rep[s], p.dict_mask[s], p.text, h, f,
+                                                              len, quoted, plain);
+                    if (slot >= 0) {
+                        ok = true;
+                        bits = (uint64_t)(uint32_t)slot;
+                    } else {
+                        atomicAdd(p.status + 1, 1);
+                        atomicMin(reinterpret_cast<long long*>(p.first_bad_row), (long long)row);
                     }
                 }
-                s_val[warp][lane][rr] = bits;
-                my_valid |= (ok ? 1u : 0u) << rr;
             }
-            __syncwarp();
-        }
-        // ---- coalesced write-out of the group: 32 rows per column
-        for (int s = 0; s < p.ncols; ++s) {
-            const uint32_t vw = __shfl_sync(0xffffffffu, my_valid, s);
+            const uint32_t vw = __ballot_sync(0xffffffffu, ok);
             if (lane < in_group) {
-                const uint64_t b = s_val[warp][s][lane];
-                if (p.kind[s] == 0) static_cast<double*>(p.out[s])[r0 + lane] = __longlong_as_double((long long)b);
-                else static_cast<int32_t*>(p.out[s])[r0 + lane] = ((vw >> lane) & 1u) ? (int32_t)b : -1;
+                if (p.kind[s] == 0) static_cast<double*>(p.out[s])[r0 + lane] = __longlong_as_double((long long)bits);
+                else static_cast<int32_t*>(p.out[s])[r0 + lane] = ok ? (int32_t)bits : -1;
             }
             if (lane == 0) p.valid[s][g] = vw;
         }
