@@ -15,10 +15,10 @@
 //      -> every block's true starting quote state and first row number
 //   3. csv_row_offsets_kernel    re-derives the masks with the true state and
 //      writes row_start[row] (int64 byte offsets)
-//   4. csv_parse_rows_kernel     one warp per 32 rows, two phases: (A) the warp
-//      tokenises the rows one after another (8 bytes per lane, quote parity by
-//      ballot, comma ranks by shuffle scan) and leaves every requested field's
-//      bounds in shared memory; (B) lane r converts row r, all lanes busy:
+//   4. csv_parse_rows_kernel     one warp per 32 rows, lane r owns row r: (A) it
+//      walks the row 8 bytes at a time (SWAR byte compares, in-word prefix xor
+//      for the quote state, ffs over the unquoted-comma mask) and leaves every
+//      requested field's bounds in shared memory; (B) it converts those fields:
 //      numerals through dec_parse (correctly rounded), strings through an open-
 //      addressing dictionary in global memory keyed by a 64-bit hash (8 bytes per
 //      step) with a byte-exact collision check.  Each column leaves as one
@@ -438,11 +438,11 @@ __device__ __forceinline__ bool dec_parse_simple(const uint8_t* p, int len, doub
     return true;
 }
 
-// Two phases per group of 32 rows:
-//   A  the warp tokenises the rows one after another (8 bytes per lane per 256-byte window) and
-//      leaves each requested field's [start, end) in shared memory;
-//   B  lane r converts row r - all 32 lanes busy - and the group's values leave as one coalesced
-//      store per column plus one ballot-built validity word.
+// One warp per group of 32 rows, lane r owns row r in both phases:
+//   A  tokenise: walk the row 8 bytes at a time and leave each requested field's [start, end) in
+//      shared memory;
+//   B  convert the requested fields; the group's values leave as one coalesced store per column
+//      plus one ballot-built validity word.
 __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const CsvParseParams p) {
     __shared__ uint32_t s_fs[PARSE_WARPS][CSV_MAX_COLS][32], s_fe[PARSE_WARPS][CSV_MAX_COLS][32];  // relative to the group
     __shared__ uint32_t s_rend[PARSE_WARPS][32];
@@ -461,68 +461,52 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
         const int64_t gbase = __shfl_sync(0xffffffffu, my_start, 0);  // offsets below are relative to this
         for (int s = 0; s < p.ncols; ++s) { s_fs[warp][s][lane] = F_NONE; s_fe[warp][s][lane] = F_NONE; }
         __syncwarp();
-        // ---------------------------------------------------------------- phase A
-        for (int rr = 0; rr < in_group; ++rr) {
-            const int64_t start = __shfl_sync(0xffffffffu, my_start, rr);
-            if (lane == 0 && s_slot_of_field[0] >= 0) s_fs[warp][s_slot_of_field[0]][rr] = (uint32_t)(start - gbase);
-            int64_t abase = start & ~(int64_t)7;
-            unsigned inside = 0, ncomma = 0;
-            int64_t row_end = -1;
-            while (true) {
-                const int64_t wpos = abase + 8 * lane;
-                uint64_t w = 0;
-                if (wpos < p.n) w = *reinterpret_cast<const uint64_t*>(p.text + wpos);
+        // ---------------------------------------------------------------- phase A: lane = row
+        // every lane walks its own row 8 bytes at a time: quote state by an in-word prefix xor plus a
+        // carried parity bit, separators by ffs over the unquoted-comma mask
+        if (lane < in_group) {
+            const int64_t start = my_start;
+            if (s_slot_of_field[0] >= 0) s_fs[warp][s_slot_of_field[0]][lane] = (uint32_t)(start - gbase);
+            int64_t pos = start & ~(int64_t)7;
+            unsigned inside = 0, fi = 0;
+            int64_t row_end = p.n;
+            while (pos < p.n) {
+                const uint64_t w = *reinterpret_cast<const uint64_t*>(p.text + pos);
                 unsigned vm = 0xff;
-                if (wpos < start) vm &= start - wpos >= 8 ? 0u : (0xffu << (start - wpos));
-                if (wpos + 8 > p.n) vm &= p.n <= wpos ? 0u : (0xffu >> (8 - (p.n - wpos)));
+                if (pos < start) vm = 0xffu << (start - pos);
+                if (pos + 8 > p.n) vm &= 0xffu >> (8 - (p.n - pos));
                 const unsigned q8 = eq8(w, 0x22222222u) & vm;
                 const unsigned c8 = eq8(w, 0x2c2c2c2cu) & vm;
                 const unsigned n8 = eq8(w, 0x0a0a0a0au) & vm;
-                const unsigned pb = __ballot_sync(0xffffffffu, __popc(q8) & 1);
-                const unsigned st = (inside ^ __popc(pb & lt)) & 1;
                 unsigned ins = q8;
                 ins ^= ins << 1; ins ^= ins << 2; ins ^= ins << 4;
                 ins = (ins << 1) & 0xff;
-                if (st) ins ^= 0xff;
-                const unsigned end8 = n8 & ~ins;
-                const unsigned eb = __ballot_sync(0xffffffffu, end8 != 0);
-                unsigned keep = 0xff;
-                if (eb) {
-                    const int end_lane = __ffs(eb) - 1;
-                    const unsigned e_first = __shfl_sync(0xffffffffu, end8, end_lane);
-                    const int ebit = __ffs(e_first) - 1;
-                    row_end = abase + 8 * end_lane + ebit;
-                    keep = lane < end_lane ? 0xffu : (lane == end_lane ? ((1u << ebit) - 1) : 0u);
-                }
+                if (inside) ins ^= 0xff;
+                const unsigned end8 = n8 & ~ins & 0xff;
+                const unsigned keep = end8 ? ((end8 & (0u - end8)) - 1) : 0xffu;  // bytes before the record end
                 unsigned oc = c8 & ~ins & keep;
-                const unsigned cnt = __popc(oc);
-                unsigned incl = cnt;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
-                    if (lane >= o) incl += up;
-                }
-                unsigned fi = ncomma + incl - cnt;
                 while (oc) {
                     const int b = __ffs(oc) - 1;
                     oc &= oc - 1;
-                    const uint32_t pos = (uint32_t)(wpos + b - gbase);
-                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fe[warp][s_slot_of_field[fi]][rr] = pos;
-                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0) s_fs[warp][s_slot_of_field[fi + 1]][rr] = pos + 1;
+                    const uint32_t at = (uint32_t)(pos + b - gbase);
+                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fe[warp][s_slot_of_field[fi]][lane] = at;
+                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0) s_fs[warp][s_slot_of_field[fi + 1]][lane] = at + 1;
                     ++fi;
                 }
-                ncomma += __shfl_sync(0xffffffffu, incl, 31);
-                inside = (inside ^ __popc(pb)) & 1;
-                if (eb) break;
-                abase += 256;
-                if (abase >= p.n) { row_end = p.n; break; }
+                if (end8) {
+                    row_end = pos + __ffs(end8) - 1;
+                    break;
+                }
+                inside ^= __popc(q8) & 1;
+                pos += 8;
             }
-            if (lane == 0) s_rend[warp][rr] = (uint32_t)(row_end - gbase);
+            s_rend[warp][lane] = (uint32_t)(row_end - gbase);
         }
         __syncwarp();
         // ---------------------------------------------------------------- phase B: lane = row
         const int64_t row = p.first_row + r0 + lane;
         const uint32_t rend = lane < in_group ? s_rend[warp][lane] : 0;
+        (void)lt;
         for (int s = 0; s < p.ncols; ++s) {
             bool ok = false;
             uint64_t bits = 0;
