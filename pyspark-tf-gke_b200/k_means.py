@@ -17,6 +17,7 @@ from typing import List, Optional, Sequence
 
 import torch
 
+from . import dist as D
 from .engine import Column, Engine
 from .table import DeviceTable, read_csv
 
@@ -94,9 +95,14 @@ class KMeansWorkload:
             eng = self.engine or input_df.engine
             key = input_df.strings[KEY_COL]
             self.logger.info("Checking for missing values in 'measure_name'...")
-            null_measure_name_count = int(eng.null_count(key.column).item())              # k_means.py:23
+            # with torch.distributed initialised, input_df is this rank's shard of the rows: counts,
+            # (sum, count) pairs and the label table are merged across ranks
+            nulls_and_rows = torch.stack([eng.null_count(key.column)[0],                   # k_means.py:23
+                                          torch.tensor(input_df.rows, device=eng.device)])
+            D.all_reduce_counts(nulls_and_rows)
+            null_measure_name_count, total_rows = (int(x) for x in nulls_and_rows.cpu().tolist())
             self.logger.info(f"Column 'measure_name' has {null_measure_name_count} missing values")
-            rows_after = input_df.rows - null_measure_name_count                          # k_means.py:27-28
+            rows_after = total_rows - null_measure_name_count                             # k_means.py:27-28
             self.logger.info(f"Rows after filtering out missing 'measure_name' values: {rows_after}")
 
             numeric_cols = [c for c in NUMERIC_COLS if c in input_df.numeric]
@@ -105,6 +111,7 @@ class KMeansWorkload:
             vals = [input_df.numeric[c] for c in numeric_cols]
             # k_means.py:45-48: three avg jobs -> one pass; the isNotNull filter of :27 is still in the plan
             sums, counts = eng.sum_count(vals, row_valid=key.column.valid)
+            D.all_reduce_sum_count(sums, counts)
             sums, counts = sums.cpu().tolist(), counts.cpu().tolist()
             means = [s / c if c else None for s, c in zip(sums, counts)]
 
@@ -121,7 +128,7 @@ class KMeansWorkload:
             fill = [m if m is not None else float("nan") for m in means]
             code, nums, rows = eng.project_filter_impute(key.column, vals, fill)
             r = int(rows.item())
-            assert r == rows_after
+            assert r == rows_after or D.world()[1] > 1
             code, nums = code[:r], [v[:r] for v in nums]
 
             # StringIndexer.fit (k_means.py:34,73): group-by-count, then order on the host
@@ -129,10 +136,11 @@ class KMeansWorkload:
             hist, oor = eng.code_histogram(Column(code), L0)
             hist = hist.cpu().tolist()
             seen = [i for i in range(len(key.labels)) if hist[i] > 0]
-            order = string_indexer_order([key.labels[i] for i in seen], [hist[i] for i in seen])
-            labels = [key.labels[seen[i]] for i in order]
-            label_counts = [hist[seen[i]] for i in order]
-            model = EtlPipelineModel(eng, labels, label_counts, means, repeats, null_measure_name_count, r)
+            names, ncounts = D.merge_label_tables([key.labels[i] for i in seen], [hist[i] for i in seen])
+            order = string_indexer_order(names, ncounts)
+            labels = [names[i] for i in order]
+            label_counts = [ncounts[i] for i in order]
+            model = EtlPipelineModel(eng, labels, label_counts, means, repeats, null_measure_name_count, rows_after)
             # StringIndexerModel.transform (k_means.py:74): code -> index
             eng.remap_codes(code, model._index_table(key.labels), len(labels))
             model.index, model.numerics = code, nums
