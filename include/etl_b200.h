@@ -305,6 +305,26 @@ ETL_API int etl_hash_partition(etl_handle* h, const int64_t* keys, int64_t key_s
                        int64_t val_stride, int64_t n, int32_t ranks, int32_t buckets, int64_t* d_part_counts,
                        int64_t* d_part_base, int64_t* out_records, void* stream);
 
+/* The exchange itself, fused into the partition: instead of building a send
+ * buffer for a separate all-to-all, the scatter pass writes every record
+ * straight into its destination rank's receive buffer over NVLink - peer memory
+ * mapped into this process (CUDA IPC / torch symmetric memory).  Protocol:
+ *   1. etl_hash_partition_count -> this rank's per-destination counts;
+ *   2. the caller all-gathers the counts (tiny) and derives, for every
+ *      destination d, the first record this rank owns in d's receive buffer
+ *      (sum of the lower ranks' counts for d) -> d_peer_offset[ranks] on the device;
+ *   3. etl_hash_partition_scatter_peers: peer_records[d] (host array of device
+ *      pointers) = rank d's receive buffer as mapped here (the local buffer for d
+ *      == this rank); record i of destination d lands at peer_records[d] + 2 *
+ *      (d_peer_offset[d] + position);
+ *   4. a cross-rank barrier after the kernel, then every rank merges what landed.
+ * No reference counterpart below the Spark shuffle. */
+ETL_API int etl_hash_partition_count(etl_handle* h, const int64_t* keys, int64_t key_stride, int64_t n, int32_t ranks,
+                             int32_t buckets, int64_t* d_part_counts, void* stream);
+ETL_API int etl_hash_partition_scatter_peers(etl_handle* h, const int64_t* keys, int64_t key_stride, const double* vals,
+                                     int64_t val_stride, int64_t n, int32_t ranks, int64_t* const* peer_records,
+                                     const int64_t* d_peer_offset, void* stream);
+
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 
 /* Spark ML Bucketizer(handleInvalid="keep"): out[i] = b with splits[b] <= x <

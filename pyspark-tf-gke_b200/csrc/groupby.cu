@@ -311,19 +311,18 @@ __global__ void __launch_bounds__(GB_THREADS) groupby_dense_kernel(const GroupBy
     }
 }
 
+// The table as a flat array of 16-byte vectors (every entry is an even number of words): vector v
+// holds words 2v, 2v + 1 of entry v / (stride / 2) - fully coalesced stores.
 __global__ void __launch_bounds__(256) groupby_init_kernel(uint64_t* table, int64_t entries, int32_t stride,
                                                            int32_t ncols, int32_t minmax) {
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < entries; e += (int64_t)gridDim.x * blockDim.x) {
-        uint64_t* w = table + e * stride;
-        if (stride == 4) {  // single value column: one 32-byte entry, two 16-byte stores
-            *reinterpret_cast<ulonglong2*>(w) = make_ulonglong2(GB_EMPTY, 0ull);
-            *reinterpret_cast<ulonglong2*>(w + 2) = make_ulonglong2(0ull, 0ull);
-            continue;
-        }
-        w[0] = GB_EMPTY;
-        for (int f = 1; f < 2 + 2 * ncols; ++f) w[f] = 0;
-        if (minmax)
-            for (int c = 0; c < ncols; ++c) { w[2 + 2 * ncols + 2 * c] = ~0ull; w[3 + 2 * ncols + 2 * c] = 0ull; }
+    const int vpe = stride / 2;  // vectors per entry
+    const int64_t total = entries * vpe;
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < total; v += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(v % vpe) * 2;  // first field of this vector
+        ulonglong2 w = make_ulonglong2(0ull, 0ull);
+        if (f == 0) w.x = GB_EMPTY;                                  // {key, rows}
+        else if (minmax && f >= 2 + 2 * ncols) { w.x = ~0ull; w.y = 0ull; }  // {min, max} in sortable form
+        reinterpret_cast<ulonglong2*>(table)[v] = w;
     }
 }
 
@@ -389,7 +388,15 @@ __global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int
     if (threadIdx.x < parts && s_cnt[threadIdx.x]) atomicAdd(counts + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
 }
 
-// exclusive scan of the <= 64 destination counts
+// Where destination d's records go: base[d] + 2 * (offset[d] + running position).  For a local
+// partition every base is the one output buffer and offset[] its exclusive scan; for the fused
+// exchange base[d] is rank d's receive buffer mapped into this GPU's address space (NVLink peer
+// memory) and offset[d] the first record this rank owns there.
+struct PartDest {
+    int64_t* base[PART_MAX];
+};
+
+// exclusive scan of the destination counts
 __global__ void partition_scan_kernel(const int64_t* counts, int64_t* base, int parts) {
     int64_t run = 0;
     for (int d = 0; d < parts; ++d) { base[d] = run; run += counts[d]; }
@@ -400,7 +407,7 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
                                                                          const double* __restrict__ vals,
                                                                          int64_t val_stride, int64_t n, int ranks,
                                                                          int buckets, const int64_t* __restrict__ part_base,
-                                                                         unsigned long long* cursor, int64_t* out_records) {
+                                                                         unsigned long long* cursor, const PartDest dst) {
     const int parts = ranks * buckets;
     __shared__ unsigned int s_cnt[PART_MAX], s_off[PART_MAX];
     __shared__ unsigned long long s_gbase[PART_MAX];
@@ -454,7 +461,7 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
             longlong2 rec;
             rec.x = s_key[i];
             rec.y = __double_as_longlong(s_val[i]);
-            *reinterpret_cast<longlong2*>(out_records + 2 * g) = rec;
+            *reinterpret_cast<longlong2*>(dst.base[d] + 2 * g) = rec;
         }
     }
 }
@@ -480,7 +487,7 @@ extern "C" int etl_groupby_init(etl_handle* hh, uint64_t* table, int64_t capacit
     Handle* h = reinterpret_cast<Handle*>(hh);
     ETL_CUDA(cudaSetDevice(h->device));
     ETL_REQUIRE(etl::aligned16(table), "groupby_init: table must be 16-byte aligned");
-    int64_t blocks = (capacity + 1 + 255) / 256;
+    int64_t blocks = ((capacity + 1) * (gb_stride(ncols, minmax) / 2) + 255) / 256;
     if (blocks > (int64_t)h->sm_count * 16) blocks = (int64_t)h->sm_count * 16;
     etl::groupby_init_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(table, capacity + 1,
                                                                                              gb_stride(ncols, minmax),
@@ -607,8 +614,60 @@ extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, int64_t k
     ETL_CUDA(cudaGetLastError());
     const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
     int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
+    etl::PartDest dst;
+    for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = out_records;
     etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(
-        keys, key_stride, vals, val_stride, n, ranks, buckets, d_part_base, cursor, out_records);
+        keys, key_stride, vals, val_stride, n, ranks, buckets, d_part_base, cursor, dst);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_hash_partition_count(etl_handle* hh, const int64_t* keys, int64_t key_stride, int64_t n, int32_t ranks,
+                                        int32_t buckets, int64_t* d_part_counts, void* stream_) {
+    ETL_REQUIRE(hh && d_part_counts, "hash_partition_count: NULL argument");
+    ETL_REQUIRE(ranks >= 1 && buckets >= 1 && (int64_t)ranks * buckets <= etl::PART_MAX,
+                "hash_partition_count: ranks=%d x buckets=%d must be in 1..%d", ranks, buckets, etl::PART_MAX);
+    ETL_REQUIRE(n >= 0 && key_stride >= 1 && (n == 0 || keys), "hash_partition_count: bad n / stride / keys");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    ETL_CUDA(cudaMemsetAsync(d_part_counts, 0, sizeof(int64_t) * ranks * buckets, stream));
+    if (n == 0) return ETL_OK;
+    int64_t blocks = (n + etl::PART_THREADS * 8 - 1) / (etl::PART_THREADS * 8);
+    if (blocks > (int64_t)h->sm_count * 8) blocks = (int64_t)h->sm_count * 8;
+    etl::partition_count_kernel<<<(unsigned)blocks, etl::PART_THREADS, 0, stream>>>(
+        keys, key_stride, n, ranks, buckets, reinterpret_cast<unsigned long long*>(d_part_counts));
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_hash_partition_scatter_peers(etl_handle* hh, const int64_t* keys, int64_t key_stride,
+                                                const double* vals, int64_t val_stride, int64_t n, int32_t ranks,
+                                                int64_t* const* peer_records, const int64_t* d_peer_offset,
+                                                void* stream_) {
+    ETL_REQUIRE(hh && peer_records && d_peer_offset, "hash_partition_scatter_peers: NULL argument");
+    ETL_REQUIRE(ranks >= 1 && ranks <= etl::PART_MAX, "hash_partition_scatter_peers: ranks=%d not in 1..%d", ranks,
+                etl::PART_MAX);
+    ETL_REQUIRE(n >= 0 && key_stride >= 1 && val_stride >= 1, "hash_partition_scatter_peers: bad n / stride");
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(keys && vals, "hash_partition_scatter_peers: keys / vals is NULL");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    etl::PartDest dst;
+    for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = nullptr;
+    for (int d = 0; d < ranks; ++d) {
+        ETL_REQUIRE(peer_records[d] && etl::aligned16(peer_records[d]), "hash_partition_scatter_peers: peer buffer %d NULL or misaligned", d);
+        dst.base[d] = peer_records[d];
+    }
+    ETL_CUDA(cudaSetDevice(h->device));
+    int rc = etl::arena_reserve(h, sizeof(unsigned long long) * etl::PART_MAX);
+    if (rc != ETL_OK) return rc;
+    unsigned long long* cursor = static_cast<unsigned long long*>(h->scratch);
+    ETL_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * etl::PART_MAX, stream));
+    const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
+    int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
+    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(
+        keys, key_stride, vals, val_stride, n, ranks, 1, d_peer_offset, cursor, dst);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

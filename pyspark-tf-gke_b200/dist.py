@@ -68,6 +68,47 @@ def exchange_records(records: torch.Tensor, send_counts: torch.Tensor, group=Non
     return out
 
 
+class PeerExchange:
+    """The shuffle exchange as ONE kernel over NVLink peer memory: every rank owns
+    a receive buffer in symmetric memory (mapped into all peers), and the
+    partition's scatter pass stores each {key, value} record straight into its
+    destination rank's buffer - no send buffer, no separate all-to-all.
+
+    Per exchange: a count pass, one all-gather of world x world counts (so every
+    rank knows where its runs start in every receive buffer and how much it will
+    receive), the fused scatter kernel, and a symmetric-memory barrier before the
+    merge reads.  A leading barrier keeps a fast rank from overwriting a buffer a
+    slow rank is still merging."""
+
+    def __init__(self, eng, capacity_records: int, group=None):
+        import torch.distributed._symmetric_memory as symm
+
+        self.eng = eng
+        self.group = group or dist.group.WORLD
+        self.rank, self.size = dist.get_rank(self.group), dist.get_world_size(self.group)
+        self.capacity = int(capacity_records)
+        self.buf = symm.empty((self.capacity, 2), dtype=torch.int64, device=eng.device)
+        self.handle = symm.rendezvous(self.buf, self.group.group_name)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+
+    def exchange(self, keys: torch.Tensor, vals: torch.Tensor):
+        """-> (records int64[m, 2] view of this rank's receive buffer, m)."""
+        eng, size, rank = self.eng, self.size, self.rank
+        counts = eng.hash_partition_count(keys, size)
+        matrix = torch.empty((size, size), dtype=torch.int64, device=eng.device)   # [source, destination]
+        dist.all_gather_into_tensor(matrix.view(-1), counts, group=self.group)
+        offsets = matrix[:rank].sum(dim=0) if rank else torch.zeros(size, dtype=torch.int64, device=eng.device)
+        incoming = matrix.sum(dim=0)
+        inc = incoming.cpu().tolist()
+        if max(inc) > self.capacity:
+            raise RuntimeError(f"PeerExchange: a rank would receive {max(inc)} records, buffer holds {self.capacity}")
+        self.handle.barrier()            # everyone is done reading the previous exchange's records
+        eng.hash_partition_scatter_peers(keys, vals, self.peer_ptrs, offsets.contiguous())
+        self.handle.barrier()            # every peer's stores into this buffer have landed
+        m = int(inc[rank])
+        return self.buf[:m], m
+
+
 def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_bytes: int = 32 << 20) -> int:
     """Buckets per rank so that the table slice being updated (capacity / buckets
     entries) stays well inside the 126 MB L2; ranks * buckets <= 256."""
@@ -78,35 +119,48 @@ def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_
 
 
 def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
-                        buckets: Optional[int] = None, group=None):
+                        buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None):
     """Config 4: hash-partition -> all-to-all -> local final merge.
 
-    One partition pass groups the rows by (destination rank, table bucket); the
-    all-to-all moves each rank's range; the receiver then merges bucket by bucket
-    (all sources' runs of bucket 0, then bucket 1, ...), so the 1/buckets slice of
-    the aggregation table being updated stays resident in L2 instead of taking a
-    DRAM round trip per row.  After the exchange every key lives on exactly one
-    rank, so no second exchange is needed.  Returns the rank-local GroupTable."""
+    Sender: one partition pass groups the rows by destination rank (few
+    destinations = long contiguous runs).  The all-to-all moves each rank's range.
+    Receiver: a second partition pass groups what arrived by table bucket (the
+    bucket comes from the same hash word as a key's home slot), then the buckets
+    are merged one after another, so the 1/buckets slice of the aggregation table
+    being updated stays resident in L2 instead of taking a DRAM round trip per
+    row.  After the exchange every key lives on exactly one rank, so no second
+    exchange is needed.  With `peer` (a PeerExchange) partition and exchange are
+    one kernel writing over NVLink into the receivers' buffers; without it the
+    send buffer goes through NCCL's all-to-all.  `mark(name)` is called at the
+    phase boundaries (for timing).  Returns the rank-local GroupTable."""
     rank, size = world()
+    mark = mark or (lambda name: None)
     gt = eng.groupby_new(capacity, 1, minmax=False)
-    B = choose_buckets(capacity, size) if buckets is None else buckets
-    if size == 1 and B == 1:
-        eng.groupby_accumulate(gt, keys, None, [vals], groups_hint=groups_hint)
-        return gt
-    records, counts, _ = eng.hash_partition(keys, vals, size, B)
-    matrix = counts.view(size, B)
-    if size == 1:
-        received, recv_matrix = records, matrix.cpu()
+    B = choose_buckets(capacity, 1) if buckets is None else buckets
+    mark("init")
+    if size > 1:
+        if peer is not None:
+            mark("partition")
+            received, _ = peer.exchange(keys, vals)
+        else:
+            records, counts, _ = eng.hash_partition(keys, vals, size, 1)
+            mark("partition")
+            received = exchange_records(records, counts, group=group)
+            del records
+        mark("exchange")
+        flat = received.view(-1)
+        rk, rv, m, stride = flat, flat[1:].view(torch.float64), received.shape[0], 2
     else:
-        recv_matrix = torch.empty_like(matrix)
-        dist.all_to_all_single(recv_matrix.view(-1), matrix.contiguous().view(-1), group=group)
-        received = exchange_records(records, matrix.sum(dim=1), group=group)
-        recv_matrix = recv_matrix.cpu()
-    # run of (source s, bucket b) inside `received`: sources are concatenated, buckets ascend within a source
-    lengths = recv_matrix.reshape(-1)
-    starts = torch.cumsum(lengths, 0) - lengths
-    starts, lengths = starts.view(size, B).tolist(), lengths.view(size, B).tolist()
-    for b in range(B):
-        for s in range(size):
-            eng.groupby_accumulate_records(gt, received, starts[s][b], starts[s][b] + lengths[s][b], groups_hint)
+        rk, rv, m, stride = keys, vals, keys.shape[0], 1
+        mark("partition")
+        mark("exchange")
+    if B == 1 or m == 0:
+        if m:
+            eng.groupby_accumulate(gt, rk, None, [rv], groups_hint=groups_hint, n=m, key_stride=stride, val_strides=[stride])
+    else:
+        by_bucket, counts, base = eng.hash_partition(rk, rv, 1, B, n=m, key_stride=stride, val_stride=stride)
+        starts, lengths = base.cpu().tolist(), counts.cpu().tolist()
+        for b in range(B):
+            eng.groupby_accumulate_records(gt, by_bucket, starts[b], starts[b] + lengths[b], groups_hint)
+    mark("merge")
     return gt

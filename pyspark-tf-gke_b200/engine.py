@@ -384,6 +384,27 @@ class Engine:
         self.launches += 3 if n else 0
         return rec[:n], counts, base
 
+    def hash_partition_count(self, keys: torch.Tensor, ranks: int, buckets: int = 1, n: Optional[int] = None,
+                             key_stride: int = 1) -> torch.Tensor:
+        n = keys.shape[0] if n is None else n
+        counts = self.empty(ranks * buckets, torch.int64)
+        _lib.check(self.lib.etl_hash_partition_count(self._h, _ptr(keys), key_stride, n, ranks, buckets, counts.data_ptr(),
+                                                     self._stream()))
+        self.launches += 1 if n else 0
+        return counts
+
+    def hash_partition_scatter_peers(self, keys: torch.Tensor, vals: torch.Tensor, peer_ptrs: Sequence[int],
+                                     peer_offset: torch.Tensor, n: Optional[int] = None, key_stride: int = 1,
+                                     val_stride: int = 1) -> None:
+        """Partition + exchange in one kernel: records go straight into the peers'
+        receive buffers (peer_ptrs[d] = rank d's buffer mapped into this process)."""
+        n = keys.shape[0] if n is None else n
+        ranks = len(peer_ptrs)
+        P = C.c_void_p * ranks
+        _lib.check(self.lib.etl_hash_partition_scatter_peers(self._h, _ptr(keys), key_stride, _ptr(vals), val_stride, n,
+                                                             ranks, P(*peer_ptrs), peer_offset.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+
     def groupby_accumulate_records(self, gt: "GroupTable", records: torch.Tensor, lo: int, hi: int,
                                    groups_hint: int = 1 << 30) -> None:
         """Rows [lo, hi) of a {key, value} record buffer into a 1-column table."""

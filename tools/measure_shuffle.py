@@ -38,6 +38,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--buckets", type=int, default=-1, help="table buckets per rank (-1 = choose from the table size)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="peer = partition fused with NVLink peer stores; nccl = send buffer + all_to_all_single")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -69,46 +71,23 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    phases = {"partition": [], "exchange": [], "merge": [], "total": []}
+    phases = {"init": [], "partition": [], "exchange": [], "merge": [], "total": []}
     gt = None
-    sent = 0
+    sent = n - n // world if world > 1 else 0  # expected rows leaving this GPU (uniform hash)
+    B = D.choose_buckets(cap, 1) if args.buckets < 0 else args.buckets
+    peer = D.PeerExchange(eng, int(n * 1.05) + (1 << 20)) if (world > 1 and args.exchange == "peer") else None
     for it in range(args.warmup + args.steps):
         gt = None
-        torch.cuda.empty_cache()
         barrier()
-        t0 = ev()
-        B = D.choose_buckets(cap, world) if args.buckets < 0 else args.buckets
-        gt = eng.groupby_new(cap, 1)
-        if world == 1 and B == 1:
-            t1 = t2 = ev()
-            eng.groupby_accumulate(gt, key, None, [val], groups_hint=args.groups)
-        else:
-            rec, counts, _ = eng.hash_partition(key, val, world, B)
-            matrix = counts.view(world, B)
-            t1 = ev()
-            if world > 1:
-                recv_matrix = torch.empty_like(matrix)
-                dist.all_to_all_single(recv_matrix.view(-1), matrix.contiguous().view(-1))
-                got = D.exchange_records(rec, matrix.sum(dim=1))
-                sent = int(matrix.sum().item()) - int(matrix[rank].sum().item())
-                recv_matrix = recv_matrix.cpu()
-            else:
-                got, recv_matrix = rec, matrix.cpu()
-            t2 = ev()
-            lengths = recv_matrix.reshape(-1)
-            starts = (torch.cumsum(lengths, 0) - lengths).view(world, B).tolist()
-            lengths = lengths.view(world, B).tolist()
-            for b in range(B):
-                for s_ in range(world):
-                    eng.groupby_accumulate_records(gt, got, starts[s_][b], starts[s_][b] + lengths[s_][b], args.groups)
-            del rec, got
-        t3 = ev()
+        marks = {"start": ev()}
+        gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer,
+                                   mark=lambda name: marks.__setitem__(name, ev()))
         torch.cuda.synchronize()
         if it >= args.warmup:
-            phases["partition"].append(max_ms(t0, t1))
-            phases["exchange"].append(max_ms(t1, t2))
-            phases["merge"].append(max_ms(t2, t3))
-            phases["total"].append(max_ms(t0, t3))
+            order = ["start", "init", "partition", "exchange", "merge"]
+            for a, b in zip(order[:-1], order[1:]):
+                phases[b].append(max_ms(marks[a], marks[b]))
+            phases["total"].append(max_ms(marks["start"], marks["merge"]))
     # ---- checks
     res = eng.groupby_result(gt, max_groups=cap)
     tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
@@ -126,7 +105,7 @@ def main():
         line = {"workload": "config4 shuffle+aggregate", "n_gpus": world, "rows_total": n * world, "groups": args.groups,
                 "distinct_keys_found": int(tot[1].item()), "rows_conserved": ok_rows, "sum_matches_column_sum": ok_sum,
                 "ms": mean, "rows_per_s": n * world / (mean["total"] * 1e-3),
-                "buckets_per_rank": B, "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
+                "buckets_per_rank": B, "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
                 "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
                 "steps": args.steps}
         print(json.dumps(line), flush=True)
