@@ -11,7 +11,8 @@
 //      the number of record starts assuming the block begins outside / inside
 //      quotes (a record start = the byte after a newline that is outside quotes,
 //      unless the line it opens is blank - Spark and csv.reader drop blank lines)
-//   2. csv_block_scan_kernel     one CTA composes the block summaries in order
+//   2. csv_span_reduce / _scan / _apply  compose the block summaries in order
+//      (an associative operator on (parity, starts-outside, starts-inside))
 //      -> every block's true starting quote state and first row number
 //   3. csv_row_offsets_kernel    re-derives the masks with the true state and
 //      writes row_start[row] (int64 byte offsets)
@@ -153,46 +154,118 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const ui
     }
 }
 
-// Single CTA: ordered composition of the block summaries.
-__global__ void __launch_bounds__(1024) csv_block_scan_kernel(const CsvBlockSummary* __restrict__ sum, int64_t blocks,
-                                                              CsvBlockStart* __restrict__ start, int64_t* total_rows) {
-    __shared__ uint32_t s_par[1024];
-    __shared__ uint64_t s_a[1024], s_b[1024];   // rows if the thread's span begins outside / inside
-    __shared__ uint32_t s_state[1024];
-    __shared__ uint64_t s_row[1024];
-    const int tid = threadIdx.x;
-    const int64_t per = (blocks + 1023) / 1024;
-    const int64_t lo = tid * per, hi = lo + per < blocks ? lo + per : blocks;
-    uint32_t par = 0;
-    uint64_t a = 0, b = 0;
-    for (int64_t i = lo; i < hi; ++i) {
-        const CsvBlockSummary s = sum[i];
-        a += par ? s.starts_if_inside : s.starts_if_outside;
-        b += par ? s.starts_if_outside : s.starts_if_inside;
-        par ^= s.parity;
+// Ordered composition of the block summaries.  A span of blocks acts on the quote state like
+// (parity, starts-if-it-begins-outside, starts-if-it-begins-inside); spans compose associatively:
+//   (p1,a1,b1) . (p2,a2,b2) = (p1^p2, a1 + (p1 ? b2 : a2), b1 + (p1 ? a2 : b2))
+// so the scan is three small kernels: reduce 256 summaries per CTA, scan the per-CTA spans in
+// one CTA, then re-scan every CTA's 256 summaries from its known starting state.
+struct CsvSpan {
+    uint32_t par;
+    uint64_t a, b;
+};
+__device__ __forceinline__ CsvSpan span_compose(const CsvSpan& x, const CsvSpan& y) {
+    CsvSpan r;
+    r.par = x.par ^ y.par;
+    r.a = x.a + (x.par ? y.b : y.a);
+    r.b = x.b + (x.par ? y.a : y.b);
+    return r;
+}
+__device__ __forceinline__ CsvSpan span_shfl_up(const CsvSpan& x, int o) {
+    CsvSpan r;
+    r.par = __shfl_up_sync(0xffffffffu, x.par, o);
+    r.a = __shfl_up_sync(0xffffffffu, x.a, o);
+    r.b = __shfl_up_sync(0xffffffffu, x.b, o);
+    return r;
+}
+// inclusive scan over the 256 threads of a CTA (thread order = block order); returns the thread's
+// inclusive span, *total = the CTA's span
+__device__ __forceinline__ CsvSpan span_block_scan(CsvSpan v, CsvSpan* s_warp, CsvSpan* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const CsvSpan up = span_shfl_up(v, o);
+        if (lane >= o) v = span_compose(up, v);
     }
-    s_par[tid] = par; s_a[tid] = a; s_b[tid] = b;
+    if (lane == 31) s_warp[warp] = v;
     __syncthreads();
-    if (tid == 0) {
-        uint32_t st = 0;
-        uint64_t row = 0;
-        for (int t = 0; t < 1024; ++t) {
-            s_state[t] = st; s_row[t] = row;
-            row += st ? s_b[t] : s_a[t];
-            st ^= s_par[t];
+    CsvSpan pre{0, 0, 0}, all{0, 0, 0};
+    for (int w = 0; w < CSV_THREADS / 32; ++w) {
+        if (w < warp) pre = span_compose(pre, s_warp[w]);
+        all = span_compose(all, s_warp[w]);
+    }
+    *total = all;
+    __syncthreads();
+    return span_compose(pre, v);
+}
+
+__global__ void __launch_bounds__(CSV_THREADS) csv_span_reduce_kernel(const CsvBlockSummary* __restrict__ sum,
+                                                                      int64_t blocks, CsvBlockSummary* __restrict__ super) {
+    __shared__ CsvSpan s_warp[CSV_THREADS / 32];
+    const int64_t i = (int64_t)blockIdx.x * CSV_THREADS + threadIdx.x;
+    CsvSpan v{0, 0, 0};
+    if (i < blocks) { v.par = sum[i].parity; v.a = sum[i].starts_if_outside; v.b = sum[i].starts_if_inside; }
+    CsvSpan total;
+    span_block_scan(v, s_warp, &total);
+    if (threadIdx.x == 0) {
+        CsvBlockSummary r;
+        r.parity = total.par; r.pad = 0; r.starts_if_outside = total.a; r.starts_if_inside = total.b; r.reserved = 0;
+        super[blockIdx.x] = r;
+    }
+}
+
+// one CTA: exclusive scan of the (few hundred to few thousand) per-CTA spans -> each CTA's start
+__global__ void __launch_bounds__(CSV_THREADS) csv_span_scan_kernel(const CsvBlockSummary* __restrict__ super, int64_t supers,
+                                                                    CsvBlockStart* __restrict__ super_start,
+                                                                    int64_t* total_rows) {
+    __shared__ CsvSpan s_warp[CSV_THREADS / 32];
+    uint32_t state = 0;   // quote state at the start of the current chunk
+    uint64_t row = 0;     // records before the current chunk
+    for (int64_t base = 0; base < supers; base += CSV_THREADS) {
+        const int64_t i = base + threadIdx.x;
+        CsvSpan v{0, 0, 0};
+        if (i < supers) { v.par = super[i].parity; v.a = super[i].starts_if_outside; v.b = super[i].starts_if_inside; }
+        CsvSpan total;
+        const CsvSpan incl = span_block_scan(v, s_warp, &total);
+        // exclusive span of thread t = inclusive span of thread t-1 (the operator has no inverse)
+        __shared__ CsvSpan s_incl[CSV_THREADS];
+        s_incl[threadIdx.x] = incl;
+        __syncthreads();
+        CsvSpan ex{0, 0, 0};
+        if (threadIdx.x > 0) ex = s_incl[threadIdx.x - 1];
+        if (i < supers) {
+            CsvBlockStart o;
+            o.inside = state ^ ex.par;
+            o.first_row = row + (state ? ex.b : ex.a);
+            o.pad = 0;
+            super_start[i] = o;
         }
-        *total_rows = (int64_t)row;
+        row += state ? total.b : total.a;
+        state ^= total.par;
+        __syncthreads();
     }
+    if (threadIdx.x == 0) *total_rows = (int64_t)row;
+}
+
+__global__ void __launch_bounds__(CSV_THREADS) csv_span_apply_kernel(const CsvBlockSummary* __restrict__ sum, int64_t blocks,
+                                                                     const CsvBlockStart* __restrict__ super_start,
+                                                                     CsvBlockStart* __restrict__ start) {
+    __shared__ CsvSpan s_warp[CSV_THREADS / 32];
+    __shared__ CsvSpan s_incl[CSV_THREADS];
+    const int64_t i = (int64_t)blockIdx.x * CSV_THREADS + threadIdx.x;
+    CsvSpan v{0, 0, 0};
+    if (i < blocks) { v.par = sum[i].parity; v.a = sum[i].starts_if_outside; v.b = sum[i].starts_if_inside; }
+    CsvSpan total;
+    s_incl[threadIdx.x] = span_block_scan(v, s_warp, &total);
     __syncthreads();
-    uint32_t st = s_state[tid];
-    uint64_t row = s_row[tid];
-    for (int64_t i = lo; i < hi; ++i) {
-        const CsvBlockSummary s = sum[i];
+    CsvSpan ex{0, 0, 0};
+    if (threadIdx.x > 0) ex = s_incl[threadIdx.x - 1];
+    const CsvBlockStart ss = super_start[blockIdx.x];
+    if (i < blocks) {
         CsvBlockStart o;
-        o.first_row = row; o.inside = st; o.pad = 0;
+        o.inside = ss.inside ^ ex.par;
+        o.first_row = ss.first_row + (ss.inside ? ex.b : ex.a);
+        o.pad = 0;
         start[i] = o;
-        row += st ? s.starts_if_inside : s.starts_if_outside;
-        st ^= s.parity;
     }
 }
 
@@ -599,13 +672,19 @@ extern "C" int etl_csv_index_rows(etl_handle* hh, const uint8_t* text, int64_t n
         return ETL_OK;
     }
     const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
-    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
+    const int64_t supers = (blocks + etl::CSV_THREADS - 1) / etl::CSV_THREADS;
+    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart)) +
+                        (size_t)supers * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
     int rc = etl::arena_reserve(h, need);
     if (rc != ETL_OK) return rc;
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
+    auto* super = reinterpret_cast<etl::CsvBlockSummary*>(start + blocks);
+    auto* super_start = reinterpret_cast<etl::CsvBlockStart*>(super + supers);
     etl::csv_block_summary_kernel<<<(unsigned)blocks, etl::CSV_THREADS, 0, stream>>>(text, nbytes, sum);
-    etl::csv_block_scan_kernel<<<1, 1024, 0, stream>>>(sum, blocks, start, d_rows);
+    etl::csv_span_reduce_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super);
+    etl::csv_span_scan_kernel<<<1, etl::CSV_THREADS, 0, stream>>>(super, supers, super_start, d_rows);
+    etl::csv_span_apply_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super_start, start);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }
