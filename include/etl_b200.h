@@ -201,6 +201,34 @@ ETL_API int etl_csv_parse_columns(etl_handle* h, const uint8_t* text, int64_t nb
 ETL_API int etl_remap_codes(etl_handle* h, int32_t* codes, int64_t n, const int32_t* table, int32_t table_size,
                     int32_t missing, void* stream);
 
+/* ---- north-star extension: Parquet page decode (no reference site) -------- */
+
+/* The reference reads CSV / JDBC only; Parquet is named by the north star.  The
+ * host parses footer and page headers (Thrift compact, a few hundred bytes per
+ * MB) and describes the work in two device tables; the row-proportional work is
+ * here.  `file` = the whole file in device memory (UNCOMPRESSED column chunks).
+ * etl_parquet_expand_streams: d_streams = nstreams records {int64 src_offset;
+ *   int32 src_bytes, bit_width; int64 out_offset; int32 max_values, exact; int64
+ *   run_offset, run_capacity} - one RLE / bit-packed hybrid stream each
+ *   (definition levels: bit_width 1; dictionary indices: width from the page);
+ *   values land in d_out[out_offset ...] (int32).  d_runs: scratch of 16-byte run
+ *   records, run_capacity >= src_bytes / 2 + 1 per stream.
+ * etl_parquet_gather_pages: d_pages = npages records {int64 row_start; int32
+ *   num_values, kind (0 f64, 1 f32, 2 i32, 3 i64 PLAIN; 4 dictionary); int64
+ *   levels_offset (-1: required column), val_offset (PLAIN: byte offset in file;
+ *   dictionary: element offset in d_indices); int32 dict_id, pad}.  Row r of a
+ *   page is null iff its definition level is 0; non-null rows take the page's
+ *   values in order.  out: double[rows] (numeric types are cast to double) or,
+ *   string_column = 1, int32[rows] codes looked up in d_dict[dict_id] (-1 where
+ *   null); valid: zeroed bitmap.  d_status (int32[3], zeroed): [0] run table
+ *   overflow, [1] stream shorter than promised, [2] dictionary index out of range. */
+ETL_API int etl_parquet_expand_streams(etl_handle* h, const uint8_t* file, const void* d_streams, int32_t nstreams,
+                               void* d_runs, int32_t* d_out, int32_t* d_status, void* stream);
+ETL_API int etl_parquet_gather_pages(etl_handle* h, const uint8_t* file, const void* d_pages, int32_t npages,
+                             const int32_t* d_levels, const int32_t* d_indices, const void* const* d_dict,
+                             const int32_t* d_dict_size, int32_t string_column, void* out, uint32_t* valid,
+                             int32_t* d_status, void* stream);
+
 /* ---- a6: StringIndexer.fit's group-by-count ------------------------------ */
 
 /* Replaces the aggregation inside StringIndexer(handleInvalid="keep").fit

@@ -415,6 +415,84 @@ class Engine:
         self.groupby_accumulate(gt, part, None, [part[1:].view(torch.float64)], groups_hint=groups_hint, n=hi - lo,
                                 key_stride=2, val_strides=[2])
 
+    # ------------------------------------------------------- Parquet (extension)
+    def parquet_decode_column(self, data: torch.Tensor, nbytes: int, rows: int, pages, kind_plain: int,
+                              string_column: bool, dicts: Sequence[torch.Tensor]) -> Column:
+        """Decode one column from the page plan of parquet.py -> Column (f64, or
+        int32 label codes for a string column) + validity."""
+        host = data  # device buffer of the file
+        raw_first = None
+        streams = []   # (src_offset, src_bytes, bit_width, out_offset, max_values, run_offset, run_capacity)
+        lvl_total = idx_total = run_total = 0
+        page_rec = []
+        widths = {}
+        # dictionary pages start their value section with a 1-byte bit width: fetch those bytes in one gather
+        dict_pages = [pg for pg in pages if pg.dict_id >= 0]
+        if dict_pages:
+            offs = torch.tensor([pg.val_offset for pg in dict_pages], dtype=torch.int64, device=self.device)
+            for pg, w in zip(dict_pages, data[offs].cpu().tolist()):
+                widths[id(pg)] = int(w)
+        lvl_streams, idx_streams = [], []
+        for pg in pages:
+            lvl_off = -1
+            if pg.def_offset >= 0:
+                lvl_off = lvl_total
+                cap = pg.def_bytes // 2 + 2
+                lvl_streams.append((pg.def_offset, pg.def_bytes, 1, lvl_off, pg.num_values, run_total, cap))
+                lvl_total += pg.num_values + 8
+                run_total += cap
+            if pg.dict_id >= 0:
+                bw = widths[id(pg)]
+                if bw > 32:
+                    raise _lib.EtlError(-4, f"parquet: dictionary index width {bw}")
+                val_off = idx_total
+                cap = (pg.val_bytes - 1) // 2 + 2
+                idx_streams.append((pg.val_offset + 1, pg.val_bytes - 1, bw, val_off, pg.num_values, run_total, cap))
+                idx_total += pg.num_values + 8
+                run_total += cap
+                page_rec.append((pg.row_start, pg.num_values, 4, lvl_off, val_off, pg.dict_id))
+            else:
+                page_rec.append((pg.row_start, pg.num_values, kind_plain, lvl_off, pg.val_offset, -1))
+        status = torch.zeros(4, dtype=torch.int32, device=self.device)
+        levels = self.empty(max(lvl_total, 1), torch.int32)
+        indices = self.empty(max(idx_total, 1), torch.int32)
+        runs = self.empty(max(run_total, 1) * 2, torch.int64)  # 16-byte records
+        sdt = np.dtype([("src", "<i8"), ("bytes", "<i4"), ("bw", "<i4"), ("out", "<i8"), ("maxv", "<i4"), ("exact", "<i4"),
+                        ("run", "<i8"), ("cap", "<i8")])
+        for group, out in ((lvl_streams, levels), (idx_streams, indices)):
+            if not group:
+                continue
+            arr = np.zeros(len(group), dtype=sdt)
+            for i, (src, nb, bw, o, mv, ro, cap) in enumerate(group):
+                arr[i] = (src, nb, bw, o, mv, 1 if out is levels else 0, ro, cap)
+            d_streams = torch.from_numpy(arr.view(np.uint8)).to(self.device)
+            _lib.check(self.lib.etl_parquet_expand_streams(self._h, data.data_ptr(), d_streams.data_ptr(), len(group),
+                                                           runs.data_ptr(), out.data_ptr(), status.data_ptr(),
+                                                           self._stream()))
+            self.launches += 1
+        pdt = np.dtype([("row", "<i8"), ("n", "<i4"), ("kind", "<i4"), ("lvl", "<i8"), ("val", "<i8"), ("dict", "<i4"),
+                        ("pad", "<i4")])
+        parr = np.zeros(len(page_rec), dtype=pdt)
+        for i, (row, n, kind, lvl, val, did) in enumerate(page_rec):
+            parr[i] = (row, n, kind, lvl, val, did, 0)
+        d_pages = torch.from_numpy(parr.view(np.uint8)).to(self.device)
+        out = self.empty(rows, torch.int32 if string_column else torch.float64)
+        valid = torch.zeros(words_for(rows), dtype=torch.int32, device=self.device)
+        nd = max(len(dicts), 1)
+        d_dict = torch.tensor([t.data_ptr() for t in dicts] or [0], dtype=torch.int64, device=self.device)
+        d_dict_size = torch.tensor([t.shape[0] for t in dicts] or [0], dtype=torch.int32, device=self.device)
+        if page_rec:
+            _lib.check(self.lib.etl_parquet_gather_pages(self._h, data.data_ptr(), d_pages.data_ptr(), len(page_rec),
+                                                         levels.data_ptr(), indices.data_ptr(), d_dict.data_ptr(),
+                                                         d_dict_size.data_ptr(), int(string_column), out.data_ptr(),
+                                                         valid.data_ptr(), status.data_ptr(), self._stream()))
+            self.launches += 1
+        st = status.cpu().tolist()
+        if st[0] or st[1] or st[2]:
+            raise _lib.EtlError(-4, f"parquet decode: run-table overflow {st[0]}, short streams {st[1]}, "
+                                    f"dictionary indices out of range {st[2]}")
+        return Column(out, valid)
+
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,
                      null_rate: float = 0.0, nan_rate: float = 0.0, with_valid: bool = True) -> Column:
