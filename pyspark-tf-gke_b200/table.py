@@ -61,15 +61,32 @@ def read_bytes(source) -> bytes:
         return fh.read()
 
 
-def upload_text(eng: Engine, raw: bytes) -> torch.Tensor:
+def _padded(n: int) -> int:
+    return (n + 127) // 64 * 64
+
+
+def upload_text(eng: Engine, raw) -> torch.Tensor:
     """File bytes -> device uint8 tensor, zero padded to a multiple of 64 (+64)
-    so the decoder's 8-byte window loads never leave the allocation."""
+    so the decoder's 8- and 16-byte window loads never leave the allocation."""
     n = len(raw)
-    padded = (n + 127) // 64 * 64
-    host = torch.zeros(padded, dtype=torch.uint8).pin_memory()
+    host = torch.zeros(_padded(n), dtype=torch.uint8).pin_memory()
     if n:
-        host[:n] = torch.frombuffer(bytearray(raw), dtype=torch.uint8)
+        host.numpy()[:n] = np.frombuffer(raw, dtype=np.uint8)
     return host.to(eng.device, non_blocking=True)
+
+
+def upload_file(eng: Engine, path: str):
+    """Local file -> (device tensor, nbytes, pinned host copy): the file is read
+    straight into pinned memory (one host copy) and sent with one async H2D."""
+    import os
+
+    n = os.path.getsize(path)
+    host = torch.zeros(_padded(n), dtype=torch.uint8).pin_memory()
+    with open(path, "rb") as fh:
+        got = fh.readinto(memoryview(host.numpy())[:n]) if n else 0
+    if got != n:
+        raise IOError(f"{path}: short read ({got} of {n} bytes)")
+    return host.to(eng.device, non_blocking=True), n, host
 
 
 def _dictionary_labels(text: torch.Tensor, hash_tab: torch.Tensor, rep_tab: torch.Tensor):
@@ -99,16 +116,21 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
     passes cost ~1 ms per GB) and decodes only its contiguous share of the records,
     so quoted newlines need no cross-rank protocol.  device_text: the file already
     on this GPU (as returned by upload_text), to keep the copy out of a timed region."""
-    raw = read_bytes(source)
-    n = len(raw)
-    text = upload_text(eng, raw) if device_text is None else device_text
+    host = None
+    if isinstance(source, str) and not source.startswith(("http://", "https://")) and device_text is None:
+        text, n, host = upload_file(eng, source)          # straight into pinned memory
+    else:
+        raw = read_bytes(source)
+        n = len(raw)
+        text = upload_text(eng, raw) if device_text is None else device_text
     rows_total = int(eng.csv_index_rows(text, n).item())
     if rows_total == 0:
         return DeviceTable(eng, 0)
     row_start = eng.csv_row_offsets(text, n, rows_total)
     # header line -> field positions (DictReader: a repeated name keeps its last position)
     hdr_end = int(row_start[1].item()) if rows_total > 1 else n
-    header = next(csv.reader(io.StringIO(raw[:hdr_end].decode("utf-8"), newline="")))
+    hdr_bytes = host.numpy()[:hdr_end].tobytes() if host is not None else bytes(raw[:hdr_end])
+    header = next(csv.reader(io.StringIO(hdr_bytes.decode("utf-8"), newline="")))
     pos = {name: j for j, name in enumerate(header)}
     rows = rows_total - 1
     first = 1

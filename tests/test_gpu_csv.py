@@ -272,3 +272,28 @@ def test_nan_to_null_then_pack(eng):
     keep = ~np.isnan(nums[1])
     assert int(rows.item()) == int(keep.sum())
     assert X[:int(rows.item())].cpu().numpy().tobytes() == np.stack([v[keep] for v in nums], axis=1).astype(np.float32).tobytes()
+
+
+def test_read_csv_from_a_path_and_from_host_columns(eng, tmp_path):
+    text = health_text("workloads")
+    path = tmp_path / "health.csv"
+    path.write_text(text)
+    cols = (["value", "lower_ci", "upper_ci"], ["measure_name"])
+    a, _ = pkg.KMeansWorkload(eng).k_means(pkg.read_csv(eng, str(path), *cols))      # pinned-file path
+    b, _ = pkg.KMeansWorkload(eng).k_means(pkg.read_csv(eng, text.encode(), *cols))  # bytes path
+    assert a.labels == b.labels and a.means == b.means
+    assert a.features().cpu().numpy().tobytes() == b.features().cpu().numpy().tobytes()
+    X1, y1, v1 = pkg.load_csv(str(path))
+    X2, y2, v2 = pkg.load_csv(text.encode())
+    assert X1.tobytes() == X2.tobytes() and y1.tobytes() == y2.tobytes() and v1 == v2
+    # the JDBC shape (google_health_SQL.py:26-37): already-decoded host columns, FLOAT numerics with SQL NULLs
+    header, c = O.read_csv_columns(text)
+    nums = {}
+    for name in cols[0]:
+        v, vv = O.to_numeric_column(c[name])
+        nums[name] = np.ma.masked_array(v.astype(np.float32), mask=~vv)
+    t = pkg.table.from_host_columns(eng, c["measure_name"], nums)
+    m, _ = pkg.KMeansWorkload(eng).k_means(t)
+    assert m.labels == a.labels and m.label_counts == a.label_counts
+    assert m.means == a.means  # every value is an integer < 2^24: exact in float32 too
+    assert m.features().cpu().numpy().tobytes() == a.features().cpu().numpy().tobytes()

@@ -1,0 +1,63 @@
+"""BASELINE.json configs at (or near) full size: size-independent properties
+instead of an oracle diff - conservation of rows and of the grand total,
+sortedness / uniqueness of keys, idempotence - as the oracle cannot finish these
+sizes in seconds."""
+import pytest
+import torch
+
+import pyspark_tf_gke_b200 as pkg
+import pyspark_tf_gke_b200.dist as D
+import pyspark_tf_gke_b200.synth as S
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = pkg.Engine(0)
+    yield e
+    e.close()
+
+
+def test_config3_groupby_100m_rows_1k_groups(eng):
+    cfg = S.CONFIG3
+    n, G = cfg["rows"], cfg["groups"]
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY32, n, modulus=G, with_valid=False)
+    cols = [eng.synth_column(cfg["seed"], 1 + c, S.KIND_EXACT, n, null_rate=cfg["val_null"][c]) for c in range(3)]
+    results = []
+    for key_range in (G, 0):  # direct-indexed kernel, then the hashed shared-memory kernel
+        gt = eng.groupby_new(4096, 3)
+        eng.groupby_accumulate(gt, key.data, None, [c.data for c in cols], [c.valid for c in cols], groups_hint=G,
+                               key_range=key_range)
+        results.append(eng.groupby_result(gt))
+    sums, counts = eng.sum_count(cols)
+    for res in results:
+        assert res["keys"].tolist() == list(range(G))           # every key present, once, sorted
+        assert int(res["rows"].sum()) == n and res["null_group_rows"] == 0
+        for c in range(3):
+            assert int(res["cols"][c]["count"].sum()) == int(counts[c])
+            assert float(res["cols"][c]["sum"].sum()) == float(sums[c])   # integer-valued data: exact
+    for c in range(3):  # the two kernels agree group by group
+        assert torch.equal(results[0]["cols"][c]["count"], results[1]["cols"][c]["count"])
+        assert torch.equal(results[0]["cols"][c]["sum"], results[1]["cols"][c]["sum"])
+    assert torch.equal(results[0]["rows"], results[1]["rows"])
+
+
+def test_config4_shape_groupby_quarter_size_single_gpu(eng):
+    cfg = S.CONFIG4
+    n, G = cfg["rows"] // 4, cfg["groups"] // 4
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=G, with_valid=False).data
+    val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False).data
+    cap = 1 << 26
+    direct = eng.groupby_new(cap, 1)
+    eng.groupby_accumulate(direct, key, None, [val], groups_hint=G)
+    bucketed = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G)   # partition by bucket, merge bucket by bucket
+    a, b = eng.groupby_result(direct, max_groups=G), eng.groupby_result(bucketed, max_groups=G)
+    s, _ = eng.sum_count([pkg.Column(val)])
+    for res in (a, b):
+        k = res["keys"]
+        assert bool((k[1:] > k[:-1]).all()) and int(k[0]) >= 0 and int(k[-1]) < G   # unique, in range
+        assert int(res["rows"].sum()) == n
+        assert float(res["cols"][0]["sum"].sum()) == float(s[0])
+    assert torch.equal(a["keys"], b["keys"]) and torch.equal(a["rows"], b["rows"])
+    assert torch.equal(a["cols"][0]["sum"], b["cols"][0]["sum"])
