@@ -363,6 +363,33 @@ ETL_API int etl_hash_partition_scatter_peers(etl_handle* h, const int64_t* keys,
 ETL_API int etl_bucketize(etl_handle* h, const double* val, const uint32_t* valid, int64_t n, const double* d_splits,
                   int32_t nsplits, int32_t* out, int64_t* d_out_of_range, void* stream);
 
+/* ---- next row: KMeans on `features` ---------------- */
+
+/* Replaces the distributed passes inside KMeans().setK(25).setSeed(1)
+ * .setMaxIter(1000).fit(dataset) (k_means.py:83-87): the closest-centre search and
+ * the per-cluster sums of one Lloyd iteration (and of the k-means|| init).  The
+ * feature rows are not materialised: row i = [onehot(index[i])] * repeats ++
+ * num[0..2][i], index in [0, num_labels] (num_labels = unknown label, all-zero
+ * block).  centers: double[k][repeats * num_labels + 3].
+ * etl_kmeans_prepare: per-centre tables -> d_onehot_sum[k][num_labels + 1],
+ *   d_num[k][3], d_norm2[k].
+ * etl_kmeans_assign: squared distance |x|^2 - 2 x.c + |c|^2 (clamped at 0) to
+ *   every centre; out_cost[i] = the minimum (min-combined with d_prev_cost[i] if
+ *   given), out_cluster[i] = cluster_offset + argmin (lowest id on ties; left
+ *   untouched where the previous cost was not beaten).  Either output may be NULL.
+ * etl_kmeans_accumulate: d_count[k], d_hist[k][num_labels + 1] (rows per cluster
+ *   and label) and d_numsum[k][3]; new centre = hist / count per label (copied
+ *   into each of the `repeats` blocks) ++ numsum / count. */
+ETL_API int etl_kmeans_prepare(etl_handle* h, const double* centers, int32_t k, int32_t num_labels, int32_t repeats,
+                       double* d_onehot_sum, double* d_num, double* d_norm2, void* stream);
+ETL_API int etl_kmeans_assign(etl_handle* h, const int32_t* index, const double* const num[3], int64_t n, int32_t k,
+                      int32_t num_labels, int32_t repeats, const double* d_onehot_sum, const double* d_num,
+                      const double* d_norm2, const double* d_prev_cost, int32_t cluster_offset,
+                      int32_t* out_cluster, double* out_cost, void* stream);
+ETL_API int etl_kmeans_accumulate(etl_handle* h, const int32_t* index, const double* const num[3],
+                          const int32_t* cluster, int64_t n, int32_t k, int32_t num_labels, int64_t* d_count,
+                          int64_t* d_hist, double* d_numsum, void* stream);
+
 /* ---- synthetic tables (bench / test infrastructure) -------------------- */
 
 /* Counter-based generator, identical to pyspark_tf_gke_b200.synth on the host:

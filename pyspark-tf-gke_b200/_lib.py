@@ -82,6 +82,13 @@ _PROTOS = {
     "etl_parquet_gather_pages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p]),
+    "etl_kmeans_prepare": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]),
+    "etl_kmeans_assign": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
+    "etl_kmeans_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "etl_synth_column": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32, C.c_uint64, C.c_double,
                                    C.c_double, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
 }

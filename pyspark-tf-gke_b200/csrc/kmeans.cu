@@ -1,0 +1,219 @@
+// KMeans on the assembled `features` (k_means.py:83-87: KMeans().setK(25)
+// .setSeed(1).setMaxIter(1000).fit(dataset)) - SURVEY.md §8f rank 2, the ETL
+// stage's in-process consumer.
+//
+// The feature rows are never materialised for this: row i is
+//   [onehot(index_i)] * repeats ++ [num0_i, num1_i, num2_i]
+// so its squared distance to a centre c needs only
+//   |x|^2 - 2 * (T[c][index_i] + sum_j num_j * c[onehot + j]) + |c|^2
+// with T[c][l] = sum_rep c[rep * L + l] (0 for the unknown label).  T, the three
+// numeric coordinates and |c|^2 of every centre are prepared once per iteration
+// (kmeans_prepare_kernel) and staged in shared memory, so an assignment pass reads
+// 28 B per row and does ~6 flops per (row, centre).
+//   kmeans_assign_kernel      nearest centre + squared distance per row (optionally
+//                             min-combined with a previous cost: the k-means|| step)
+//   kmeans_accumulate_kernel  per-cluster row count, label histogram and numeric
+//                             sums -> the next centres (shared-memory partials,
+//                             native 32-bit atomics for counts, fp64 adds for sums)
+#include "common.cuh"
+
+namespace etl {
+
+constexpr int KM_THREADS = 256;
+
+struct KmPrepared {          // device arrays derived from the centres [k][D]
+    const double* onehot_sum; // [k][L + 1]: T[c][l]; column L = 0 (unknown label)
+    const double* num;        // [k][3]
+    const double* norm2;      // [k]
+};
+
+__global__ void __launch_bounds__(256) kmeans_prepare_kernel(const double* __restrict__ centers, int k, int L, int repeats,
+                                                             double* __restrict__ onehot_sum, double* __restrict__ num,
+                                                             double* __restrict__ norm2) {
+    const int D = repeats * L + 3;
+    const int c = blockIdx.x;
+    const double* row = centers + (int64_t)c * D;
+    __shared__ double s_part[256];
+    double acc = 0.0;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) acc = __dadd_rn(acc, __dmul_rn(row[d], row[d]));
+    s_part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {  // fixed tree: reproducible
+        if (threadIdx.x < o) s_part[threadIdx.x] += s_part[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) norm2[c] = s_part[0];
+    for (int l = threadIdx.x; l <= L; l += blockDim.x) {
+        double t = 0.0;
+        if (l < L)
+            for (int r = 0; r < repeats; ++r) t += row[r * L + l];
+        onehot_sum[(int64_t)c * (L + 1) + l] = t;
+    }
+    if (threadIdx.x < 3) num[c * 3 + threadIdx.x] = row[repeats * L + threadIdx.x];
+}
+
+struct KmAssignParams {
+    const int32_t* index;
+    const double* num[3];
+    int64_t n;
+    int32_t k, L, repeats;
+    KmPrepared prep;
+    const double* prev_cost;  // optional: cost[i] = min(prev_cost[i], new); the cluster is only updated when new wins
+    int32_t* out_cluster;     // optional
+    double* out_cost;         // optional
+    int32_t cluster_offset;   // added to the winning centre's id (k-means|| appends candidate batches)
+};
+
+__global__ void __launch_bounds__(KM_THREADS) kmeans_assign_kernel(const KmAssignParams p) {
+    extern __shared__ double km_smem[];
+    const int L1 = p.L + 1;
+    double* s_T = km_smem;                         // [k][L + 1]
+    double* s_num = s_T + (size_t)p.k * L1;        // [k][3]
+    double* s_norm = s_num + (size_t)p.k * 3;      // [k]
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS) s_T[i] = p.prep.onehot_sum[i];
+    for (int i = threadIdx.x; i < p.k * 3; i += KM_THREADS) s_num[i] = p.prep.num[i];
+    for (int i = threadIdx.x; i < p.k; i += KM_THREADS) s_norm[i] = p.prep.norm2[i];
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * KM_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * KM_THREADS) {
+        int32_t idx = p.index[i];
+        const bool known = idx >= 0 && idx < p.L;
+        if (!known) idx = p.L;
+        const double a = p.num[0][i], b = p.num[1][i], c = p.num[2][i];
+        // explicit _rn ops: no FMA contraction, so the CPU oracle (NumPy, same order) gets the same bits
+        const double x2 = __dadd_rn(__dadd_rn(__dadd_rn(known ? (double)p.repeats : 0.0, __dmul_rn(a, a)), __dmul_rn(b, b)),
+                                    __dmul_rn(c, c));
+        double best = 1.7976931348623157e308;
+        int best_c = 0;
+        for (int j = 0; j < p.k; ++j) {
+            const double dot = __dadd_rn(__dadd_rn(__dadd_rn(s_T[j * L1 + idx], __dmul_rn(a, s_num[j * 3])),
+                                                   __dmul_rn(b, s_num[j * 3 + 1])), __dmul_rn(c, s_num[j * 3 + 2]));
+            double d2 = __dadd_rn(__dadd_rn(x2, -__dmul_rn(2.0, dot)), s_norm[j]);
+            d2 = d2 < 0.0 ? 0.0 : d2;  // cancellation can leave a tiny negative
+            if (d2 < best) { best = d2; best_c = j; }   // ties keep the lower centre id, as Spark's findClosest does
+        }
+        bool wins = true;
+        if (p.prev_cost) {
+            const double old = p.prev_cost[i];
+            wins = best < old;
+            if (!wins) best = old;
+        }
+        if (p.out_cost) p.out_cost[i] = best;
+        if (p.out_cluster && wins) p.out_cluster[i] = best_c + p.cluster_offset;
+    }
+}
+
+struct KmAccumParams {
+    const int32_t* index;
+    const double* num[3];
+    const int32_t* cluster;
+    int64_t n;
+    int32_t k, L;
+    unsigned long long* count;  // [k]
+    unsigned long long* hist;   // [k][L + 1]
+    double* numsum;             // [k][3]
+};
+
+__global__ void __launch_bounds__(KM_THREADS) kmeans_accumulate_kernel(const KmAccumParams p) {
+    extern __shared__ double km_smem[];
+    const int L1 = p.L + 1;
+    double* s_sum = km_smem;                                             // [k][3]
+    uint32_t* s_cnt = reinterpret_cast<uint32_t*>(s_sum + (size_t)p.k * 3);  // [k]
+    uint32_t* s_hist = s_cnt + p.k;                                      // [k][L + 1]
+    for (int i = threadIdx.x; i < p.k * 3; i += KM_THREADS) s_sum[i] = 0.0;
+    for (int i = threadIdx.x; i < p.k; i += KM_THREADS) s_cnt[i] = 0;
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * KM_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * KM_THREADS) {
+        const int c = p.cluster[i];
+        if (c < 0 || c >= p.k) continue;
+        int32_t idx = p.index[i];
+        if (idx < 0 || idx >= p.L) idx = p.L;
+        atomicAdd(s_cnt + c, 1u);
+        atomicAdd(s_hist + c * L1 + idx, 1u);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) atomicAdd(s_sum + c * 3 + j, p.num[j][i]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.k; i += KM_THREADS)
+        if (s_cnt[i]) atomicAdd(p.count + i, (unsigned long long)s_cnt[i]);
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS)
+        if (s_hist[i]) atomicAdd(p.hist + i, (unsigned long long)s_hist[i]);
+    for (int i = threadIdx.x; i < p.k * 3; i += KM_THREADS)
+        if (s_sum[i] != 0.0) atomicAdd(p.numsum + i, s_sum[i]);
+}
+
+}  // namespace etl
+
+using etl::Handle;
+
+extern "C" int etl_kmeans_prepare(etl_handle* hh, const double* centers, int32_t k, int32_t num_labels, int32_t repeats,
+                                  double* d_onehot_sum, double* d_num, double* d_norm2, void* stream_) {
+    ETL_REQUIRE(hh && centers && d_onehot_sum && d_num && d_norm2, "kmeans_prepare: NULL argument");
+    ETL_REQUIRE(k >= 1 && num_labels >= 0 && repeats >= 1, "kmeans_prepare: k=%d num_labels=%d repeats=%d", k, num_labels, repeats);
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    etl::kmeans_prepare_kernel<<<(unsigned)k, 256, 0, static_cast<cudaStream_t>(stream_)>>>(centers, k, num_labels, repeats,
+                                                                                         d_onehot_sum, d_num, d_norm2);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+static size_t km_assign_smem(int k, int L) { return sizeof(double) * ((size_t)k * (L + 1) + (size_t)k * 4); }
+static size_t km_accum_smem(int k, int L) { return sizeof(double) * (size_t)k * 3 + sizeof(uint32_t) * ((size_t)k * (L + 2)); }
+
+extern "C" int etl_kmeans_assign(etl_handle* hh, const int32_t* index, const double* const num[3], int64_t n, int32_t k,
+                                 int32_t num_labels, int32_t repeats, const double* d_onehot_sum, const double* d_num,
+                                 const double* d_norm2, const double* d_prev_cost, int32_t cluster_offset,
+                                 int32_t* out_cluster, double* out_cost, void* stream_) {
+    ETL_REQUIRE(hh && num && d_onehot_sum && d_num && d_norm2, "kmeans_assign: NULL argument");
+    ETL_REQUIRE(n >= 0 && k >= 1 && num_labels >= 0 && repeats >= 1, "kmeans_assign: bad sizes");
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(index && num[0] && num[1] && num[2], "kmeans_assign: NULL column");
+    const size_t smem = km_assign_smem(k, num_labels);
+    ETL_REQUIRE(smem <= 200 * 1024, "kmeans_assign: k * (num_labels + 5) = %lld doubles exceed shared memory",
+                (long long)(smem / 8));
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    etl::KmAssignParams p{};
+    p.index = index; p.n = n; p.k = k; p.L = num_labels; p.repeats = repeats;
+    for (int j = 0; j < 3; ++j) p.num[j] = num[j];
+    p.prep.onehot_sum = d_onehot_sum; p.prep.num = d_num; p.prep.norm2 = d_norm2;
+    p.prev_cost = d_prev_cost; p.out_cluster = out_cluster; p.out_cost = out_cost; p.cluster_offset = cluster_offset;
+    ETL_CUDA(cudaFuncSetAttribute(etl::kmeans_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
+    const int per_sm = smem > 100 * 1024 ? 1 : (smem > 50 * 1024 ? 2 : 4);
+    if (blocks > (int64_t)h->sm_count * per_sm) blocks = (int64_t)h->sm_count * per_sm;
+    etl::kmeans_assign_kernel<<<(unsigned)blocks, etl::KM_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_kmeans_accumulate(etl_handle* hh, const int32_t* index, const double* const num[3],
+                                     const int32_t* cluster, int64_t n, int32_t k, int32_t num_labels, int64_t* d_count,
+                                     int64_t* d_hist, double* d_numsum, void* stream_) {
+    ETL_REQUIRE(hh && num && d_count && d_hist && d_numsum, "kmeans_accumulate: NULL argument");
+    ETL_REQUIRE(n >= 0 && k >= 1 && num_labels >= 0, "kmeans_accumulate: bad sizes");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    ETL_CUDA(cudaMemsetAsync(d_count, 0, sizeof(int64_t) * k, stream));
+    ETL_CUDA(cudaMemsetAsync(d_hist, 0, sizeof(int64_t) * k * (num_labels + 1), stream));
+    ETL_CUDA(cudaMemsetAsync(d_numsum, 0, sizeof(double) * k * 3, stream));
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(index && cluster && num[0] && num[1] && num[2], "kmeans_accumulate: NULL column");
+    const size_t smem = km_accum_smem(k, num_labels);
+    ETL_REQUIRE(smem <= 200 * 1024, "kmeans_accumulate: k * (num_labels + 2) too large for shared memory");
+    etl::KmAccumParams p{};
+    p.index = index; p.cluster = cluster; p.n = n; p.k = k; p.L = num_labels;
+    for (int j = 0; j < 3; ++j) p.num[j] = num[j];
+    p.count = reinterpret_cast<unsigned long long*>(d_count);
+    p.hist = reinterpret_cast<unsigned long long*>(d_hist);
+    p.numsum = d_numsum;
+    ETL_CUDA(cudaFuncSetAttribute(etl::kmeans_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
+    const int per_sm = smem > 100 * 1024 ? 1 : (smem > 50 * 1024 ? 2 : 4);
+    if (blocks > (int64_t)h->sm_count * per_sm) blocks = (int64_t)h->sm_count * per_sm;
+    etl::kmeans_accumulate_kernel<<<(unsigned)blocks, etl::KM_THREADS, smem, stream>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}

@@ -493,6 +493,45 @@ class Engine:
                                     f"dictionary indices out of range {st[2]}")
         return Column(out, valid)
 
+    # ------------------------------------------------- KMeans passes (8f rank 2)
+    def kmeans_prepare(self, centers: torch.Tensor, num_labels: int, repeats: int):
+        k = centers.shape[0]
+        T = torch.empty((k, num_labels + 1), dtype=torch.float64, device=self.device)
+        cn = torch.empty((k, 3), dtype=torch.float64, device=self.device)
+        n2 = self.empty(k, torch.float64)
+        _lib.check(self.lib.etl_kmeans_prepare(self._h, centers.data_ptr(), k, num_labels, repeats, T.data_ptr(),
+                                               cn.data_ptr(), n2.data_ptr(), self._stream()))
+        self.launches += 1
+        return T, cn, n2
+
+    def kmeans_assign(self, index: torch.Tensor, nums: Sequence[torch.Tensor], centers: torch.Tensor, num_labels: int,
+                      repeats: int, prev_cost: Optional[torch.Tensor] = None, cluster: Optional[torch.Tensor] = None,
+                      cluster_offset: int = 0, want_cluster: bool = True):
+        """Closest centre per row -> (cluster int32[n] or None, cost f64[n])."""
+        n, k = index.shape[0], centers.shape[0]
+        T, cn, n2 = self.kmeans_prepare(centers.contiguous(), num_labels, repeats)
+        if want_cluster and cluster is None:
+            cluster = torch.zeros(n, dtype=torch.int32, device=self.device)
+        cost = self.empty(n, torch.float64)
+        _lib.check(self.lib.etl_kmeans_assign(self._h, _ptr(index), C.byref(VP3(*[t.data_ptr() for t in nums])), n, k,
+                                              num_labels, repeats, T.data_ptr(), cn.data_ptr(), n2.data_ptr(),
+                                              _ptr(prev_cost), cluster_offset, _ptr(cluster) if want_cluster else None,
+                                              cost.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return cluster, cost
+
+    def kmeans_accumulate(self, index: torch.Tensor, nums: Sequence[torch.Tensor], cluster: torch.Tensor, k: int,
+                          num_labels: int):
+        n = index.shape[0]
+        count = self.empty(k, torch.int64)
+        hist = torch.empty((k, num_labels + 1), dtype=torch.int64, device=self.device)
+        numsum = torch.empty((k, 3), dtype=torch.float64, device=self.device)
+        _lib.check(self.lib.etl_kmeans_accumulate(self._h, _ptr(index), C.byref(VP3(*[t.data_ptr() for t in nums])),
+                                                  _ptr(cluster), n, k, num_labels, count.data_ptr(), hist.data_ptr(),
+                                                  numsum.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return count, hist, numsum
+
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,
                      null_rate: float = 0.0, nan_rate: float = 0.0, with_valid: bool = True) -> Column:

@@ -5,9 +5,10 @@ MEASURE_NAME_WEIGHT handling and error behaviour (log, then re-raise,
 k_means.py:108-110); `input_df` is a DeviceTable instead of a Spark DataFrame
 and every operation of lines 22-77 runs as a CUDA kernel through the C ABI.
 The stage ends where the reference's does: `dataset = select("features")`
-(k_means.py:77).  KMeans.fit (k_means.py:83-87) is the next component
-(SURVEY.md §8f), so `model` is None for now and the feature matrix is exposed on
-the returned pipeline model."""
+(k_means.py:77); then, as in the reference, KMeans(k=25, seed=1, maxIter=1000) is
+fitted on it (k_means.py:83-87; kmeans.py here - same algorithm, its random
+streams are not Spark's) and (pipeline_model, model) is returned.  Set
+ETL_SKIP_KMEANS=1 to stop after the ETL stage (model = None)."""
 from __future__ import annotations
 
 import logging
@@ -145,9 +146,37 @@ class KMeansWorkload:
             eng.remap_codes(code, model._index_table(key.labels), len(labels))
             model.index, model.numerics = code, nums
             model.features_dim = repeats * len(labels) + 3
-            return model, None
+            if os.environ.get("ETL_SKIP_KMEANS", "").lower() in ("1", "true", "yes", "y"):
+                return model, None
+            # K-Means Model Training (k_means.py:83-87)
+            from .kmeans import KMeans
+
+            kmeans = KMeans().setK(25).setSeed(1).setMaxIter(1000)
+            self.logger.info("Training K-Means model...")
+            kmeans_model = kmeans.fit(model)
+            return model, kmeans_model
         except Exception as e:
             self.logger.error(f"Error training K-Means model: {e}")
+            raise
+
+    def infer_single_row(self, spark=None, entry_str: str = "Able-Bodied", entry_num: int = 0):
+        """k_means.py:138-162: one hard-coded row (entry_str, n, n + 7, n + 5) through
+        the in-memory pipeline and KMeans models -> (prediction, features row)."""
+        try:
+            if not KMeansWorkload.pipeline_model or not KMeansWorkload.kmeans_model:
+                raise RuntimeError("In-memory models not available. Ensure k_means() has been executed before inference.")
+            pm, km = KMeansWorkload.pipeline_model, KMeansWorkload.kmeans_model
+            eng = pm.engine
+            L = len(pm.labels)
+            idx = pm.labels.index(entry_str) if entry_str in pm.labels else L   # handleInvalid="keep"
+            index = torch.tensor([idx], dtype=torch.int32, device=eng.device)
+            nums = [torch.tensor([float(v)], dtype=torch.float64, device=eng.device)
+                    for v in (entry_num, entry_num + 7, entry_num + 5)]
+            prediction = int(km.predict_structured(index, nums)[0].item())
+            self.logger.info(f"Inference prediction: {prediction}")
+            return prediction, pm.features(index=index, numerics=nums)
+        except Exception as e:
+            self.logger.error(f"Error during inference: {e}")
             raise
 
     @classmethod
@@ -164,6 +193,15 @@ class KMeansWorkload:
             src = source or os.environ.get("HEALTH_CSV", "health.csv")
             table = read_csv(eng, src, NUMERIC_COLS, [KEY_COL])
             cls.pipeline_model, cls.kmeans_model = instance.k_means(table)
+            instance.logger.info("Running inference on a single row to verify the model is working correctly...")
+            if os.environ.get("RUN_INFERENCE", "true").lower() in ("1", "true", "yes", "y") and cls.kmeans_model:
+                try:  # k_means.py:187-195
+                    data_strings = ["Able-Bodied", "Asthma", "Avoided Care Due to Cost", "Cancer",
+                                    "Cardiovascular Diseases", "Child Poverty", "Premature Death"]
+                    for label, num in zip(data_strings, [0, 10, 20, 30, 40, 50, 60]):
+                        instance.infer_single_row(None, entry_str=label, entry_num=num)
+                except Exception as ie:
+                    instance.logger.warning(f"Single-row inference skipped due to error: {ie}")
         except Exception as e:
             instance.logger.error(f"An error occurred: {e}")
         return instance

@@ -25,6 +25,11 @@ def eng():
     e.close()
 
 
+@pytest.fixture(autouse=True)
+def _etl_stage_only(monkeypatch):
+    monkeypatch.setenv("ETL_SKIP_KMEANS", "1")  # these tests cover the ETL stage; KMeans has its own file
+
+
 def _cases():
     with open(os.path.join(GOLDEN, "load_csv_cases.json")) as fh:
         return json.load(fh)

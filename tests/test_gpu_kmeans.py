@@ -1,0 +1,104 @@
+"""KMeans on the structured features (k_means.py:83-87): the
+CUDA passes + host driver against an independent dense NumPy restatement of the
+same algorithm with the same counter-based random numbers.  Data are integer
+valued, so per-cluster sums are exact and the two trajectories coincide; centres
+are compared to 1e-12 relative, assignments and cluster sizes exactly."""
+import numpy as np
+import pytest
+import torch
+
+import pyspark_tf_gke_b200 as pkg
+from oracle import kmeans_oracle as KO
+from pyspark_tf_gke_b200.kmeans import dense_rows
+from tests.conftest import health_text
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = pkg.Engine(0)
+    yield e
+    e.close()
+
+
+class _Dataset:  # what KMeans.fit needs from an EtlPipelineModel
+    def __init__(self, eng, index, nums, L, repeats):
+        self.engine, self.labels, self.repeats = eng, ["l%d" % i for i in range(L)], repeats
+        self.index = torch.from_numpy(index).to(eng.device)
+        self.numerics = [torch.from_numpy(v).to(eng.device) for v in nums]
+
+
+def _blobs(n, L, seed):
+    rng = np.random.default_rng(seed)
+    blob = rng.integers(0, 6, n)
+    index = ((blob * 3 + rng.integers(0, 2, n)) % (L + 1)).astype(np.int32)      # L itself = unknown label
+    centres = rng.integers(0, 2000, (6, 3)).astype(np.float64)
+    nums = [np.floor(centres[blob, j] + rng.integers(-20, 21, n)) for j in range(3)]
+    return index, nums
+
+
+def test_assign_and_accumulate_match_dense_numpy(eng):
+    n, L, repeats, k = 50_000, 12, 3, 9
+    index, nums = _blobs(n, L, 1)
+    rng = np.random.default_rng(2)
+    centers = rng.random((k, repeats * L + 3)) * np.array([1.0] * (repeats * L) + [2000.0] * 3)
+    X = dense_rows(index, nums, L, repeats)
+    d = KO.sq_dist(X, index, L, repeats, centers)
+    ds = _Dataset(eng, index, nums, L, repeats)
+    cluster, cost = eng.kmeans_assign(ds.index, ds.numerics, torch.from_numpy(centers).to(eng.device), L, repeats)
+    assert cluster.cpu().numpy().tolist() == d.argmin(axis=1).tolist()
+    assert cost.cpu().numpy().tobytes() == d.min(axis=1).tobytes()          # same operations, same bits
+    direct = ((X[:, None, :] - centers[None, :, :]) ** 2).sum(axis=2)       # and it is the Euclidean distance
+    np.testing.assert_allclose(cost.cpu().numpy(), direct.min(axis=1), rtol=1e-9, atol=1e-6)
+    count, hist, numsum = eng.kmeans_accumulate(ds.index, ds.numerics, cluster, k, L)
+    a = d.argmin(axis=1)
+    assert count.cpu().numpy().tolist() == np.bincount(a, minlength=k).tolist()
+    for c in range(k):
+        idx = np.where((index >= 0) & (index < L), index, L)[a == c]
+        assert hist[c].cpu().numpy().tolist() == np.bincount(idx, minlength=L + 1).tolist()
+        assert numsum[c].cpu().numpy().tolist() == [float(v[a == c].sum()) for v in nums]
+    # k-means|| step: min-combine with a previous cost, cluster ids offset, untouched where not beaten
+    prev = torch.from_numpy(np.where(np.arange(n) % 2 == 0, 0.0, np.inf)).to(eng.device)
+    cl = torch.full((n,), -5, dtype=torch.int32, device=eng.device)
+    cl2, cost2 = eng.kmeans_assign(ds.index, ds.numerics, torch.from_numpy(centers).to(eng.device), L, repeats,
+                                   prev_cost=prev, cluster=cl, cluster_offset=100)
+    assert (cost2.cpu().numpy()[::2] == 0).all() and (cl2.cpu().numpy()[::2] == -5).all()
+    assert (cl2.cpu().numpy()[1::2] == a[1::2] + 100).all()
+
+
+@pytest.mark.parametrize("n,L,repeats,k,seed", [(20_000, 12, 3, 6, 1), (5_000, 30, 5, 25, 1), (300, 4, 1, 3, 7)])
+def test_fit_matches_the_numpy_restatement(eng, n, L, repeats, k, seed):
+    index, nums = _blobs(n, L, seed + 10)
+    ds = _Dataset(eng, index, nums, L, repeats)
+    model = pkg.KMeans().setK(k).setSeed(seed).setMaxIter(40).fit(ds)
+    X = dense_rows(index, nums, L, repeats)
+    centers, cost, iters, sizes = KO.kmeans_fit(X, index, L, repeats, k, seed, max_iter=40)
+    assert model.centers.shape == centers.shape
+    np.testing.assert_allclose(model.centers, centers, rtol=1e-12, atol=1e-12)
+    assert model.summary.numIter == iters and model.summary.clusterSizes == sizes.tolist()
+    assert abs(model.summary.trainingCost - cost) <= 1e-9 * max(1.0, cost)
+    pred = model.predict_structured(ds.index, ds.numerics).cpu().numpy()
+    assert pred.tolist() == KO.sq_dist(X, index, L, repeats, model.centers).argmin(axis=1).tolist()
+    assert len(model.clusterCenters()) == centers.shape[0]
+
+
+def test_kmeans_workload_returns_both_models_and_infers_single_rows(eng, monkeypatch):
+    monkeypatch.delenv("ETL_SKIP_KMEANS", raising=False)
+    monkeypatch.setenv("MEASURE_NAME_WEIGHT", "5")
+    table = pkg.read_csv(eng, health_text("workloads").encode(), ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    wl = pkg.KMeansWorkload(eng)
+    pipeline_model, model = wl.k_means(table)                      # k_means.py:17,107: (pipeline_model, model)
+    assert model is not None and model.centers.shape == (25, 153)  # setK(25) on the 153-dim features
+    assert sum(model.summary.clusterSizes) == 18155 and model.summary.numIter <= 1000
+    # the cost of the returned centres is a local optimum of Lloyd: one more pass does not increase it
+    d_centers = torch.from_numpy(model.centers).to(eng.device)
+    _, cost = eng.kmeans_assign(pipeline_model.index, pipeline_model.numerics, d_centers, 30, 5)
+    assert float(cost.sum()) <= model.summary.trainingCost * (1 + 1e-9)
+    pkg.KMeansWorkload.pipeline_model, pkg.KMeansWorkload.kmeans_model = pipeline_model, model
+    pred, feats = wl.infer_single_row(None, "Asthma", 10)          # k_means.py:138: row (label, 10, 17, 15)
+    f = feats.cpu().numpy()[0]
+    assert 0 <= pred < 25 and f.shape == (153,) and f[150:].tolist() == [10.0, 17.0, 15.0]
+    assert f[:150].sum() == 5 and f[pipeline_model.labels.index("Asthma")] == 1
+    pred2, feats2 = wl.infer_single_row(None, "no such measure", 0)  # unseen label -> all-zero one-hot blocks
+    assert feats2.cpu().numpy()[0, :150].sum() == 0 and 0 <= pred2 < 25

@@ -98,6 +98,7 @@ def test_parquet_unsupported_inputs_fail_loudly(eng):
 def test_health_parquet_gives_the_same_stage_output_as_health_csv(eng, which, monkeypatch):
     text = health_text(which)
     monkeypatch.setenv("MEASURE_NAME_WEIGHT", "5")
+    monkeypatch.setenv("ETL_SKIP_KMEANS", "1")
     arrow = pacsv.read_csv(io.BytesIO(text.encode()), convert_options=pacsv.ConvertOptions(strings_can_be_null=True))
     raw = _write(arrow)
     cols = (["value", "lower_ci", "upper_ci"], ["measure_name"])

@@ -269,7 +269,23 @@ def m_parquet(eng, args):
                  "includes per-column host glue (descriptor upload, status check)")
 
 
-ALL = {"parquet": m_parquet, "null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
+def m_kmeans(eng, args):
+    n, L, repeats, k = 10_000_000, 30, 5, 25
+    idx = eng.synth_column(1, 0, S.KIND_KEY32, n, modulus=31, with_valid=False).data
+    nums = [eng.synth_column(1, 1 + c, S.KIND_EXACT, n, with_valid=False).data for c in range(3)]
+    centers = torch.rand((k, repeats * L + 3), dtype=torch.float64, device=eng.device)
+    cluster = torch.zeros(n, dtype=torch.int32, device=eng.device)
+    res = []
+    mean, mn = timed(lambda: eng.kmeans_assign(idx, nums, centers, L, repeats, cluster=cluster), steps=10)
+    res.append(entry("kmeans_prepare + kmeans_assign k=25, D=153 (k_means.py:83-87, one Lloyd pass)", n, n * (28 + 12), mean, mn,
+                     None, "reads 28 B and writes cluster + cost (12 B) per row; the dense [N,153] matrix is never built"))
+    # `cluster` now holds the assignment to the random centres above (skewed, as real assignments are)
+    mean, mn = timed(lambda: eng.kmeans_accumulate(idx, nums, cluster, k, L), steps=10)
+    res.append(entry("kmeans_accumulate k=25 (per-cluster counts, label histogram, numeric sums)", n, n * 32, mean, mn))
+    return res
+
+
+ALL = {"kmeans": m_kmeans, "parquet": m_parquet, "null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
        "groupby4": m_groupby4, "partition": m_partition, "csv": m_csv, "features": m_features}
 
 
