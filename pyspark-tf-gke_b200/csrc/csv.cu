@@ -329,6 +329,7 @@ struct CsvParseParams {
     uint64_t* dict_hash[CSV_MAX_COLS];  // string columns: capacity words, 0 = empty
     uint64_t* dict_rep[CSV_MAX_COLS];   // representative field of the slot (packed offset / length / quoted)
     uint32_t dict_mask[CSV_MAX_COLS];   // capacity - 1 (capacity is a power of two)
+    int32_t last_field;                 // largest requested field position: the row scan stops once it is closed
     int flags;                          // CSV_TRIM_STRINGS | CSV_NAN_IS_NULL
     int32_t* status;                    // [0] numerals outside the exact domain, [1] dictionary overflows,
                                         // [2] bit s set: column s saw a non-integer numeral, [3] unparsable numerals
@@ -570,6 +571,10 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                     row_end = pos + __ffs(end8) - 1;
                     break;
                 }
+                if ((int)fi > p.last_field) {  // every requested field is closed: the rest of the row is not needed
+                    row_end = pos;             // (unused then; kept inside the group's 32-bit offset range)
+                    break;
+                }
                 inside ^= __popc(q8) & 1;
                 pos += 8;
             }
@@ -725,6 +730,8 @@ extern "C" int etl_csv_parse_columns(etl_handle* hh, const uint8_t* text, int64_
     etl::CsvParseParams p{};
     p.text = text; p.n = nbytes; p.row_start = row_start; p.first_row = first_row; p.rows = rows; p.ncols = ncols;
     p.flags = flags; p.status = d_status; p.first_bad_row = d_first_bad_row;
+    p.last_field = 0;
+    for (int s = 0; s < ncols; ++s) p.last_field = field[s] > p.last_field ? field[s] : p.last_field;
     for (int s = 0; s < ncols; ++s) {
         ETL_REQUIRE(field[s] >= 0 && field[s] < etl::CSV_MAX_FIELDS, "csv_parse_columns: field[%d]=%d out of range", s,
                     field[s]);
