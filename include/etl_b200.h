@@ -169,10 +169,11 @@ ETL_API int etl_csv_row_offsets(etl_handle* h, const uint8_t* text, int64_t nbyt
  * of the string in the column's dictionary (-1 where null).  valid[s] =
  * ceil(rows/32) bitmap words, fully written.  An empty cell, a cell missing from
  * a short record and (numeric) an unparsable cell are null.  Numerals are
- * converted correctly rounded (as Double.parseDouble / float() do) for <= 19
- * significant digits and |decimal exponent| <= 19 (<= 22 when the digits fit
- * 2^53); a numeral outside that domain is never approximated: it is counted in
- * d_status[0] and the caller must treat the decode as failed.
+ * converted correctly rounded (as Double.parseDouble / float() do) for up to 19
+ * significant digits and any exponent (overflow to inf, underflow through the
+ * subnormals); a numeral with more significant digits and a non-zero tail is
+ * never approximated: it is counted in d_status[0] and the caller must treat the
+ * decode as failed.
  * Dictionaries (string columns): dict_hash[s] / dict_rep[s] = uint64[capacity]
  * device arrays zeroed by the caller before the first call (they persist across
  * calls, so several calls share one dictionary); capacity = power of two.  A slot

@@ -7,10 +7,13 @@
 //   A/B  <= 2^53 mantissa, |exp10| <= 22: one IEEE multiply / divide of two
 //        exactly representable numbers (Clinger's fast path);
 //   C    any <= 19-digit mantissa, |exp10| <= 19: exact 128-bit integer
-//        product / quotient with remainder, rounded half-even by hand.
-// Outside that domain (more than 19 significant digits with a non-zero tail, or
-// |exp10| > 19 beyond path A/B) the result is DEC_INEXACT and the caller fails
-// loudly.  Shared by the CUDA kernels and, compiled as plain C++, by the CPU
+//        product / quotient with remainder, rounded half-even by hand;
+//   D    any <= 19-digit mantissa, any exponent (overflow to inf, underflow
+//        through the subnormals to 0): exact multi-word integers - m * 5^e for
+//        e >= 0, a 66-step shift-subtract division by 5^-e for e < 0 - rounded
+//        half-even with a sticky bit.  Slow (thousands of integer ops) but rare.
+// More than 19 significant digits with a non-zero tail is DEC_INEXACT and the
+// caller fails loudly.  Shared by the CUDA kernels and, compiled as plain C++, by the CPU
 // unit test that checks it against strtod on millions of numerals.
 #pragma once
 #include <stdint.h>
@@ -74,6 +77,155 @@ DEC_HD double dec_round128(dec_u128 Q, bool sticky, int e2) {
     const dec_u128 half = ((dec_u128)1) << (shift - 1);
     if (rem > half || (rem == half && (sticky || (q & 1)))) ++q;
     return dec_ldexp(q, e2 + shift);
+}
+
+// ---- path D: multi-word exact scaling ------------------------------------------
+constexpr int DEC_WORDS = 16;  // 1024 bits: 5^345 (801 bits) and m * 5^310 (784 bits) fit
+
+struct DecBig {
+    uint64_t w[DEC_WORDS];  // little endian
+    int n;                  // words in use (w[n-1] != 0), 0 = zero
+};
+DEC_HD void big_set(DecBig& a, uint64_t v) {
+    for (int i = 0; i < DEC_WORDS; ++i) a.w[i] = 0;
+    a.w[0] = v;
+    a.n = v ? 1 : 0;
+}
+DEC_HD void big_mul_small(DecBig& a, uint64_t f) {
+    uint64_t carry = 0;
+    for (int i = 0; i < a.n; ++i) {
+        const dec_u128 p = (dec_u128)a.w[i] * f + carry;
+        a.w[i] = (uint64_t)p;
+        carry = (uint64_t)(p >> 64);
+    }
+    if (carry && a.n < DEC_WORDS) a.w[a.n++] = carry;
+}
+DEC_HD void big_pow5(DecBig& a, int k) {  // a *= 5^k
+    const uint64_t p27 = 7450580596923828125ull;  // 5^27 < 2^63
+    while (k >= 27) { big_mul_small(a, p27); k -= 27; }
+    uint64_t f = 1;
+    for (int i = 0; i < k; ++i) f *= 5;
+    if (f > 1) big_mul_small(a, f);
+}
+DEC_HD int big_bits(const DecBig& a) { return a.n ? 64 * (a.n - 1) + 64 - dec_clz64(a.w[a.n - 1]) : 0; }
+DEC_HD bool big_bit(const DecBig& a, int i) { return (a.w[i >> 6] >> (i & 63)) & 1; }
+DEC_HD int big_cmp(const DecBig& a, const DecBig& b) {
+    if (a.n != b.n) return a.n < b.n ? -1 : 1;
+    for (int i = a.n - 1; i >= 0; --i)
+        if (a.w[i] != b.w[i]) return a.w[i] < b.w[i] ? -1 : 1;
+    return 0;
+}
+DEC_HD void big_sub(DecBig& a, const DecBig& b) {  // a -= b, a >= b
+    uint64_t borrow = 0;
+    for (int i = 0; i < a.n; ++i) {
+        const uint64_t bi = i < b.n ? b.w[i] : 0;
+        const uint64_t d = a.w[i] - bi - borrow;
+        borrow = (a.w[i] < bi) || (a.w[i] == bi && borrow) ? 1 : 0;
+        a.w[i] = d;
+    }
+    while (a.n && a.w[a.n - 1] == 0) --a.n;
+}
+DEC_HD void big_shl1_or(DecBig& a, bool bit) {  // a = (a << 1) | bit
+    uint64_t carry = bit ? 1 : 0;
+    for (int i = 0; i < a.n; ++i) {
+        const uint64_t nc = a.w[i] >> 63;
+        a.w[i] = (a.w[i] << 1) | carry;
+        carry = nc;
+    }
+    if (carry && a.n < DEC_WORDS) a.w[a.n++] = carry;
+    if (a.n == 0 && bit) { a.w[0] = 1; a.n = 1; }
+}
+// bits [lo, lo + 64) of a (lo may be negative: zero-filled)
+DEC_HD uint64_t big_extract64(const DecBig& a, int lo) {
+    uint64_t r = 0;
+    for (int i = 0; i < 64; ++i) {
+        const int b = lo + i;
+        if (b >= 0 && b < 64 * a.n && big_bit(a, b)) r |= 1ull << i;
+    }
+    return r;
+}
+DEC_HD bool big_any_below(const DecBig& a, int lo) {  // any set bit strictly below position lo
+    for (int i = 0; i < a.n; ++i) {
+        const int base = 64 * i;
+        if (base >= lo) break;
+        const uint64_t mask = lo - base >= 64 ? ~0ull : ((1ull << (lo - base)) - 1);
+        if (a.w[i] & mask) return true;
+    }
+    return false;
+}
+
+DEC_HD double dec_ldexp_any(uint64_t q, int e2) {  // q * 2^e2, exact (callers keep q within the precision available)
+    double r = (double)q;
+    while (e2 > 0) { const int s = e2 > 512 ? 512 : e2; r *= dec_ldexp(1, s); e2 -= s; }
+    while (e2 < 0) { const int s = e2 < -512 ? 512 : -e2; r *= dec_ldexp(1, -s); e2 += s; }
+    return r;
+}
+
+// the exact value is (Q + theta) * 2^E, 0 <= theta < 1, sticky = theta > 0, Q has 64 or 65 bits -> nearest-even double
+DEC_HD double dec_round_qe(dec_u128 Q, bool sticky, int E) {
+    const int nb = dec_bits128(Q);
+    const int top = nb - 1 + E;  // unbiased exponent of the value
+    if (top > 1023) {
+        const uint64_t inf = 0x7ff0000000000000ull;
+        return *reinterpret_cast<const double*>(&inf);
+    }
+    int p = 53;
+    if (top < -1022) p = 53 - (-1022 - top);  // subnormal: fewer mantissa bits
+    if (p < 0) return 0.0;
+    const int shift = nb - p;  // >= 11
+    uint64_t q = shift >= 128 ? 0 : (uint64_t)(Q >> shift);
+    const dec_u128 rem = shift >= 128 ? Q : (Q & ((((dec_u128)1) << shift) - 1));
+    const dec_u128 half = ((dec_u128)1) << (shift - 1);
+    if (rem > half || (rem == half && (sticky || (q & 1)))) ++q;
+    if (q == 0) return 0.0;
+    // q <= 2^53; q * 2^(E + shift) is representable (for subnormals by construction of p), except the carry to inf
+    if (E + shift > 971 && q >= (1ull << 53)) {
+        const uint64_t inf = 0x7ff0000000000000ull;
+        return *reinterpret_cast<const double*>(&inf);
+    }
+    return dec_ldexp_any(q, E + shift);
+}
+
+// m * 10^e10 (m != 0) correctly rounded, any e10
+DEC_HD double dec_scale_exact(uint64_t m, long long e10) {
+    if (e10 > 310) {
+        const uint64_t inf = 0x7ff0000000000000ull;
+        return *reinterpret_cast<const double*>(&inf);
+    }
+    if (e10 < -345) return 0.0;
+    if (e10 >= 0) {
+        DecBig N;
+        big_set(N, m);
+        big_pow5(N, (int)e10);                     // value = N * 2^e10
+        const int nb = big_bits(N);
+        const int sh = nb > 64 ? nb - 64 : 0;
+        const uint64_t Q = big_extract64(N, sh);
+        return dec_round_qe((dec_u128)Q, sh > 0 && big_any_below(N, sh), sh + (int)e10);
+    }
+    const int k = (int)-e10;
+    DecBig D;
+    big_set(D, 1);
+    big_pow5(D, k);                                // value = m / D * 2^-k
+    const int bd = big_bits(D), bm = 64 - dec_clz64(m);
+    // N = m << a with a = bd - bm + 64: the quotient has 64 or 65 bits.  Shift-subtract division: start the
+    // remainder with the top bd - 1 bits of N, then bring down the remaining 66 bits one at a time.
+    const int a = bd - bm + 64;
+    const int nbits = bm + a;                      // = bd + 64
+    DecBig R;
+    big_set(R, 0);
+    int i = nbits - 1;
+    for (; i > nbits - bd; --i) {                  // bd - 1 bits: no quotient bit can be set yet
+        const int mb = i - a;                      // bit of m (negative: the zero padding)
+        big_shl1_or(R, mb >= 0 && ((m >> mb) & 1));
+    }
+    dec_u128 Q = 0;
+    for (; i >= 0; --i) {
+        const int mb = i - a;
+        big_shl1_or(R, mb >= 0 && ((m >> mb) & 1));
+        Q <<= 1;
+        if (big_cmp(R, D) >= 0) { big_sub(R, D); Q |= 1; }
+    }
+    return dec_round_qe(Q, R.n != 0, -a - k);
 }
 
 DEC_HD bool dec_is_space(uint8_t c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n' || c == '\v' || c == '\f'; }
@@ -170,7 +322,7 @@ DEC_HD int dec_parse(const uint8_t* p, int len, double* out, int* flags) {
         const uint64_t d = dec_pow10_u64((int)-e10);
         r = dec_round128(N / d, (N % d) != 0, -(64 + lz));
     } else {
-        return DEC_INEXACT;
+        r = dec_scale_exact(m, e10);
     }
     *out = neg ? -r : r;
     return DEC_OK;

@@ -51,11 +51,6 @@ def test_load_csv_health_matches_reference_golden(eng, which):
 def test_load_csv_cases_match_reference_golden(eng, name):
     case = _cases()[name]
     raw = case["text"].encode()
-    if name == "big_and_small":
-        # 3.4e38 is outside the exactly-converted numeral domain: loud failure, never an approximation
-        with pytest.raises(pkg.EtlError, match="outside the exactly-converted domain"):
-            pkg.load_csv(raw)
-        return
     if "raises" in case:
         with pytest.raises(RuntimeError, match="No valid rows"):
             pkg.load_csv(raw)
@@ -66,13 +61,22 @@ def test_load_csv_cases_match_reference_golden(eng, name):
     assert vocab == case["vocab"]
 
 
-def test_load_csv_numerals_inside_the_exact_domain(eng):
+def test_load_csv_numerals_across_the_double_range(eng):
     text = ("subpopulation,value,lower_ci,upper_ci\n"
             "A,123456789012345,0.1,1e-5\nB,16777217,9007199254740993,1e22\n"
-            "C,0.30000000000000004,12345678901234567890,-0\nD,1234567890123456789e-19,.5,5.\n")
+            "C,0.30000000000000004,12345678901234567890,-0\nD,1234567890123456789e-19,.5,5.\n"
+            "E,3.4e38,1e23,1.7976931348623157e308\nF,4.9e-324,2.2250738585072011e-308,1e-400\nG,1e400,-1e309,6.02214076e23\n")
     X, y, vocab = pkg.load_csv(text.encode())
     eX, ey, ev = O.load_csv(text)
     assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev
+    t = pkg.read_csv(eng, text.encode(), ["value", "lower_ci", "upper_ci"], ["subpopulation"])
+    header, cols = O.read_csv_columns(text)
+    for c in ("value", "lower_ci", "upper_ci"):   # fp64 before the float32 cast: bit for bit
+        v, vv = O.to_numeric_column(cols[c])
+        assert t.numeric[c].data.cpu().numpy().tobytes() == v.tobytes()
+    # 20+ significant digits with a non-zero tail stay outside the exactly-converted domain: loud failure
+    with pytest.raises(pkg.EtlError, match="outside the exactly-converted domain"):
+        pkg.load_csv(b"subpopulation,value,lower_ci,upper_ci\nA,0.12345678901234567891,1,2\n")
 
 
 def test_load_csv_other_columns_and_label_map(eng, tmp_path):
