@@ -169,7 +169,7 @@ ETL_API int etl_csv_row_offsets(etl_handle* h, const uint8_t* text, int64_t nbyt
  * of the string in the column's dictionary (-1 where null).  valid[s] =
  * ceil(rows/32) bitmap words, fully written.  An empty cell, a cell missing from
  * a short record and (numeric) an unparsable cell are null.  Numerals are
- * converted correctly rounded (as Double.parseDouble / float() do) for up to 19
+ * converted correctly rounded (as Double.parseDouble / float() do) for up to 60
  * significant digits and any exponent (overflow to inf, underflow through the
  * subnormals); a numeral with more significant digits and a non-zero tail is
  * never approximated: it is counted in d_status[0] and the caller must treat the

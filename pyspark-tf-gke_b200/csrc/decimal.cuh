@@ -12,7 +12,9 @@
 //        through the subnormals to 0): exact multi-word integers - m * 5^e for
 //        e >= 0, a 66-step shift-subtract division by 5^-e for e < 0 - rounded
 //        half-even with a sticky bit.  Slow (thousands of integer ops) but rare.
-// More than 19 significant digits with a non-zero tail is DEC_INEXACT and the
+//        A numeral with 20..60 significant digits takes the same path with a
+//        multi-word mantissa.
+// More than 60 significant digits with a non-zero tail is DEC_INEXACT and the
 // caller fails loudly.  Shared by the CUDA kernels and, compiled as plain C++, by the CPU
 // unit test that checks it against strtod on millions of numerals.
 #pragma once
@@ -186,46 +188,53 @@ DEC_HD double dec_round_qe(dec_u128 Q, bool sticky, int E) {
     return dec_ldexp_any(q, E + shift);
 }
 
-// m * 10^e10 (m != 0) correctly rounded, any e10
-DEC_HD double dec_scale_exact(uint64_t m, long long e10) {
+// M * 10^e10 (M != 0, a multi-word integer of at most ~200 bits) correctly rounded, any e10
+DEC_HD double dec_scale_exact_big(DecBig& M, long long e10) {
+    const int bm = big_bits(M);
     if (e10 > 310) {
         const uint64_t inf = 0x7ff0000000000000ull;
         return *reinterpret_cast<const double*>(&inf);
     }
-    if (e10 < -345) return 0.0;
+    if (e10 < -345 - 61) return 0.0;               // below 10^-345 even with 61 more digits in M
     if (e10 >= 0) {
-        DecBig N;
-        big_set(N, m);
-        big_pow5(N, (int)e10);                     // value = N * 2^e10
-        const int nb = big_bits(N);
+        big_pow5(M, (int)e10);                     // value = M * 2^e10
+        const int nb = big_bits(M);
         const int sh = nb > 64 ? nb - 64 : 0;
-        const uint64_t Q = big_extract64(N, sh);
-        return dec_round_qe((dec_u128)Q, sh > 0 && big_any_below(N, sh), sh + (int)e10);
+        const uint64_t Q = big_extract64(M, sh);
+        return dec_round_qe((dec_u128)Q, sh > 0 && big_any_below(M, sh), sh + (int)e10);
     }
     const int k = (int)-e10;
+    if (k > 345 + 61) return 0.0;
     DecBig D;
     big_set(D, 1);
-    big_pow5(D, k);                                // value = m / D * 2^-k
-    const int bd = big_bits(D), bm = 64 - dec_clz64(m);
-    // N = m << a with a = bd - bm + 64: the quotient has 64 or 65 bits.  Shift-subtract division: start the
-    // remainder with the top bd - 1 bits of N, then bring down the remaining 66 bits one at a time.
+    big_pow5(D, k);                                // value = M / D * 2^-k   (5^406 = 943 bits: fits)
+    const int bd = big_bits(D);
+    // N = M << a with a = bd - bm + 64 (> 0 or < 0): the quotient has 64 or 65 bits.  Shift-subtract division:
+    // start the remainder with the top bd - 1 bits of N, then bring down the remaining 66 bits one at a time.
     const int a = bd - bm + 64;
     const int nbits = bm + a;                      // = bd + 64
     DecBig R;
     big_set(R, 0);
+    bool dropped = false;                          // a < 0: the low -a bits of M never enter the division
+    if (a < 0) dropped = big_any_below(M, -a);
     int i = nbits - 1;
     for (; i > nbits - bd; --i) {                  // bd - 1 bits: no quotient bit can be set yet
-        const int mb = i - a;                      // bit of m (negative: the zero padding)
-        big_shl1_or(R, mb >= 0 && ((m >> mb) & 1));
+        const int mb = i - a;                      // bit of M (negative: the zero padding)
+        big_shl1_or(R, mb >= 0 && big_bit(M, mb));
     }
     dec_u128 Q = 0;
     for (; i >= 0; --i) {
         const int mb = i - a;
-        big_shl1_or(R, mb >= 0 && ((m >> mb) & 1));
+        big_shl1_or(R, mb >= 0 && big_bit(M, mb));
         Q <<= 1;
         if (big_cmp(R, D) >= 0) { big_sub(R, D); Q |= 1; }
     }
-    return dec_round_qe(Q, R.n != 0, -a - k);
+    return dec_round_qe(Q, R.n != 0 || dropped, -a - k);
+}
+DEC_HD double dec_scale_exact(uint64_t m, long long e10) {
+    DecBig M;
+    big_set(M, m);
+    return dec_scale_exact_big(M, e10);
 }
 
 DEC_HD bool dec_is_space(uint8_t c) { return c == ' ' || c == '\t' || c == '\r' || c == '\n' || c == '\v' || c == '\f'; }
@@ -271,6 +280,7 @@ DEC_HD int dec_parse(const uint8_t* p, int len, double* out, int* flags) {
     bool tail_nonzero = false;
     int frac_taken = 0;   // fraction digits taken into m
     int ndigits = 0;
+    const int digits_at = i;  // a numeral with 20..60 significant digits is re-read into a multi-word mantissa
     for (; i < len && p[i] >= '0' && p[i] <= '9'; ++i) {
         ++ndigits;
         const unsigned d = p[i] - '0';
@@ -289,6 +299,7 @@ DEC_HD int dec_parse(const uint8_t* p, int len, double* out, int* flags) {
             else tail_nonzero |= d != 0;
         }
     }
+    const int digits_end = i;
     if (ndigits == 0) return DEC_INVALID;
     long long e10 = (long long)dropped - frac_taken;
     if (i < len && (p[i] == 'e' || p[i] == 'E')) {
@@ -311,7 +322,33 @@ DEC_HD int dec_parse(const uint8_t* p, int len, double* out, int* flags) {
     if (m == 0) {
         r = 0.0;
     } else if (tail_nonzero) {
-        return DEC_INEXACT;
+        // 20..60 significant digits: exact through a multi-word mantissa; longer ones are refused
+        DecBig M;
+        big_set(M, 0);
+        int sig2 = 0, frac2 = 0, extra_int = 0;
+        bool seen_dot = false, tail2 = false;
+        for (int j = digits_at; j < digits_end; ++j) {
+            if (p[j] == '.') { seen_dot = true; continue; }
+            const unsigned d = p[j] - '0';
+            if (sig2 == 0 && d == 0) { frac2 += seen_dot ? 1 : 0; continue; }
+            if (sig2 < 60) {
+                big_mul_small(M, 10);
+                uint64_t carry = d;  // M += d
+                for (int w = 0; w < DEC_WORDS && carry; ++w) {
+                    const uint64_t t = M.w[w] + carry;
+                    carry = t < M.w[w] ? 1 : 0;
+                    M.w[w] = t;
+                    if (w >= M.n && t) M.n = w + 1;
+                }
+                ++sig2;
+                frac2 += seen_dot ? 1 : 0;
+            } else {
+                extra_int += seen_dot ? 0 : 1;
+                tail2 |= d != 0;
+            }
+        }
+        if (tail2) return DEC_INEXACT;
+        r = dec_scale_exact_big(M, e10 - ((long long)dropped - frac_taken) + ((long long)extra_int - frac2));
     } else if (m <= ((uint64_t)1 << 53) && e10 >= -22 && e10 <= 22) {
         r = e10 >= 0 ? (double)m * dec_pow10((int)e10) : (double)m / dec_pow10((int)-e10);
     } else if (e10 >= 0 && e10 <= 19) {

@@ -151,7 +151,7 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
                                                         [k for _, k in present], dicts, flags)
         st = status.cpu().numpy()
         if st[0]:
-            raise EtlError(-4, f"{int(st[0])} numeral(s) outside the exactly-converted domain (more than 19 significant "
+            raise EtlError(-4, f"{int(st[0])} numeral(s) outside the exactly-converted domain (more than 60 significant "
                                f"digits); first at CSV record {int(first_bad.item())}")
         if st[1]:
             raise EtlError(-5, f"string dictionary full (capacity {dict_capacity}); first at CSV record "

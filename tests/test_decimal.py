@@ -59,8 +59,16 @@ def test_known_numerals(lib):
     assert (st == 0).all()
     for s, v in zip(wide, out):
         assert bits(v) == bits(float(s)), s
-    # more than 19 significant digits with a non-zero tail: reported, never approximated
-    out, st, fl = parse_many(lib, ["99999999999999999999", "0.12345678901234567891"])
+    # 20..60 significant digits go through the multi-word mantissa, still exact
+    longer = ["99999999999999999999", "0.12345678901234567891", "3.14159265358979323846264338327950288",
+              "9007199254740993.000000000000000000001", "9007199254740992.999999999999999999999",
+              "2.22507385850720138309023271733240406421921598046233e-308", "1" + "0" * 80]
+    out, st, fl = parse_many(lib, longer)
+    assert (st == 0).all()
+    for s, v in zip(longer, out):
+        assert bits(v) == bits(float(s)), s
+    # more than 60 significant digits with a non-zero tail: reported, never approximated
+    out, st, fl = parse_many(lib, ["1" * 61, "0." + "7" * 70])
     assert (st == 3).all()
 
 
@@ -73,7 +81,7 @@ def test_random_numerals_are_correctly_rounded(lib):
     rnd = random.Random(20261106)
     strings = []
     while len(strings) < 300_000:
-        nd = rnd.randint(1, 19)
+        nd = rnd.choice([rnd.randint(1, 19), rnd.randint(1, 60)])
         digits = "".join(rnd.choice("0123456789") for _ in range(nd))
         k = rnd.randint(0, nd)
         s = digits[:k] + ("." if rnd.random() < 0.7 else "") + digits[k:]
@@ -85,7 +93,7 @@ def test_random_numerals_are_correctly_rounded(lib):
             s = "-" + s
         strings.append(s)
     out, st, fl = parse_many(lib, strings)
-    assert set(st.tolist()) <= {0}          # <= 19 significant digits: always converted exactly
+    assert set(st.tolist()) <= {0}          # <= 60 significant digits: always converted exactly
     exact = np.nonzero(st == 0)[0]
     ref = np.array([float(strings[i]) for i in exact])
     assert out[exact].tobytes() == ref.tobytes()

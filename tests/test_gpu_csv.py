@@ -65,7 +65,8 @@ def test_load_csv_numerals_across_the_double_range(eng):
     text = ("subpopulation,value,lower_ci,upper_ci\n"
             "A,123456789012345,0.1,1e-5\nB,16777217,9007199254740993,1e22\n"
             "C,0.30000000000000004,12345678901234567890,-0\nD,1234567890123456789e-19,.5,5.\n"
-            "E,3.4e38,1e23,1.7976931348623157e308\nF,4.9e-324,2.2250738585072011e-308,1e-400\nG,1e400,-1e309,6.02214076e23\n")
+            "E,3.4e38,1e23,1.7976931348623157e308\nF,4.9e-324,2.2250738585072011e-308,1e-400\nG,1e400,-1e309,6.02214076e23\n"
+            "H,3.14159265358979323846264338327950288,0.12345678901234567891,9007199254740992.999999999999999999999\n")
     X, y, vocab = pkg.load_csv(text.encode())
     eX, ey, ev = O.load_csv(text)
     assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev
@@ -74,9 +75,9 @@ def test_load_csv_numerals_across_the_double_range(eng):
     for c in ("value", "lower_ci", "upper_ci"):   # fp64 before the float32 cast: bit for bit
         v, vv = O.to_numeric_column(cols[c])
         assert t.numeric[c].data.cpu().numpy().tobytes() == v.tobytes()
-    # 20+ significant digits with a non-zero tail stay outside the exactly-converted domain: loud failure
+    # more than 60 significant digits with a non-zero tail stay outside the exactly-converted domain: loud failure
     with pytest.raises(pkg.EtlError, match="outside the exactly-converted domain"):
-        pkg.load_csv(b"subpopulation,value,lower_ci,upper_ci\nA,0.12345678901234567891,1,2\n")
+        pkg.load_csv(("subpopulation,value,lower_ci,upper_ci\nA,0.%s,1,2\n" % ("7" * 70)).encode())
 
 
 def test_load_csv_other_columns_and_label_map(eng, tmp_path):
