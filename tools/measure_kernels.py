@@ -7,8 +7,8 @@ For each kernel: synthetic input of the BASELINE.json shape resident in HBM,
 >= 3 warm-up launches, K timed launches bracketed by CUDA events on the launching
 stream (inputs are larger than L2 everywhere), algorithmic bytes per launch
  / mean launch time = achieved GB/s, against the measured copy peak
-of MEASURED_PEAKS.json.  A CPU figure for the same operation (NumPy / pyarrow /
-the compiled oracle, bounded sample, thread count stated) is taken beside it.
+of MEASURED_PEAKS.json.  A CPU figure for the same operation (NumPy or pyarrow,
+bounded sample, thread count stated - never oracle/) is taken beside it.
 These are kernel numbers; the headline line stays with bench.py."""
 from __future__ import annotations
 

@@ -2,10 +2,9 @@
 """Config 1 / config 5 (BASELINE.json configs[0], [4]): the full stage on CSV text -
 decode -> null count -> means -> filter/impute -> StringIndexer -> features - timed
 per step with CUDA events (text already in HBM; the H2D copy is timed separately),
-on 1 GPU or sharded by rows over N GPUs (torchrun).  The CPU figures beside it: the
-reference's own load_csv is not importable on the GPU box, so its restatement
-(oracle.load_csv, pinned to it bit for bit) and the oracle's Spark-stage
-restatement are timed on the default input.
+on 1 GPU or sharded by rows over N GPUs (torchrun).  (CPU figures for the default
+input come from the test suite's oracle, never from here: only tests/, smoke() and
+bench.py may touch oracle/.)
 
     python tools/measure_pipeline.py [--rows 10000000] [--dtype f32]
 """
@@ -84,13 +83,6 @@ def main():
                 "h2d_copy_s": h2d_s, "labels": len(model.labels), "means": model.means,
                 "rows_after_filter": model.rows_after_filter, "null_keys": model.null_key_count}
         print(json.dumps(line), flush=True)
-        if world == 1 and args.rows <= 20000:
-            from oracle import etl_oracle as O
-
-            txt = raw.decode()
-            t0 = time.perf_counter(); O.load_csv(txt); t_load = time.perf_counter() - t0
-            t0 = time.perf_counter(); O.k_means_etl(txt); t_etl = time.perf_counter() - t0
-            print(json.dumps({"cpu": {"oracle.load_csv_s": t_load, "oracle.k_means_etl_s": t_etl, "cores": 1}}), flush=True)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
