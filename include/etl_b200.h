@@ -391,6 +391,30 @@ ETL_API int etl_kmeans_accumulate(etl_handle* h, const int32_t* index, const dou
                           const int32_t* cluster, int64_t n, int32_t k, int32_t num_labels, int64_t* d_count,
                           int64_t* d_hist, double* d_numsum, void* stream);
 
+/* ---- next row: device-resident hand-off to the trainer */
+
+/* Replaces model.fit / the custom train step on the tabular model of
+ * workloads/raw-tf/train_tf_ps.py:328-343 (Dense 16-32-64 relu, softmax output,
+ * sparse categorical cross-entropy, Adam) fed by from_tensor_slices((X, y))
+ * .shuffle().batch().repeat() (train_tf_ps.py:596-601,664-672): X float32[n][3]
+ * and y int32[n] stay where etl_pack_tf_features left them, in device memory.
+ * Parameters: one float32 blob of etl_mlp_param_count(classes) values laid out
+ * (W1[3][16], b1, W2[16][32], b2, W3[32][64], b3, W4[64][classes], b4), kernels
+ * [in][out] row-major as Keras stores them.
+ * etl_mlp_train_steps runs `steps` consecutive optimiser steps in ONE launch
+ * (parameters and Adam moments live in shared memory for its duration): step s
+ * trains on rows d_order[s * batch .. + batch); d_params / d_adam_m / d_adam_v are
+ * updated in place; step0 = optimiser steps already taken (Adam bias correction);
+ * d_loss[s] / d_acc[s] = mean loss / accuracy of step s's batch before its update.
+ * etl_mlp_evaluate: forward only - per-sample loss (needs y) and / or arg-max class. */
+ETL_API int etl_mlp_param_count(int32_t classes);
+ETL_API int etl_mlp_train_steps(etl_handle* h, const float* X, const int32_t* y, int64_t n, const int32_t* d_order,
+                        int32_t batch, int32_t steps, int32_t classes, float* d_params, float* d_adam_m,
+                        float* d_adam_v, int64_t step0, float lr, float beta1, float beta2, float eps,
+                        float* d_loss, float* d_acc, void* stream);
+ETL_API int etl_mlp_evaluate(etl_handle* h, const float* X, const int32_t* y, int64_t n, const float* d_params,
+                     int32_t classes, float* d_loss, int32_t* d_pred, void* stream);
+
 /* ---- synthetic tables (bench / test infrastructure) -------------------- */
 
 /* Counter-based generator, identical to pyspark_tf_gke_b200.synth on the host:

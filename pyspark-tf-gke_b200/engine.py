@@ -532,6 +532,34 @@ class Engine:
         self.launches += 1 if n else 0
         return count, hist, numsum
 
+    # --------------------------------------------- trainer hand-off (8f rank 1)
+    def mlp_param_count(self, classes: int) -> int:
+        return int(self.lib.etl_mlp_param_count(classes))
+
+    def mlp_train_steps(self, X: torch.Tensor, y: torch.Tensor, order: torch.Tensor, batch: int, classes: int,
+                        params: torch.Tensor, adam_m: torch.Tensor, adam_v: torch.Tensor, step0: int = 0,
+                        lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-7):
+        """`order` int32[steps * batch] row indices -> (loss f32[steps], acc f32[steps]);
+        params / moments are updated in place."""
+        steps = order.numel() // batch
+        loss = self.empty(max(steps, 1), torch.float32)
+        acc = self.empty(max(steps, 1), torch.float32)
+        _lib.check(self.lib.etl_mlp_train_steps(self._h, X.data_ptr(), y.data_ptr(), X.shape[0], order.data_ptr(), batch,
+                                                steps, classes, params.data_ptr(), adam_m.data_ptr(), adam_v.data_ptr(),
+                                                step0, lr, beta1, beta2, eps, loss.data_ptr(), acc.data_ptr(),
+                                                self._stream()))
+        self.launches += 1 if steps else 0
+        return loss[:steps], acc[:steps]
+
+    def mlp_evaluate(self, X: torch.Tensor, y: Optional[torch.Tensor], params: torch.Tensor, classes: int):
+        n = X.shape[0]
+        loss = self.empty(n, torch.float32) if y is not None else None
+        pred = self.empty(n, torch.int32)
+        _lib.check(self.lib.etl_mlp_evaluate(self._h, X.data_ptr(), _ptr(y), n, params.data_ptr(), classes, _ptr(loss),
+                                             pred.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return loss, pred
+
     # ------------------------------------------------------------ synth
     def synth_column(self, seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1,
                      null_rate: float = 0.0, nan_rate: float = 0.0, with_valid: bool = True) -> Column:

@@ -285,7 +285,24 @@ def m_kmeans(eng, args):
     return res
 
 
-ALL = {"kmeans": m_kmeans, "parquet": m_parquet, "null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
+def m_trainer(eng, args):
+    from pyspark_tf_gke_b200 import trainer as T
+
+    n, C, B = 12284, 15, 64   # the default input's training split (80 % of 15355 rows), batch 64
+    rng = np.random.default_rng(0)
+    X = torch.from_numpy(rng.random((n, 3)).astype(np.float32) * 1000).to(eng.device)
+    y = torch.from_numpy(rng.integers(0, C, n).astype(np.int32)).to(eng.device)
+    steps = n // B
+    order = torch.from_numpy(T.shuffle_buffer_order(n, 3000, steps * B, rng)).to(eng.device)
+    params = torch.from_numpy(T.glorot_uniform_params(C, rng)).to(eng.device)
+    m, v = torch.zeros_like(params), torch.zeros_like(params)
+    mean, mn = timed(lambda: eng.mlp_train_steps(X, y, order, B, C, params, m, v), steps=5)
+    e = entry(f"mlp_train_kernel: one epoch = {steps} steps of batch {B} (train_tf_ps.py:328-343,664-672)", steps * B,
+              steps * B * 16, mean, mn, None, "single CTA, launch-latency-bound problem: %.2f us per optimiser step" % (mean * 1e3 / steps))
+    return e
+
+
+ALL = {"trainer": m_trainer, "kmeans": m_kmeans, "parquet": m_parquet, "null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
        "groupby4": m_groupby4, "partition": m_partition, "csv": m_csv, "features": m_features}
 
 
