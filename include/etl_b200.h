@@ -354,6 +354,39 @@ ETL_API int etl_hash_partition_scatter_peers(etl_handle* h, const int64_t* keys,
                                      int64_t val_stride, int64_t n, int32_t ranks, int64_t* const* peer_records,
                                      const int64_t* d_peer_offset, void* stream);
 
+/* The reduce side of the exchange with the aggregation table in SHARED memory
+ * (the final HashAggregate above the Exchange node; north-star item 4).  The
+ * records a rank owns after the exchange are cut into `fine` = buckets * sub
+ * pieces by fine index (lo32(h) * fine) >> 32 - small enough that the groups of
+ * one piece fit one CTA's shared-memory table - and merged piece by piece:
+ *   1. etl_hash_partition(ranks = 1, buckets)   -> records grouped by bucket,
+ *      d_part_counts / d_part_base on the device;
+ *   2. etl_hash_subpartition (only when fine > buckets): every bucket into `sub`
+ *      pieces in one launch; piece f = bucket * sub + s occupies records
+ *      [d_fine_base[f], + d_fine_counts[f]) of out_records.  max_bucket_records:
+ *      an upper bound of the largest bucket (n is always one) - it only sizes the
+ *      grid.  buckets * sub <= 65536, sub <= 256;
+ *   3. etl_groupby_merge_partitioned: one piece at a time per CTA; the groups are
+ *      appended (in no particular order) to out_keys / out_rows / out_count /
+ *      out_sum [out_capacity]; smem_slots = table size (power of two, 64..8192;
+ *      20 bytes of shared memory each).  A record whose key finds no slot within
+ *      the probe limit goes to spill_records (int64[2 * spill_capacity], may be
+ *      the level-1 buffer, which is dead by then); the caller aggregates those
+ *      with etl_groupby_accumulate - a key is never in both outputs.
+ *      d_counters int64[4]: [0] groups appended, [1] records spilled (either may
+ *      exceed its capacity: then the surplus was dropped and the caller must
+ *      retry with more room), [3] records carrying the reserved key INT64_MIN.
+ * Records carry no nulls, so count(value) = rows.  No reference counterpart below
+ * the Spark shuffle. */
+ETL_API int etl_hash_subpartition(etl_handle* h, const int64_t* records, int32_t buckets, int32_t sub,
+                          const int64_t* d_bucket_counts, const int64_t* d_bucket_base, int64_t max_bucket_records,
+                          int64_t* d_fine_counts, int64_t* d_fine_base, int64_t* out_records, void* stream);
+ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records, int32_t fine,
+                                  const int64_t* d_fine_counts, const int64_t* d_fine_base, int32_t smem_slots,
+                                  int64_t out_capacity, int64_t* out_keys, int64_t* out_rows, int64_t* out_count,
+                                  double* out_sum, int64_t* spill_records, int64_t spill_capacity,
+                                  int64_t* d_counters, void* stream);
+
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 
 /* Spark ML Bucketizer(handleInvalid="keep"): out[i] = b with splits[b] <= x <

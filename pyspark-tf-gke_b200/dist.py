@@ -119,7 +119,8 @@ def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_
 
 
 def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
-                        buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None):
+                        buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None,
+                        merge: str = "smem"):
     """Config 4: hash-partition -> all-to-all -> local final merge.
 
     Sender: one partition pass groups the rows by destination rank (few
@@ -132,10 +133,19 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     exchange is needed.  With `peer` (a PeerExchange) partition and exchange are
     one kernel writing over NVLink into the receivers' buffers; without it the
     send buffer goes through NCCL's all-to-all.  `mark(name)` is called at the
-    phase boundaries (for timing).  Returns the rank-local GroupTable."""
+    phase boundaries (for timing).
+
+    merge="smem" (default) replaces the receiver's bucket-by-bucket table merge by
+    Engine.groupby_partitioned_sum: two partition levels cut what arrived into
+    pieces whose groups fit a shared-memory table, so no table update touches L2 or
+    HBM (`capacity` is then the room for output groups; `groups_hint` = expected
+    distinct keys over ALL ranks sizes the pieces).  merge="table" keeps the global
+    table.  Returns the rank-local result for Engine.groupby_result."""
     rank, size = world()
     mark = mark or (lambda name: None)
-    gt = eng.groupby_new(capacity, 1, minmax=False)
+    if merge not in ("smem", "table"):
+        raise ValueError(f"merge={merge!r}")
+    gt = eng.groupby_new(capacity, 1, minmax=False) if merge == "table" else None
     B = choose_buckets(capacity, 1) if buckets is None else buckets
     mark("init")
     if size > 1:
@@ -154,6 +164,12 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
         rk, rv, m, stride = keys, vals, keys.shape[0], 1
         mark("partition")
         mark("exchange")
+    if merge == "smem":
+        local_hint = -(-groups_hint // size) + (groups_hint // (8 * size) if size > 1 else 0) if groups_hint > 0 else 0
+        pg = eng.groupby_partitioned_sum(rk, rv, capacity, groups_hint=local_hint, n=m, key_stride=stride, val_stride=stride,
+                                         mark=mark)
+        mark("merge")
+        return pg
     if B == 1 or m == 0:
         if m:
             eng.groupby_accumulate(gt, rk, None, [rv], groups_hint=groups_hint, n=m, key_stride=stride, val_strides=[stride])

@@ -74,6 +74,22 @@ class GroupTable:
     status: torch.Tensor
 
 
+@dataclass
+class PartitionedGroups:
+    """Result of the shared-memory merge (etl_groupby_merge_partitioned): dense
+    columns in no particular order + device counters [groups, spilled, -, reserved]
+    + the spilled records; Engine.groupby_result turns it into the sorted dict."""
+
+    keys: torch.Tensor
+    rows: torch.Tensor
+    count: torch.Tensor
+    sum: torch.Tensor
+    counters: torch.Tensor
+    spill: torch.Tensor
+    capacity: int
+    pieces: int
+
+
 class Engine:
     """One per GPU (replaces the per-executor SparkSession state,
     spark_session.py:37-88)."""
@@ -338,6 +354,8 @@ class Engine:
     def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None) -> dict:
         """Dense result sorted by key: keys, rows, per column count/sum/mean[/min/max]
         (device tensors), plus the null-key group.  Raises if rows were dropped."""
+        if isinstance(gt, PartitionedGroups):
+            return self._partitioned_result(gt)
         cap = gt.capacity if max_groups is None else max_groups
         nc = gt.ncols
         keys = self.empty(cap, torch.int64)
@@ -414,6 +432,78 @@ class Engine:
         part = flat[2 * lo:]
         self.groupby_accumulate(gt, part, None, [part[1:].view(torch.float64)], groups_hint=groups_hint, n=hi - lo,
                                 key_stride=2, val_strides=[2])
+
+    # ------------------------------------------- shared-memory merge of the exchange
+    MERGE_SLOTS = 4096          # shared-table slots per CTA (80 KB: two CTAs per SM)
+    MERGE_GROUPS_PER_PIECE = 1536   # target groups per piece: load factor ~0.37
+
+    @staticmethod
+    def merge_plan(records: int, groups_hint: int, groups_per_piece: int = MERGE_GROUPS_PER_PIECE):
+        """-> (buckets, sub): how finely to cut `records` records holding about
+        `groups_hint` distinct keys so one piece's groups fit a shared table."""
+        g = max(1, min(int(groups_hint) if groups_hint > 0 else records, records))
+        fine = min(65536, max(1, -(-g // groups_per_piece)))
+        if fine <= 256:
+            return fine, 1
+        b = int(np.ceil(np.sqrt(fine)))
+        return b, min(256, -(-fine // b))
+
+    def groupby_partitioned_sum(self, keys: torch.Tensor, vals: torch.Tensor, out_capacity: int, groups_hint: int = 0,
+                                n: Optional[int] = None, key_stride: int = 1, val_stride: int = 1,
+                                plan: Optional[Tuple[int, int]] = None, slots: Optional[int] = None,
+                                mark=None) -> "PartitionedGroups":
+        """groupBy(key).agg(count, sum(value)) of (key int64, value f64) rows through
+        two partition levels and a shared-memory merge (csrc/merge.cu).  Everything is
+        enqueued on the current stream; nothing is read back until groupby_result."""
+        n = keys.shape[0] if n is None else n
+        buckets, sub = plan or self.merge_plan(n, groups_hint)
+        slots = slots or self.MERGE_SLOTS
+        mark = mark or (lambda name: None)
+        level1, counts, base = self.hash_partition(keys, vals, 1, buckets, n=n, key_stride=key_stride, val_stride=val_stride)
+        mark("level1")
+        fine, pieces, spill = buckets, level1, None
+        if sub > 1 and n:
+            fine = buckets * sub
+            fcounts, fbase = self.empty(fine, torch.int64), self.empty(fine, torch.int64)
+            pieces = torch.empty((n, 2), dtype=torch.int64, device=self.device)
+            _lib.check(self.lib.etl_hash_subpartition(self._h, level1.data_ptr(), buckets, sub, counts.data_ptr(),
+                                                      base.data_ptr(), n, fcounts.data_ptr(), fbase.data_ptr(),
+                                                      pieces.data_ptr(), self._stream()))
+            self.launches += 3
+            counts, base, spill = fcounts, fbase, level1     # the level-1 buffer is dead: it takes the spill
+        mark("level2")
+        if spill is None:
+            spill = torch.empty((max(n, 1), 2), dtype=torch.int64, device=self.device)
+        out_keys, out_rows = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.int64)
+        out_cnt, out_sum = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.float64)
+        counters = self.empty(4, torch.int64)
+        _lib.check(self.lib.etl_groupby_merge_partitioned(
+            self._h, pieces.data_ptr() if n else None, fine, counts.data_ptr(), base.data_ptr(), slots, out_capacity,
+            out_keys.data_ptr(), out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), spill.data_ptr(),
+            spill.shape[0], counters.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine)
+
+    def _partitioned_result(self, pg: "PartitionedGroups") -> dict:
+        groups, spilled, _, reserved = pg.counters.cpu().tolist()
+        if reserved:
+            raise _lib.EtlError(-5, f"groupBy: 0 row(s) dropped (table full), {reserved} row(s) with the reserved key")
+        if groups > pg.capacity:
+            raise _lib.EtlError(-5, f"groupBy: {groups} groups exceed the output capacity {pg.capacity}")
+        if spilled > pg.spill.shape[0]:
+            raise _lib.EtlError(-5, f"groupBy: {spilled} spilled records exceed the spill buffer {pg.spill.shape[0]}")
+        keys, rows, cnt, sm = pg.keys[:groups], pg.rows[:groups], pg.count[:groups], pg.sum[:groups]
+        if spilled:   # pieces with more groups than the shared table holds: the global-table path takes them
+            cap = 1 << max(4, int(np.ceil(np.log2(2 * spilled))))
+            gt = self.groupby_new(cap, 1)
+            self.groupby_accumulate_records(gt, pg.spill, 0, spilled, groups_hint=spilled)
+            extra = self.groupby_result(gt, max_groups=spilled)
+            keys, rows = torch.cat([keys, extra["keys"]]), torch.cat([rows, extra["rows"]])
+            cnt, sm = torch.cat([cnt, extra["cols"][0]["count"]]), torch.cat([sm, extra["cols"][0]["sum"]])
+        order = torch.argsort(keys)
+        col = {"count": cnt[order], "sum": sm[order]}
+        col["mean"] = col["sum"] / col["count"].to(torch.float64)
+        return {"keys": keys[order], "rows": rows[order], "cols": [col], "null_group_rows": 0, "spilled_records": spilled}
 
     # ------------------------------------------------------- Parquet (extension)
     def parquet_decode_column(self, data: torch.Tensor, nbytes: int, rows: int, pages, kind_plain: int,

@@ -51,8 +51,15 @@ def test_config4_shape_groupby_quarter_size_single_gpu(eng):
     cap = 1 << 26
     direct = eng.groupby_new(cap, 1)
     eng.groupby_accumulate(direct, key, None, [val], groups_hint=G)
-    bucketed = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G)   # partition by bucket, merge bucket by bucket
-    a, b = eng.groupby_result(direct, max_groups=G), eng.groupby_result(bucketed, max_groups=G)
+    pieces = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G)     # two partition levels + shared-memory merge
+    b = eng.groupby_result(pieces)
+    assert b["spilled_records"] == 0
+    del pieces
+    bucketed = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G, merge="table")   # bucket-by-bucket table merge
+    a, c = eng.groupby_result(direct, max_groups=G), eng.groupby_result(bucketed, max_groups=G)
+    assert torch.equal(a["keys"], c["keys"]) and torch.equal(a["rows"], c["rows"])
+    assert torch.equal(a["cols"][0]["sum"], c["cols"][0]["sum"])
+    del c, bucketed
     s, _ = eng.sum_count([pkg.Column(val)])
     for res in (a, b):
         k = res["keys"]

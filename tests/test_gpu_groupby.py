@@ -176,9 +176,63 @@ def test_bucketed_single_gpu_shuffle_path(eng):
     vals, _ = S.host_column(4, 1, S.KIND_EXACT, n)
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     exp = O.groupby_agg_fast(keys, [vals], [None])
-    for buckets in (1, 16):
-        gt = D.shuffle_groupby_sum(eng, dk, dv, 1 << 18, groups_hint=groups, buckets=buckets)
+    for buckets, merge in ((1, "table"), (16, "table"), (None, "smem")):
+        gt = D.shuffle_groupby_sum(eng, dk, dv, 1 << 18, groups_hint=groups, buckets=buckets, merge=merge)
         res = eng.groupby_result(gt)
         assert res["keys"].cpu().numpy().tolist() == exp["keys"].tolist()
         assert res["cols"][0]["sum"].cpu().numpy().tobytes() == exp["cols"][0]["sum"].tobytes()
     assert D.choose_buckets(1 << 28, 1) == 256 and D.choose_buckets(1 << 25, 8) == 32 and D.choose_buckets(1 << 10, 8) == 1
+
+
+# ---- shared-memory merge (csrc/merge.cu): partition levels + per-piece tables + spill list
+@pytest.mark.parametrize("n,groups,plan,slots", [
+    (0, 10, None, None),                    # nothing to do
+    (1, 1, None, None),
+    (300_007, 1000, None, None),            # one piece
+    (300_007, 100_000, None, None),         # one level (66 pieces)
+    (1_000_003, 600_000, None, None),       # two levels (20 x 20 pieces)
+    (400_000, 200_000, (3, 5), 4096),       # far too few pieces: most keys spill to the global-table path
+    (400_000, 50_000, (7, 1), 64),          # tiny tables: nearly everything spills
+    (500_000, 70_000, (256, 256), 256),     # the finest cut: 65536 pieces, most of them tiny or empty
+])
+def test_smem_merge_matches_oracle(eng, n, groups, plan, slots):
+    keys, _ = S.host_column(21, 0, S.KIND_KEY64, n, modulus=groups)
+    keys = keys - groups // 2                                   # negative keys too
+    vals, _ = S.host_column(21, 1, S.KIND_EXACT, n)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    pg = eng.groupby_partitioned_sum(dk, dv, max(n, 1), groups_hint=groups, plan=plan, slots=slots)
+    res = eng.groupby_result(pg)
+    exp = O.groupby_agg_fast(keys, [vals], [None])
+    _check(res, exp, exact_sums=True, minmax=False)
+    if plan in ((3, 5), (7, 1)):
+        assert res["spilled_records"] > n // 2
+    elif plan is None:
+        assert res["spilled_records"] == 0
+
+
+def test_smem_merge_skew_real_values_and_strided_records(eng):
+    # 90% of the rows on one key (one piece takes nearly everything), real-valued sums, and the
+    # {key, value} record layout of the exchange as input
+    n, groups = 700_001, 40_000
+    keys, _ = S.host_column(22, 0, S.KIND_KEY64, n, modulus=groups)
+    hot, _ = S.host_column(22, 2, S.KIND_KEY64, n, modulus=10)
+    keys = np.where(hot != 0, np.int64(123456789012345), keys)
+    vals, _ = S.host_column(22, 1, S.KIND_REAL, n)
+    rec = torch.from_numpy(np.stack([keys, vals.view(np.int64)], axis=1)).to(eng.device)
+    flat = rec.view(-1)
+    pg = eng.groupby_partitioned_sum(flat, flat[1:].view(torch.float64), n, groups_hint=groups, n=n, key_stride=2, val_stride=2)
+    res = eng.groupby_result(pg)
+    _check(res, O.groupby_agg_fast(keys, [vals], [None]), exact_sums=False, minmax=False)
+
+
+def test_smem_merge_reports_reserved_key_and_small_output(eng):
+    keys = np.arange(1000, dtype=np.int64)
+    vals = np.ones(1000)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    with pytest.raises(pkg.EtlError, match="exceed the output capacity"):
+        eng.groupby_result(eng.groupby_partitioned_sum(dk, dv, 999, groups_hint=1000))
+    keys[17] = np.iinfo(np.int64).min
+    with pytest.raises(pkg.EtlError, match="reserved key"):
+        eng.groupby_result(eng.groupby_partitioned_sum(torch.from_numpy(keys).to(eng.device), dv, 1000, groups_hint=1000))
+    assert pkg.Engine.merge_plan(10**9, 10**8) == (256, 255) and pkg.Engine.merge_plan(1000, 0) == (1, 1)
+    assert pkg.Engine.merge_plan(125_000_000, 14_000_000) == (96, 95)

@@ -40,6 +40,9 @@ def main():
     ap.add_argument("--buckets", type=int, default=-1, help="table buckets per rank (-1 = choose from the table size)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="peer = partition fused with NVLink peer stores; nccl = send buffer + all_to_all_single")
+    ap.add_argument("--merge", default="smem", choices=["smem", "table"],
+                    help="smem = two partition levels + shared-memory tables; table = bucket-by-bucket global table")
+    ap.add_argument("--out-capacity", type=int, default=0, help="room for output groups per rank (0 = table capacity)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -71,7 +74,9 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    phases = {"init": [], "partition": [], "exchange": [], "merge": [], "total": []}
+    phases = {"init": [], "partition": [], "exchange": [], "merge": [], "total": [], "level1": [], "level2": []}
+    if args.out_capacity:
+        cap = args.out_capacity
     gt = None
     sent = n - n // world if world > 1 else 0  # expected rows leaving this GPU (uniform hash)
     B = D.choose_buckets(cap, 1) if args.buckets < 0 else args.buckets
@@ -80,7 +85,7 @@ def main():
         gt = None
         barrier()
         marks = {"start": ev()}
-        gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer,
+        gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer, merge=args.merge,
                                    mark=lambda name: marks.__setitem__(name, ev()))
         torch.cuda.synchronize()
         if it >= args.warmup:
@@ -88,6 +93,9 @@ def main():
             for a, b in zip(order[:-1], order[1:]):
                 phases[b].append(max_ms(marks[a], marks[b]))
             phases["total"].append(max_ms(marks["start"], marks["merge"]))
+            if "level1" in marks:   # inside "merge": the two partition levels of the shared-memory path
+                phases["level1"].append(max_ms(marks["exchange"], marks["level1"]))
+                phases["level2"].append(max_ms(marks["level1"], marks["level2"]))
     # ---- checks
     res = eng.groupby_result(gt, max_groups=cap)
     tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
@@ -101,11 +109,12 @@ def main():
     ok_rows = int(tot[0].item()) == n * world
     ok_sum = float(gsum.item()) == float(direct.item())  # integer-valued data: exact
     if rank == 0:
-        mean = {k: float(np.mean(v)) for k, v in phases.items()}
+        mean = {k: float(np.mean(v)) for k, v in phases.items() if v}
         line = {"workload": "config4 shuffle+aggregate", "n_gpus": world, "rows_total": n * world, "groups": args.groups,
                 "distinct_keys_found": int(tot[1].item()), "rows_conserved": ok_rows, "sum_matches_column_sum": ok_sum,
                 "ms": mean, "rows_per_s": n * world / (mean["total"] * 1e-3),
-                "buckets_per_rank": B, "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
+                "buckets_per_rank": B if args.merge == "table" else None, "merge": args.merge,
+                "pieces_per_rank": getattr(gt, "pieces", None), "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
                 "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
                 "steps": args.steps}
         print(json.dumps(line), flush=True)
