@@ -20,8 +20,8 @@ def main(path):
         for w in WANT:
             if w in hdr:
                 i = hdr.index(w); print(f'  {w:70s} {r[i]} {units[i]}')
-        stalls = [(float(r[i] or 0), h) for i, h in enumerate(hdr) if 'warp_issue_stalled' in h and h.endswith('_per_warp_active.pct') and r[i]]
+        stalls = [(float(r[i] or 0), h) for i, h in enumerate(hdr) if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued") and r[i]]
         for v, h in sorted(stalls, reverse=True)[:6]:
-            print(f'  stall {h.split("stalled_")[1][:-20]:40s} {v:.1f} %')
+            print(f'  stall samples {h.split("stalled_")[1]:40s} {v:.0f}')
 if __name__ == '__main__':
     main(sys.argv[1])

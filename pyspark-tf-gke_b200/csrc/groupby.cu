@@ -19,6 +19,7 @@
 // the exchange (hash_partition), so a key's rank and its slot are independent
 // bits of one hash.
 #include "common.cuh"
+#include "scatter.cuh"
 
 namespace etl {
 
@@ -362,17 +363,6 @@ __global__ void __launch_bounds__(256) groupby_compact_kernel(const uint64_t* __
 // Hash partition of (key, value) rows into P destination ranges of one output
 // buffer of 16-byte records {key, value bits} - the send buffer of the
 // all-to-all.  dest = (hi32(mix64(key)) * P) >> 32.
-constexpr int PART_TILE = 2048;
-constexpr int PART_THREADS = 256;
-constexpr int PART_MAX = 256;
-
-// destination = rank * buckets + bucket: rank from the high hash word, bucket from the low one
-// (Lemire range reductions; the bucket matches the slot ranges of gb_global_slot)
-__device__ __forceinline__ int part_dest(uint64_t key, int ranks, int buckets) {
-    const uint64_t h = mix64(key);
-    return (int)(__umulhi((unsigned)(h >> 32), (unsigned)ranks) * (unsigned)buckets + __umulhi((unsigned)h, (unsigned)buckets));
-}
-
 __global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int64_t* __restrict__ keys,
                                                                        int64_t key_stride, int64_t n, int ranks,
                                                                        int buckets, unsigned long long* counts) {
@@ -388,29 +378,23 @@ __global__ void __launch_bounds__(PART_THREADS) partition_count_kernel(const int
     if (threadIdx.x < parts && s_cnt[threadIdx.x]) atomicAdd(counts + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
 }
 
-// Where destination d's records go: base[d] + 2 * (offset[d] + running position).  For a local
-// partition every base is the one output buffer and offset[] its exclusive scan; for the fused
-// exchange base[d] is rank d's receive buffer mapped into this GPU's address space (NVLink peer
-// memory) and offset[d] the first record this rank owns there.
-struct PartDest {
-    int64_t* base[PART_MAX];
-};
-
 // exclusive scan of the destination counts
 __global__ void partition_scan_kernel(const int64_t* counts, int64_t* base, int parts) {
     int64_t run = 0;
     for (int d = 0; d < parts; ++d) { base[d] = run; run += counts[d]; }
 }
 
-__global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const int64_t* __restrict__ keys,
+__global__ void __launch_bounds__(PART_THREADS, 4) partition_scatter_kernel(const int64_t* __restrict__ keys,
                                                                          int64_t key_stride,
                                                                          const double* __restrict__ vals,
                                                                          int64_t val_stride, int64_t n, int ranks,
                                                                          int buckets, const int64_t* __restrict__ part_base,
                                                                          unsigned long long* cursor, const PartDest dst) {
+    constexpr int PER = PART_TILE / PART_THREADS;
+    constexpr int THREADS = PART_THREADS;
     const int parts = ranks * buckets;
     __shared__ unsigned int s_cnt[PART_MAX], s_off[PART_MAX];
-    __shared__ unsigned long long s_gbase[PART_MAX];
+    __shared__ long long s_delta[PART_MAX];   // record index in dst.base[d] of staged position 0
     __shared__ int64_t s_key[PART_TILE];
     __shared__ double s_val[PART_TILE];
     __shared__ uint8_t s_dest[PART_TILE];
@@ -422,13 +406,13 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
         const int64_t row0 = t * PART_TILE;
         const int rows = n - row0 < PART_TILE ? (int)(n - row0) : PART_TILE;
         // pass 1: destination and rank within (tile, destination)
-        unsigned rank[PART_TILE / PART_THREADS];
-        int dest[PART_TILE / PART_THREADS];
-        int64_t k[PART_TILE / PART_THREADS];
-        double v[PART_TILE / PART_THREADS];
+        unsigned rank[PER];
+        int dest[PER];
+        int64_t k[PER];
+        double v[PER];
 #pragma unroll
-        for (int j = 0; j < PART_TILE / PART_THREADS; ++j) {
-            const int r = j * PART_THREADS + threadIdx.x;
+        for (int j = 0; j < PER; ++j) {
+            const int r = j * THREADS + threadIdx.x;
             dest[j] = -1;
             if (r < rows) {
                 k[j] = keys[(row0 + r) * key_stride];
@@ -438,16 +422,38 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
             }
         }
         __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned run = 0;
-            for (int d = 0; d < parts; ++d) { s_off[d] = run; run += s_cnt[d]; }
-        }
+        // reserve this tile's run in every destination (atomics in flight while the offsets are scanned)
+        unsigned long long gb = 0;
         if (threadIdx.x < parts && s_cnt[threadIdx.x])
-            s_gbase[threadIdx.x] = atomicAdd(cursor + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+            gb = atomicAdd(cursor + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+        if (parts <= 32) {
+            if (threadIdx.x == 0) {
+                unsigned run = 0;
+                for (int d = 0; d < parts; ++d) { s_off[d] = run; run += s_cnt[d]; }
+            }
+        } else if (threadIdx.x < 32) {  // one warp, PART_MAX / 32 destinations per lane
+            unsigned tot = 0;
+#pragma unroll
+            for (int q = 0; q < PART_MAX / 32; ++q) tot += s_cnt[threadIdx.x * (PART_MAX / 32) + q];
+            unsigned incl = tot;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned up = __shfl_up_sync(0xffffffffu, incl, d);
+                if ((int)threadIdx.x >= d) incl += up;
+            }
+            unsigned run = incl - tot;
+#pragma unroll
+            for (int q = 0; q < PART_MAX / 32; ++q) {
+                s_off[threadIdx.x * (PART_MAX / 32) + q] = run;
+                run += s_cnt[threadIdx.x * (PART_MAX / 32) + q];
+            }
+        }
         __syncthreads();
+        if (threadIdx.x < parts)
+            s_delta[threadIdx.x] = (long long)part_base[threadIdx.x] + (long long)gb - (long long)s_off[threadIdx.x];
         // pass 2: stage by destination, then write each destination's run contiguously
 #pragma unroll
-        for (int j = 0; j < PART_TILE / PART_THREADS; ++j) {
+        for (int j = 0; j < PER; ++j) {
             if (dest[j] < 0) continue;
             const unsigned pos = s_off[dest[j]] + rank[j];
             s_key[pos] = k[j];
@@ -455,9 +461,9 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
             s_dest[pos] = (uint8_t)dest[j];
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < rows; i += PART_THREADS) {
+        for (int i = threadIdx.x; i < rows; i += THREADS) {
             const int d = s_dest[i];
-            const int64_t g = part_base[d] + (int64_t)s_gbase[d] + (i - (int)s_off[d]);
+            const int64_t g = (int64_t)s_delta[d] + i;
             longlong2 rec;
             rec.x = s_key[i];
             rec.y = __double_as_longlong(s_val[i]);
@@ -469,6 +475,29 @@ __global__ void __launch_bounds__(PART_THREADS) partition_scatter_kernel(const i
 }  // namespace etl
 
 using etl::Handle;
+
+// The scatter pass: input by bulk async copies (scatter.cuh) when the rows are two contiguous
+// columns or {key, value} records; the register-staged kernel takes every other stride / alignment.
+static cudaError_t launch_partition_scatter(const Handle* h, const int64_t* keys, int64_t key_stride, const double* vals,
+                                            int64_t val_stride, int64_t n, int ranks, int buckets, const int64_t* part_base,
+                                            unsigned long long* cursor, const etl::PartDest& dst, cudaStream_t stream) {
+    static const int pipe = [] { const char* e = getenv("ETL_PART_PIPE"); return e ? atoi(e) : 1; }();
+    const bool columns = key_stride == 1 && val_stride == 1 && etl::aligned16(keys) && etl::aligned16(vals);
+    const bool records = key_stride == 2 && val_stride == 2 && etl::aligned16(keys) &&
+                         reinterpret_cast<const int64_t*>(vals) == keys + 1;
+    if (pipe && (columns || records)) {
+        etl::ScatterJob job{};
+        job.keys = keys; job.vals = vals; job.n = n; job.ranks = ranks; job.buckets = buckets;
+        job.parts = ranks * buckets; job.dest_base = part_base; job.cursor = cursor;
+        return columns ? etl::launch_scatter_pipelined<false>(h->sm_count, job, dst, 1, n, stream)
+                       : etl::launch_scatter_pipelined<true>(h->sm_count, job, dst, 1, n, stream);
+    }
+    const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
+    const int64_t g = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
+    etl::partition_scatter_kernel<<<(unsigned)g, etl::PART_THREADS, 0, stream>>>(keys, key_stride, vals, val_stride, n, ranks,
+                                                                                buckets, part_base, cursor, dst);
+    return cudaGetLastError();
+}
 
 static inline int gb_stride(int ncols, int minmax) { return 2 + 2 * ncols + (minmax ? 2 * ncols : 0); }
 
@@ -612,13 +641,9 @@ extern "C" int etl_hash_partition(etl_handle* hh, const int64_t* keys, int64_t k
     ETL_CUDA(cudaGetLastError());
     etl::partition_scan_kernel<<<1, 1, 0, stream>>>(d_part_counts, d_part_base, parts);
     ETL_CUDA(cudaGetLastError());
-    const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
-    int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
     etl::PartDest dst;
     for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = out_records;
-    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(
-        keys, key_stride, vals, val_stride, n, ranks, buckets, d_part_base, cursor, dst);
-    ETL_CUDA(cudaGetLastError());
+    ETL_CUDA(launch_partition_scatter(h, keys, key_stride, vals, val_stride, n, ranks, buckets, d_part_base, cursor, dst, stream));
     return ETL_OK;
 }
 
@@ -664,10 +689,6 @@ extern "C" int etl_hash_partition_scatter_peers(etl_handle* hh, const int64_t* k
     if (rc != ETL_OK) return rc;
     unsigned long long* cursor = static_cast<unsigned long long*>(h->scratch);
     ETL_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * etl::PART_MAX, stream));
-    const int64_t tiles = (n + etl::PART_TILE - 1) / etl::PART_TILE;
-    int64_t sblocks = tiles < (int64_t)h->sm_count * 4 ? tiles : (int64_t)h->sm_count * 4;
-    etl::partition_scatter_kernel<<<(unsigned)sblocks, etl::PART_THREADS, 0, stream>>>(
-        keys, key_stride, vals, val_stride, n, ranks, 1, d_peer_offset, cursor, dst);
-    ETL_CUDA(cudaGetLastError());
+    ETL_CUDA(launch_partition_scatter(h, keys, key_stride, vals, val_stride, n, ranks, 1, d_peer_offset, cursor, dst, stream));
     return ETL_OK;
 }

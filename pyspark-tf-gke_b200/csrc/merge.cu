@@ -8,7 +8,7 @@
 //
 //   level A   etl_hash_partition(ranks = 1, buckets = B)            (groupby.cu)
 //   level B   etl_hash_subpartition: every level-A bucket into `sub` pieces, one launch for all
-//             buckets (grid.y = bucket); fine index = umulhi(lo32(mix64(key)), B * sub), so
+//             buckets (grid.y = bucket; the scatter pass is scatter.cuh's pipelined kernel); fine index = umulhi(lo32(mix64(key)), B * sub), so
 //             fine / sub is the level-A bucket and the fine buckets of bucket b are the output
 //             range level A gave b - the two levels compose into one ordering;
 //   merge     etl_groupby_merge_partitioned: persistent CTAs, one fine bucket at a time: clear the
@@ -23,6 +23,7 @@
 // a key is either entirely in shared memory or entirely spilled (slots never empty again, so every
 // row of a key ends the same probe sequence the same way), hence the two outputs are disjoint.
 #include "common.cuh"
+#include "scatter.cuh"
 
 namespace etl {
 
@@ -39,8 +40,6 @@ __device__ __forceinline__ longlong2 ld_record(const longlong2* p) {
     asm volatile("ld.global.nc.L1::no_allocate.v2.s64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p));
     return r;
 }
-
-__device__ __forceinline__ unsigned fine_index(uint64_t key, unsigned fine) { return __umulhi((unsigned)mix64(key), fine); }
 
 // ---------------------------------------------------------------- level B
 __global__ void __launch_bounds__(SUB_THREADS) subpartition_count_kernel(const longlong2* __restrict__ rec,
@@ -92,78 +91,6 @@ __global__ void __launch_bounds__(1024) fine_scan_kernel(const int64_t* __restri
     for (int i = lo; i < lo + per && i < n; ++i) {
         base[i] = run;
         run += counts[i];
-    }
-}
-
-__global__ void __launch_bounds__(SUB_THREADS) subpartition_scatter_kernel(const longlong2* __restrict__ rec,
-                                                                           const int64_t* __restrict__ bucket_base,
-                                                                           const int64_t* __restrict__ bucket_counts,
-                                                                           int sub, unsigned fine,
-                                                                           const int64_t* __restrict__ fine_base,
-                                                                           unsigned long long* cursor,
-                                                                           longlong2* __restrict__ out) {
-    __shared__ unsigned int s_cnt[SUB_MAX], s_off[SUB_MAX];
-    __shared__ unsigned long long s_gbase[SUB_MAX];
-    __shared__ longlong2 s_rec[SUB_TILE];
-    __shared__ uint8_t s_dest[SUB_TILE];
-    const int b = blockIdx.y;
-    const int64_t lo = bucket_base[b], cnt = bucket_counts[b];
-    const int64_t tiles = (cnt + SUB_TILE - 1) / SUB_TILE;
-    const size_t f0 = (size_t)b * sub;
-    for (int64_t t = blockIdx.x; t < tiles; t += gridDim.x) {
-        __syncthreads();
-        s_cnt[threadIdx.x] = 0;
-        __syncthreads();
-        const int64_t row0 = lo + t * SUB_TILE;
-        const int rows = cnt - t * SUB_TILE < SUB_TILE ? (int)(cnt - t * SUB_TILE) : SUB_TILE;
-        unsigned rank[SUB_TILE / SUB_THREADS];
-        int dest[SUB_TILE / SUB_THREADS];
-        longlong2 r[SUB_TILE / SUB_THREADS];
-#pragma unroll
-        for (int j = 0; j < SUB_TILE / SUB_THREADS; ++j) {
-            const int i = j * SUB_THREADS + threadIdx.x;
-            if (i < rows) r[j] = ld_record(rec + row0 + i);
-        }
-#pragma unroll
-        for (int j = 0; j < SUB_TILE / SUB_THREADS; ++j) {
-            const int i = j * SUB_THREADS + threadIdx.x;
-            dest[j] = -1;
-            if (i < rows) {
-                dest[j] = (int)((fine_index((uint64_t)r[j].x, fine) - (unsigned)f0) & (SUB_MAX - 1));
-                rank[j] = atomicAdd(&s_cnt[dest[j]], 1u);
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x < 32) {  // exclusive scan of the tile's counts by one warp, 8 per lane
-            unsigned c[SUB_MAX / 32], tot = 0;
-#pragma unroll
-            for (int k = 0; k < SUB_MAX / 32; ++k) { c[k] = s_cnt[threadIdx.x * (SUB_MAX / 32) + k]; tot += c[k]; }
-            unsigned incl = tot;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const unsigned up = __shfl_up_sync(0xffffffffu, incl, d);
-                if ((int)threadIdx.x >= d) incl += up;
-            }
-            unsigned run = incl - tot;
-#pragma unroll
-            for (int k = 0; k < SUB_MAX / 32; ++k) { s_off[threadIdx.x * (SUB_MAX / 32) + k] = run; run += c[k]; }
-        }
-        if (threadIdx.x < sub && s_cnt[threadIdx.x])
-            s_gbase[threadIdx.x] = atomicAdd(cursor + f0 + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < SUB_TILE / SUB_THREADS; ++j) {
-            if (dest[j] < 0) continue;
-            const unsigned pos = s_off[dest[j]] + rank[j];
-            s_rec[pos] = r[j];
-            s_dest[pos] = (uint8_t)dest[j];
-        }
-        __syncthreads();
-        for (int i = threadIdx.x; i < rows; i += SUB_THREADS) {
-            const int d = s_dest[i];
-            const int64_t g = fine_base[f0 + d] + (int64_t)s_gbase[d] + (i - (int)s_off[d]);
-            out[g] = s_rec[i];
-        }
     }
 }
 
@@ -313,10 +240,12 @@ extern "C" int etl_hash_subpartition(etl_handle* hh, const int64_t* records, int
     ETL_CUDA(cudaGetLastError());
     etl::fine_scan_kernel<<<1, 1024, 0, stream>>>(d_fine_counts, d_fine_base, fine);
     ETL_CUDA(cudaGetLastError());
-    etl::subpartition_scatter_kernel<<<grid, etl::SUB_THREADS, 0, stream>>>(
-        rec, d_bucket_base, d_bucket_counts, sub, (unsigned)fine, d_fine_base, cursor,
-        reinterpret_cast<longlong2*>(out_records));
-    ETL_CUDA(cudaGetLastError());
+    etl::ScatterJob job{};
+    job.keys = records; job.seg_base = d_bucket_base; job.seg_counts = d_bucket_counts; job.sub = sub;
+    job.fine = (unsigned)fine; job.parts = sub; job.dest_base = d_fine_base; job.cursor = cursor;
+    etl::PartDest dst;
+    for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = out_records;
+    ETL_CUDA(etl::launch_scatter_pipelined<true>(h->sm_count, job, dst, buckets, max_bucket_records, stream));
     return ETL_OK;
 }
 

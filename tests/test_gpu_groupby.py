@@ -236,3 +236,25 @@ def test_smem_merge_reports_reserved_key_and_small_output(eng):
         eng.groupby_result(eng.groupby_partitioned_sum(torch.from_numpy(keys).to(eng.device), dv, 1000, groups_hint=1000))
     assert pkg.Engine.merge_plan(10**9, 10**8) == (256, 255) and pkg.Engine.merge_plan(1000, 0) == (1, 1)
     assert pkg.Engine.merge_plan(125_000_000, 14_000_000) == (96, 95)
+
+
+def test_hash_partition_unaligned_and_strided_inputs_take_the_register_staged_kernel(eng):
+    # bulk async copies need 16-byte aligned sources: a column view that starts 8 bytes into an
+    # allocation, and a stride-3 layout, must give the same partition through the other kernel
+    n, ranks, buckets = 100_001, 2, 4
+    keys, _ = S.host_column(5, 0, S.KIND_KEY64, n + 1, modulus=10**6)
+    vals, _ = S.host_column(5, 1, S.KIND_REAL, n + 1)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    wide = torch.zeros(3 * n, dtype=torch.int64, device=eng.device)
+    wide[0::3], wide[1::3] = dk[1:], dv[1:].view(torch.int64)
+    dest = O.partition_dest(keys[1:], ranks, buckets)
+    want_counts = np.bincount(dest, minlength=ranks * buckets).tolist()
+    for k_in, v_in, ks, vs in ((dk[1:], dv[1:], 1, 1), (wide, wide[1:].view(torch.float64), 3, 3)):
+        rec, counts, base = eng.hash_partition(k_in, v_in, ranks, buckets, n=n, key_stride=ks, val_stride=vs)
+        assert counts.cpu().tolist() == want_counts
+        rec = rec.cpu().numpy()
+        b = base.cpu().tolist() + [n]
+        for d in range(ranks * buckets):
+            got = rec[b[d]:b[d + 1]]
+            want = np.stack([keys[1:][dest == d], vals[1:][dest == d].view(np.int64)], axis=1)
+            assert np.array_equal(got[np.lexsort((got[:, 1], got[:, 0]))], want[np.lexsort((want[:, 1], want[:, 0]))])

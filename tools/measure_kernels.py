@@ -167,6 +167,48 @@ def m_partition(eng, args):
                  "count pass reads keys (8 B), scatter pass reads 16 B and writes 16 B per row")
 
 
+def m_merge(eng, args):
+    """The shared-memory merge of config 4 stage by stage (csrc/merge.cu)."""
+    from pyspark_tf_gke_b200 import _lib
+    cfg = S.CONFIG4
+    n = cfg["rows"] if args.full else cfg["rows"] // 4
+    groups = cfg["groups"] if args.full else cfg["groups"] // 4
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=groups, with_valid=False).data
+    val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False).data
+    B, sub = eng.merge_plan(n, groups)
+    fine = B * sub
+    res = []
+    mean, mn = timed(lambda: eng.hash_partition(key, val, 1, B), steps=3, warmup=1)
+    res.append(entry(f"level 1: hash_partition into {B} buckets, {n} rows", n, n * 40, mean, mn, None,
+                     "count pass reads keys (8 B), scatter reads 16 B and writes 16 B per row"))
+    level1, counts, base = eng.hash_partition(key, val, 1, B)
+    fcounts, fbase = eng.empty(fine, torch.int64), eng.empty(fine, torch.int64)
+    pieces = torch.empty((n, 2), dtype=torch.int64, device=eng.device)
+
+    def level2():
+        _lib.check(eng.lib.etl_hash_subpartition(eng._h, level1.data_ptr(), B, sub, counts.data_ptr(), base.data_ptr(), n,
+                                                 fcounts.data_ptr(), fbase.data_ptr(), pieces.data_ptr(), eng._stream()))
+
+    mean, mn = timed(level2, steps=3, warmup=1)
+    res.append(entry(f"level 2: hash_subpartition {B} x {sub} = {fine} pieces", n, n * 48, mean, mn, None,
+                     "count pass reads the records (16 B), scatter reads 16 B and writes 16 B per row"))
+    cap = groups + groups // 8
+    outs = [eng.empty(cap, torch.int64) for _ in range(3)] + [eng.empty(cap, torch.float64)]
+    counters = eng.empty(4, torch.int64)
+
+    def merge():
+        _lib.check(eng.lib.etl_groupby_merge_partitioned(
+            eng._h, pieces.data_ptr(), fine, fcounts.data_ptr(), fbase.data_ptr(), eng.MERGE_SLOTS, cap, outs[0].data_ptr(),
+            outs[1].data_ptr(), outs[2].data_ptr(), outs[3].data_ptr(), level1.data_ptr(), n, counters.data_ptr(),
+            eng._stream()))
+
+    mean, mn = timed(merge, steps=3, warmup=1)
+    g, spilled = counters.cpu().tolist()[:2]
+    res.append(entry(f"groupby_merge_kernel: {fine} pieces, {g} groups, {spilled} spilled", n, n * 16 + g * 32, mean, mn, None,
+                     "reads 16 B per record, writes 32 B per group; table updates stay in shared memory"))
+    return res
+
+
 def health_like_text(target_rows):
     with gzip.open(os.path.join(ROOT, "tests", "golden", "health_workloads.csv.gz"), "rb") as fh:
         raw = fh.read()
@@ -303,7 +345,7 @@ def m_trainer(eng, args):
 
 
 ALL = {"trainer": m_trainer, "kmeans": m_kmeans, "parquet": m_parquet, "null_count": m_null_count, "sum_count": m_sum_count, "histogram": m_histogram, "groupby3": m_groupby3,
-       "groupby4": m_groupby4, "partition": m_partition, "csv": m_csv, "features": m_features}
+       "groupby4": m_groupby4, "merge": m_merge, "partition": m_partition, "csv": m_csv, "features": m_features}
 
 
 def main():
