@@ -338,21 +338,26 @@ ETL_API int etl_hash_partition(etl_handle* h, const int64_t* keys, int64_t key_s
  * buffer for a separate all-to-all, the scatter pass writes every record
  * straight into its destination rank's receive buffer over NVLink - peer memory
  * mapped into this process (CUDA IPC / torch symmetric memory).  Protocol:
- *   1. etl_hash_partition_count -> this rank's per-destination counts;
+ *   1. etl_hash_partition_count -> this rank's counts per destination
+ *      (rank r, bucket b) = r * buckets + b;
  *   2. the caller all-gathers the counts (tiny) and derives, for every
- *      destination d, the first record this rank owns in d's receive buffer
- *      (sum of the lower ranks' counts for d) -> d_peer_offset[ranks] on the device;
- *   3. etl_hash_partition_scatter_peers: peer_records[d] (host array of device
- *      pointers) = rank d's receive buffer as mapped here (the local buffer for d
- *      == this rank); record i of destination d lands at peer_records[d] + 2 *
- *      (d_peer_offset[d] + position);
+ *      destination, the first record this rank owns in rank r's receive buffer
+ *      -> d_peer_offset[ranks * buckets] on the device.  With buckets > 1 a
+ *      receive buffer is laid out bucket by bucket (within a bucket: source rank
+ *      by source rank), i.e. it arrives already partitioned for
+ *      etl_hash_subpartition / a bucket-wise merge - the receiver's own first
+ *      partition pass is folded into the exchange;
+ *   3. etl_hash_partition_scatter_peers: peer_records[r] (host array of `ranks`
+ *      device pointers) = rank r's receive buffer as mapped here (the local
+ *      buffer for r == this rank); record i of destination d = r * buckets + b
+ *      lands at peer_records[r] + 2 * (d_peer_offset[d] + position);
  *   4. a cross-rank barrier after the kernel, then every rank merges what landed.
  * No reference counterpart below the Spark shuffle. */
 ETL_API int etl_hash_partition_count(etl_handle* h, const int64_t* keys, int64_t key_stride, int64_t n, int32_t ranks,
                              int32_t buckets, int64_t* d_part_counts, void* stream);
 ETL_API int etl_hash_partition_scatter_peers(etl_handle* h, const int64_t* keys, int64_t key_stride, const double* vals,
-                                     int64_t val_stride, int64_t n, int32_t ranks, int64_t* const* peer_records,
-                                     const int64_t* d_peer_offset, void* stream);
+                                     int64_t val_stride, int64_t n, int32_t ranks, int32_t buckets,
+                                     int64_t* const* peer_records, const int64_t* d_peer_offset, void* stream);
 
 /* The reduce side of the exchange with the aggregation table in SHARED memory
  * (the final HashAggregate above the Exchange node; north-star item 4).  The

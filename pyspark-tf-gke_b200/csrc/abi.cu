@@ -59,7 +59,7 @@ using etl::Handle;
 
 extern "C" {
 
-int etl_abi_version(void) { return 1; }
+int etl_abi_version(void) { return 2; }
 
 const char* etl_last_error(void) { return etl::g_err; }
 

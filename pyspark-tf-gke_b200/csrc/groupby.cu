@@ -668,11 +668,11 @@ extern "C" int etl_hash_partition_count(etl_handle* hh, const int64_t* keys, int
 
 extern "C" int etl_hash_partition_scatter_peers(etl_handle* hh, const int64_t* keys, int64_t key_stride,
                                                 const double* vals, int64_t val_stride, int64_t n, int32_t ranks,
-                                                int64_t* const* peer_records, const int64_t* d_peer_offset,
-                                                void* stream_) {
+                                                int32_t buckets, int64_t* const* peer_records,
+                                                const int64_t* d_peer_offset, void* stream_) {
     ETL_REQUIRE(hh && peer_records && d_peer_offset, "hash_partition_scatter_peers: NULL argument");
-    ETL_REQUIRE(ranks >= 1 && ranks <= etl::PART_MAX, "hash_partition_scatter_peers: ranks=%d not in 1..%d", ranks,
-                etl::PART_MAX);
+    ETL_REQUIRE(ranks >= 1 && buckets >= 1 && (int64_t)ranks * buckets <= etl::PART_MAX,
+                "hash_partition_scatter_peers: ranks=%d x buckets=%d must be in 1..%d", ranks, buckets, etl::PART_MAX);
     ETL_REQUIRE(n >= 0 && key_stride >= 1 && val_stride >= 1, "hash_partition_scatter_peers: bad n / stride");
     if (n == 0) return ETL_OK;
     ETL_REQUIRE(keys && vals, "hash_partition_scatter_peers: keys / vals is NULL");
@@ -682,13 +682,14 @@ extern "C" int etl_hash_partition_scatter_peers(etl_handle* hh, const int64_t* k
     for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = nullptr;
     for (int d = 0; d < ranks; ++d) {
         ETL_REQUIRE(peer_records[d] && etl::aligned16(peer_records[d]), "hash_partition_scatter_peers: peer buffer %d NULL or misaligned", d);
-        dst.base[d] = peer_records[d];
+        for (int b = 0; b < buckets; ++b) dst.base[d * buckets + b] = peer_records[d];
     }
     ETL_CUDA(cudaSetDevice(h->device));
     int rc = etl::arena_reserve(h, sizeof(unsigned long long) * etl::PART_MAX);
     if (rc != ETL_OK) return rc;
     unsigned long long* cursor = static_cast<unsigned long long*>(h->scratch);
     ETL_CUDA(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long) * etl::PART_MAX, stream));
-    ETL_CUDA(launch_partition_scatter(h, keys, key_stride, vals, val_stride, n, ranks, 1, d_peer_offset, cursor, dst, stream));
+    ETL_CUDA(launch_partition_scatter(h, keys, key_stride, vals, val_stride, n, ranks, buckets, d_peer_offset, cursor, dst,
+                                      stream));
     return ETL_OK;
 }

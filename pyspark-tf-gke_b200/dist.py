@@ -91,22 +91,37 @@ class PeerExchange:
         self.handle = symm.rendezvous(self.buf, self.group.group_name)
         self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
 
-    def exchange(self, keys: torch.Tensor, vals: torch.Tensor):
-        """-> (records int64[m, 2] view of this rank's receive buffer, m)."""
+    def exchange(self, keys: torch.Tensor, vals: torch.Tensor, buckets: int = 1):
+        """-> (records int64[m, 2] view of this rank's receive buffer, m, bucket_counts,
+        bucket_base).  With buckets > 1 the records arrive grouped by table bucket
+        (device int64[buckets] counts / first records): the receiver's first partition
+        level is done by the senders' scatter.  world_size * buckets <= 256."""
         eng, size, rank = self.eng, self.size, self.rank
-        counts = eng.hash_partition_count(keys, size)
-        matrix = torch.empty((size, size), dtype=torch.int64, device=eng.device)   # [source, destination]
+        counts = eng.hash_partition_count(keys, size, buckets)
+        matrix = torch.empty((size, size * buckets), dtype=torch.int64, device=eng.device)   # [source, destination]
         dist.all_gather_into_tensor(matrix.view(-1), counts, group=self.group)
-        offsets = matrix[:rank].sum(dim=0) if rank else torch.zeros(size, dtype=torch.int64, device=eng.device)
-        incoming = matrix.sum(dim=0)
-        inc = incoming.cpu().tolist()
+        offsets, tot, bucket_start = peer_layout(matrix, rank, size, buckets)
+        inc = tot.sum(dim=1).cpu().tolist()
         if max(inc) > self.capacity:
             raise RuntimeError(f"PeerExchange: a rank would receive {max(inc)} records, buffer holds {self.capacity}")
         self.handle.barrier()            # everyone is done reading the previous exchange's records
-        eng.hash_partition_scatter_peers(keys, vals, self.peer_ptrs, offsets.contiguous())
+        eng.hash_partition_scatter_peers(keys, vals, self.peer_ptrs, offsets, buckets=buckets)
         self.handle.barrier()            # every peer's stores into this buffer have landed
         m = int(inc[rank])
-        return self.buf[:m], m
+        return self.buf[:m], m, tot[rank].contiguous(), bucket_start[rank].contiguous()
+
+
+def peer_layout(matrix: torch.Tensor, rank: int, size: int, buckets: int):
+    """Layout of the receive buffers of a bucketed peer exchange.  matrix[s, r * buckets + b]
+    = records source s sends to (rank r, bucket b).  A receive buffer holds its buckets one
+    after another and, inside a bucket, the sources one after another.  -> (offsets
+    int64[size * buckets]: first record of this rank's run for every (r, b); tot[r, b]:
+    records of bucket b on rank r; bucket_start[r, b]: first record of that bucket)."""
+    per = matrix.view(size, size, buckets)              # [source, rank, bucket]
+    tot = per.sum(dim=0)
+    bucket_start = torch.cumsum(tot, dim=1) - tot
+    offsets = bucket_start + per[:rank].sum(dim=0)
+    return offsets.contiguous().view(-1), tot, bucket_start
 
 
 def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_bytes: int = 32 << 20) -> int:
@@ -120,7 +135,7 @@ def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_
 
 def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
                         buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None,
-                        merge: str = "smem"):
+                        merge: str = "smem", exchange_buckets: Optional[int] = None):
     """Config 4: hash-partition -> all-to-all -> local final merge.
 
     Sender: one partition pass groups the rows by destination rank (few
@@ -140,7 +155,10 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     pieces whose groups fit a shared-memory table, so no table update touches L2 or
     HBM (`capacity` is then the room for output groups; `groups_hint` = expected
     distinct keys over ALL ranks sizes the pieces).  merge="table" keeps the global
-    table.  Returns the rank-local result for Engine.groupby_result."""
+    table.  exchange_buckets: None = the fused exchange also does the receiver's
+    first partition level (destinations = ranks x buckets, shorter runs over
+    NVLink); 1 = the exchange partitions by rank only and the receiver runs the
+    first level itself.  Returns the rank-local result for Engine.groupby_result."""
     rank, size = world()
     mark = mark or (lambda name: None)
     if merge not in ("smem", "table"):
@@ -149,9 +167,23 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     B = choose_buckets(capacity, 1) if buckets is None else buckets
     mark("init")
     if size > 1:
+        if peer is not None and merge == "smem" and exchange_buckets != 1:
+            # the senders' scatter also does the receiver's first partition level
+            n_local = keys.shape[0]
+            hint = -(-groups_hint // size) + groups_hint // (8 * size) if groups_hint > 0 else 0
+            B, sub = eng.merge_plan(n_local, hint, max_buckets=min(exchange_buckets or 256, max(1, 256 // size)))
+            mark("partition")
+            received, m, bcounts, bbase = peer.exchange(keys, vals, buckets=B)
+            mark("exchange")
+            mark("level1")
+            # the receive buffer is overwritten by the next exchange: spilled records get their own room
+            spill = torch.empty((max(m // 8, 1 << 16), 2), dtype=torch.int64, device=eng.device)
+            pg = eng.groupby_merge_buckets(received, bcounts, bbase, B, sub, m, capacity, mark=mark, spill=spill)
+            mark("merge")
+            return pg
         if peer is not None:
             mark("partition")
-            received, _ = peer.exchange(keys, vals)
+            received, _, _, _ = peer.exchange(keys, vals)
         else:
             records, counts, _ = eng.hash_partition(keys, vals, size, 1)
             mark("partition")

@@ -413,14 +413,16 @@ class Engine:
 
     def hash_partition_scatter_peers(self, keys: torch.Tensor, vals: torch.Tensor, peer_ptrs: Sequence[int],
                                      peer_offset: torch.Tensor, n: Optional[int] = None, key_stride: int = 1,
-                                     val_stride: int = 1) -> None:
+                                     val_stride: int = 1, buckets: int = 1) -> None:
         """Partition + exchange in one kernel: records go straight into the peers'
-        receive buffers (peer_ptrs[d] = rank d's buffer mapped into this process)."""
+        receive buffers (peer_ptrs[r] = rank r's buffer mapped into this process);
+        peer_offset int64[ranks * buckets] = first record of every (rank, bucket) run."""
         n = keys.shape[0] if n is None else n
         ranks = len(peer_ptrs)
         P = C.c_void_p * ranks
         _lib.check(self.lib.etl_hash_partition_scatter_peers(self._h, _ptr(keys), key_stride, _ptr(vals), val_stride, n,
-                                                             ranks, P(*peer_ptrs), peer_offset.data_ptr(), self._stream()))
+                                                             ranks, buckets, P(*peer_ptrs), peer_offset.data_ptr(),
+                                                             self._stream()))
         self.launches += 1 if n else 0
 
     def groupby_accumulate_records(self, gt: "GroupTable", records: torch.Tensor, lo: int, hi: int,
@@ -438,14 +440,15 @@ class Engine:
     MERGE_GROUPS_PER_PIECE = 1536   # target groups per piece: load factor ~0.37
 
     @staticmethod
-    def merge_plan(records: int, groups_hint: int, groups_per_piece: int = MERGE_GROUPS_PER_PIECE):
+    def merge_plan(records: int, groups_hint: int, groups_per_piece: int = MERGE_GROUPS_PER_PIECE, max_buckets: int = 256):
         """-> (buckets, sub): how finely to cut `records` records holding about
-        `groups_hint` distinct keys so one piece's groups fit a shared table."""
+        `groups_hint` distinct keys so one piece's groups fit a shared table.
+        max_buckets bounds the first level (256 / ranks when the exchange does it)."""
         g = max(1, min(int(groups_hint) if groups_hint > 0 else records, records))
         fine = min(65536, max(1, -(-g // groups_per_piece)))
-        if fine <= 256:
+        if fine <= max_buckets:
             return fine, 1
-        b = int(np.ceil(np.sqrt(fine)))
+        b = min(max_buckets, int(np.ceil(np.sqrt(fine))))
         return b, min(256, -(-fine // b))
 
     def groupby_partitioned_sum(self, keys: torch.Tensor, vals: torch.Tensor, out_capacity: int, groups_hint: int = 0,
@@ -457,11 +460,22 @@ class Engine:
         enqueued on the current stream; nothing is read back until groupby_result."""
         n = keys.shape[0] if n is None else n
         buckets, sub = plan or self.merge_plan(n, groups_hint)
-        slots = slots or self.MERGE_SLOTS
-        mark = mark or (lambda name: None)
         level1, counts, base = self.hash_partition(keys, vals, 1, buckets, n=n, key_stride=key_stride, val_stride=val_stride)
-        mark("level1")
-        fine, pieces, spill = buckets, level1, None
+        if mark:
+            mark("level1")
+        return self.groupby_merge_buckets(level1, counts, base, buckets, sub, n, out_capacity, slots=slots, mark=mark)
+
+    def groupby_merge_buckets(self, level1: torch.Tensor, counts: torch.Tensor, base: torch.Tensor, buckets: int, sub: int,
+                              n: int, out_capacity: int, slots: Optional[int] = None, mark=None,
+                              spill: Optional[torch.Tensor] = None) -> "PartitionedGroups":
+        """The part after the first partition level: `level1` int64[>= n, 2] holds n
+        records grouped into `buckets` buckets (device counts / base), as written by
+        hash_partition(ranks=1) or by a bucketed peer exchange.  sub > 1 cuts every
+        bucket into `sub` pieces first.  `spill` (int64[k, 2]) takes records of
+        over-full pieces; by default the level-1 buffer when the second level has made
+        it redundant, else a new buffer of n records."""
+        slots = slots or self.MERGE_SLOTS
+        fine, pieces = buckets, level1
         if sub > 1 and n:
             fine = buckets * sub
             fcounts, fbase = self.empty(fine, torch.int64), self.empty(fine, torch.int64)
@@ -470,8 +484,11 @@ class Engine:
                                                       base.data_ptr(), n, fcounts.data_ptr(), fbase.data_ptr(),
                                                       pieces.data_ptr(), self._stream()))
             self.launches += 3
-            counts, base, spill = fcounts, fbase, level1     # the level-1 buffer is dead: it takes the spill
-        mark("level2")
+            counts, base = fcounts, fbase
+            if spill is None:
+                spill = level1[:n]     # dead from here on
+        if mark:
+            mark("level2")
         if spill is None:
             spill = torch.empty((max(n, 1), 2), dtype=torch.int64, device=self.device)
         out_keys, out_rows = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.int64)

@@ -72,3 +72,29 @@ def test_single_process_paths_are_identity():
     assert D.exchange_records(rec, torch.tensor([5])) is rec
     assert D.merge_label_tables(["a"], [3]) == (["a"], [3])
     assert D.world() == (0, 1)
+
+
+def test_peer_layout_places_every_run_exactly_once():
+    # bucketed peer exchange: receive buffers hold their buckets one after another, inside a
+    # bucket the sources one after another; every rank derives its own runs from the gathered
+    # count matrix - together the runs must tile each buffer without gap or overlap
+    rng = np.random.default_rng(7)
+    for size, buckets in ((1, 1), (2, 1), (2, 5), (4, 64), (8, 32)):
+        m = rng.integers(0, 50, size=(size, size * buckets)).astype(np.int64)
+        m[rng.random(m.shape) < 0.2] = 0
+        matrix = torch.from_numpy(m)
+        runs = {r: [] for r in range(size)}
+        for rank in range(size):
+            off, tot, start = D.peer_layout(matrix, rank, size, buckets)
+            assert tot.shape == (size, buckets) and tot.numpy().tolist() == m.reshape(size, size, buckets).sum(0).tolist()
+            for r in range(size):
+                for b in range(buckets):
+                    d = r * buckets + b
+                    runs[r].append((int(off[d]), int(m[rank, d]), b, rank))
+                    assert int(start[r, b]) <= int(off[d])
+        for r in range(size):
+            pos, last = 0, (-1, -1)
+            for first, length, b, src in sorted(runs[r], key=lambda x: (x[2], x[3])):   # bucket-major, then source
+                assert first == pos
+                pos += length
+            assert pos == int(m.reshape(size, size, buckets)[:, r, :].sum())

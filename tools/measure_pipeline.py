@@ -31,6 +31,9 @@ def main():
     ap.add_argument("--rows", type=int, default=10_000_000)
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64", "none"])
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--split-text", action="store_true",
+                    help="N GPUs: every rank holds only its own 1/N of the text (config 5: the file split by byte range "
+                         "at record boundaries) instead of the whole text sharded by row index")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -39,7 +42,8 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = pkg.Engine(local)
-    raw, rows = health_like_text(args.rows)
+    split = args.split_text and world > 1
+    raw, rows = health_like_text(args.rows // world if split else args.rows)
     t0 = time.perf_counter()
     text = pkg.table.upload_text(eng, raw)
     torch.cuda.synchronize()
@@ -47,7 +51,7 @@ def main():
     os.environ.setdefault("ETL_SKIP_KMEANS", "1")  # this tool times the ETL stage; KMeans is measured in measure_kernels
     wl = pkg.KMeansWorkload(eng)
     wl.logger.setLevel("ERROR")
-    shard = (rank, world) if world > 1 else None
+    shard = (rank, world) if (world > 1 and not split) else None
     dtype = {"f32": torch.float32, "f64": torch.float64, "none": None}[args.dtype]
 
     def run():
@@ -75,10 +79,15 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     if rank == 0:
         total = float(tt.sum().item())
-        line = {"workload": f"full stage on {rows} CSV records ({len(raw) / 1e9:.2f} GB of text)", "n_gpus": world,
+        if split:
+            rows, nbytes = rows * world, len(raw) * world
+        else:
+            nbytes = len(raw)
+        line = {"workload": f"full stage on {rows} CSV records ({nbytes / 1e9:.2f} GB of text)", "n_gpus": world,
+                "text": "one byte range per rank" if split else "whole text on every rank, rows sharded",
                 "ms": {"decode": float(tt[0]), "aggregate+project+index": float(tt[1]), "features": float(tt[2]),
                        "total": total},
-                "rows_per_s": rows / (total * 1e-3), "text_gb_per_s": len(raw) / 1e9 / (total * 1e-3),
+                "rows_per_s": rows / (total * 1e-3), "text_gb_per_s": nbytes / 1e9 / (total * 1e-3),
                 "features": None if F is None else [int(x) for x in F.shape] + [str(F.dtype)],
                 "h2d_copy_s": h2d_s, "labels": len(model.labels), "means": model.means,
                 "rows_after_filter": model.rows_after_filter, "null_keys": model.null_key_count}

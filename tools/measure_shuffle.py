@@ -42,6 +42,8 @@ def main():
                     help="peer = partition fused with NVLink peer stores; nccl = send buffer + all_to_all_single")
     ap.add_argument("--merge", default="smem", choices=["smem", "table"],
                     help="smem = two partition levels + shared-memory tables; table = bucket-by-bucket global table")
+    ap.add_argument("--exchange-buckets", type=int, default=0,
+                    help="peer + smem: 0 = the exchange also cuts by table bucket; 1 = by rank only, receiver partitions")
     ap.add_argument("--out-capacity", type=int, default=0, help="room for output groups per rank (0 = table capacity)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -86,6 +88,7 @@ def main():
         barrier()
         marks = {"start": ev()}
         gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer, merge=args.merge,
+                                   exchange_buckets=args.exchange_buckets or None,
                                    mark=lambda name: marks.__setitem__(name, ev()))
         torch.cuda.synchronize()
         if it >= args.warmup:
@@ -113,7 +116,7 @@ def main():
         line = {"workload": "config4 shuffle+aggregate", "n_gpus": world, "rows_total": n * world, "groups": args.groups,
                 "distinct_keys_found": int(tot[1].item()), "rows_conserved": ok_rows, "sum_matches_column_sum": ok_sum,
                 "ms": mean, "rows_per_s": n * world / (mean["total"] * 1e-3),
-                "buckets_per_rank": B if args.merge == "table" else None, "merge": args.merge,
+                "buckets_per_rank": B if args.merge == "table" else None, "merge": args.merge, "exchange_buckets": args.exchange_buckets or "auto",
                 "pieces_per_rank": getattr(gt, "pieces", None), "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
                 "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
                 "steps": args.steps}
