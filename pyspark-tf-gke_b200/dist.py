@@ -155,10 +155,11 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     pieces whose groups fit a shared-memory table, so no table update touches L2 or
     HBM (`capacity` is then the room for output groups; `groups_hint` = expected
     distinct keys over ALL ranks sizes the pieces).  merge="table" keeps the global
-    table.  exchange_buckets: None = the fused exchange also does the receiver's
-    first partition level (destinations = ranks x buckets, shorter runs over
-    NVLink); 1 = the exchange partitions by rank only and the receiver runs the
-    first level itself.  Returns the rank-local result for Engine.groupby_result."""
+    table.  exchange_buckets > 1: the fused exchange also does the receiver's
+    first partition level (destinations = ranks x buckets: one pass less, but
+    shorter runs over NVLink - 385 instead of 555 GB/s per GPU); 1 = the exchange
+    partitions by rank only and the receiver runs the first level itself; None
+    picks the faster one as measured on config 4 (cut by bucket on 2 GPUs only).  Returns the rank-local result for Engine.groupby_result."""
     rank, size = world()
     mark = mark or (lambda name: None)
     if merge not in ("smem", "table"):
@@ -167,6 +168,8 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     B = choose_buckets(capacity, 1) if buckets is None else buckets
     mark("init")
     if size > 1:
+        if exchange_buckets is None and size > 2:
+            exchange_buckets = 1   # measured (config 4): short NVLink runs cost more than the receiver's own pass
         if peer is not None and merge == "smem" and exchange_buckets != 1:
             # the senders' scatter also does the receiver's first partition level
             n_local = keys.shape[0]
