@@ -13,5 +13,6 @@ from .table import DeviceTable, read_csv  # noqa: F401
 from .parquet import ParquetUnsupported, read_parquet  # noqa: F401
 from .train_input import load_csv, load_csv_device, write_label_map  # noqa: F401
 from .trainer import DeepModel, run_deep_training  # noqa: F401
+from . import mlformat  # noqa: F401
 
 __all__ = ["EtlError", "Engine", "Column"]

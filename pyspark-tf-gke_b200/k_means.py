@@ -75,6 +75,16 @@ class EtlPipelineModel:
         numerics = self.numerics if numerics is None else numerics
         return self.engine.assemble_dense(index, numerics, len(self.labels), self.repeats, dtype=dtype)
 
+    def save(self, path: str) -> None:
+        """PipelineModel.save(path): Spark ML's directory layout (mlformat.py)."""
+        from . import mlformat
+        mlformat.save_pipeline_model(self, path)
+
+    @staticmethod
+    def load(path: str, engine: Optional[Engine] = None) -> "EtlPipelineModel":
+        from . import mlformat
+        return mlformat.load_pipeline_model(engine, path)
+
     def features_sparse(self, index=None, numerics=None):
         """ELL form of the SparseVector rows: (indices int32[n, repeats+3], values f64[n, repeats+3])."""
         index = self.index if index is None else index
@@ -154,10 +164,43 @@ class KMeansWorkload:
             kmeans = KMeans().setK(25).setSeed(1).setMaxIter(1000)
             self.logger.info("Training K-Means model...")
             kmeans_model = kmeans.fit(model)
+            # the reference keeps this block commented out ("using in-memory models instead",
+            # k_means.py:88-104); here it is live but off unless SAVE_MODELS is set
+            if kmeans_model is not None and os.environ.get("SAVE_MODELS", "false").lower() in ("1", "true", "yes", "y"):
+                model_path, pipeline_path = self._get_model_paths()
+                self.logger.info(f"Saving K-Means model to {model_path}")
+                kmeans_model.save(model_path, params={"k": kmeans.k, "seed": kmeans.seed, "maxIter": kmeans.maxIter})
+                self.logger.info(f"Saving K-Means pipeline to {pipeline_path}")
+                model.save(pipeline_path)
             return model, kmeans_model
         except Exception as e:
             self.logger.error(f"Error training K-Means model: {e}")
             raise
+
+    # Legacy method (k_means.py:111-116)
+    def _get_model_paths(self):
+        base_dir = os.environ.get("MODEL_OUTPUT_DIR", "/opt/spark/work-dir/models")
+        return os.path.join(base_dir, "health_kmeans_model"), os.path.join(base_dir, "health_kmeans_pipeline")
+
+    # Legacy method (k_means.py:118-135): PipelineModel.load / KMeansModel.load from Spark ML's on-disk layout
+    def load_models(self):
+        from . import mlformat
+        pr_model_path, pr_pipeline_path = self._get_model_paths()
+        self.logger.info(f"Loading K-Means model from {pr_model_path}")
+        self.logger.info(f"Loading Pipeline model from {pr_pipeline_path}")
+        try:
+            pr_pipeline_model = mlformat.load_pipeline_model(self.engine, pr_pipeline_path)
+            self.logger.info(pr_pipeline_model.__class__.__name__)
+        except Exception as e:
+            self.logger.error(f"Error loading Pipeline model: {e}")
+            raise
+        try:
+            pr_kmeans_model = mlformat.load_kmeans_model(self.engine, pr_model_path)
+            self.logger.info(pr_kmeans_model.__class__.__name__)
+        except Exception as e:
+            self.logger.error(f"Error loading KMeans model: {e}")
+            raise
+        return pr_pipeline_model, pr_kmeans_model
 
     def infer_single_row(self, spark=None, entry_str: str = "Able-Bodied", entry_num: int = 0):
         """k_means.py:138-162: one hard-coded row (entry_str, n, n + 7, n + 5) through

@@ -100,6 +100,16 @@ class KMeansModel:
     def clusterCenters(self) -> List[np.ndarray]:
         return [c.copy() for c in self.centers]
 
+    def save(self, path: str, params: Optional[dict] = None) -> None:
+        """KMeansModel.save(path): Spark ML's directory layout (mlformat.py)."""
+        from . import mlformat
+        mlformat.save_kmeans_model(self, path, params)
+
+    @staticmethod
+    def load(path: str, engine: Optional[Engine] = None) -> "KMeansModel":
+        from . import mlformat
+        return mlformat.load_kmeans_model(engine, path)
+
     def predict_structured(self, index: torch.Tensor, nums: Sequence[torch.Tensor]) -> torch.Tensor:
         c = torch.from_numpy(self.centers).to(self.engine.device)
         cluster, _ = self.engine.kmeans_assign(index, nums, c, self.num_labels, self.repeats)

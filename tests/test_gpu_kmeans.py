@@ -83,9 +83,11 @@ def test_fit_matches_the_numpy_restatement(eng, n, L, repeats, k, seed):
     assert len(model.clusterCenters()) == centers.shape[0]
 
 
-def test_kmeans_workload_returns_both_models_and_infers_single_rows(eng, monkeypatch):
+def test_kmeans_workload_returns_both_models_and_infers_single_rows(eng, monkeypatch, tmp_path):
     monkeypatch.delenv("ETL_SKIP_KMEANS", raising=False)
     monkeypatch.setenv("MEASURE_NAME_WEIGHT", "5")
+    monkeypatch.setenv("SAVE_MODELS", "true")                      # the block k_means.py:94-104 keeps commented out
+    monkeypatch.setenv("MODEL_OUTPUT_DIR", str(tmp_path))
     table = pkg.read_csv(eng, health_text("workloads").encode(), ["value", "lower_ci", "upper_ci"], ["measure_name"])
     wl = pkg.KMeansWorkload(eng)
     pipeline_model, model = wl.k_means(table)                      # k_means.py:17,107: (pipeline_model, model)
@@ -102,3 +104,12 @@ def test_kmeans_workload_returns_both_models_and_infers_single_rows(eng, monkeyp
     assert f[:150].sum() == 5 and f[pipeline_model.labels.index("Asthma")] == 1
     pred2, feats2 = wl.infer_single_row(None, "no such measure", 0)  # unseen label -> all-zero one-hot blocks
     assert feats2.cpu().numpy()[0, :150].sum() == 0 and 0 <= pred2 < 25
+    # models saved in Spark ML's layout and loaded back (k_means.py:118-135) give the same answers
+    loaded_pipeline, loaded_model = wl.load_models()
+    assert loaded_pipeline.labels == pipeline_model.labels and loaded_pipeline.means == pipeline_model.means
+    assert loaded_model.centers.tobytes() == model.centers.tobytes()
+    index2, nums2 = loaded_pipeline.transform(table)
+    assert torch.equal(index2, pipeline_model.index) and all(torch.equal(a, b) for a, b in zip(nums2, pipeline_model.numerics))
+    assert torch.equal(loaded_model.transform(loaded_pipeline, index2, nums2), model.transform(pipeline_model))
+    pkg.KMeansWorkload.pipeline_model, pkg.KMeansWorkload.kmeans_model = loaded_pipeline, loaded_model
+    assert wl.infer_single_row(None, "Asthma", 10)[0] == pred
