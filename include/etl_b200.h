@@ -212,8 +212,9 @@ ETL_API int etl_remap_codes(etl_handle* h, int32_t* codes, int64_t n, const int3
  *   int32 src_bytes, bit_width; int64 out_offset; int32 max_values, exact; int64
  *   run_offset, run_capacity} - one RLE / bit-packed hybrid stream each
  *   (definition levels: bit_width 1; dictionary indices: width from the page);
- *   values land in d_out[out_offset ...] (int32).  d_runs: scratch of 16-byte run
- *   records, run_capacity >= src_bytes / 2 + 1 per stream.
+ *   values land in d_out[out_offset ...] (int32).  One warp per stream walks the
+ *   run headers and expands each run as it is read; d_runs and the run_offset /
+ *   run_capacity fields are unused since ABI 2 (pass NULL / 0).
  * etl_parquet_gather_pages: d_pages = npages records {int64 row_start; int32
  *   num_values, kind (0 f64, 1 f32, 2 i32, 3 i64 PLAIN; 4 dictionary); int64
  *   levels_offset (-1: required column), val_offset (PLAIN: byte offset in file;

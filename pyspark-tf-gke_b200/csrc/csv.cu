@@ -54,42 +54,84 @@ __device__ __forceinline__ unsigned eq4(uint32_t w, uint32_t pat) {
     return (r * 0x01010101u) >> 24;  // distinct bits per byte: the byte sum is the mask
 }
 
-// Masks over the 64 bytes [base, base + 64) of the text: quotes, newlines, and
-// `opens` = the byte FOLLOWING position i exists and opens a non-blank line.
-__device__ __forceinline__ void csv_masks64(const uint8_t* __restrict__ text, int64_t base, int64_t n, uint64_t* quotes,
-                                            uint64_t* newlines, uint64_t* opens) {
+// bit 7 of every byte of w that equals the byte replicated in pat (exact per byte)
+__device__ __forceinline__ uint32_t eq_flags(uint32_t w, uint32_t pat) {
+    const uint32_t t = w ^ pat;
+    return ~(((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;
+}
+// those four flags as a 4-bit mask: one multiply moves bits 0 / 8 / 16 / 24 to 24..27
+__device__ __forceinline__ uint32_t flags_nibble(uint32_t f) { return ((f >> 7) * 0x01020408u) >> 24; }
+
+// The index passes stage the text in shared memory: a CTA's block of CSV_BLOCK_BYTES (+16 bytes of
+// look-ahead) arrives by one bulk async copy, double buffered, while the previous block is
+// processed; every thread then reads ITS 64-byte window from shared memory.  (Read straight from
+// global memory, the 64-byte-per-thread windows make every 16-byte load of a warp hit 32 different
+// sectors: ncu showed 1.7x the text size in DRAM reads and 31 % L2 hits.)
+constexpr int CSV_STAGE_BYTES = CSV_BLOCK_BYTES + 128;   // look-ahead + padding that keeps both buffers 128-byte aligned
+constexpr size_t CSV_STAGE_SMEM = 2 * CSV_STAGE_BYTES + 16;
+
+// thread 0: start the copy of block `blk` into `dst`; the < 16 bytes a bulk copy cannot move go by hand
+__device__ __forceinline__ void csv_stage_issue(const uint8_t* __restrict__ text, int64_t n, int64_t blk, unsigned char* dst,
+                                                uint64_t* bar) {
+    const int64_t base = blk * CSV_BLOCK_BYTES;
+    int64_t want = n - base;
+    if (want > CSV_BLOCK_BYTES + 16) want = CSV_BLOCK_BYTES + 16;
+    const unsigned bulk = (unsigned)(want & ~(int64_t)15);
+    for (int64_t i = bulk; i < want; ++i) dst[i] = text[base + i];
+    mbar_arrive_expect_tx(bar, bulk);
+    if (bulk) bulk_load(dst, text + base, bulk, bar);
+}
+
+// csv_masks64 on a staged block: `win` = the thread's window in shared memory, `base` its text offset
+__device__ __forceinline__ void csv_masks64_staged(const unsigned char* win, int64_t base, int64_t n, uint64_t* quotes,
+                                                   uint64_t* newlines, uint64_t* opens) {
     uint64_t q = 0, nl = 0, cr = 0;
-    if (base + 64 <= n) {
+    uint8_t a = 0, b = 0;
+    if (base + 66 <= n) {
+        uint32_t mq[4], mn[4], any_cr = 0;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
-            const int4 x = ld_stream_v4(text + base + 16 * v);
-            const uint32_t w[4] = {(uint32_t)x.x, (uint32_t)x.y, (uint32_t)x.z, (uint32_t)x.w};
+            const uint4 x = *reinterpret_cast<const uint4*>(win + 16 * v);
+            const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+            mq[v] = 0;
+            mn[v] = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const int sh = 16 * v + 4 * k;
-                q |= (uint64_t)eq4(w[k], 0x22222222u) << sh;
-                nl |= (uint64_t)eq4(w[k], 0x0a0a0a0au) << sh;
-                cr |= (uint64_t)eq4(w[k], 0x0d0d0d0du) << sh;
+                mq[v] |= flags_nibble(eq_flags(w[k], 0x22222222u)) << (4 * k);
+                mn[v] |= flags_nibble(eq_flags(w[k], 0x0a0a0a0au)) << (4 * k);
+                const uint32_t t = w[k] ^ 0x0d0d0d0du;
+                any_cr |= (t - 0x01010101u) & ~t;   // bit 7 of some byte set <=> the word holds a '\r'
+            }
+        }
+        q = (uint64_t)(mq[0] | (mq[1] << 16)) | ((uint64_t)(mq[2] | (mq[3] << 16)) << 32);
+        nl = (uint64_t)(mn[0] | (mn[1] << 16)) | ((uint64_t)(mn[2] | (mn[3] << 16)) << 32);
+        a = win[64];
+        b = win[65];
+        if (any_cr & 0x80808080u) {   // carriage returns are rare (none in LF files): their mask is built on demand
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const uint4 x = *reinterpret_cast<const uint4*>(win + 16 * v);
+                const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) cr |= (uint64_t)flags_nibble(eq_flags(w[k], 0x0d0d0d0du)) << (16 * v + 4 * k);
             }
         }
     } else {
         for (int i = 0; i < 64 && base + i < n; ++i) {
-            const uint8_t c = text[base + i];
+            const uint8_t c = win[i];
             q |= (uint64_t)(c == '"') << i;
             nl |= (uint64_t)(c == '\n') << i;
             cr |= (uint64_t)(c == '\r') << i;
         }
+        a = base + 64 < n ? win[64] : 0;
+        b = base + 65 < n ? win[65] : 0;
     }
-    // the two bytes after the window decide whether positions 62/63 open a non-blank line
-    const uint8_t a = base + 64 < n ? text[base + 64] : 0, b = base + 65 < n ? text[base + 65] : 0;
     const uint64_t nl1 = (nl >> 1) | ((uint64_t)(a == '\n') << 63);
     const uint64_t cr1 = (cr >> 1) | ((uint64_t)(a == '\r') << 63);
     const uint64_t nl2 = (nl >> 2) | ((uint64_t)(a == '\n') << 62) | ((uint64_t)(b == '\n') << 63);
-    // in1 / in2: byte i+1 / i+2 is inside the text
-    const int64_t left = n - base;  // bytes of the text from `base`
+    const int64_t left = n - base;
     const uint64_t in1 = left >= 65 ? ~0ull : (left <= 1 ? 0ull : ((1ull << (left - 1)) - 1));
     const uint64_t in2 = left >= 66 ? ~0ull : (left <= 2 ? 0ull : ((1ull << (left - 2)) - 1));
-    // next byte exists, is not '\n', and is not a '\r' that ends the text or precedes '\n'
     *opens = in1 & ~nl1 & ~(cr1 & (~in2 | nl2));
     *quotes = q;
     *newlines = nl;
@@ -112,45 +154,62 @@ __device__ __forceinline__ bool csv_first_line_nonblank(const uint8_t* text, int
 }
 
 __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const uint8_t* __restrict__ text, int64_t n,
-                                                                        CsvBlockSummary* __restrict__ out) {
+                                                                        int64_t blocks, CsvBlockSummary* __restrict__ out) {
+    extern __shared__ __align__(128) unsigned char csv_smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(csv_smem + 2 * CSV_STAGE_BYTES);
     __shared__ uint32_t s_par[CSV_THREADS / 32];
     __shared__ uint32_t s_out[CSV_THREADS / 32], s_in[CSV_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t base = (int64_t)blockIdx.x * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
-    uint64_t q, nl, opens;
-    csv_masks64(text, base, n, &q, &nl, &opens);
-    const uint64_t ins = inside_mask(q);
-    unsigned c_out = __popcll(nl & ~ins & opens), c_in = __popcll(nl & ins & opens);  // thread starts outside / inside
-    const unsigned tp = __popcll(q) & 1;
-    // thread's starting state relative to the block start
-    const unsigned wb = __ballot_sync(0xffffffffu, tp);
-    const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
-    if (lane == 0) s_par[warp] = __popc(wb) & 1;
-    __syncthreads();
-    unsigned warp_state = 0, block_par = 0;
-#pragma unroll
-    for (int w = 0; w < CSV_THREADS / 32; ++w) {
-        if (w < warp) warp_state ^= s_par[w];
-        block_par ^= s_par[w];
-    }
-    const unsigned st = lane_state ^ warp_state;
-    unsigned a = st ? c_in : c_out;   // starts if the block begins outside quotes
-    unsigned b = st ? c_out : c_in;   // ... inside quotes
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        a += __shfl_xor_sync(0xffffffffu, a, o);
-        b += __shfl_xor_sync(0xffffffffu, b, o);
-    }
-    if (lane == 0) { s_out[warp] = a; s_in[warp] = b; }
-    __syncthreads();
     if (tid == 0) {
-        uint64_t ta = 0, tb = 0;
+        mbar_init(bar, 1);
+        mbar_init(bar + 1, 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+    int64_t blk = blockIdx.x;
+    if (tid == 0 && blk < blocks) csv_stage_issue(text, n, blk, csv_smem, bar);
+    for (int it = 0; blk < blocks; blk += gridDim.x, ++it) {
+        const int buf = it & 1;
+        __syncthreads();  // the other buffer and the s_* words of the previous block are free
+        if (tid == 0 && blk + gridDim.x < blocks)
+            csv_stage_issue(text, n, blk + gridDim.x, csv_smem + (buf ^ 1) * CSV_STAGE_BYTES, bar + (buf ^ 1));
+        mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
+        const int64_t base = blk * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
+        uint64_t q, nl, opens;
+        csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens);
+        const uint64_t ins = inside_mask(q);
+        unsigned c_out = __popcll(nl & ~ins & opens), c_in = __popcll(nl & ins & opens);  // thread starts outside / inside
+        const unsigned tp = __popcll(q) & 1;
+        // thread's starting state relative to the block start
+        const unsigned wb = __ballot_sync(0xffffffffu, tp);
+        const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
+        if (lane == 0) s_par[warp] = __popc(wb) & 1;
+        __syncthreads();
+        unsigned warp_state = 0, block_par = 0;
 #pragma unroll
-        for (int w = 0; w < CSV_THREADS / 32; ++w) { ta += s_out[w]; tb += s_in[w]; }
-        if (blockIdx.x == 0 && csv_first_line_nonblank(text, n)) { ta += 1; tb += 1; }  // row 0 starts at byte 0
-        CsvBlockSummary r;
-        r.parity = block_par; r.pad = 0; r.starts_if_outside = ta; r.starts_if_inside = tb; r.reserved = 0;
-        out[blockIdx.x] = r;
+        for (int w = 0; w < CSV_THREADS / 32; ++w) {
+            if (w < warp) warp_state ^= s_par[w];
+            block_par ^= s_par[w];
+        }
+        const unsigned st = lane_state ^ warp_state;
+        unsigned a = st ? c_in : c_out;   // starts if the block begins outside quotes
+        unsigned b = st ? c_out : c_in;   // ... inside quotes
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if (lane == 0) { s_out[warp] = a; s_in[warp] = b; }
+        __syncthreads();
+        if (tid == 0) {
+            uint64_t ta = 0, tb = 0;
+#pragma unroll
+            for (int w = 0; w < CSV_THREADS / 32; ++w) { ta += s_out[w]; tb += s_in[w]; }
+            if (blk == 0 && csv_first_line_nonblank(text, n)) { ta += 1; tb += 1; }  // row 0 starts at byte 0
+            CsvBlockSummary r;
+            r.parity = block_par; r.pad = 0; r.starts_if_outside = ta; r.starts_if_inside = tb; r.reserved = 0;
+            out[blk] = r;
+        }
     }
 }
 
@@ -270,46 +329,63 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_span_apply_kernel(const CsvBl
 }
 
 __global__ void __launch_bounds__(CSV_THREADS) csv_row_offsets_kernel(const uint8_t* __restrict__ text, int64_t n,
-                                                                      const CsvBlockStart* __restrict__ start,
+                                                                      int64_t blocks, const CsvBlockStart* __restrict__ start,
                                                                       int64_t* __restrict__ row_start) {
+    extern __shared__ __align__(128) unsigned char csv_smem[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(csv_smem + 2 * CSV_STAGE_BYTES);
     __shared__ uint32_t s_par[CSV_THREADS / 32];
     __shared__ uint32_t s_cnt[CSV_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t base = (int64_t)blockIdx.x * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
-    uint64_t q, nl, opens;
-    csv_masks64(text, base, n, &q, &nl, &opens);
-    const CsvBlockStart bs = start[blockIdx.x];
-    const unsigned tp = __popcll(q) & 1;
-    const unsigned wb = __ballot_sync(0xffffffffu, tp);
-    const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
-    if (lane == 0) s_par[warp] = __popc(wb) & 1;
-    __syncthreads();
-    unsigned st = lane_state ^ bs.inside;
-#pragma unroll
-    for (int w = 0; w < CSV_THREADS / 32; ++w)
-        if (w < warp) st ^= s_par[w];
-    uint64_t ins = inside_mask(q);
-    if (st) ins = ~ins;
-    uint64_t ev = nl & ~ins & opens;  // newlines outside quotes whose next byte opens a non-blank line
-    const bool virt = blockIdx.x == 0 && tid == 0 && csv_first_line_nonblank(text, n);
-    unsigned cnt = __popcll(ev) + (virt ? 1 : 0);
-    unsigned incl = cnt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += up;
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_init(bar + 1, 1);
+        mbar_init_fence();
     }
-    if (lane == 31) s_cnt[warp] = incl;
     __syncthreads();
-    uint64_t row = bs.first_row + (incl - cnt);
+    int64_t blk = blockIdx.x;
+    if (tid == 0 && blk < blocks) csv_stage_issue(text, n, blk, csv_smem, bar);
+    for (int it = 0; blk < blocks; blk += gridDim.x, ++it) {
+        const int buf = it & 1;
+        __syncthreads();
+        if (tid == 0 && blk + gridDim.x < blocks)
+            csv_stage_issue(text, n, blk + gridDim.x, csv_smem + (buf ^ 1) * CSV_STAGE_BYTES, bar + (buf ^ 1));
+        const CsvBlockStart bs = start[blk];
+        mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
+        const int64_t base = blk * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
+        uint64_t q, nl, opens;
+        csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens);
+        const unsigned tp = __popcll(q) & 1;
+        const unsigned wb = __ballot_sync(0xffffffffu, tp);
+        const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
+        if (lane == 0) s_par[warp] = __popc(wb) & 1;
+        __syncthreads();
+        unsigned st = lane_state ^ bs.inside;
 #pragma unroll
-    for (int w = 0; w < CSV_THREADS / 32; ++w)
-        if (w < warp) row += s_cnt[w];
-    if (virt) row_start[row++] = 0;
-    while (ev) {
-        const int i = __ffsll((long long)ev) - 1;
-        ev &= ev - 1;
-        row_start[row++] = base + i + 1;
+        for (int w = 0; w < CSV_THREADS / 32; ++w)
+            if (w < warp) st ^= s_par[w];
+        uint64_t ins = inside_mask(q);
+        if (st) ins = ~ins;
+        uint64_t ev = nl & ~ins & opens;  // newlines outside quotes whose next byte opens a non-blank line
+        const bool virt = blk == 0 && tid == 0 && csv_first_line_nonblank(text, n);
+        unsigned cnt = __popcll(ev) + (virt ? 1 : 0);
+        unsigned incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        if (lane == 31) s_cnt[warp] = incl;
+        __syncthreads();
+        uint64_t row = bs.first_row + (incl - cnt);
+#pragma unroll
+        for (int w = 0; w < CSV_THREADS / 32; ++w)
+            if (w < warp) row += s_cnt[w];
+        if (virt) row_start[row++] = 0;
+        while (ev) {
+            const int i = __ffsll((long long)ev) - 1;
+            ev &= ev - 1;
+            row_start[row++] = base + i + 1;
+        }
     }
 }
 
@@ -686,7 +762,9 @@ extern "C" int etl_csv_index_rows(etl_handle* hh, const uint8_t* text, int64_t n
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
     auto* super = reinterpret_cast<etl::CsvBlockSummary*>(start + blocks);
     auto* super_start = reinterpret_cast<etl::CsvBlockStart*>(super + supers);
-    etl::csv_block_summary_kernel<<<(unsigned)blocks, etl::CSV_THREADS, 0, stream>>>(text, nbytes, sum);
+    ETL_CUDA(cudaFuncSetAttribute(etl::csv_block_summary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)etl::CSV_STAGE_SMEM));
+    const int64_t grid = blocks < (int64_t)h->sm_count * 6 ? blocks : (int64_t)h->sm_count * 6;   // 33 KB each: 6 CTAs per SM
+    etl::csv_block_summary_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, sum);
     etl::csv_span_reduce_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super);
     etl::csv_span_scan_kernel<<<1, etl::CSV_THREADS, 0, stream>>>(super, supers, super_start, d_rows);
     etl::csv_span_apply_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super_start, start);
@@ -708,7 +786,10 @@ extern "C" int etl_csv_row_offsets(etl_handle* hh, const uint8_t* text, int64_t 
     ETL_REQUIRE(h->scratch_bytes >= need, "csv_row_offsets: call etl_csv_index_rows on the same text first");
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
-    etl::csv_row_offsets_kernel<<<(unsigned)blocks, etl::CSV_THREADS, 0, stream>>>(text, nbytes, start, row_start);
+    ETL_CUDA(cudaFuncSetAttribute(etl::csv_row_offsets_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)etl::CSV_STAGE_SMEM));
+    const int64_t grid = blocks < (int64_t)h->sm_count * 6 ? blocks : (int64_t)h->sm_count * 6;
+    etl::csv_row_offsets_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, start,
+                                                                                                  row_start);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

@@ -43,75 +43,180 @@ struct PqPage {
     int32_t pad;
 };
 
+// bw bits (<= 32) starting `bit` bits after p: two aligned 32-bit loads and a funnel shift.  Reads at
+// most 7 bytes past the value - inside the file buffer, a stream is never the file's last bytes (the
+// footer and the closing magic follow).
 __device__ __forceinline__ uint32_t pq_extract(const uint8_t* p, int64_t bit, int bw) {
-    const uint8_t* q = p + (bit >> 3);
-    const int sh = (int)(bit & 7);
-    uint64_t w = 0;
-    const int need = (sh + bw + 7) >> 3;  // <= 5 bytes for bw <= 32
-    for (int i = 0; i < need; ++i) w |= (uint64_t)q[i] << (8 * i);
-    return (uint32_t)((w >> sh) & ((bw >= 32) ? 0xffffffffull : ((1ull << bw) - 1)));
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+    bit += 8 * (int64_t)(addr & 3);
+    const uint32_t lo = __ldg(w + (bit >> 5)), hi = __ldg(w + (bit >> 5) + 1);
+    const uint32_t v = __funnelshift_r(lo, hi, (unsigned)(bit & 31));
+    return bw >= 32 ? v : (v & ((1u << bw) - 1));
+}
+// 8 / 4 bytes at any alignment (PLAIN value sections start wherever the page header ended)
+__device__ __forceinline__ uint64_t pq_load_u64(const uint8_t* p) {
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+    const uint64_t* w = reinterpret_cast<const uint64_t*>(addr & ~(uintptr_t)7);
+    const unsigned sh = 8 * (unsigned)(addr & 7);
+    const uint64_t lo = __ldg(w);
+    if (sh == 0) return lo;
+    return (lo >> sh) | (__ldg(w + 1) << (64 - sh));
+}
+__device__ __forceinline__ uint32_t pq_load_u32(const uint8_t* p) {
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(addr & ~(uintptr_t)3);
+    const unsigned sh = 8 * (unsigned)(addr & 3);
+    const uint32_t lo = __ldg(w);
+    if (sh == 0) return lo;
+    return __funnelshift_r(lo, __ldg(w + 1), sh);
 }
 
+constexpr int PQ_WINDOW = 2048;   // bytes of its stream a warp keeps in shared memory while it walks the run headers
+constexpr int PQ_WARPS = PQ_THREADS / 32;
+
+// One WARP per hybrid stream.  Run headers can only be found one after another, and writers emit
+// short runs (Arrow switches between RLE and bit-packed runs every few values: ~1250 runs per
+// 20 000-value page of definition levels), so the walk is a latency chain: the warp walks it in
+// lockstep (every lane runs the same scalar code) over a window of the stream held in shared
+// memory - a header byte costs a shared-memory access, not a dependent trip to L2 - and expands
+// each run as soon as its header is read, all lanes storing.  One warp per stream (not one CTA)
+// puts 64 streams in flight per SM; there is no run table.
 __global__ void __launch_bounds__(PQ_THREADS) pq_hybrid_decode_kernel(const uint8_t* __restrict__ file,
-                                                                      const PqStream* __restrict__ streams,
-                                                                      PqRun* __restrict__ runs, int32_t* __restrict__ out,
-                                                                      int32_t* status) {
-    __shared__ int s_nruns;
-    const PqStream st = streams[blockIdx.x];
+                                                                      const PqStream* __restrict__ streams, int nstreams,
+                                                                      int32_t* __restrict__ out, int32_t* status) {
+    __shared__ __align__(16) uint8_t s_win_all[PQ_WARPS][PQ_WINDOW + 16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sidx = blockIdx.x * PQ_WARPS + warp;
+    if (sidx >= nstreams) return;
+    uint8_t* s_win = s_win_all[warp];
+    const PqStream st = streams[sidx];
     const uint8_t* src = file + st.src_offset;
-    PqRun* my_runs = runs + st.run_offset;
-    if (threadIdx.x == 0) {
-        int pos = 0, produced = 0, n = 0;
-        const int vbytes = (st.bit_width + 7) >> 3;
-        while (pos < st.src_bytes && produced < st.max_values) {
-            uint32_t h = 0;
-            int shift = 0;
-            while (pos < st.src_bytes) {  // ULEB128 run header
-                const uint8_t c = src[pos++];
-                h |= (uint32_t)(c & 0x7f) << shift;
+    int32_t* dst = out + st.out_offset;
+    const uintptr_t src_addr = reinterpret_cast<uintptr_t>(src);
+    int64_t win_lo = 0, win_hi = 0;   // stream positions [win_lo, win_hi) are in s_win
+    // make [pos, pos + need) resident (need <= PQ_WINDOW - 16)
+    auto ensure = [&](int pos, int need) {
+        if (pos >= win_lo && pos + need <= win_hi) return;
+        __syncwarp();
+        const uintptr_t g0 = (src_addr + (uintptr_t)pos) & ~(uintptr_t)15;   // 16-byte aligned global address
+        const uint4* g = reinterpret_cast<const uint4*>(g0);
+        // no further than the 16-byte chunk after the one holding the stream's last byte (what follows a
+        // stream in the file - at the very least the footer - keeps those chunks inside the buffer)
+        const int64_t chunks = (int64_t)((src_addr + (uintptr_t)st.src_bytes + 31 - g0) >> 4);
+        for (int i = lane; i < PQ_WINDOW / 16 && i < chunks; i += 32) reinterpret_cast<uint4*>(s_win)[i] = __ldg(g + i);
+        win_lo = (int64_t)(g0 - src_addr);
+        win_hi = win_lo + PQ_WINDOW;
+        __syncwarp();
+    };
+    // 8 stream bytes from position pos (resident), little endian
+    auto peek64 = [&](int pos) -> uint64_t {
+        const unsigned idx = (unsigned)(pos - win_lo);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(s_win) + (idx >> 2);
+        const unsigned sh = 8 * (idx & 3);
+        const uint32_t a = w[0], b = w[1], c = w[2];
+        return (uint64_t)__funnelshift_r(a, b, sh) | ((uint64_t)__funnelshift_r(b, c, sh) << 32);
+    };
+    int64_t pos = 0;
+    int produced = 0;
+    const int bw = st.bit_width;
+    const int vbytes = (bw + 7) >> 3;
+    const uint32_t vmask = vbytes >= 4 ? 0xffffffffu : ((1u << (8 * vbytes)) - 1);
+    const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_win);
+    constexpr int SMALL = 64;        // runs up to this many values are expanded by the lane that decoded them
+    constexpr int LOOKAHEAD = 32 + 5 + SMALL * 4 + 16;
+    bool stop = false;
+    while (!stop && pos < st.src_bytes && produced < st.max_values) {
+        // Span = the next 32 stream bytes.  Lane j decodes a run header AS IF one started at pos + j;
+        // which lanes guessed right is then settled by hopping along the chain (one shuffle per run
+        // instead of a full serial decode per run), and the lanes on the chain expand their runs.
+        ensure((int)pos, LOOKAHEAD);
+        const int64_t my = pos + lane;
+        const uint64_t w = peek64((int)my);
+        uint32_t h = (uint32_t)w & 0x7f;
+        int hl = 1;
+        if (w & 0x80) {
+            int shift = 7;
+            while (hl < 5) {
+                const uint32_t c = (uint32_t)(w >> (8 * hl)) & 0xff;
+                h |= (c & 0x7f) << shift;
                 shift += 7;
+                ++hl;
                 if (!(c & 0x80)) break;
             }
-            PqRun r;
-            r.out_start = produced;
-            if (h & 1) {  // bit-packed groups of 8 values
-                const int groups = (int)(h >> 1);
-                r.count = groups * 8;
-                r.src_pos = pos;
-                r.value = -1;
-                pos += groups * st.bit_width;
-            } else {      // run-length: value repeated h >> 1 times
-                r.count = (int)(h >> 1);
-                r.src_pos = pos;
-                uint32_t v = 0;
-                for (int i = 0; i < vbytes && pos + i < st.src_bytes; ++i) v |= (uint32_t)src[pos + i] << (8 * i);
-                r.value = (int32_t)v;
-                pos += vbytes;
+        }
+        const bool lit = h & 1;
+        const uint32_t units = h >> 1;                      // groups of 8 (bit-packed) or repetitions (RLE)
+        const bool sane = units > 0 && units < (1u << 24) && my < st.src_bytes;
+        const int cnt = sane ? (int)(lit ? units * 8 : units) : 0;
+        const int dlen = lit ? (int)((sane ? units : 0) * (unsigned)bw) : vbytes;
+        const int adv = hl + dlen;
+        const uint32_t val = hl + vbytes <= 8 ? ((uint32_t)(w >> (8 * hl)) & vmask) : ((uint32_t)peek64((int)my + hl) & vmask);
+        unsigned chain = 0;
+        int64_t j = 0;
+        while (j < 32) {
+            const int a = __shfl_sync(0xffffffffu, adv, (int)j);
+            const int ok = __shfl_sync(0xffffffffu, (int)sane, (int)j);
+            if (!ok) { stop = true; break; }               // end of the stream (or a malformed header): nothing follows
+            chain |= 1u << j;
+            j += a;
+        }
+        const bool mine = (chain >> lane) & 1u;
+        int c = mine ? cnt : 0;
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        int start = produced + incl - c;
+        if (start >= st.max_values) c = 0;
+        else if (c > st.max_values - start) c = st.max_values - start;
+        const int data = (int)my + hl;
+        if (c > 0 && c <= SMALL) {   // every lane on the chain writes its own short run
+            if (!lit || bw == 0) {
+                const int32_t v = lit ? 0 : (int32_t)val;
+                for (int i = 0; i < c; ++i) dst[start + i] = v;
+            } else {
+                const unsigned base_bit = 8u * (unsigned)(data - win_lo);
+                for (int i = 0; i < c; ++i) {
+                    const unsigned bit = base_bit + (unsigned)i * (unsigned)bw;
+                    const uint32_t v = __funnelshift_r(sw[bit >> 5], sw[(bit >> 5) + 1], bit & 31);
+                    dst[start + i] = (int32_t)(bw >= 32 ? v : (v & ((1u << bw) - 1)));
+                }
             }
-            if (r.count <= 0) break;
-            if (r.count > st.max_values - produced) r.count = st.max_values - produced;
-            if (n >= st.run_capacity) { atomicAdd(status, 1); break; }
-            my_runs[n++] = r;
-            produced += r.count;
         }
-        if (st.exact && produced < st.max_values) atomicAdd(status + 1, 1);  // stream ended early
-        s_nruns = n;
-    }
-    __syncthreads();
-    const int nruns = s_nruns;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int32_t* dst = out + st.out_offset;
-    for (int r = warp; r < nruns; r += PQ_THREADS / 32) {
-        const PqRun run = my_runs[r];
-        if (run.value >= 0 || st.bit_width == 0) {
-            const int32_t v = st.bit_width == 0 ? 0 : run.value;
-            for (int i = lane; i < run.count; i += 32) dst[run.out_start + i] = v;
-        } else {
-            const uint8_t* p = src + run.src_pos;
-            for (int i = lane; i < run.count; i += 32)
-                dst[run.out_start + i] = (int32_t)pq_extract(p, (int64_t)i * st.bit_width, st.bit_width);
+        unsigned big = __ballot_sync(0xffffffffu, c > SMALL);
+        while (big) {                // long runs: the whole warp expands them, one after another
+            const int f = __ffs(big) - 1;
+            big &= big - 1;
+            const int f_start = __shfl_sync(0xffffffffu, start, f), f_c = __shfl_sync(0xffffffffu, c, f);
+            const int f_lit = __shfl_sync(0xffffffffu, (int)lit, f), f_data = __shfl_sync(0xffffffffu, data, f);
+            const uint32_t f_val = __shfl_sync(0xffffffffu, val, f);
+            if (!f_lit || bw == 0) {
+                const int32_t v = f_lit ? 0 : (int32_t)f_val;
+                for (int i = lane; i < f_c; i += 32) dst[f_start + i] = v;
+            } else {
+                const int nbytes = (int)(((int64_t)f_c * bw + 7) >> 3);
+                if (nbytes + 8 <= PQ_WINDOW - 16) {
+                    ensure(f_data, nbytes + 8);
+                    const unsigned base_bit = 8u * (unsigned)(f_data - win_lo);
+                    for (int i = lane; i < f_c; i += 32) {
+                        const unsigned bit = base_bit + (unsigned)i * (unsigned)bw;
+                        const uint32_t v = __funnelshift_r(sw[bit >> 5], sw[(bit >> 5) + 1], bit & 31);
+                        dst[f_start + i] = (int32_t)(bw >= 32 ? v : (v & ((1u << bw) - 1)));
+                    }
+                } else {             // longer than the window: straight from global memory
+                    const uint8_t* p = src + f_data;
+                    for (int i = lane; i < f_c; i += 32) dst[f_start + i] = (int32_t)pq_extract(p, (int64_t)i * bw, bw);
+                }
+            }
         }
+        produced = total > st.max_values - produced ? st.max_values : produced + total;
+        pos += j;
     }
+    if (lane == 0 && st.exact && produced < st.max_values) atomicAdd(status + 1, 1);  // stream ended early
 }
 
 struct PqGatherParams {
@@ -165,17 +270,12 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_gather_kernel(const PqGatherPar
                     }
                 } else {
                     const uint8_t* src = p.file + pg.val_offset;
-                    if (pg.kind == PQ_KIND_F64) {
-                        uint64_t u = 0;  // pages are not 8-byte aligned in the file
-                        for (int k = 0; k < 8; ++k) u |= (uint64_t)src[(int64_t)rank * 8 + k] << (8 * k);
-                        v = __longlong_as_double((long long)u);
+                    if (pg.kind == PQ_KIND_F64) {   // pages are not 8-byte aligned in the file
+                        v = __longlong_as_double((long long)pq_load_u64(src + (int64_t)rank * 8));
                     } else if (pg.kind == PQ_KIND_I64) {
-                        uint64_t u = 0;
-                        for (int k = 0; k < 8; ++k) u |= (uint64_t)src[(int64_t)rank * 8 + k] << (8 * k);
-                        v = (double)(long long)u;
+                        v = (double)(long long)pq_load_u64(src + (int64_t)rank * 8);
                     } else {
-                        uint32_t u = 0;
-                        for (int k = 0; k < 4; ++k) u |= (uint32_t)src[(int64_t)rank * 4 + k] << (8 * k);
+                        const uint32_t u = pq_load_u32(src + (int64_t)rank * 4);
                         v = pg.kind == PQ_KIND_F32 ? (double)__uint_as_float(u) : (double)(int32_t)u;
                     }
                 }
@@ -205,11 +305,13 @@ extern "C" int etl_parquet_expand_streams(etl_handle* hh, const uint8_t* file, c
     ETL_REQUIRE(hh && d_status, "parquet_expand_streams: NULL argument");
     ETL_REQUIRE(nstreams >= 0, "parquet_expand_streams: nstreams < 0");
     if (nstreams == 0) return ETL_OK;
-    ETL_REQUIRE(file && d_streams && d_runs && d_out, "parquet_expand_streams: NULL buffer");
+    ETL_REQUIRE(file && d_streams && d_out, "parquet_expand_streams: NULL buffer");
+    (void)d_runs;  // ABI 1 kept a run table here; runs are expanded as they are parsed now
     Handle* h = reinterpret_cast<Handle*>(hh);
     ETL_CUDA(cudaSetDevice(h->device));
-    etl::pq_hybrid_decode_kernel<<<(unsigned)nstreams, etl::PQ_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
-        file, static_cast<const etl::PqStream*>(d_streams), static_cast<etl::PqRun*>(d_runs), d_out, d_status);
+    const unsigned grid = (unsigned)((nstreams + etl::PQ_WARPS - 1) / etl::PQ_WARPS);
+    etl::pq_hybrid_decode_kernel<<<grid, etl::PQ_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        file, static_cast<const etl::PqStream*>(d_streams), nstreams, d_out, d_status);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

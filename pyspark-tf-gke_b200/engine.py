@@ -523,82 +523,99 @@ class Engine:
         return {"keys": keys[order], "rows": rows[order], "cols": [col], "null_group_rows": 0, "spilled_records": spilled}
 
     # ------------------------------------------------------- Parquet (extension)
-    def parquet_decode_column(self, data: torch.Tensor, nbytes: int, rows: int, pages, kind_plain: int,
-                              string_column: bool, dicts: Sequence[torch.Tensor]) -> Column:
-        """Decode one column from the page plan of parquet.py -> Column (f64, or
-        int32 label codes for a string column) + validity."""
-        host = data  # device buffer of the file
-        raw_first = None
-        streams = []   # (src_offset, src_bytes, bit_width, out_offset, max_values, run_offset, run_capacity)
-        lvl_total = idx_total = run_total = 0
-        page_rec = []
-        widths = {}
-        # dictionary pages start their value section with a 1-byte bit width: fetch those bytes in one gather
-        dict_pages = [pg for pg in pages if pg.dict_id >= 0]
-        if dict_pages:
-            offs = torch.tensor([pg.val_offset for pg in dict_pages], dtype=torch.int64, device=self.device)
-            for pg, w in zip(dict_pages, data[offs].cpu().tolist()):
-                widths[id(pg)] = int(w)
-        lvl_streams, idx_streams = [], []
-        for pg in pages:
-            lvl_off = -1
-            if pg.def_offset >= 0:
-                lvl_off = lvl_total
-                cap = pg.def_bytes // 2 + 2
-                lvl_streams.append((pg.def_offset, pg.def_bytes, 1, lvl_off, pg.num_values, run_total, cap))
-                lvl_total += pg.num_values + 8
-                run_total += cap
-            if pg.dict_id >= 0:
-                bw = widths[id(pg)]
-                if bw > 32:
-                    raise _lib.EtlError(-4, f"parquet: dictionary index width {bw}")
-                val_off = idx_total
-                cap = (pg.val_bytes - 1) // 2 + 2
-                idx_streams.append((pg.val_offset + 1, pg.val_bytes - 1, bw, val_off, pg.num_values, run_total, cap))
-                idx_total += pg.num_values + 8
-                run_total += cap
-                page_rec.append((pg.row_start, pg.num_values, 4, lvl_off, val_off, pg.dict_id))
-            else:
-                page_rec.append((pg.row_start, pg.num_values, kind_plain, lvl_off, pg.val_offset, -1))
+    _PQ_STREAM = np.dtype([("src", "<i8"), ("bytes", "<i4"), ("bw", "<i4"), ("out", "<i8"), ("maxv", "<i4"), ("exact", "<i4"),
+                           ("run", "<i8"), ("cap", "<i8")])
+    _PQ_PAGE = np.dtype([("row", "<i8"), ("n", "<i4"), ("kind", "<i4"), ("lvl", "<i8"), ("val", "<i8"), ("dict", "<i4"),
+                         ("pad", "<i4")])
+
+    def parquet_decode_columns(self, data: torch.Tensor, rows: int, jobs: Sequence[dict]) -> List[Column]:
+        """Decode several columns of one file (device buffer `data`) from the page
+        tables of parquet.py.  jobs[i] = {"pages": int64[p, 8] (row_start, num_values,
+        def_offset, def_bytes, val_offset, val_bytes, dict_id, bit_width),
+        "kind_plain", "string", "dicts": [device lookup tables]}.  All hybrid streams
+        of all columns (definition levels and dictionary indices) expand in ONE
+        launch into one int32 buffer; then one gather launch per column; the tables
+        reach the device in one copy and the status words are read back once."""
+        if not jobs:
+            return []
+        streams, pages, dict_ptrs, dict_sizes, keep = [], [], [], [], []
+        out_total = run_total = 0
+        page_slices = []
+        for job in jobs:
+            P = np.asarray(job["pages"], dtype=np.int64).reshape(-1, 8)
+            n_pages = P.shape[0]
+            row, nv, def_off, def_bytes, val_off, val_bytes, dict_id, bw = (P[:, i] for i in range(8))
+            has_def, is_dict = def_off >= 0, dict_id >= 0
+            if (bw[is_dict] > 32).any():
+                raise _lib.EtlError(-4, f"parquet: dictionary index width {int(bw[is_dict].max())}")
+            # output / run-table offsets: levels of the pages that have them, then the indices of the dictionary pages
+            span = nv + 8
+            lvl_out = np.full(n_pages, -1, dtype=np.int64)
+            lvl_out[has_def] = out_total + np.cumsum(span[has_def]) - span[has_def]
+            out_total += int(span[has_def].sum())
+            idx_out = np.zeros(n_pages, dtype=np.int64)
+            idx_out[is_dict] = out_total + np.cumsum(span[is_dict]) - span[is_dict]
+            out_total += int(span[is_dict].sum())
+            for mask, src, nbytes, width, out, exact in ((has_def, def_off, def_bytes, np.ones_like(bw), lvl_out, 1),
+                                                         (is_dict, val_off + 1, val_bytes - 1, bw, idx_out, 0)):
+                k = int(mask.sum())
+                if not k:
+                    continue
+                st = np.zeros(k, dtype=self._PQ_STREAM)
+                cap = nbytes[mask] // 2 + 2
+                st["src"], st["bytes"], st["bw"], st["out"] = src[mask], nbytes[mask], width[mask], out[mask]
+                st["maxv"], st["exact"], st["cap"] = nv[mask], exact, cap
+                st["run"] = run_total + np.cumsum(cap) - cap
+                run_total += int(cap.sum())
+                streams.append(st)
+            pg = np.zeros(n_pages, dtype=self._PQ_PAGE)
+            pg["row"], pg["n"], pg["lvl"] = row, nv, lvl_out
+            pg["kind"] = np.where(is_dict, 4, job["kind_plain"])
+            pg["val"] = np.where(is_dict, idx_out, val_off)
+            pg["dict"] = np.where(is_dict, dict_id + len(dict_ptrs), -1)
+            page_slices.append((sum(x.shape[0] for x in pages), n_pages))
+            pages.append(pg)
+            dict_ptrs += [t.data_ptr() for t in job["dicts"]]
+            dict_sizes += [t.shape[0] for t in job["dicts"]]
+            keep += list(job["dicts"])
+        # one host blob -> one copy: streams | pages | dictionary pointers | dictionary sizes (16-byte aligned parts)
+        parts = [np.concatenate(streams).view(np.uint8) if streams else np.zeros(0, np.uint8),
+                 np.concatenate(pages).view(np.uint8),
+                 np.asarray(dict_ptrs or [0], dtype=np.int64).view(np.uint8),
+                 np.asarray(dict_sizes or [0], dtype=np.int32).view(np.uint8)]
+        offs, total = [], 0
+        for part in parts:
+            offs.append(total)
+            total += (part.nbytes + 15) // 16 * 16
+        blob = np.zeros(total, dtype=np.uint8)
+        for o, part in zip(offs, parts):
+            blob[o:o + part.nbytes] = part
+        d_blob = torch.from_numpy(blob).to(self.device)
+        base = d_blob.data_ptr()
         status = torch.zeros(4, dtype=torch.int32, device=self.device)
-        levels = self.empty(max(lvl_total, 1), torch.int32)
-        indices = self.empty(max(idx_total, 1), torch.int32)
-        runs = self.empty(max(run_total, 1) * 2, torch.int64)  # 16-byte records
-        sdt = np.dtype([("src", "<i8"), ("bytes", "<i4"), ("bw", "<i4"), ("out", "<i8"), ("maxv", "<i4"), ("exact", "<i4"),
-                        ("run", "<i8"), ("cap", "<i8")])
-        for group, out in ((lvl_streams, levels), (idx_streams, indices)):
-            if not group:
-                continue
-            arr = np.zeros(len(group), dtype=sdt)
-            for i, (src, nb, bw, o, mv, ro, cap) in enumerate(group):
-                arr[i] = (src, nb, bw, o, mv, 1 if out is levels else 0, ro, cap)
-            d_streams = torch.from_numpy(arr.view(np.uint8)).to(self.device)
-            _lib.check(self.lib.etl_parquet_expand_streams(self._h, data.data_ptr(), d_streams.data_ptr(), len(group),
-                                                           runs.data_ptr(), out.data_ptr(), status.data_ptr(),
-                                                           self._stream()))
+        decoded = self.empty(max(out_total, 1), torch.int32)
+        nstreams = sum(x.shape[0] for x in streams)
+        if nstreams:
+            _lib.check(self.lib.etl_parquet_expand_streams(self._h, data.data_ptr(), base + offs[0], nstreams, None,
+                                                           decoded.data_ptr(), status.data_ptr(), self._stream()))
             self.launches += 1
-        pdt = np.dtype([("row", "<i8"), ("n", "<i4"), ("kind", "<i4"), ("lvl", "<i8"), ("val", "<i8"), ("dict", "<i4"),
-                        ("pad", "<i4")])
-        parr = np.zeros(len(page_rec), dtype=pdt)
-        for i, (row, n, kind, lvl, val, did) in enumerate(page_rec):
-            parr[i] = (row, n, kind, lvl, val, did, 0)
-        d_pages = torch.from_numpy(parr.view(np.uint8)).to(self.device)
-        out = self.empty(rows, torch.int32 if string_column else torch.float64)
-        valid = torch.zeros(words_for(rows), dtype=torch.int32, device=self.device)
-        nd = max(len(dicts), 1)
-        d_dict = torch.tensor([t.data_ptr() for t in dicts] or [0], dtype=torch.int64, device=self.device)
-        d_dict_size = torch.tensor([t.shape[0] for t in dicts] or [0], dtype=torch.int32, device=self.device)
-        if page_rec:
-            _lib.check(self.lib.etl_parquet_gather_pages(self._h, data.data_ptr(), d_pages.data_ptr(), len(page_rec),
-                                                         levels.data_ptr(), indices.data_ptr(), d_dict.data_ptr(),
-                                                         d_dict_size.data_ptr(), int(string_column), out.data_ptr(),
-                                                         valid.data_ptr(), status.data_ptr(), self._stream()))
-            self.launches += 1
+        cols = []
+        for job, (first, count) in zip(jobs, page_slices):
+            out = self.empty(rows, torch.int32 if job["string"] else torch.float64)
+            valid = torch.zeros(words_for(rows), dtype=torch.int32, device=self.device)
+            if count:
+                _lib.check(self.lib.etl_parquet_gather_pages(
+                    self._h, data.data_ptr(), base + offs[1] + first * self._PQ_PAGE.itemsize, count, decoded.data_ptr(),
+                    decoded.data_ptr(), base + offs[2], base + offs[3], int(job["string"]), out.data_ptr(), valid.data_ptr(),
+                    status.data_ptr(), self._stream()))
+                self.launches += 1
+            cols.append(Column(out, valid))
         st = status.cpu().tolist()
         if st[0] or st[1] or st[2]:
             raise _lib.EtlError(-4, f"parquet decode: run-table overflow {st[0]}, short streams {st[1]}, "
                                     f"dictionary indices out of range {st[2]}")
-        return Column(out, valid)
+        del keep
+        return cols
 
     # ------------------------------------------------- KMeans passes (8f rank 2)
     def kmeans_prepare(self, centers: torch.Tensor, num_labels: int, repeats: int):

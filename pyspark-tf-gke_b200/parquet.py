@@ -115,6 +115,7 @@ class _Page:
     val_bytes: int
     encoding: int           # ENC_PLAIN or a dictionary encoding
     dict_id: int            # index into the column's dictionaries, -1 if PLAIN
+    bit_width: int = 0      # dictionary pages: width of the indices (first byte of the value section)
 
 
 @dataclass
@@ -124,6 +125,14 @@ class _ColumnPlan:
     optional: bool
     pages: List[_Page] = field(default_factory=list)
     dictionaries: List[object] = field(default_factory=list)  # list[str] or np.ndarray per row group
+
+    def page_table(self) -> np.ndarray:
+        """int64[pages, 8]: row_start, num_values, def_offset, def_bytes, val_offset, val_bytes,
+        dict_id, bit_width - what Engine.parquet_decode_columns vectorises over."""
+        if getattr(self, "_table", None) is None or self._table.shape[0] != len(self.pages):
+            self._table = np.array([[p.row_start, p.num_values, p.def_offset, p.def_bytes, p.val_offset, p.val_bytes,
+                                     p.dict_id, p.bit_width] for p in self.pages], dtype=np.int64).reshape(-1, 8)
+        return self._table
 
 
 def _plain_strings(buf: bytes, n: int) -> List[str]:
@@ -202,8 +211,9 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
                         (def_bytes,) = struct.unpack_from("<I", raw, p)
                         def_off = p + 4
                         p += 4 + def_bytes
-                    plan.pages.append(_Page(row, nv, def_off, def_bytes, p, body + size - p, enc,
-                                            dict_id if enc in (ENC_PLAIN_DICT, ENC_RLE_DICT) else -1))
+                    is_dict = enc in (ENC_PLAIN_DICT, ENC_RLE_DICT)
+                    plan.pages.append(_Page(row, nv, def_off, def_bytes, p, body + size - p, enc, dict_id if is_dict else -1,
+                                            raw[p] if is_dict and body + size > p else 0))
                     row += nv
                 elif ph[1] == PAGE_DATA_V2:
                     dh = ph[8]
@@ -212,8 +222,10 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
                     if rl:
                         raise ParquetUnsupported(f"column {name}: repetition levels present")
                     def_off = body if (plan.optional and dl) else -1
-                    plan.pages.append(_Page(row, nv, def_off, dl, body + dl + rl, size - dl - rl, enc,
-                                            dict_id if enc in (ENC_PLAIN_DICT, ENC_RLE_DICT) else -1))
+                    is_dict = enc in (ENC_PLAIN_DICT, ENC_RLE_DICT)
+                    vo = body + dl + rl
+                    plan.pages.append(_Page(row, nv, def_off, dl, vo, size - dl - rl, enc, dict_id if is_dict else -1,
+                                            raw[vo] if is_dict and size > dl + rl else 0))
                     row += nv
                 else:
                     pass  # index pages carry no values
@@ -231,6 +243,7 @@ def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[
     rows, plans = _plan(raw, list(numeric) + list(strings))
     data = upload_text(eng, raw)
     table = DeviceTable(eng, rows, header=list(plans))
+    jobs = []   # (name, want_string, labels, plan): decoded together, one launch for all their streams
     for name in list(numeric) + list(strings):
         want_string = name in strings
         if name not in plans:  # absent column: all null, as read_csv does
@@ -244,25 +257,34 @@ def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[
         if want_string != (plan.ptype == T_BYTE_ARRAY):
             raise ParquetUnsupported(f"column {name}: physical type {plan.ptype} does not match the requested kind")
         labels: List[str] = []
-        remaps: List[torch.Tensor] = []
         if want_string:
             if any(pg.dict_id < 0 for pg in plan.pages):
                 raise ParquetUnsupported(f"column {name}: PLAIN-encoded string pages (dictionary fallback) are not supported")
             labels = sorted({s for d in plan.dictionaries for s in d})
-            pos = {s: i for i, s in enumerate(labels)}
-            remaps = [torch.tensor([pos[s] for s in d] or [0], dtype=torch.int32, device=eng.device) for d in plan.dictionaries]
         else:
             if plan.ptype not in _TYPE_WIDTH:
                 raise ParquetUnsupported(f"column {name}: physical type {plan.ptype}")
-            remaps = [torch.from_numpy(np.ascontiguousarray(d)).to(eng.device) for d in plan.dictionaries]
             for pg in plan.pages:
                 if pg.dict_id < 0 and pg.encoding != ENC_PLAIN:
                     raise ParquetUnsupported(f"column {name}: value encoding {pg.encoding}")
-        kind_plain = {T_DOUBLE: KIND_F64, T_FLOAT: KIND_F32, T_INT32: KIND_I32, T_INT64: KIND_I64}.get(plan.ptype, KIND_DICT)
-        col = eng.parquet_decode_column(data, len(raw), rows, plan.pages, kind_plain, want_string, remaps)
+        jobs.append((name, want_string, labels, plan))
+    cols = eng.parquet_decode_columns(data, rows, [column_job(eng, plan, want_string, labels) for _, want_string, labels, plan in jobs])
+    for (name, want_string, labels, plan), col in zip(jobs, cols):
         if want_string:
             table.strings[name] = StringColumn(col, labels)
         else:
             table.numeric[name] = col
             table.inferred_types[name] = {T_DOUBLE: "double", T_FLOAT: "float", T_INT32: "int", T_INT64: "long"}[plan.ptype]
     return table
+
+
+def column_job(eng: Engine, plan: _ColumnPlan, want_string: bool, labels: Sequence[str]) -> dict:
+    """One column's work order for Engine.parquet_decode_columns: the page table, the PLAIN value
+    kind and the per-row-group lookup tables (labels -> sorted codes, or numeric dictionary values)."""
+    if want_string:
+        pos = {s: i for i, s in enumerate(labels)}
+        dicts = [torch.tensor([pos[s] for s in d] or [0], dtype=torch.int32, device=eng.device) for d in plan.dictionaries]
+    else:
+        dicts = [torch.from_numpy(np.ascontiguousarray(d)).to(eng.device) for d in plan.dictionaries]
+    kind = {T_DOUBLE: KIND_F64, T_FLOAT: KIND_F32, T_INT32: KIND_I32, T_INT64: KIND_I64}.get(plan.ptype, KIND_DICT)
+    return {"pages": plan.page_table(), "kind_plain": kind, "string": want_string, "dicts": dicts}
