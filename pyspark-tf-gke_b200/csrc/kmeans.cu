@@ -142,6 +142,74 @@ __global__ void __launch_bounds__(KM_THREADS) kmeans_accumulate_kernel(const KmA
         if (s_sum[i] != 0.0) atomicAdd(p.numsum + i, s_sum[i]);
 }
 
+// k <= 32: the numeric sums without a single floating-point atomic.  fp64 shared atomics are CAS
+// loops on sm_100a and 25 clusters x 3 sums are 75 hot addresses: the kernel above spends its time
+// retrying.  Here lane c of every warp OWNS cluster c: per batch of 32 rows the warp stages the three
+// numerics in shared memory, one ballot per cluster tells lane c which rows are its own, and it adds
+// them into registers in row order (deterministic within a launch shape).  Registers live across the
+// whole grid-stride loop; the CTA folds its warps at the end and issues one global add per (cluster,
+// coordinate).  The label histogram keeps its native 32-bit shared atomics; the row count of a
+// cluster is its histogram row's sum.
+__global__ void __launch_bounds__(KM_THREADS) kmeans_accumulate_owner_kernel(const KmAccumParams p) {
+    extern __shared__ double km_smem[];
+    const int L1 = p.L + 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double* s_stage = km_smem;                                               // [warps][3][32]
+    double* s_fold = s_stage + (KM_THREADS / 32) * 96;                       // [warps][32][3]
+    uint32_t* s_hist = reinterpret_cast<uint32_t*>(s_fold + (KM_THREADS / 32) * 96);   // [k][L + 1]
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    double* mine = s_stage + warp * 96;
+    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0;
+    const int64_t batches = (p.n + 31) / 32;
+    for (int64_t b = (int64_t)blockIdx.x * (KM_THREADS / 32) + warp; b < batches; b += (int64_t)gridDim.x * (KM_THREADS / 32)) {
+        const int64_t i = b * 32 + lane;
+        int c = -1;
+        if (i < p.n) {
+            c = p.cluster[i];
+            if (c < 0 || c >= p.k) c = -1;
+        }
+        if (c >= 0) {
+            int32_t idx = p.index[i];
+            if (idx < 0 || idx >= p.L) idx = p.L;
+            atomicAdd(s_hist + c * L1 + idx, 1u);
+            mine[lane] = p.num[0][i];
+            mine[32 + lane] = p.num[1][i];
+            mine[64 + lane] = p.num[2][i];
+        }
+        unsigned own = 0;   // rows of this batch that belong to cluster `lane`
+        for (int q = 0; q < p.k; ++q) {
+            const unsigned m = __ballot_sync(0xffffffffu, c == q);
+            if (lane == q) own = m;
+        }
+        __syncwarp();
+        while (own) {
+            const int r = __ffs(own) - 1;
+            own &= own - 1;
+            acc0 += mine[r];
+            acc1 += mine[32 + r];
+            acc2 += mine[64 + r];
+        }
+        __syncwarp();
+    }
+    double* fold = s_fold + (warp * 32 + lane) * 3;
+    fold[0] = acc0; fold[1] = acc1; fold[2] = acc2;
+    __syncthreads();
+    if (threadIdx.x < p.k * 3) {
+        const int c = threadIdx.x / 3, j = threadIdx.x % 3;
+        double t = 0.0;
+        for (int w = 0; w < KM_THREADS / 32; ++w) t += s_fold[(w * 32 + c) * 3 + j];   // fixed order
+        if (t != 0.0) atomicAdd(p.numsum + c * 3 + j, t);
+    }
+    for (int c = threadIdx.x; c < p.k; c += KM_THREADS) {
+        unsigned long long rows = 0;
+        for (int l = 0; l < L1; ++l) rows += s_hist[c * L1 + l];
+        if (rows) atomicAdd(p.count + c, rows);
+    }
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS)
+        if (s_hist[i]) atomicAdd(p.hist + i, (unsigned long long)s_hist[i]);
+}
+
 }  // namespace etl
 
 using etl::Handle;
@@ -209,6 +277,17 @@ extern "C" int etl_kmeans_accumulate(etl_handle* hh, const int32_t* index, const
     p.count = reinterpret_cast<unsigned long long*>(d_count);
     p.hist = reinterpret_cast<unsigned long long*>(d_hist);
     p.numsum = d_numsum;
+    static const int owner = [] { const char* e = getenv("ETL_KM_OWNER"); return e ? atoi(e) : 1; }();
+    const size_t osmem = (size_t)(etl::KM_THREADS / 32) * 96 * 2 * sizeof(double) + (size_t)k * (num_labels + 1) * sizeof(uint32_t);
+    if (owner && k <= 32 && osmem <= 200 * 1024) {   // lane c owns cluster c: no floating-point atomics in the row loop
+        ETL_CUDA(cudaFuncSetAttribute(etl::kmeans_accumulate_owner_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)osmem));
+        int64_t ob = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
+        const int opsm = osmem > 100 * 1024 ? 1 : (osmem > 50 * 1024 ? 2 : 8);
+        if (ob > (int64_t)h->sm_count * opsm) ob = (int64_t)h->sm_count * opsm;
+        etl::kmeans_accumulate_owner_kernel<<<(unsigned)ob, etl::KM_THREADS, osmem, stream>>>(p);
+        ETL_CUDA(cudaGetLastError());
+        return ETL_OK;
+    }
     ETL_CUDA(cudaFuncSetAttribute(etl::kmeans_accumulate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t blocks = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
     const int per_sm = smem > 100 * 1024 ? 1 : (smem > 50 * 1024 ? 2 : 4);

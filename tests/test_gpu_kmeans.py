@@ -113,3 +113,22 @@ def test_kmeans_workload_returns_both_models_and_infers_single_rows(eng, monkeyp
     assert torch.equal(loaded_model.transform(loaded_pipeline, index2, nums2), model.transform(pipeline_model))
     pkg.KMeansWorkload.pipeline_model, pkg.KMeansWorkload.kmeans_model = loaded_pipeline, loaded_model
     assert wl.infer_single_row(None, "Asthma", 10)[0] == pred
+
+
+@pytest.mark.parametrize("k", [1, 25, 32, 40])
+def test_accumulate_owner_and_atomic_kernels_match_numpy(eng, k):
+    # k <= 32: lane c of every warp owns cluster c (no floating-point atomics); above: shared atomics
+    n, L = 70_001, 30
+    index, nums = _blobs(n, L, 3)
+    rng = np.random.default_rng(k)
+    cluster = rng.integers(-1, k + 1, n).astype(np.int32)         # -1 and k are out of range: skipped
+    cluster[rng.random(n) < 0.5] = 0                              # a hot cluster
+    ds = _Dataset(eng, index, nums, L, 5)
+    count, hist, numsum = eng.kmeans_accumulate(ds.index, ds.numerics, torch.from_numpy(cluster).to(eng.device), k, L)
+    ok = (cluster >= 0) & (cluster < k)
+    assert count.cpu().numpy().tolist() == np.bincount(cluster[ok], minlength=k).tolist()
+    idx = np.where((index >= 0) & (index < L), index, L)
+    for c in range(k):
+        sel = cluster == c
+        assert hist[c].cpu().numpy().tolist() == np.bincount(idx[sel], minlength=L + 1).tolist()
+        assert numsum[c].cpu().numpy().tolist() == [float(v[sel].sum()) for v in nums]
