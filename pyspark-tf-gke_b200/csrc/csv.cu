@@ -50,8 +50,14 @@ struct CsvBlockStart {
 
 // 4-bit mask of the bytes of w equal to the byte replicated in `pat`
 __device__ __forceinline__ unsigned eq4(uint32_t w, uint32_t pat) {
-    const uint32_t r = __vcmpeq4(w, pat) & 0x08040201u;
-    return (r * 0x01010101u) >> 24;  // distinct bits per byte: the byte sum is the mask
+    const uint32_t t = w ^ pat;   // exact zero-byte flags (bit 7 of each matching byte), then one multiply gathers them
+    const uint32_t f = ~(((t & 0x7f7f7f7fu) + 0x7f7f7f7fu) | t) & 0x80808080u;
+    return ((f >> 7) * 0x01020408u) >> 24;
+}
+// does w hold a byte equal to the byte replicated in pat?  (bit 7 of some byte of the result is set)
+__device__ __forceinline__ uint32_t has_byte(uint32_t w, uint32_t pat) {
+    const uint32_t t = w ^ pat;
+    return (t - 0x01010101u) & ~t;
 }
 
 // bit 7 of every byte of w that equals the byte replicated in pat (exact per byte)
@@ -625,16 +631,25 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                 unsigned vm = 0xff;
                 if (pos < start) vm = 0xffu << (start - pos);
                 if (pos + 8 > p.n) vm &= 0xffu >> (8 - (p.n - pos));
-                const unsigned q8 = eq8(w, 0x22222222u) & vm;
                 const unsigned c8 = eq8(w, 0x2c2c2c2cu) & vm;
-                const unsigned n8 = eq8(w, 0x0a0a0a0au) & vm;
-                unsigned ins = q8;
-                ins ^= ins << 1; ins ^= ins << 2; ins ^= ins << 4;
-                ins = (ins << 1) & 0xff;
-                if (inside) ins ^= 0xff;
-                const unsigned end8 = n8 & ~ins & 0xff;
-                const unsigned keep = end8 ? ((end8 & (0u - end8)) - 1) : 0xffu;  // bytes before the record end
-                unsigned oc = c8 & ~ins & keep;
+                // a word with neither a quote nor a newline (and outside quotes) needs only its commas - the
+                // usual case when the requested fields end before the row does (a false positive from the
+                // bytes outside vm merely takes the exact path)
+                const uint32_t lo = (uint32_t)w, hi = (uint32_t)(w >> 32);
+                const uint32_t special = (has_byte(lo, 0x22222222u) | has_byte(hi, 0x22222222u) | has_byte(lo, 0x0a0a0a0au) |
+                                          has_byte(hi, 0x0a0a0a0au)) & 0x80808080u;
+                unsigned q8 = 0, end8 = 0, oc = c8;
+                if (special | inside) {
+                    q8 = eq8(w, 0x22222222u) & vm;
+                    const unsigned n8 = eq8(w, 0x0a0a0a0au) & vm;
+                    unsigned ins = q8;
+                    ins ^= ins << 1; ins ^= ins << 2; ins ^= ins << 4;
+                    ins = (ins << 1) & 0xff;
+                    if (inside) ins ^= 0xff;
+                    end8 = n8 & ~ins & 0xff;
+                    const unsigned keep = end8 ? ((end8 & (0u - end8)) - 1) : 0xffu;  // bytes before the record end
+                    oc = c8 & ~ins & keep;
+                }
                 while (oc) {
                     const int b = __ffs(oc) - 1;
                     oc &= oc - 1;
