@@ -232,67 +232,106 @@ struct PqGatherParams {
     int32_t* status;            // [2] dictionary index out of range
 };
 
+// One CTA per data page, in spans of PQ_SPAN values: (1) warp per 32 values: definition levels ->
+// validity word + non-null count (no block barrier inside the loop); (2) one block scan of the
+// span's counts; (3) warp per 32 values again: rank among the page's non-null values = scanned base
+// + popcount below the lane, value fetched (PLAIN) or looked up (dictionary), row written.
+constexpr int PQ_SPAN = 32 * 1024;   // values per span: 1024 groups of 32
+
 __global__ void __launch_bounds__(PQ_THREADS) pq_gather_kernel(const PqGatherParams p) {
-    __shared__ uint32_t s_warp[PQ_THREADS / 32];
+    __shared__ uint32_t s_bits[PQ_SPAN / 32];
+    __shared__ uint32_t s_base[PQ_SPAN / 32];
+    __shared__ uint32_t s_warp[PQ_WARPS];
     __shared__ uint32_t s_running;
     const PqPage pg = p.pages[blockIdx.x];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_running = 0;
-    __syncthreads();
-    for (int base = 0; base < pg.num_values; base += PQ_THREADS) {
-        const int i = base + threadIdx.x;
-        const bool in = i < pg.num_values;
-        const bool ok = in && (pg.levels_offset < 0 || p.levels[pg.levels_offset + i] > 0);
-        const unsigned b = __ballot_sync(0xffffffffu, ok);
-        if (lane == 0) s_warp[warp] = __popc(b);
-        __syncthreads();
-        uint32_t before = s_running;
-        uint32_t chunk = 0;
-#pragma unroll
-        for (int w = 0; w < PQ_THREADS / 32; ++w) {
-            if (w < warp) before += s_warp[w];
-            chunk += s_warp[w];
+    for (int span0 = 0; span0 < pg.num_values; span0 += PQ_SPAN) {
+        const int span_n = pg.num_values - span0 < PQ_SPAN ? pg.num_values - span0 : PQ_SPAN;
+        const int groups = (span_n + 31) >> 5;
+        __syncthreads();   // s_bits / s_base of the previous span are no longer read; s_running is visible
+        for (int g = warp; g < groups; g += PQ_WARPS) {
+            const int i = span0 + g * 32 + lane;
+            const bool ok = i < pg.num_values && (pg.levels_offset < 0 || p.levels[pg.levels_offset + i] > 0);
+            const unsigned b = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) s_bits[g] = b;
         }
-        const uint32_t rank = before + __popc(b & lanemask_lt());  // position among the page's non-null values
-        const int64_t row = pg.row_start + i;
-        if (in) {
-            double v = 0.0;
-            int32_t code = -1;
-            if (ok) {
-                if (pg.kind == PQ_KIND_DICT) {
-                    const int32_t ix = p.indices[pg.val_offset + rank];
-                    if (ix < 0 || ix >= p.dict_size[pg.dict_id]) {
-                        atomicAdd(p.status + 2, 1);
-                    } else if (p.string_column) {
-                        code = static_cast<const int32_t*>(p.dict[pg.dict_id])[ix];
+        __syncthreads();
+        // exclusive scan of the groups' non-null counts: PQ_SPAN / 32 / PQ_THREADS consecutive groups per thread
+        constexpr int PER = PQ_SPAN / 32 / PQ_THREADS;
+        uint32_t c[PER], mine = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const int g = threadIdx.x * PER + k;
+            c[k] = g < groups ? __popc(s_bits[g]) : 0;
+            mine += c[k];
+        }
+        uint32_t incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += up;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t run = s_running + incl - mine;
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < PQ_WARPS; ++w) {
+            if (w < warp) run += s_warp[w];
+            total += s_warp[w];
+        }
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            const int g = threadIdx.x * PER + k;
+            if (g < groups) s_base[g] = run;
+            run += c[k];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_running += total;
+        for (int g = warp; g < groups; g += PQ_WARPS) {
+            const int i = span0 + g * 32 + lane;
+            const bool in = i < pg.num_values;
+            const unsigned b = s_bits[g];
+            const bool ok = (b >> lane) & 1u;
+            const uint32_t rank = s_base[g] + __popc(b & lanemask_lt());  // position among the page's non-null values
+            const int64_t row = pg.row_start + i;
+            if (in) {
+                double v = 0.0;
+                int32_t code = -1;
+                if (ok) {
+                    if (pg.kind == PQ_KIND_DICT) {
+                        const int32_t ix = p.indices[pg.val_offset + rank];
+                        if (ix < 0 || ix >= p.dict_size[pg.dict_id]) {
+                            atomicAdd(p.status + 2, 1);
+                        } else if (p.string_column) {
+                            code = static_cast<const int32_t*>(p.dict[pg.dict_id])[ix];
+                        } else {
+                            v = static_cast<const double*>(p.dict[pg.dict_id])[ix];
+                        }
                     } else {
-                        v = static_cast<const double*>(p.dict[pg.dict_id])[ix];
-                    }
-                } else {
-                    const uint8_t* src = p.file + pg.val_offset;
-                    if (pg.kind == PQ_KIND_F64) {   // pages are not 8-byte aligned in the file
-                        v = __longlong_as_double((long long)pq_load_u64(src + (int64_t)rank * 8));
-                    } else if (pg.kind == PQ_KIND_I64) {
-                        v = (double)(long long)pq_load_u64(src + (int64_t)rank * 8);
-                    } else {
-                        const uint32_t u = pq_load_u32(src + (int64_t)rank * 4);
-                        v = pg.kind == PQ_KIND_F32 ? (double)__uint_as_float(u) : (double)(int32_t)u;
+                        const uint8_t* src = p.file + pg.val_offset;
+                        if (pg.kind == PQ_KIND_F64) {   // pages are not 8-byte aligned in the file
+                            v = __longlong_as_double((long long)pq_load_u64(src + (int64_t)rank * 8));
+                        } else if (pg.kind == PQ_KIND_I64) {
+                            v = (double)(long long)pq_load_u64(src + (int64_t)rank * 8);
+                        } else {
+                            const uint32_t u = pq_load_u32(src + (int64_t)rank * 4);
+                            v = pg.kind == PQ_KIND_F32 ? (double)__uint_as_float(u) : (double)(int32_t)u;
+                        }
                     }
                 }
+                if (p.string_column) static_cast<int32_t*>(p.out)[row] = code;
+                else static_cast<double*>(p.out)[row] = v;
             }
-            if (p.string_column) static_cast<int32_t*>(p.out)[row] = code;
-            else static_cast<double*>(p.out)[row] = v;
+            // validity bits: this group's 32 rows may straddle two bitmap words
+            if (lane == 0 && b) {
+                const int64_t r0 = pg.row_start + span0 + g * 32;
+                const int sh = (int)(r0 & 31);
+                atomicOr(p.valid + (r0 >> 5), b << sh);
+                if (sh && (b >> (32 - sh))) atomicOr(p.valid + (r0 >> 5) + 1, b >> (32 - sh));
+            }
         }
-        // validity bits: this warp's 32 rows may straddle two bitmap words
-        if (lane == 0 && b) {
-            const int64_t r0 = pg.row_start + base + warp * 32;
-            const int sh = (int)(r0 & 31);
-            atomicOr(p.valid + (r0 >> 5), b << sh);
-            if (sh && (b >> (32 - sh))) atomicOr(p.valid + (r0 >> 5) + 1, b >> (32 - sh));
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) s_running += chunk;
-        __syncthreads();
     }
 }
 
