@@ -429,6 +429,11 @@ ETL_API int etl_kmeans_assign(etl_handle* h, const int32_t* index, const double*
 ETL_API int etl_kmeans_accumulate(etl_handle* h, const int32_t* index, const double* const num[3],
                           const int32_t* cluster, int64_t n, int32_t k, int32_t num_labels, int64_t* d_count,
                           int64_t* d_hist, double* d_numsum, void* stream);
+/* The centre update that follows (Spark does it on the driver): centers[c] <- hist[c] / count[c] per label,
+ * copied into each of the `repeats` blocks, ++ numsum[c] / count[c]; a cluster with count 0 keeps its
+ * centre.  centers: double[k][repeats * num_labels + 3], updated in place on the device. */
+ETL_API int etl_kmeans_update(etl_handle* h, const int64_t* d_count, const int64_t* d_hist, const double* d_numsum,
+                      int32_t k, int32_t num_labels, int32_t repeats, double* centers, void* stream);
 
 /* ---- next row: device-resident hand-off to the trainer */
 

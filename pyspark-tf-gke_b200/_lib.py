@@ -92,6 +92,8 @@ _PROTOS = {
     "etl_kmeans_assign": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
+    "etl_kmeans_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                    C.c_void_p, C.c_void_p]),
     "etl_kmeans_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "etl_mlp_param_count": (C.c_int, [C.c_int32]),

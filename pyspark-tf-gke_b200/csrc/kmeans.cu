@@ -210,6 +210,24 @@ __global__ void __launch_bounds__(KM_THREADS) kmeans_accumulate_owner_kernel(con
         if (s_hist[i]) atomicAdd(p.hist + i, (unsigned long long)s_hist[i]);
 }
 
+// the centre update of one Lloyd iteration, on the device: centre c <- mean of its rows (unchanged when
+// the cluster is empty); the divisions are the ones the host did before, so the centres keep their bits
+__global__ void __launch_bounds__(256) kmeans_update_kernel(const unsigned long long* __restrict__ count,
+                                                            const unsigned long long* __restrict__ hist,
+                                                            const double* __restrict__ numsum, int L, int repeats,
+                                                            double* __restrict__ centers) {
+    const int c = blockIdx.x;
+    const unsigned long long rows = count[c];
+    if (rows == 0) return;
+    const int D = repeats * L + 3;
+    const double denom = (double)rows;
+    double* row = centers + (int64_t)c * D;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        const int j = d - repeats * L;
+        row[d] = j < 0 ? (double)hist[(int64_t)c * (L + 1) + d % L] / denom : numsum[c * 3 + j] / denom;
+    }
+}
+
 }  // namespace etl
 
 using etl::Handle;
@@ -293,6 +311,19 @@ extern "C" int etl_kmeans_accumulate(etl_handle* hh, const int32_t* index, const
     const int per_sm = smem > 100 * 1024 ? 1 : (smem > 50 * 1024 ? 2 : 4);
     if (blocks > (int64_t)h->sm_count * per_sm) blocks = (int64_t)h->sm_count * per_sm;
     etl::kmeans_accumulate_kernel<<<(unsigned)blocks, etl::KM_THREADS, smem, stream>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_kmeans_update(etl_handle* hh, const int64_t* d_count, const int64_t* d_hist, const double* d_numsum,
+                                 int32_t k, int32_t num_labels, int32_t repeats, double* centers, void* stream_) {
+    ETL_REQUIRE(hh && d_count && d_hist && d_numsum && centers, "kmeans_update: NULL argument");
+    ETL_REQUIRE(k >= 1 && num_labels >= 0 && repeats >= 1, "kmeans_update: k=%d num_labels=%d repeats=%d", k, num_labels, repeats);
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    etl::kmeans_update_kernel<<<(unsigned)k, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        reinterpret_cast<const unsigned long long*>(d_count), reinterpret_cast<const unsigned long long*>(d_hist), d_numsum,
+        num_labels, repeats, centers);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

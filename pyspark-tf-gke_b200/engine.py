@@ -656,6 +656,13 @@ class Engine:
         self.launches += 1 if n else 0
         return count, hist, numsum
 
+    def kmeans_update(self, count: torch.Tensor, hist: torch.Tensor, numsum: torch.Tensor, centers: torch.Tensor,
+                      num_labels: int, repeats: int) -> None:
+        """centers[c] <- mean of cluster c's rows, in place (empty clusters keep theirs)."""
+        _lib.check(self.lib.etl_kmeans_update(self._h, count.data_ptr(), hist.data_ptr(), numsum.data_ptr(), centers.shape[0],
+                                              num_labels, repeats, centers.data_ptr(), self._stream()))
+        self.launches += 1
+
     # --------------------------------------------- trainer hand-off (8f rank 1)
     def mlp_param_count(self, classes: int) -> int:
         return int(self.lib.etl_mlp_param_count(classes))

@@ -190,22 +190,17 @@ class KMeans:
             raise ValueError("KMeans.fit: empty dataset")
         centers = self._init_parallel(eng, index, nums, L, repeats)
         k = centers.shape[0]
-        onehot = repeats * L
         it, cost_sum, count = 0, 0.0, None
+        d_centers = torch.from_numpy(np.ascontiguousarray(centers)).to(eng.device)
         while it < self.maxIter:
-            d_centers = torch.from_numpy(np.ascontiguousarray(centers)).to(eng.device)
+            # one Lloyd iteration, all on the device: assign, per-cluster sums, new centres; a single
+            # read-back (the new centres + the cost) decides about convergence
             cluster, cost = eng.kmeans_assign(index, nums, d_centers, L, repeats)
             count, hist, numsum = eng.kmeans_accumulate(index, nums, cluster, k, L)
             s, _ = eng.sum_count([Column(cost)])
+            eng.kmeans_update(count, hist, numsum, d_centers, L, repeats)
+            new = d_centers.cpu().numpy()
             cost_sum = float(s[0])
-            count_h, hist_h, numsum_h = count.cpu().numpy(), hist.cpu().numpy(), numsum.cpu().numpy()
-            new = centers.copy()
-            for c in range(k):
-                if count_h[c] > 0:
-                    block = hist_h[c, :L] / float(count_h[c])
-                    for r in range(repeats):
-                        new[c, r * L:(r + 1) * L] = block
-                    new[c, onehot:] = numsum_h[c] / float(count_h[c])
             moved = ((new - centers) ** 2).sum(axis=1)
             centers = new
             it += 1
