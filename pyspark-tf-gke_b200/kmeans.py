@@ -153,32 +153,67 @@ class KMeans:
         sel = torch.from_numpy(rows.astype(np.int64)).to(index.device)
         return dense_rows(index[sel].cpu().numpy(), [t[sel].cpu().numpy() for t in nums], L, repeats)
 
+    # With torch.distributed initialised the dataset is this rank's shard of the rows (rank order = row
+    # order): per-cluster sums, costs and candidate weights are all-reduced and the sampled candidate
+    # rows all-gathered, so every rank ends with the model a single GPU would have fitted on all rows
+    # (bit for bit when the sums are exact).  Random draws are keyed by the GLOBAL row number.
+    @staticmethod
+    def _all_sum(t: torch.Tensor) -> torch.Tensor:
+        from . import dist as D
+        if D.world()[1] > 1:
+            import torch.distributed as td
+            td.all_reduce(t)
+        return t
+
+    @staticmethod
+    def _all_rows(local: np.ndarray) -> np.ndarray:
+        """concatenation over ranks (rank order) of a few dense rows"""
+        from . import dist as D
+        if D.world()[1] == 1:
+            return local
+        import torch.distributed as td
+        parts = [None] * D.world()[1]
+        td.all_gather_object(parts, local)
+        return np.concatenate(parts)
+
     def _init_parallel(self, eng: Engine, index, nums, L, repeats) -> np.ndarray:
+        from . import dist as D
+        rank, size = D.world()
         n, k = index.shape[0], self.k
-        first = int(synth.bits(self.seed, STREAM_FIRST, 0, 1)[0] % np.uint64(n))
-        candidates = self._gather_dense(index, nums, np.array([first]), L, repeats)
+        counts = torch.zeros(size, dtype=torch.int64, device=eng.device)
+        counts[rank] = n
+        counts = self._all_sum(counts).cpu().numpy()
+        row0, total = int(counts[:rank].sum()), int(counts.sum())
+        D_feat = repeats * L + 3
+        first = int(synth.bits(self.seed, STREAM_FIRST, 0, 1)[0] % np.uint64(total))
+        mine = row0 <= first < row0 + n
+        candidates = self._all_rows(self._gather_dense(index, nums, np.array([first - row0]), L, repeats) if mine
+                                    else np.zeros((0, D_feat)))
         new = candidates
         cost = torch.full((n,), float("inf"), dtype=torch.float64, device=eng.device)
         for step in range(self.initSteps):
             _, cost = eng.kmeans_assign(index, nums, torch.from_numpy(new).to(eng.device), L, repeats, prev_cost=cost,
                                         want_cluster=False)
             s, _ = eng.sum_count([Column(cost)])
-            sum_costs = float(s[0])
+            sum_costs = float(self._all_sum(s[:1].clone())[0])
             if not sum_costs > 0.0:
                 break
             # u * 1e5 < 1e5 * 2k * cost / sumCosts  (the synthetic generator hands out u * 1e5)
-            u = eng.synth_column(self.seed, STREAM_STEP0 + step, synth.KIND_REAL, n, with_valid=False).data
+            lead = row0 % 32      # the generator starts at multiples of 32 rows
+            u = eng.synth_column(self.seed, STREAM_STEP0 + step, synth.KIND_REAL, n + lead, row0=row0 - lead,
+                                 with_valid=False).data[lead:]
             chosen = torch.nonzero(u < cost * (100000.0 * 2.0 * k / sum_costs)).flatten().cpu().numpy()
-            if chosen.size == 0:
+            picked = self._all_rows(self._gather_dense(index, nums, chosen, L, repeats) if chosen.size else np.zeros((0, D_feat)))
+            if picked.shape[0] == 0:
                 continue
-            new = self._gather_dense(index, nums, chosen, L, repeats)
+            new = picked
             candidates = np.concatenate([candidates, new])
         distinct = np.unique(candidates, axis=0)
         if distinct.shape[0] <= k:
             return distinct
         cluster, _ = eng.kmeans_assign(index, nums, torch.from_numpy(distinct).to(eng.device), L, repeats)
-        weights = torch.bincount(cluster.to(torch.int64), minlength=distinct.shape[0]).cpu().numpy().astype(np.float64)
-        return local_kmeans_pp(np.random.default_rng(self.seed), distinct, weights, k)
+        weights = self._all_sum(torch.bincount(cluster.to(torch.int64), minlength=distinct.shape[0]))
+        return local_kmeans_pp(np.random.default_rng(self.seed), distinct, weights.cpu().numpy().astype(np.float64), k)
 
     def fit(self, dataset) -> KMeansModel:
         """dataset: the EtlPipelineModel returned by KMeansWorkload.k_means (its
@@ -198,6 +233,8 @@ class KMeans:
             cluster, cost = eng.kmeans_assign(index, nums, d_centers, L, repeats)
             count, hist, numsum = eng.kmeans_accumulate(index, nums, cluster, k, L)
             s, _ = eng.sum_count([Column(cost)])
+            for t in (count, hist, numsum, s):   # rows sharded over ranks: the sums of all of them
+                self._all_sum(t)
             eng.kmeans_update(count, hist, numsum, d_centers, L, repeats)
             new = d_centers.cpu().numpy()
             cost_sum = float(s[0])

@@ -132,3 +132,16 @@ def test_accumulate_owner_and_atomic_kernels_match_numpy(eng, k):
         sel = cluster == c
         assert hist[c].cpu().numpy().tolist() == np.bincount(idx[sel], minlength=L + 1).tolist()
         assert numsum[c].cpu().numpy().tolist() == [float(v[sel].sum()) for v in nums]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (run by hand with gpurun --gpus 2)")
+def test_sharded_fit_equals_single_gpu_fit():
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29533", os.path.join(root, "tools", "check_dist_kmeans.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert '"identical": true' in r.stdout
