@@ -160,7 +160,8 @@ __device__ __forceinline__ bool csv_first_line_nonblank(const uint8_t* text, int
 }
 
 __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const uint8_t* __restrict__ text, int64_t n,
-                                                                        int64_t blocks, CsvBlockSummary* __restrict__ out) {
+                                                                        int64_t blocks, CsvBlockSummary* __restrict__ out,
+                                                                        ulonglong2* __restrict__ masks) {
     extern __shared__ __align__(128) unsigned char csv_smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(csv_smem + 2 * CSV_STAGE_BYTES);
     __shared__ uint32_t s_par[CSV_THREADS / 32];
@@ -183,6 +184,9 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const ui
         const int64_t base = blk * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
         uint64_t q, nl, opens;
         csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens);
+        // pass 2 needs exactly these two words per window: kept (16 B per 64 B of text) so that it neither
+        // re-reads the text nor rebuilds the masks
+        masks[blk * CSV_THREADS + tid] = make_ulonglong2(q, nl & opens);
         const uint64_t ins = inside_mask(q);
         unsigned c_out = __popcll(nl & ~ins & opens), c_in = __popcll(nl & ins & opens);  // thread starts outside / inside
         const unsigned tp = __popcll(q) & 1;
@@ -336,33 +340,20 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_span_apply_kernel(const CsvBl
 
 __global__ void __launch_bounds__(CSV_THREADS) csv_row_offsets_kernel(const uint8_t* __restrict__ text, int64_t n,
                                                                       int64_t blocks, const CsvBlockStart* __restrict__ start,
+                                                                      const ulonglong2* __restrict__ masks,
                                                                       int64_t* __restrict__ row_start) {
-    extern __shared__ __align__(128) unsigned char csv_smem[];
-    uint64_t* bar = reinterpret_cast<uint64_t*>(csv_smem + 2 * CSV_STAGE_BYTES);
     __shared__ uint32_t s_par[CSV_THREADS / 32];
     __shared__ uint32_t s_cnt[CSV_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) {
-        mbar_init(bar, 1);
-        mbar_init(bar + 1, 1);
-        mbar_init_fence();
-    }
-    __syncthreads();
-    int64_t blk = blockIdx.x;
-    if (tid == 0 && blk < blocks) csv_stage_issue(text, n, blk, csv_smem, bar);
-    for (int it = 0; blk < blocks; blk += gridDim.x, ++it) {
-        const int buf = it & 1;
-        __syncthreads();
-        if (tid == 0 && blk + gridDim.x < blocks)
-            csv_stage_issue(text, n, blk + gridDim.x, csv_smem + (buf ^ 1) * CSV_STAGE_BYTES, bar + (buf ^ 1));
+    for (int64_t blk = blockIdx.x; blk < blocks; blk += gridDim.x) {
         const CsvBlockStart bs = start[blk];
-        mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
+        const ulonglong2 m = masks[blk * CSV_THREADS + tid];   // {quotes, newlines that open a non-blank line} of the window
+        const uint64_t q = m.x;
         const int64_t base = blk * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
-        uint64_t q, nl, opens;
-        csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens);
         const unsigned tp = __popcll(q) & 1;
         const unsigned wb = __ballot_sync(0xffffffffu, tp);
         const unsigned lane_state = __popc(wb & lanemask_lt()) & 1;
+        __syncthreads();   // the previous block's s_par / s_cnt are no longer read
         if (lane == 0) s_par[warp] = __popc(wb) & 1;
         __syncthreads();
         unsigned st = lane_state ^ bs.inside;
@@ -371,7 +362,7 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_row_offsets_kernel(const uint
             if (w < warp) st ^= s_par[w];
         uint64_t ins = inside_mask(q);
         if (st) ins = ~ins;
-        uint64_t ev = nl & ~ins & opens;  // newlines outside quotes whose next byte opens a non-blank line
+        uint64_t ev = m.y & ~ins;  // newlines outside quotes whose next byte opens a non-blank line
         const bool virt = blk == 0 && tid == 0 && csv_first_line_nonblank(text, n);
         unsigned cnt = __popcll(ev) + (virt ? 1 : 0);
         unsigned incl = cnt;
@@ -769,17 +760,20 @@ extern "C" int etl_csv_index_rows(etl_handle* hh, const uint8_t* text, int64_t n
     }
     const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
     const int64_t supers = (blocks + etl::CSV_THREADS - 1) / etl::CSV_THREADS;
-    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart)) +
+    // scratch: block summaries | block starts | per-window masks (16 B per 64 B of text) | span arrays
+    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart) +
+                                          etl::CSV_THREADS * sizeof(ulonglong2)) +
                         (size_t)supers * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
     int rc = etl::arena_reserve(h, need);
     if (rc != ETL_OK) return rc;
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
-    auto* super = reinterpret_cast<etl::CsvBlockSummary*>(start + blocks);
+    auto* masks = reinterpret_cast<ulonglong2*>(start + blocks);
+    auto* super = reinterpret_cast<etl::CsvBlockSummary*>(masks + blocks * etl::CSV_THREADS);
     auto* super_start = reinterpret_cast<etl::CsvBlockStart*>(super + supers);
     ETL_CUDA(cudaFuncSetAttribute(etl::csv_block_summary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)etl::CSV_STAGE_SMEM));
     const int64_t grid = blocks < (int64_t)h->sm_count * 6 ? blocks : (int64_t)h->sm_count * 6;   // 33 KB each: 6 CTAs per SM
-    etl::csv_block_summary_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, sum);
+    etl::csv_block_summary_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, sum, masks);
     etl::csv_span_reduce_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super);
     etl::csv_span_scan_kernel<<<1, etl::CSV_THREADS, 0, stream>>>(super, supers, super_start, d_rows);
     etl::csv_span_apply_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super_start, start);
@@ -797,14 +791,14 @@ extern "C" int etl_csv_row_offsets(etl_handle* hh, const uint8_t* text, int64_t 
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     ETL_CUDA(cudaSetDevice(h->device));
     const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
-    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
+    const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart) +
+                                          etl::CSV_THREADS * sizeof(ulonglong2));
     ETL_REQUIRE(h->scratch_bytes >= need, "csv_row_offsets: call etl_csv_index_rows on the same text first");
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
-    ETL_CUDA(cudaFuncSetAttribute(etl::csv_row_offsets_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)etl::CSV_STAGE_SMEM));
-    const int64_t grid = blocks < (int64_t)h->sm_count * 6 ? blocks : (int64_t)h->sm_count * 6;
-    etl::csv_row_offsets_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, start,
-                                                                                                  row_start);
+    auto* masks = reinterpret_cast<const ulonglong2*>(start + blocks);   // left there by etl_csv_index_rows
+    const int64_t grid = blocks < (int64_t)h->sm_count * 8 ? blocks : (int64_t)h->sm_count * 8;
+    etl::csv_row_offsets_kernel<<<(unsigned)grid, etl::CSV_THREADS, 0, stream>>>(text, nbytes, blocks, start, masks, row_start);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }
