@@ -192,6 +192,10 @@ ETL_API int etl_csv_row_offsets(etl_handle* h, const uint8_t* text, int64_t nbyt
  * lowest record with a [0] or [1] event. */
 #define ETL_CSV_TRIM_STRINGS 1
 #define ETL_CSV_NAN_IS_NULL 2
+/* The caller vouches that `text` is byte for byte the text the handle's last etl_csv_index_rows call
+ * indexed: the row scan then walks the quote / comma / newline masks that call left in the arena (no
+ * byte compares).  Ignored - the text itself is scanned - when the arena no longer holds them. */
+#define ETL_CSV_USE_INDEX_MASKS 4
 ETL_API int etl_csv_parse_columns(etl_handle* h, const uint8_t* text, int64_t nbytes, const int64_t* row_start,
                           int64_t first_row, int64_t rows, int32_t ncols, const int32_t* field,
                           const int32_t* kind, void* const* out, uint32_t* const* valid,

@@ -13,6 +13,7 @@ void set_error(const char* fmt, ...) {
 }
 
 int arena_reserve(Handle* h, size_t bytes) {
+    h->csv_text = nullptr;   // whoever reserves the arena is about to overwrite what the CSV index left in it
     if (bytes <= h->scratch_bytes) return ETL_OK;
     size_t want = h->scratch_bytes ? h->scratch_bytes : (size_t)1 << 20;
     while (want < bytes) want *= 2;

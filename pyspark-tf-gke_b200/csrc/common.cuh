@@ -28,6 +28,10 @@ struct Handle {
     // staging for the *_host entry points
     void* stage = nullptr;
     size_t stage_bytes = 0;
+    // CSV index state kept in the arena by etl_csv_index_rows (masks of every 64-byte window of that text);
+    // cleared whenever the arena is reallocated
+    const void* csv_text = nullptr;
+    int64_t csv_nbytes = 0;
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t events[12] = {};
 };

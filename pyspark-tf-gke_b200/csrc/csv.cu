@@ -90,27 +90,30 @@ __device__ __forceinline__ void csv_stage_issue(const uint8_t* __restrict__ text
 
 // csv_masks64 on a staged block: `win` = the thread's window in shared memory, `base` its text offset
 __device__ __forceinline__ void csv_masks64_staged(const unsigned char* win, int64_t base, int64_t n, uint64_t* quotes,
-                                                   uint64_t* newlines, uint64_t* opens) {
-    uint64_t q = 0, nl = 0, cr = 0;
+                                                   uint64_t* newlines, uint64_t* opens, uint64_t* commas) {
+    uint64_t q = 0, nl = 0, cr = 0, cm = 0;
     uint8_t a = 0, b = 0;
     if (base + 66 <= n) {
-        uint32_t mq[4], mn[4], any_cr = 0;
+        uint32_t mq[4], mn[4], mc[4], any_cr = 0;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
             const uint4 x = *reinterpret_cast<const uint4*>(win + 16 * v);
             const uint32_t w[4] = {x.x, x.y, x.z, x.w};
             mq[v] = 0;
             mn[v] = 0;
+            mc[v] = 0;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 mq[v] |= flags_nibble(eq_flags(w[k], 0x22222222u)) << (4 * k);
                 mn[v] |= flags_nibble(eq_flags(w[k], 0x0a0a0a0au)) << (4 * k);
+                mc[v] |= flags_nibble(eq_flags(w[k], 0x2c2c2c2cu)) << (4 * k);
                 const uint32_t t = w[k] ^ 0x0d0d0d0du;
                 any_cr |= (t - 0x01010101u) & ~t;   // bit 7 of some byte set <=> the word holds a '\r'
             }
         }
         q = (uint64_t)(mq[0] | (mq[1] << 16)) | ((uint64_t)(mq[2] | (mq[3] << 16)) << 32);
         nl = (uint64_t)(mn[0] | (mn[1] << 16)) | ((uint64_t)(mn[2] | (mn[3] << 16)) << 32);
+        cm = (uint64_t)(mc[0] | (mc[1] << 16)) | ((uint64_t)(mc[2] | (mc[3] << 16)) << 32);
         a = win[64];
         b = win[65];
         if (any_cr & 0x80808080u) {   // carriage returns are rare (none in LF files): their mask is built on demand
@@ -128,6 +131,7 @@ __device__ __forceinline__ void csv_masks64_staged(const unsigned char* win, int
             q |= (uint64_t)(c == '"') << i;
             nl |= (uint64_t)(c == '\n') << i;
             cr |= (uint64_t)(c == '\r') << i;
+            cm |= (uint64_t)(c == ',') << i;
         }
         a = base + 64 < n ? win[64] : 0;
         b = base + 65 < n ? win[65] : 0;
@@ -141,6 +145,7 @@ __device__ __forceinline__ void csv_masks64_staged(const unsigned char* win, int
     *opens = in1 & ~nl1 & ~(cr1 & (~in2 | nl2));
     *quotes = q;
     *newlines = nl;
+    *commas = cm;
 }
 
 // bit i = parity of the quotes strictly before position i (window-relative)
@@ -161,7 +166,8 @@ __device__ __forceinline__ bool csv_first_line_nonblank(const uint8_t* text, int
 
 __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const uint8_t* __restrict__ text, int64_t n,
                                                                         int64_t blocks, CsvBlockSummary* __restrict__ out,
-                                                                        ulonglong2* __restrict__ masks) {
+                                                                        ulonglong2* __restrict__ masks,
+                                                                        ulonglong2* __restrict__ field_masks) {
     extern __shared__ __align__(128) unsigned char csv_smem[];
     uint64_t* bar = reinterpret_cast<uint64_t*>(csv_smem + 2 * CSV_STAGE_BYTES);
     __shared__ uint32_t s_par[CSV_THREADS / 32];
@@ -182,11 +188,12 @@ __global__ void __launch_bounds__(CSV_THREADS) csv_block_summary_kernel(const ui
             csv_stage_issue(text, n, blk + gridDim.x, csv_smem + (buf ^ 1) * CSV_STAGE_BYTES, bar + (buf ^ 1));
         mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
         const int64_t base = blk * CSV_BLOCK_BYTES + (int64_t)tid * CSV_BYTES_PER_THREAD;
-        uint64_t q, nl, opens;
-        csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens);
+        uint64_t q, nl, opens, cm;
+        csv_masks64_staged(csv_smem + buf * CSV_STAGE_BYTES + tid * CSV_BYTES_PER_THREAD, base, n, &q, &nl, &opens, &cm);
         // pass 2 needs exactly these two words per window: kept (16 B per 64 B of text) so that it neither
-        // re-reads the text nor rebuilds the masks
+        // re-reads the text nor rebuilds the masks; the field parse walks rows over them plus the comma mask
         masks[blk * CSV_THREADS + tid] = make_ulonglong2(q, nl & opens);
+        field_masks[blk * CSV_THREADS + tid] = make_ulonglong2(cm, nl);   // {commas, newlines}
         const uint64_t ins = inside_mask(q);
         unsigned c_out = __popcll(nl & ~ins & opens), c_in = __popcll(nl & ins & opens);  // thread starts outside / inside
         const unsigned tp = __popcll(q) & 1;
@@ -407,6 +414,8 @@ struct CsvParseParams {
     int32_t* status;                    // [0] numerals outside the exact domain, [1] dictionary overflows,
                                         // [2] bit s set: column s saw a non-integer numeral, [3] unparsable numerals
     int64_t* first_bad_row;             // smallest row (file order) with a status[0] / status[1] event
+    const ulonglong2* quote_masks;      // MASKS kernel: per 64-byte window {quotes, -} and {commas, newlines}, as
+    const ulonglong2* field_masks;      // etl_csv_index_rows left them in the arena
 };
 constexpr int CSV_TRIM_STRINGS = 1;  // load_csv strips the label cell (train_tf_ps.py:120)
 constexpr int CSV_NAN_IS_NULL = 2;   // load_csv drops rows whose numeric text is "nan" (train_tf_ps.py:129)
@@ -590,14 +599,29 @@ __device__ __forceinline__ bool dec_parse_simple(const uint8_t* p, int len, doub
 //      shared memory;
 //   B  convert the requested fields; the group's values leave as one coalesced store per column
 //      plus one ballot-built validity word.
+template <bool MASKS>
 __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const CsvParseParams p) {
     __shared__ uint32_t s_fs[PARSE_WARPS][CSV_MAX_COLS][32], s_fe[PARSE_WARPS][CSV_MAX_COLS][32];  // relative to the group
     __shared__ uint32_t s_rend[PARSE_WARPS][32];
-    __shared__ int8_t s_slot_of_field[CSV_MAX_FIELDS];
+    // the requested columns in ascending field order: the row scan keeps two cursors into this list (the
+    // next field to close, the next field to open), so a separator costs two register compares
+    __shared__ int s_ord_field[CSV_MAX_COLS + 1], s_ord_slot[CSV_MAX_COLS + 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < CSV_MAX_FIELDS; i += blockDim.x) s_slot_of_field[i] = -1;
-    __syncthreads();
-    if (tid < p.ncols) s_slot_of_field[p.field[tid]] = (int8_t)tid;
+    if (tid == 0) {
+        int nf = 0;
+        for (int c = 0; c < p.ncols; ++c) {   // insertion sort of <= 8 entries
+            int j = nf++;
+            while (j > 0 && s_ord_field[j - 1] > p.field[c]) {
+                s_ord_field[j] = s_ord_field[j - 1];
+                s_ord_slot[j] = s_ord_slot[j - 1];
+                --j;
+            }
+            s_ord_field[j] = p.field[c];
+            s_ord_slot[j] = c;
+        }
+        s_ord_field[nf] = 0x7fffffff;   // sentinel: never reached
+        s_ord_slot[nf] = 0;
+    }
     __syncthreads();
     const unsigned lt = lanemask_lt();
     const int64_t groups = (p.rows + 31) / 32;
@@ -611,9 +635,66 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
         // ---------------------------------------------------------------- phase A: lane = row
         // every lane walks its own row 8 bytes at a time: quote state by an in-word prefix xor plus a
         // carried parity bit, separators by ffs over the unquoted-comma mask
-        if (lane < in_group) {
+        if (MASKS && lane < in_group) {
+            // the index pass kept, for every 64-byte window of the text, the positions of quotes, commas
+            // and newlines: the row is walked a window at a time with no byte compares at all
             const int64_t start = my_start;
-            if (s_slot_of_field[0] >= 0) s_fs[warp][s_slot_of_field[0]][lane] = (uint32_t)(start - gbase);
+            int ci = 0, oi = 0;                       // cursors: next requested field to close / to open
+            int cf = s_ord_field[0], cslot = s_ord_slot[0], of = cf, oslot = cslot;
+            if (of == 0) {                            // field 0 opens at the row start
+                s_fs[warp][oslot][lane] = (uint32_t)(start - gbase);
+                ++oi; of = s_ord_field[oi]; oslot = s_ord_slot[oi];
+            }
+            int64_t win = start >> 6;
+            const int64_t nwin = (p.n + 63) >> 6;
+            uint64_t m = ~0ull << (start & 63);   // bits of the window that belong to the row
+            unsigned inside = 0, fi = 0;
+            int64_t row_end = p.n;
+            while (win < nwin) {
+                const uint64_t q = p.quote_masks[win].x & m;
+                const ulonglong2 fm = p.field_masks[win];
+                uint64_t ins = inside_mask(q);
+                if (inside) ins = ~ins;
+                const uint64_t e = fm.y & ~ins & m;                              // newlines outside quotes
+                const uint64_t keep = e ? ((e & (0ull - e)) - 1) : ~0ull;        // bytes before the record end
+                uint64_t oc = fm.x & ~ins & m & keep;
+                const int64_t wbase = win << 6;
+                while (oc) {
+                    const int b = __ffsll((long long)oc) - 1;
+                    oc &= oc - 1;
+                    const uint32_t at = (uint32_t)(wbase + b - gbase);
+                    if ((int)fi == cf) {              // separator fi closes field fi ...
+                        s_fe[warp][cslot][lane] = at;
+                        ++ci; cf = s_ord_field[ci]; cslot = s_ord_slot[ci];
+                    }
+                    ++fi;
+                    if ((int)fi == of) {              // ... and opens field fi + 1
+                        s_fs[warp][oslot][lane] = at + 1;
+                        ++oi; of = s_ord_field[oi]; oslot = s_ord_slot[oi];
+                    }
+                }
+                if (e) {
+                    row_end = wbase + __ffsll((long long)e) - 1;
+                    break;
+                }
+                if ((int)fi > p.last_field) {  // every requested field is closed: the rest of the row is not needed
+                    row_end = wbase > start ? wbase : start;
+                    break;
+                }
+                inside ^= __popcll(q) & 1;
+                ++win;
+                m = ~0ull;
+            }
+            s_rend[warp][lane] = (uint32_t)(row_end - gbase);
+        }
+        if (!MASKS && lane < in_group) {
+            const int64_t start = my_start;
+            int ci = 0, oi = 0;                       // cursors: next requested field to close / to open
+            int cf = s_ord_field[0], cslot = s_ord_slot[0], of = cf, oslot = cslot;
+            if (of == 0) {                            // field 0 opens at the row start
+                s_fs[warp][oslot][lane] = (uint32_t)(start - gbase);
+                ++oi; of = s_ord_field[oi]; oslot = s_ord_slot[oi];
+            }
             int64_t pos = start & ~(int64_t)7;
             unsigned inside = 0, fi = 0;
             int64_t row_end = p.n;
@@ -645,9 +726,15 @@ __global__ void __launch_bounds__(PARSE_WARPS * 32) csv_parse_rows_kernel(const 
                     const int b = __ffs(oc) - 1;
                     oc &= oc - 1;
                     const uint32_t at = (uint32_t)(pos + b - gbase);
-                    if (fi < CSV_MAX_FIELDS && s_slot_of_field[fi] >= 0) s_fe[warp][s_slot_of_field[fi]][lane] = at;
-                    if (fi + 1 < CSV_MAX_FIELDS && s_slot_of_field[fi + 1] >= 0) s_fs[warp][s_slot_of_field[fi + 1]][lane] = at + 1;
+                    if ((int)fi == cf) {              // separator fi closes field fi ...
+                        s_fe[warp][cslot][lane] = at;
+                        ++ci; cf = s_ord_field[ci]; cslot = s_ord_slot[ci];
+                    }
                     ++fi;
+                    if ((int)fi == of) {              // ... and opens field fi + 1
+                        s_fs[warp][oslot][lane] = at + 1;
+                        ++oi; of = s_ord_field[oi]; oslot = s_ord_slot[oi];
+                    }
                 }
                 if (end8) {
                     row_end = pos + __ffs(end8) - 1;
@@ -762,18 +849,22 @@ extern "C" int etl_csv_index_rows(etl_handle* hh, const uint8_t* text, int64_t n
     const int64_t supers = (blocks + etl::CSV_THREADS - 1) / etl::CSV_THREADS;
     // scratch: block summaries | block starts | per-window masks (16 B per 64 B of text) | span arrays
     const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart) +
-                                          etl::CSV_THREADS * sizeof(ulonglong2)) +
+                                          etl::CSV_THREADS * 2 * sizeof(ulonglong2)) +
                         (size_t)supers * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart));
     int rc = etl::arena_reserve(h, need);
     if (rc != ETL_OK) return rc;
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
     auto* masks = reinterpret_cast<ulonglong2*>(start + blocks);
-    auto* super = reinterpret_cast<etl::CsvBlockSummary*>(masks + blocks * etl::CSV_THREADS);
+    auto* field_masks = masks + blocks * etl::CSV_THREADS;
+    auto* super = reinterpret_cast<etl::CsvBlockSummary*>(field_masks + blocks * etl::CSV_THREADS);
+    h->csv_text = text;      // the masks in the arena describe this text (until the arena is reallocated)
+    h->csv_nbytes = nbytes;
     auto* super_start = reinterpret_cast<etl::CsvBlockStart*>(super + supers);
     ETL_CUDA(cudaFuncSetAttribute(etl::csv_block_summary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)etl::CSV_STAGE_SMEM));
     const int64_t grid = blocks < (int64_t)h->sm_count * 6 ? blocks : (int64_t)h->sm_count * 6;   // 33 KB each: 6 CTAs per SM
-    etl::csv_block_summary_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, sum, masks);
+    etl::csv_block_summary_kernel<<<(unsigned)grid, etl::CSV_THREADS, etl::CSV_STAGE_SMEM, stream>>>(text, nbytes, blocks, sum, masks,
+                                                                                                    field_masks);
     etl::csv_span_reduce_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super);
     etl::csv_span_scan_kernel<<<1, etl::CSV_THREADS, 0, stream>>>(super, supers, super_start, d_rows);
     etl::csv_span_apply_kernel<<<(unsigned)supers, etl::CSV_THREADS, 0, stream>>>(sum, blocks, super_start, start);
@@ -843,7 +934,19 @@ extern "C" int etl_csv_parse_columns(etl_handle* hh, const uint8_t* text, int64_
     int64_t blocks = (groups + etl::PARSE_WARPS - 1) / etl::PARSE_WARPS;
     const int64_t cap = (int64_t)h->sm_count * 16;
     if (blocks > cap) blocks = cap;
-    etl::csv_parse_rows_kernel<<<(unsigned)blocks, etl::PARSE_WARPS * 32, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+    // the masks etl_csv_index_rows left in the arena, if the caller vouches that this is still the text it indexed
+    const int64_t csv_blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
+    const size_t mask_end = (size_t)csv_blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart) +
+                                                  etl::CSV_THREADS * 2 * sizeof(ulonglong2));
+    if ((flags & ETL_CSV_USE_INDEX_MASKS) && h->csv_text == text && h->csv_nbytes == nbytes && h->scratch_bytes >= mask_end) {
+        auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
+        auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + csv_blocks);
+        p.quote_masks = reinterpret_cast<const ulonglong2*>(start + csv_blocks);
+        p.field_masks = p.quote_masks + csv_blocks * etl::CSV_THREADS;
+        etl::csv_parse_rows_kernel<true><<<(unsigned)blocks, etl::PARSE_WARPS * 32, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+    } else {
+        etl::csv_parse_rows_kernel<false><<<(unsigned)blocks, etl::PARSE_WARPS * 32, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+    }
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

@@ -22,6 +22,7 @@ from .engine import Column, Engine
 
 CSV_TRIM_STRINGS = 1
 CSV_NAN_IS_NULL = 2
+CSV_USE_INDEX_MASKS = 4   # the row scan may walk the masks the index passes left in the handle (same text, same engine)
 
 
 @dataclass
@@ -143,7 +144,8 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
     present = [(c, k) for c, k in wanted if c in pos]
     if len(present) > 8:
         raise ValueError("read_csv: at most 8 columns per call")
-    flags = (CSV_TRIM_STRINGS if trim_strings else 0) | (CSV_NAN_IS_NULL if nan_is_null else 0)
+    # the index passes above ran on this very text through this engine's handle: the row scan may use their masks
+    flags = (CSV_TRIM_STRINGS if trim_strings else 0) | (CSV_NAN_IS_NULL if nan_is_null else 0) | CSV_USE_INDEX_MASKS
     dicts = [None if k == 0 else (torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device),
                                   torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device)) for _, k in present]
     if present and rows:

@@ -307,3 +307,33 @@ def test_read_csv_from_a_path_and_from_host_columns(eng, tmp_path):
     assert m.labels == a.labels and m.label_counts == a.label_counts
     assert m.means == a.means  # every value is an integer < 2^24: exact in float32 too
     assert m.features().cpu().numpy().tobytes() == a.features().cpu().numpy().tobytes()
+
+
+@pytest.mark.parametrize("rows,seed", [(37, 11), (60_000, 12)])
+def test_row_scan_over_index_masks_equals_row_scan_over_text(eng, rows, seed, monkeypatch):
+    # read_csv lets the field parse walk the quote / comma / newline masks the index pass kept; without
+    # the flag the same kernel scans the text bytes - both must decode every cell identically
+    import pyspark_tf_gke_b200.table as T
+    text = _synthetic_csv(rows, seed).encode()
+    cols_n, cols_s = ["value", "lower_ci", "upper_ci"], ["measure_name", "filler"]
+    with_masks = pkg.read_csv(eng, text, cols_n, cols_s)
+    monkeypatch.setattr(T, "CSV_USE_INDEX_MASKS", 0)
+    from_text = pkg.read_csv(eng, text, cols_n, cols_s)
+    assert with_masks.rows == from_text.rows
+    for c in cols_n:
+        a, b = with_masks.numeric[c], from_text.numeric[c]
+        assert torch.equal(a.valid, b.valid) and a.data.cpu().numpy().tobytes() == b.data.cpu().numpy().tobytes()
+    for c in cols_s:
+        a, b = with_masks.strings[c], from_text.strings[c]
+        assert torch.equal(a.column.valid, b.column.valid)
+        la = [a.labels[i] if i >= 0 else None for i in a.column.data.cpu().tolist()]
+        lb = [b.labels[i] if i >= 0 else None for i in b.column.data.cpu().tolist()]
+        assert la == lb
+    # any other use of the handle's arena drops the masks: the flag is then ignored, not trusted
+    n = len(text)
+    d_text = T.upload_text(eng, text)
+    total = int(eng.csv_index_rows(d_text, n).item())
+    row_start = eng.csv_row_offsets(d_text, n, total)
+    eng.reserve(1 << 20)
+    cols, status, _ = eng.csv_parse_columns(d_text, n, row_start, 1, total - 1, [3], [0], [None], flags=T.CSV_NAN_IS_NULL | 4)
+    assert cols[0].data.cpu().numpy().tobytes() == from_text.numeric["value"].data.cpu().numpy().tobytes()

@@ -234,10 +234,13 @@ def m_csv(eng, args):
     row_start = eng.csv_row_offsets(text, n, total)
     cap = 1 << 16
 
-    def parse():
+    def parse(flags=4):   # 4 = ETL_CSV_USE_INDEX_MASKS: walk the masks the index pass kept (what read_csv does)
         d = (torch.zeros(cap, dtype=torch.int64, device=eng.device), torch.zeros(cap, dtype=torch.int64, device=eng.device))
-        return eng.csv_parse_columns(text, n, row_start, 1, rows, [5, 6, 7, 2], [0, 0, 0, 1], [None, None, None, d])
+        return eng.csv_parse_columns(text, n, row_start, 1, rows, [5, 6, 7, 2], [0, 0, 0, 1], [None, None, None, d], flags=flags)
 
+    mean0, mn0 = timed(lambda: parse(0), steps=5)
+    res.append(entry("csv_parse_rows_kernel<text scan> (4 columns; fallback when the index masks are gone)", rows,
+                     n + rows * 28.5, mean0, mn0))
     mean, mn = timed(parse, steps=5)
     import io
 
