@@ -224,8 +224,8 @@ def m_csv(eng, args):
     torch.cuda.synchronize()
     res = []
     mean, mn = timed(lambda: eng.csv_index_rows(text, n), steps=10)
-    res.append(entry("csv_block_summary + span scan (row index, pass 1: reads the text, keeps 16 B of masks per 64 B)", rows,
-                     n + n // 4, mean, mn))
+    res.append(entry("csv_block_summary + span scan (row index, pass 1: reads the text, keeps 32 B of masks per 64 B)", rows,
+                     n + n // 2, mean, mn))
     total = int(eng.csv_index_rows(text, n).item())
     assert total == rows + 1
     mean, mn = timed(lambda: eng.csv_row_offsets(text, n, total), steps=10)
