@@ -442,6 +442,22 @@ ETL_API int etl_kmeans_accumulate(etl_handle* h, const int32_t* index, const dou
 ETL_API int etl_kmeans_update(etl_handle* h, const int64_t* d_count, const int64_t* d_hist, const double* d_numsum,
                       int32_t k, int32_t num_labels, int32_t repeats, double* centers, void* stream);
 
+/* ClusteringEvaluator().evaluate(predictions) - silhouette with squared Euclidean distance
+ * (spark_workload_to_cloud_k8s.py:139-144), Spark's O(n k) formulation: with N_G rows, Psi_G = sum of
+ * |y|^2 and Y_G = vector sum of cluster G, the mean squared distance from x to G is
+ * |x|^2 + Psi_G / N_G - 2 x.Y_G / N_G; a = that for x's own cluster times N / (N - 1), b = the minimum over
+ * the other clusters, coefficient = 1 - a / b (a < b), b / a - 1 (a > b), 0 (equal, or a cluster of one).
+ * etl_kmeans_row_norms: out[i] = |x_i|^2 (its per-cluster sums Psi come from etl_kmeans_accumulate).
+ * etl_kmeans_silhouette: out[i] = the coefficient of row i; d_label_sum[k][num_labels + 1] = repeats * rows of
+ *   the cluster with that label (column num_labels = 0), d_num_sum[k][3], d_psi[k], d_count[k] (rows as
+ *   double, 0 = no such cluster).  The evaluator's value is the mean of out (etl_column_sum_count). */
+ETL_API int etl_kmeans_row_norms(etl_handle* h, const int32_t* index, const double* const num[3], int64_t n,
+                         int32_t num_labels, int32_t repeats, double* out, void* stream);
+ETL_API int etl_kmeans_silhouette(etl_handle* h, const int32_t* index, const double* const num[3], const int32_t* cluster,
+                          int64_t n, int32_t k, int32_t num_labels, int32_t repeats, const double* d_label_sum,
+                          const double* d_num_sum, const double* d_psi, const double* d_count, double* out,
+                          void* stream);
+
 /* ---- next row: device-resident hand-off to the trainer */
 
 /* Replaces model.fit / the custom train step on the tabular model of

@@ -121,3 +121,62 @@ def kmeans_fit(X: np.ndarray, index: np.ndarray, L: int, repeats: int, k: int, s
         if (moved <= tol * tol).all():
             break
     return centers, cost_sum, it, sizes
+
+
+def silhouette(X: np.ndarray, index: np.ndarray, L: int, repeats: int, cluster: np.ndarray) -> np.ndarray:
+    """Per-row silhouette coefficient with squared Euclidean distance, as Spark's
+    ClusteringEvaluator computes it (org.apache.spark.ml.evaluation.SquaredEuclideanSilhouette;
+    called at spark_workload_to_cloud_k8s.py:139-144 - Spark itself is an unpinned third-party
+    dependency, so this follows its published algorithm): per cluster G the count N_G, Psi_G =
+    sum |y|^2 and Y_G = sum y; mean squared distance x -> G = |x|^2 + Psi_G / N_G - 2 x.Y_G / N_G;
+    a = own-cluster value * N / (N - 1); b = min over the other clusters; 1 - a/b, b/a - 1 or 0;
+    0 for a cluster of one.  Operation order = the CUDA kernel's (structured dot product, no FMA)."""
+    n = X.shape[0]
+    onehot = repeats * L
+    known = (index >= 0) & (index < L)
+    a, b, c = X[:, onehot], X[:, onehot + 1], X[:, onehot + 2]
+    x2 = ((np.where(known, float(repeats), 0.0) + a * a) + b * b) + c * c
+    ks = np.unique(cluster)
+    out = np.zeros(n)
+    stats = {}
+    for g in ks:
+        sel = cluster == g
+        lab = np.bincount(np.where(known, index, L)[sel], minlength=L + 1).astype(np.float64) * float(repeats)
+        lab[L] = 0.0
+        stats[g] = (float(sel.sum()), lab, [float(X[sel, onehot + j].sum()) for j in range(3)], float(_seq_sum(x2[sel])))
+    idx = np.where(known, index, L)
+    dist = {}
+    for g, (ng, lab, ns, psi) in stats.items():
+        dot = ((lab[idx] + a * ns[0]) + b * ns[1]) + c * ns[2]
+        dist[g] = (x2 + psi / ng) + -((2.0 * dot) / ng)
+    for i in range(n):
+        own = cluster[i]
+        n_own = stats[own][0]
+        others = [dist[g][i] for g in ks if g != own]
+        if n_own <= 1.0 or not others:
+            continue
+        cur = (dist[own][i] * n_own) / (n_own - 1.0)
+        nb = min(others)
+        out[i] = 1.0 - cur / nb if cur < nb else (nb / cur - 1.0 if cur > nb else 0.0)
+    return out
+
+
+def _seq_sum(v: np.ndarray) -> float:
+    return float(np.sum(v))
+
+
+def silhouette_direct(X: np.ndarray, cluster: np.ndarray) -> np.ndarray:
+    """The textbook O(n^2) definition (mean squared distance to every other row of the own
+    cluster / nearest other cluster) - used on small inputs to check the O(n k) formula."""
+    n = X.shape[0]
+    d = ((X[:, None, :] - X[None, :, :]) ** 2).sum(axis=2)
+    out = np.zeros(n)
+    ks = np.unique(cluster)
+    for i in range(n):
+        own = cluster == cluster[i]
+        if own.sum() <= 1 or len(ks) < 2:
+            continue
+        a = d[i, own].sum() / (own.sum() - 1)
+        b = min(d[i, cluster == g].mean() for g in ks if g != cluster[i])
+        out[i] = 1 - a / b if a < b else (b / a - 1 if a > b else 0.0)
+    return out

@@ -8,7 +8,7 @@ from . import _lib, synth  # noqa: F401
 from ._lib import EtlError  # noqa: F401
 from .engine import Column, Engine  # noqa: F401
 from .k_means import EtlPipelineModel, KMeansWorkload  # noqa: F401
-from .kmeans import KMeans, KMeansModel  # noqa: F401
+from .kmeans import ClusteringEvaluator, KMeans, KMeansModel  # noqa: F401
 from .table import DeviceTable, read_csv  # noqa: F401
 from .parquet import ParquetUnsupported, read_parquet  # noqa: F401
 from .train_input import load_csv, load_csv_device, write_label_map  # noqa: F401

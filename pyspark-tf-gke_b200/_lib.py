@@ -92,6 +92,10 @@ _PROTOS = {
     "etl_kmeans_assign": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
+    "etl_kmeans_row_norms": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                       C.c_void_p]),
+    "etl_kmeans_silhouette": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                        C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "etl_kmeans_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                     C.c_void_p, C.c_void_p]),
     "etl_kmeans_accumulate": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.c_void_p, C.c_int64, C.c_int32, C.c_int32,

@@ -228,6 +228,79 @@ __global__ void __launch_bounds__(256) kmeans_update_kernel(const unsigned long 
     }
 }
 
+// ---------------------------------------------------------------- silhouette
+// ClusteringEvaluator (metric "silhouette", squared Euclidean distance) as Spark computes it, in
+// O(n k): per cluster G the row count N_G, Psi_G = sum of |y|^2 and the vector sum Y_G; the mean
+// squared distance from x to the rows of G is |x|^2 + Psi_G / N_G - 2 x.Y_G / N_G
+// (spark_workload_to_cloud_k8s.py:139-144 -> org.apache.spark.ml.evaluation.SquaredEuclideanSilhouette).
+// Pass 1 writes |x|^2 per row (its per-cluster sums come from kmeans_accumulate); pass 2 the
+// coefficient of every row from the per-cluster tables.  Same explicit _rn arithmetic as the assign
+// kernel, so the NumPy restatement gets the same bits.
+__global__ void __launch_bounds__(KM_THREADS) kmeans_row_norms_kernel(const int32_t* __restrict__ index, const double* num0,
+                                                                      const double* num1, const double* num2, int64_t n, int L,
+                                                                      int repeats, double* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * KM_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * KM_THREADS) {
+        const int32_t idx = index[i];
+        const bool known = idx >= 0 && idx < L;
+        const double a = num0[i], b = num1[i], c = num2[i];
+        out[i] = __dadd_rn(__dadd_rn(__dadd_rn(known ? (double)repeats : 0.0, __dmul_rn(a, a)), __dmul_rn(b, b)), __dmul_rn(c, c));
+    }
+}
+
+struct KmSilhouetteParams {
+    const int32_t* index;
+    const double* num[3];
+    const int32_t* cluster;
+    int64_t n;
+    int32_t k, L, repeats;
+    const double* label_sum;   // [k][L + 1]: repeats * (rows of the cluster with that label); column L = 0
+    const double* num_sum;     // [k][3]
+    const double* psi;         // [k]: sum of |y|^2 over the cluster
+    const double* count;       // [k]: rows (as double); 0 = the cluster does not exist
+    double* out;               // [n]
+};
+
+__global__ void __launch_bounds__(KM_THREADS) kmeans_silhouette_kernel(const KmSilhouetteParams p) {
+    extern __shared__ double km_smem[];
+    const int L1 = p.L + 1;
+    double* s_T = km_smem;                         // [k][L + 1]
+    double* s_num = s_T + (size_t)p.k * L1;        // [k][3]
+    double* s_psi = s_num + (size_t)p.k * 3;       // [k]
+    double* s_cnt = s_psi + p.k;                   // [k]
+    for (int i = threadIdx.x; i < p.k * L1; i += KM_THREADS) s_T[i] = p.label_sum[i];
+    for (int i = threadIdx.x; i < p.k * 3; i += KM_THREADS) s_num[i] = p.num_sum[i];
+    for (int i = threadIdx.x; i < p.k; i += KM_THREADS) { s_psi[i] = p.psi[i]; s_cnt[i] = p.count[i]; }
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * KM_THREADS + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * KM_THREADS) {
+        int32_t idx = p.index[i];
+        const bool known = idx >= 0 && idx < p.L;
+        if (!known) idx = p.L;
+        const int own = p.cluster[i];
+        const double a = p.num[0][i], b = p.num[1][i], c = p.num[2][i];
+        const double x2 = __dadd_rn(__dadd_rn(__dadd_rn(known ? (double)p.repeats : 0.0, __dmul_rn(a, a)), __dmul_rn(b, b)),
+                                    __dmul_rn(c, c));
+        double neighbour = 1.7976931348623157e308, mine = 0.0;
+        for (int j = 0; j < p.k; ++j) {
+            const double nj = s_cnt[j];
+            if (nj == 0.0) continue;
+            const double dot = __dadd_rn(__dadd_rn(__dadd_rn(s_T[j * L1 + idx], __dmul_rn(a, s_num[j * 3])),
+                                                   __dmul_rn(b, s_num[j * 3 + 1])), __dmul_rn(c, s_num[j * 3 + 2]));
+            // pointDotSquaredNorm + squaredNormSum / numOfPoints - 2 * dot / numOfPoints
+            const double d = __dadd_rn(__dadd_rn(x2, __ddiv_rn(s_psi[j], nj)), -__ddiv_rn(__dmul_rn(2.0, dot), nj));
+            if (j == own) mine = d;
+            else if (d < neighbour) neighbour = d;
+        }
+        double sil = 0.0;
+        if (own >= 0 && own < p.k && s_cnt[own] > 1.0 && neighbour < 1.7976931348623157e308) {
+            const double n_own = s_cnt[own];
+            const double cur = __ddiv_rn(__dmul_rn(mine, n_own), __dadd_rn(n_own, -1.0));
+            if (cur < neighbour) sil = __dadd_rn(1.0, -__ddiv_rn(cur, neighbour));
+            else if (cur > neighbour) sil = __dadd_rn(__ddiv_rn(neighbour, cur), -1.0);
+        }
+        p.out[i] = sil;
+    }
+}
+
 }  // namespace etl
 
 using etl::Handle;
@@ -324,6 +397,47 @@ extern "C" int etl_kmeans_update(etl_handle* hh, const int64_t* d_count, const i
     etl::kmeans_update_kernel<<<(unsigned)k, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
         reinterpret_cast<const unsigned long long*>(d_count), reinterpret_cast<const unsigned long long*>(d_hist), d_numsum,
         num_labels, repeats, centers);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_kmeans_row_norms(etl_handle* hh, const int32_t* index, const double* const num[3], int64_t n,
+                                    int32_t num_labels, int32_t repeats, double* out, void* stream_) {
+    ETL_REQUIRE(hh && num, "kmeans_row_norms: NULL argument");
+    ETL_REQUIRE(n >= 0 && num_labels >= 0 && repeats >= 1, "kmeans_row_norms: bad n / num_labels / repeats");
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(index && num[0] && num[1] && num[2] && out, "kmeans_row_norms: NULL column");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    int64_t blocks = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
+    if (blocks > (int64_t)h->sm_count * 8) blocks = (int64_t)h->sm_count * 8;
+    etl::kmeans_row_norms_kernel<<<(unsigned)blocks, etl::KM_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        index, num[0], num[1], num[2], n, num_labels, repeats, out);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_kmeans_silhouette(etl_handle* hh, const int32_t* index, const double* const num[3], const int32_t* cluster,
+                                     int64_t n, int32_t k, int32_t num_labels, int32_t repeats, const double* d_label_sum,
+                                     const double* d_num_sum, const double* d_psi, const double* d_count, double* out,
+                                     void* stream_) {
+    ETL_REQUIRE(hh && num && d_label_sum && d_num_sum && d_psi && d_count, "kmeans_silhouette: NULL argument");
+    ETL_REQUIRE(n >= 0 && k >= 1 && num_labels >= 0 && repeats >= 1, "kmeans_silhouette: bad n / k / num_labels / repeats");
+    if (n == 0) return ETL_OK;
+    ETL_REQUIRE(index && cluster && num[0] && num[1] && num[2] && out, "kmeans_silhouette: NULL column");
+    const size_t smem = ((size_t)k * (num_labels + 1) + (size_t)k * 5) * sizeof(double);
+    ETL_REQUIRE(smem <= 200 * 1024, "kmeans_silhouette: k * (num_labels + 6) too large for shared memory");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    etl::KmSilhouetteParams p{};
+    p.index = index; p.cluster = cluster; p.n = n; p.k = k; p.L = num_labels; p.repeats = repeats;
+    for (int j = 0; j < 3; ++j) p.num[j] = num[j];
+    p.label_sum = d_label_sum; p.num_sum = d_num_sum; p.psi = d_psi; p.count = d_count; p.out = out;
+    ETL_CUDA(cudaFuncSetAttribute(etl::kmeans_silhouette_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (n + etl::KM_THREADS - 1) / etl::KM_THREADS;
+    const int per_sm = smem > 100 * 1024 ? 1 : (smem > 50 * 1024 ? 2 : 4);
+    if (blocks > (int64_t)h->sm_count * per_sm) blocks = (int64_t)h->sm_count * per_sm;
+    etl::kmeans_silhouette_kernel<<<(unsigned)blocks, etl::KM_THREADS, smem, static_cast<cudaStream_t>(stream_)>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

@@ -663,6 +663,28 @@ class Engine:
                                               num_labels, repeats, centers.data_ptr(), self._stream()))
         self.launches += 1
 
+    def kmeans_row_norms(self, index: torch.Tensor, nums: Sequence[torch.Tensor], num_labels: int, repeats: int) -> torch.Tensor:
+        """|x_i|^2 of every structured feature row -> f64[n]."""
+        n = index.shape[0]
+        out = self.empty(n, torch.float64)
+        _lib.check(self.lib.etl_kmeans_row_norms(self._h, _ptr(index), C.byref(VP3(*[t.data_ptr() for t in nums])), n,
+                                                 num_labels, repeats, out.data_ptr(), self._stream()))
+        self.launches += 1 if n else 0
+        return out
+
+    def kmeans_silhouette(self, index: torch.Tensor, nums: Sequence[torch.Tensor], cluster: torch.Tensor, label_sum: torch.Tensor,
+                          num_sum: torch.Tensor, psi: torch.Tensor, count: torch.Tensor, num_labels: int,
+                          repeats: int) -> torch.Tensor:
+        """Silhouette coefficient (squared Euclidean) of every row from the per-cluster tables -> f64[n]."""
+        n, k = index.shape[0], count.shape[0]
+        out = self.empty(n, torch.float64)
+        _lib.check(self.lib.etl_kmeans_silhouette(self._h, _ptr(index), C.byref(VP3(*[t.data_ptr() for t in nums])),
+                                                  _ptr(cluster), n, k, num_labels, repeats, label_sum.data_ptr(),
+                                                  num_sum.data_ptr(), psi.data_ptr(), count.data_ptr(), out.data_ptr(),
+                                                  self._stream()))
+        self.launches += 1 if n else 0
+        return out
+
     # --------------------------------------------- trainer hand-off (8f rank 1)
     def mlp_param_count(self, classes: int) -> int:
         return int(self.lib.etl_mlp_param_count(classes))

@@ -166,6 +166,14 @@ class KMeans:
         return t
 
     @staticmethod
+    def _all_max(t: torch.Tensor) -> torch.Tensor:
+        from . import dist as D
+        if D.world()[1] > 1:
+            import torch.distributed as td
+            td.all_reduce(t, op=td.ReduceOp.MAX)
+        return t
+
+    @staticmethod
     def _all_rows(local: np.ndarray) -> np.ndarray:
         """concatenation over ranks (rank order) of a few dense rows"""
         from . import dist as D
@@ -245,3 +253,35 @@ class KMeans:
                 break
         sizes = count.cpu().tolist() if count is not None else []
         return KMeansModel(eng, centers, L, repeats, KMeansSummary(cost_sum, it, [int(x) for x in sizes], k))
+
+
+class ClusteringEvaluator:
+    """pyspark.ml.evaluation.ClusteringEvaluator as spark_workload_to_cloud_k8s.py:139-144 uses it:
+    default metric "silhouette", default distance "squaredEuclidean".  evaluate() takes what
+    model.transform produced: the dataset (structured features) and its predictions.  With
+    torch.distributed initialised the rows are this rank's shard: the per-cluster statistics and the
+    final (sum, count) are all-reduced."""
+
+    def __init__(self, metricName: str = "silhouette", distanceMeasure: str = "squaredEuclidean"):
+        if metricName != "silhouette" or distanceMeasure != "squaredEuclidean":
+            raise ValueError("ClusteringEvaluator: only silhouette / squaredEuclidean (the reference's defaults) are implemented")
+
+    def evaluate(self, dataset, predictions: torch.Tensor, k: Optional[int] = None) -> float:
+        eng, index, nums = dataset.engine, dataset.index, dataset.numerics
+        L, repeats = len(dataset.labels), dataset.repeats
+        if k is None:
+            kk = predictions.max().reshape(1).to(torch.int64) + 1 if predictions.numel() else torch.ones(1, dtype=torch.int64, device=eng.device)
+            k = int(KMeans._all_max(kk)[0])
+        xi = eng.kmeans_row_norms(index, nums, L, repeats)
+        count, hist, numsum = eng.kmeans_accumulate(index, nums, predictions, k, L)
+        _, _, psi3 = eng.kmeans_accumulate(index, [xi, xi, xi], predictions, k, L)
+        psi = psi3[:, 0].contiguous()
+        for t in (count, hist, numsum, psi):
+            KMeans._all_sum(t)
+        label_sum = (hist.to(torch.float64) * float(repeats)).contiguous()
+        label_sum[:, L] = 0.0                               # unknown label: the all-zero one-hot block
+        sil = eng.kmeans_silhouette(index, nums, predictions, label_sum, numsum, psi, count.to(torch.float64), L, repeats)
+        s, c = eng.sum_count([Column(sil)])
+        tot = torch.stack([s[0], c[0].to(torch.float64)])
+        KMeans._all_sum(tot)
+        return float(tot[0]) / float(tot[1]) if float(tot[1]) else float("nan")

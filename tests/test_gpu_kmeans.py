@@ -145,3 +145,61 @@ def test_sharded_fit_equals_single_gpu_fit():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert '"identical": true' in r.stdout
+
+
+def test_silhouette_matches_spark_formula_and_textbook_definition(eng):
+    # ClusteringEvaluator (silhouette, squared Euclidean): spark_workload_to_cloud_k8s.py:139-144
+    n, L, repeats, k = 3000, 12, 3, 7
+    index, nums = _blobs(n, L, 5)
+    rng = np.random.default_rng(9)
+    cluster = rng.integers(0, k - 1, n).astype(np.int32)
+    cluster[11] = k - 1                                   # a cluster of one row: coefficient 0
+    ds = _Dataset(eng, index, nums, L, repeats)
+    d_cluster = torch.from_numpy(cluster).to(eng.device)
+    X = dense_rows(index, nums, L, repeats)
+    want = KO.silhouette(X, index, L, repeats, cluster)
+    # per row, through the C ABI pieces
+    xi = eng.kmeans_row_norms(ds.index, ds.numerics, L, repeats)
+    count, hist, numsum = eng.kmeans_accumulate(ds.index, ds.numerics, d_cluster, k, L)
+    psi = eng.kmeans_accumulate(ds.index, [xi, xi, xi], d_cluster, k, L)[2][:, 0].contiguous()
+    label_sum = (hist.to(torch.float64) * float(repeats)).contiguous()
+    label_sum[:, L] = 0.0
+    got = eng.kmeans_silhouette(ds.index, ds.numerics, d_cluster, label_sum, numsum, psi, count.to(torch.float64), L, repeats)
+    assert got.cpu().numpy().tobytes() == want.tobytes()              # integer-valued data: same operations, same bits
+    assert want[11] == 0.0 and -1.0 <= want.min() and want.max() <= 1.0
+    sub = slice(0, 400)                                               # the O(n^2) definition on a slice with its own clusters
+    np.testing.assert_allclose(KO.silhouette(X[sub], index[sub], L, repeats, cluster[sub]), KO.silhouette_direct(X[sub], cluster[sub]),
+                               rtol=0, atol=1e-10)
+    value = pkg.ClusteringEvaluator().evaluate(ds, d_cluster)
+    assert abs(value - float(want.mean())) <= 1e-12
+    with pytest.raises(ValueError):
+        pkg.ClusteringEvaluator(metricName="other")
+
+
+def test_silhouette_of_a_fitted_model_is_high_on_separated_blobs(eng):
+    index, nums = _blobs(20_000, 12, 4)
+    ds = _Dataset(eng, index, nums, 12, 3)
+    model = pkg.KMeans().setK(6).setSeed(1).fit(ds)
+    predictions = model.transform(ds)
+    value = pkg.ClusteringEvaluator().evaluate(ds, predictions)
+    assert 0.5 < value <= 1.0
+
+
+def test_csv_twin_script_end_to_end(eng, tmp_path, capsys):
+    # spark_workload_to_cloud_k8s.py:48-154 on the default input: un-repeated one-hot block, k = 5, seed 1,
+    # silhouette, both models saved and loadable
+    from pyspark_tf_gke_b200 import workload_to_cloud as W
+    pipeline_model, model, sil = W.run(health_text("workloads").encode(), model_dir=str(tmp_path), engine=eng)
+    out = capsys.readouterr().out
+    assert "Total number of rows: 18155" in out and "Column 'measure_name' has 0 missing values" in out
+    assert "Silhouette with squared Euclidean distance = " in out and "Saving K-Means pipeline to" in out
+    assert pipeline_model.repeats == 1 and model.centers.shape == (5, 33) and -1.0 <= sil <= 1.0
+    # the evaluator against the O(n k) restatement on the same predictions
+    pred = model.transform(pipeline_model).cpu().numpy()
+    index = pipeline_model.index.cpu().numpy()
+    nums = [t.cpu().numpy() for t in pipeline_model.numerics]
+    want = KO.silhouette(dense_rows(index, nums, 30, 1), index, 30, 1, pred)
+    assert abs(sil - float(want.mean())) <= 1e-9
+    back = pkg.KMeansModel.load(str(tmp_path / "health_kmeans_model"))
+    assert back.centers.tobytes() == model.centers.tobytes() and back.repeats == 1
+    assert pkg.EtlPipelineModel.load(str(tmp_path / "health_kmeans_pipeline")).labels == pipeline_model.labels
