@@ -6,24 +6,26 @@
 // Quoting is RFC 4180 (quote ", doubled-quote escape; a quoted field may hold
 // commas and newlines); backslash escapes are outside the documented domain.
 //
-// Three steps, all byte-parallel until the field parse:
-//   1. csv_block_summary_kernel  per 16 KiB block: parity of the quote count and
-//      the number of record starts assuming the block begins outside / inside
-//      quotes (a record start = the byte after a newline that is outside quotes,
-//      unless the line it opens is blank - Spark and csv.reader drop blank lines)
+// Four steps, all byte-parallel until the field parse:
+//   1. csv_block_summary_kernel  per 16 KiB block (staged in shared memory by a bulk async copy):
+//      every thread builds the quote / newline / comma masks of its 64-byte window; the block's
+//      summary = parity of the quote count and the number of record starts assuming the block
+//      begins outside / inside quotes (a record start = the byte after a newline that is outside
+//      quotes, unless the line it opens is blank - Spark and csv.reader drop blank lines).  The
+//      window masks (32 B per 64 B of text) are KEPT in the handle's arena for steps 3 and 4.
 //   2. csv_span_reduce / _scan / _apply  compose the block summaries in order
 //      (an associative operator on (parity, starts-outside, starts-inside))
 //      -> every block's true starting quote state and first row number
-//   3. csv_row_offsets_kernel    re-derives the masks with the true state and
+//   3. csv_row_offsets_kernel    reads the kept masks (not the text), applies the true state and
 //      writes row_start[row] (int64 byte offsets)
-//   4. csv_parse_rows_kernel     one warp per 32 rows, lane r owns row r: (A) it
-//      walks the row 8 bytes at a time (SWAR byte compares, in-word prefix xor
-//      for the quote state, ffs over the unquoted-comma mask) and leaves every
-//      requested field's bounds in shared memory; (B) it converts those fields:
-//      numerals through dec_parse (correctly rounded), strings through an open-
-//      addressing dictionary in global memory keyed by a 64-bit hash (8 bytes per
-//      step) with a byte-exact collision check.  Each column leaves as one
-//      coalesced store plus one ballot-built validity word per 32 rows.
+//   4. csv_parse_rows_kernel     one warp per 32 rows, lane r owns row r: (A) it walks the row over
+//      the kept masks, a 64-byte window at a time (prefix xor for the quote state, ffs over the
+//      unquoted-comma mask; without the masks it scans the text 8 bytes at a time with SWAR byte
+//      compares) and leaves every requested field's bounds in shared memory; (B) it converts those
+//      fields: numerals through dec_parse (correctly rounded), strings through an open-addressing
+//      dictionary in global memory keyed by a 64-bit hash (8 bytes per step) with a byte-exact
+//      collision check.  Each column leaves as one coalesced store plus one ballot-built validity
+//      word per 32 rows.
 #include "common.cuh"
 #include "decimal.cuh"
 

@@ -2,9 +2,11 @@
 // the reference reads CSV / JDBC).  The host (parquet.py) parses footer and page
 // headers and hands over a table of page descriptors; everything that scales
 // with the number of rows happens here:
-//   pq_hybrid_decode_kernel  one CTA per RLE / bit-packed hybrid stream
-//        (definition levels, dictionary indices): one thread walks the run
-//        headers into a run table, then the warps expand the runs in parallel;
+//   pq_hybrid_decode_kernel  one WARP per RLE / bit-packed hybrid stream
+//        (definition levels, dictionary indices) of ANY column: the lanes decode a
+//        run header speculatively at 32 consecutive byte offsets, a shuffle hop per
+//        run settles which guesses lie on the real chain, and the runs are expanded
+//        at once (no run table);
 //   pq_gather_kernel         one CTA per data page: definition levels -> validity
 //        bits (ballot) and, through a block scan, each row's position among the
 //        page's non-null values; PLAIN values are cast to double, dictionary

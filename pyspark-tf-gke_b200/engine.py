@@ -4,6 +4,7 @@ is in libetl_b200.so.  No CPU path exists here: every method needs CUDA."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence, Tuple
 
@@ -436,8 +437,10 @@ class Engine:
                                 key_stride=2, val_strides=[2])
 
     # ------------------------------------------- shared-memory merge of the exchange
-    MERGE_SLOTS = 4096          # shared-table slots per CTA (80 KB: two CTAs per SM)
-    MERGE_GROUPS_PER_PIECE = 1536   # target groups per piece: load factor ~0.37
+    # shared-table slots per CTA (4096 = 80 KB: two CTAs per SM) and target groups per piece (load factor ~0.37);
+    # the environment overrides are tuning knobs for tools/measure_shuffle.py
+    MERGE_SLOTS = int(os.environ.get("ETL_MERGE_SLOTS", "4096"))
+    MERGE_GROUPS_PER_PIECE = int(os.environ.get("ETL_MERGE_GROUPS", "1536"))
 
     @staticmethod
     def merge_plan(records: int, groups_hint: int, groups_per_piece: int = MERGE_GROUPS_PER_PIECE, max_buckets: int = 256):
