@@ -68,3 +68,55 @@ def test_config4_shape_groupby_quarter_size_single_gpu(eng):
         assert float(res["cols"][0]["sum"].sum()) == float(s[0])
     assert torch.equal(a["keys"], b["keys"]) and torch.equal(a["rows"], b["rows"])
     assert torch.equal(a["cols"][0]["sum"], b["cols"][0]["sum"])
+
+
+def test_config4_full_size_single_gpu(eng):
+    # BASELINE configs[3] on one GPU at its full size: 1 B rows, 100 M groups through the two partition
+    # levels and the shared-memory merge; conservation of rows, of the grand total and of the key set
+    cfg = S.CONFIG4
+    n, G = cfg["rows"], cfg["groups"]
+    key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=G, with_valid=False).data
+    val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False).data
+    pieces = D.shuffle_groupby_sum(eng, key, val, G + G // 8, groups_hint=G)
+    res = eng.groupby_result(pieces)
+    del pieces
+    s, _ = eng.sum_count([pkg.Column(val)])
+    k = res["keys"]
+    assert res["spilled_records"] == 0
+    assert bool((k[1:] > k[:-1]).all()) and int(k[0]) >= 0 and int(k[-1]) < G          # unique, sorted, in range
+    assert G - k.shape[0] < G // 1000                                                   # ~e^-10 of the keys never drawn
+    assert int(res["rows"].sum()) == n and int(res["cols"][0]["count"].sum()) == n
+    assert float(res["cols"][0]["sum"].sum()) == float(s[0])                            # integer-valued data: exact
+    # a key's row count is what a direct count of that key gives (spot check on the busiest group)
+    top = int(torch.argmax(res["rows"]))
+    assert int((key == k[top]).sum()) == int(res["rows"][top])
+
+
+def test_config5_shape_csv_decode_10m_records(eng):
+    # the default input repeated to ~10 M records (1.4 GB of text): every statistic of the stage must be
+    # the default input's, scaled - label table, null counts, means
+    import gzip
+    import os
+
+    from tests.conftest import ROOT
+    with gzip.open(os.path.join(ROOT, "tests", "golden", "health_workloads.csv.gz"), "rb") as fh:
+        raw = fh.read()
+    head, body = raw.split(b"\n", 1)
+    reps = 550
+    numeric, strings = ["value", "lower_ci", "upper_ci"], ["measure_name"]
+    small = pkg.read_csv(eng, raw, numeric, strings)
+    big = pkg.read_csv(eng, head + b"\n" + body * reps, numeric, strings)
+    assert big.rows == small.rows * reps == 18155 * reps
+    assert big.strings["measure_name"].labels == small.strings["measure_name"].labels
+    hist_small = torch.bincount(small.strings["measure_name"].column.data.to(torch.int64), minlength=30)
+    hist_big = torch.bincount(big.strings["measure_name"].column.data.to(torch.int64), minlength=30)
+    assert torch.equal(hist_big, hist_small * reps)
+    for c in numeric:
+        (s1, c1), (s2, c2) = eng.sum_count([small.numeric[c]]), eng.sum_count([big.numeric[c]])
+        assert int(c2[0]) == int(c1[0]) * reps
+        assert abs(float(s2[0]) / float(c2[0]) - float(s1[0]) / float(c1[0])) <= 1e-9 * abs(float(s1[0]) / float(c1[0]))
+        # the first and the last copy of the block decode to the same bits as the single one
+        ok = torch.from_numpy(small.numeric[c].valid_host()).to(eng.device)
+        want = small.numeric[c].data.view(torch.int64)[ok]
+        assert torch.equal(big.numeric[c].data[:small.rows].view(torch.int64)[ok], want)
+        assert torch.equal(big.numeric[c].data[-small.rows:].view(torch.int64)[ok], want)
