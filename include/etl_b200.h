@@ -156,8 +156,8 @@ ETL_API int etl_column_sum_count(etl_handle* h, int32_t ncols,
  * blank lines are dropped, as Spark and csv.reader do.
  *
  * etl_csv_index_rows:  *d_rows (device int64) = number of records, header line
- *                      included.  Leaves per-block state and the quote / line-start
- *                      masks of every 64-byte window (nbytes / 4 bytes) in the
+ *                      included.  Leaves per-block state and the quote / line-start / comma / newline
+ *                      masks of every 64-byte window (nbytes / 2 bytes) in the
  *                      handle's arena, so that the second pass reads those
  *                      instead of the text.
  * etl_csv_row_offsets: row_start[r] (device int64[rows]) = byte offset of record
