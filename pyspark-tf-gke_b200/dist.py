@@ -36,14 +36,37 @@ def all_reduce_counts(counts: torch.Tensor, group=None) -> torch.Tensor:
     return counts
 
 
+LABEL_BLOB_BYTES = 16384
+
+
 def merge_label_tables(labels: Sequence[str], counts: Sequence[int], group=None):
     """StringIndexer.fit across ranks: every rank holds (label, count) pairs for
     its rows; the union with summed counts is what the driver would see."""
     rank, size = world()
     if size == 1:
         return list(labels), list(counts)
+    # one tensor all-gather of a fixed-size, length-prefixed JSON blob (a label table is a few hundred bytes);
+    # all_gather_object - pickling plus a size exchange plus a payload exchange - only if some rank's table
+    # does not fit
+    import json
+    blob = json.dumps([list(labels), [int(c) for c in counts]]).encode("utf-8")
+    device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    buf = torch.zeros(LABEL_BLOB_BYTES, dtype=torch.uint8)
+    fits = len(blob) <= LABEL_BLOB_BYTES - 8
+    buf[:8] = torch.tensor(list((len(blob) if fits else 0xFFFFFFFF).to_bytes(8, "little")), dtype=torch.uint8)
+    if fits:
+        buf[8:8 + len(blob)] = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+    out = torch.empty(size * LABEL_BLOB_BYTES, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(out, buf.to(device), group=group)
+    host = out.cpu().numpy().reshape(size, LABEL_BLOB_BYTES)
+    lengths = [int.from_bytes(host[r, :8].tobytes(), "little") for r in range(size)]
     gathered: List[Optional[list]] = [None] * size
-    dist.all_gather_object(gathered, list(zip(labels, counts)), group=group)
+    if all(n != 0xFFFFFFFF for n in lengths):
+        for r in range(size):
+            names, cnts = json.loads(host[r, 8:8 + lengths[r]].tobytes().decode("utf-8"))
+            gathered[r] = list(zip(names, cnts))
+    else:
+        dist.all_gather_object(gathered, list(zip(labels, counts)), group=group)
     total = {}
     for part in gathered:
         for s, c in part:

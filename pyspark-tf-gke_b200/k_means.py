@@ -108,22 +108,27 @@ class KMeansWorkload:
             self.logger.info("Checking for missing values in 'measure_name'...")
             # with torch.distributed initialised, input_df is this rank's shard of the rows: counts,
             # (sum, count) pairs and the label table are merged across ranks
-            nulls_and_rows = torch.stack([eng.null_count(key.column)[0],                   # k_means.py:23
-                                          torch.tensor(input_df.rows, device=eng.device)])
-            D.all_reduce_counts(nulls_and_rows)
-            null_measure_name_count, total_rows = (int(x) for x in nulls_and_rows.cpu().tolist())
-            self.logger.info(f"Column 'measure_name' has {null_measure_name_count} missing values")
-            rows_after = total_rows - null_measure_name_count                             # k_means.py:27-28
-            self.logger.info(f"Rows after filtering out missing 'measure_name' values: {rows_after}")
-
             numeric_cols = [c for c in NUMERIC_COLS if c in input_df.numeric]
             if len(numeric_cols) != 3:
                 raise KeyError(f"input needs the numeric columns {NUMERIC_COLS}")
             vals = [input_df.numeric[c] for c in numeric_cols]
-            # k_means.py:45-48: three avg jobs -> one pass; the isNotNull filter of :27 is still in the plan
+            # k_means.py:23 (null keys) and k_means.py:45-48 (three avg jobs -> one pass; the isNotNull filter of
+            # :27 is still in the plan) run back to back; their eight numbers cross the ranks in ONE all-reduce
+            # and reach the host in ONE copy (exact as doubles: counts stay far below 2^53)
+            nulls = eng.null_count(key.column)
             sums, counts = eng.sum_count(vals, row_valid=key.column.valid)
-            D.all_reduce_sum_count(sums, counts)
-            sums, counts = sums.cpu().tolist(), counts.cpu().tolist()
+            local = torch.cat([nulls.to(torch.float64), torch.tensor([float(input_df.rows)], device=eng.device),
+                               sums, counts.to(torch.float64)])
+            merged = local.clone()
+            if D.world()[1] > 1:
+                D.all_reduce_counts(merged)
+            both = torch.stack([local, merged]).cpu().tolist()
+            local_nulls, local_rows = int(both[0][0]), int(both[0][1])
+            null_measure_name_count, total_rows = int(both[1][0]), int(both[1][1])
+            self.logger.info(f"Column 'measure_name' has {null_measure_name_count} missing values")
+            rows_after = total_rows - null_measure_name_count                             # k_means.py:27-28
+            self.logger.info(f"Rows after filtering out missing 'measure_name' values: {rows_after}")
+            sums, counts = both[1][2:5], [int(c) for c in both[1][5:8]]
             means = [s / c if c else None for s, c in zip(sums, counts)]
 
             try:
@@ -137,9 +142,8 @@ class KMeansWorkload:
 
             # k_means.py:27 + :49-51: filter, impute, cast - one kernel
             fill = [m if m is not None else float("nan") for m in means]
-            code, nums, rows = eng.project_filter_impute(key.column, vals, fill)
-            r = int(rows.item())
-            assert r == rows_after or D.world()[1] > 1
+            code, nums, _ = eng.project_filter_impute(key.column, vals, fill)
+            r = local_rows - local_nulls            # rows this rank keeps: known from the null count, no read-back
             code, nums = code[:r], [v[:r] for v in nums]
 
             # StringIndexer.fit (k_means.py:34,73): group-by-count, then order on the host

@@ -41,6 +41,10 @@ def _worker(rank, world, port, n, groups, out):
         s, c = O.sum_count(vals, vv)
         sums, cnts = D.all_reduce_sum_count(torch.tensor([s], dtype=torch.float64), torch.tensor([c], dtype=torch.int64))
         names, lc = D.merge_label_tables(["b", f"r{rank}"], [2 + rank, 1])
+        # a table too large for the fixed-size blob on ONE rank: every rank must take the object path together
+        big = [f"label {rank} {i:05d} " + "x" * 40 for i in range(600 if rank == 1 else 3)]
+        bn, bc = D.merge_label_tables(big + ["é shared"], [1] * len(big) + [5])
+        assert len(bn) == 604 and bc[bn.index("é shared")] == 10 and sum(bc) == 613
         torch.save({"keys": local["keys"], "rows": local["rows"], "sum": local["cols"][0]["sum"], "sums": sums,
                     "cnts": cnts, "names": names, "lc": lc}, f"{out}/r{rank}.pt")
     finally:
