@@ -92,9 +92,10 @@ def upload_file(eng: Engine, path: str):
 
 def _dictionary_labels(text: torch.Tensor, hash_tab: torch.Tensor, rep_tab: torch.Tensor):
     """Used slots of a decode dictionary and their strings (one small gather)."""
-    h = hash_tab.cpu().numpy().view(np.uint64)
-    used = np.nonzero(h)[0]
-    rep = rep_tab.cpu().numpy().view(np.uint64)[used]
+    # the tables hold 2 x capacity x 8 bytes but only a handful of used slots: compact on the device, copy those
+    used_d = torch.nonzero(hash_tab).flatten()
+    used = used_d.cpu().numpy()
+    rep = rep_tab[used_d].cpu().numpy().view(np.uint64)
     off = (rep >> np.uint64(24)).astype(np.int64)
     quoted = ((rep >> np.uint64(23)) & np.uint64(1)).astype(bool)
     length = (rep & np.uint64((1 << 23) - 1)).astype(np.int64)
