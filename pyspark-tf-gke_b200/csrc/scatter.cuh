@@ -108,14 +108,15 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
         return (unsigned)part_dest(key, job.ranks, job.buckets) & (PART_MAX - 1);
     };
 
+    // Three block barriers per tile.  The counters are cleared for the NEXT tile right after the scan has
+    // read them, and the copy of the next tile is issued after the first barrier of the current one - by
+    // then every thread has left the previous tile's write loop, the last reader of that buffer.
     int64_t t = blockIdx.x;
     if (threadIdx.x == 0 && t < tiles) issue(t, 0);
+    if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
     for (int it = 0; t < tiles; t += gridDim.x, ++it) {
         const int buf = it & 1;
-        __syncthreads();  // every thread is done with the other buffer and with this tile's scratch
-        if (threadIdx.x == 0 && t + gridDim.x < tiles) issue(t + gridDim.x, buf ^ 1);
-        if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;
-        __syncthreads();
         mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
         const int64_t left = cnt - t * PART_TILE;
         const int rows = left < PART_TILE ? (int)left : PART_TILE;
@@ -132,7 +133,8 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
                 dr[j] = (d << 16) | atomicAdd(&s_cnt[d], 1u);
             }
         }
-        __syncthreads();
+        __syncthreads();   // counts complete; nobody is in the previous tile's write loop any more
+        if (threadIdx.x == 0 && t + gridDim.x < tiles) issue(t + gridDim.x, buf ^ 1);
         // 2. reserve this tile's run in every destination (atomics in flight while the offsets are scanned)
         unsigned long long gb = 0;
         if (threadIdx.x < parts && s_cnt[threadIdx.x])
@@ -160,6 +162,7 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
             }
         }
         __syncthreads();
+        if (threadIdx.x < PART_MAX) s_cnt[threadIdx.x] = 0;   // for the next tile (read for the last time above)
         // 3. sorted position -> source row (the reservations' round trip to L2 overlaps this)
 #pragma unroll
         for (int j = 0; j < PER; ++j)
