@@ -4,9 +4,9 @@
 // One CTA works on tiles of PART_TILE rows of one "segment" (level 1: the whole input; level 2:
 // one level-1 bucket per blockIdx.y).  The tile's input arrives in shared memory by 1-D bulk
 // async copies (TMA engine, completion on an mbarrier), double buffered: the copy of the CTA's
-// next tile is issued before the current tile is touched, so the HBM read latency that stalled
-// the register-staged version (ncu: 56 % of stall samples long_scoreboard, DRAM at 45 %) overlaps
-// the shared-memory work.  Per tile:
+// next tile is in flight while the current one is ranked, permuted and written, so the HBM read
+// latency that stalled the register-staged version (ncu: 56 % of stall samples long_scoreboard,
+// DRAM at 45 %) overlaps the shared-memory work.  Three block barriers per tile.  Per tile:
 //   1. destination d of every row; rank of the row within (tile, d) by a shared atomic;
 //   2. exclusive scan of the tile's per-destination counts; one global atomic per destination
 //      reserves the tile's run in that destination's range;
