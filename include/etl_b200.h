@@ -145,6 +145,18 @@ ETL_API int etl_column_sum_count(etl_handle* h, int32_t ncols,
                          const int32_t val_dtype[], const uint32_t* row_valid, int64_t n,
                          double* d_sum, int64_t* d_count, void* stream);
 
+/* StandardScaler.fit's summary of up to 3 columns (north-star item 5 "feature
+ * standardisation"; the reference's pipeline stops at VectorAssembler,
+ * k_means.py:64-68, so there is no reference call site): over the same cells
+ * etl_column_sum_count takes (row_valid & val_valid & ~isnan), d_count[c] = cells,
+ * d_mean[c] = sum / count, d_m2[c] = sum of (x - mean)^2 - two passes of the same
+ * fixed-shape tree, the mean never leaves the device.  Spark's unbiased std is
+ * sqrt(m2 / (count - 1)); feed shift = mean (withMean) and scale = 1 / std to
+ * etl_assemble_features_* / etl_pack_tf_features. */
+ETL_API int etl_column_moments(etl_handle* h, int32_t ncols, const void* const val[], const uint32_t* const val_valid[],
+                       const int32_t val_dtype[], const uint32_t* row_valid, int64_t n, int64_t* d_count,
+                       double* d_mean, double* d_m2, void* stream);
+
 /* ---- a1: CSV text -> columnar device buffers ----------------------------- */
 
 /* Together these replace spark.read.csv(path, header=True, inferSchema=True)
@@ -399,6 +411,56 @@ ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records,
                                   int64_t out_capacity, int64_t* out_keys, int64_t* out_rows, int64_t* out_count,
                                   double* out_sum, int64_t* spill_records, int64_t spill_capacity,
                                   int64_t* d_counters, void* stream);
+
+/* The same exchange and the same two partition levels WITHOUT their count passes
+ * (the Exchange + final HashAggregate under k_means.py:23-48; north-star item 4;
+ * no reference counterpart below the Spark shuffle).  Every destination of a
+ * scatter owns a fixed-capacity SLAB of a record buffer and a cursor word that
+ * persists across calls (caller-owned, zeroed by the caller before the first
+ * call), so rows can be scattered chunk by chunk: a sender streams its table over
+ * NVLink in chunks while the receivers already partition what has arrived.
+ *   etl_slab_partition_rows: destination d = rank * buckets + bucket (as in
+ *     etl_hash_partition) writes into dest_records[rank] at record index
+ *     slab_origin + d * slab_stride + position, position < slab_capacity.  For a
+ *     local first level: ranks = 1, one buffer, slab_stride = slab_capacity.  For
+ *     the exchange: buckets = 1, dest_records[r] = rank r's receive buffer as
+ *     mapped here, slab_origin = (this rank) * slab_capacity, slab_stride = 0.
+ *     Rows: two contiguous 16-byte aligned columns (strides 1) or {key, value}
+ *     records (strides 2, vals == keys + 1).  max_ctas > 0 caps the grid so a
+ *     link-bound exchange leaves SMs to the kernels it overlaps with.
+ *   etl_slab_partition_records: input = `segments` slabs of `records`, seg_capacity
+ *     records apart; segment s holds the records [min(d_seg_prev[s], cap),
+ *     min(d_seg_counts[s], cap)) (d_seg_prev NULL = from 0).  sub == 0: all segments
+ *     scatter into the same `buckets` slabs of out_records (the receiver's first
+ *     level over what each source has delivered since d_seg_prev).  sub > 0:
+ *     segments == buckets, segment b is cut into pieces b * sub .. b * sub + sub - 1
+ *     of `buckets * sub` (the second level); d_cursor has buckets * sub words.
+ *     max_seg_records only sizes the grid.
+ *   etl_groupby_merge_slabs: etl_groupby_merge_partitioned over slabs: piece f =
+ *     records [f * piece_capacity, + min(d_cursor[f], piece_capacity)).
+ *   etl_peer_publish_counts: peer_tables[r][slot] = d_cursor[r] for every rank r
+ *     (system-scope release stores; follow with a cross-rank barrier) - how a
+ *     receiver learns how much of each source's slab is filled.
+ * Overflow: a record that finds its slab full is counted in *d_overflow (int64,
+ * caller-zeroed) and DROPPED.  A non-zero count means the result is incomplete:
+ * repeat on the counted path (etl_hash_partition / etl_hash_subpartition), which
+ * sizes every destination exactly.  With slabs of mean + 6 sigma records that
+ * only happens for heavily skewed keys. */
+ETL_API int etl_slab_partition_rows(etl_handle* h, const int64_t* keys, int64_t key_stride, const double* vals,
+                            int64_t val_stride, int64_t n, int32_t ranks, int32_t buckets,
+                            int64_t* const* dest_records, int64_t slab_origin, int64_t slab_stride,
+                            int64_t slab_capacity, int64_t* d_cursor, int64_t* d_overflow, int32_t max_ctas,
+                            void* stream);
+ETL_API int etl_slab_partition_records(etl_handle* h, const int64_t* records, int32_t segments, int64_t seg_capacity,
+                               const int64_t* d_seg_counts, const int64_t* d_seg_prev, int64_t max_seg_records,
+                               int32_t buckets, int32_t sub, int64_t* out_records, int64_t slab_capacity,
+                               int64_t* d_cursor, int64_t* d_overflow, int32_t max_ctas, void* stream);
+ETL_API int etl_groupby_merge_slabs(etl_handle* h, const int64_t* records, int32_t fine, const int64_t* d_cursor,
+                            int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity, int64_t* out_keys,
+                            int64_t* out_rows, int64_t* out_count, double* out_sum, int64_t* spill_records,
+                            int64_t spill_capacity, int64_t* d_counters, void* stream);
+ETL_API int etl_peer_publish_counts(etl_handle* h, const int64_t* d_cursor, int32_t ranks, int64_t* const* peer_tables,
+                            int64_t slot, void* stream);
 
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 

@@ -39,6 +39,10 @@ def load():
         lib.oracle_project_filter_impute.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(VP3), C.POINTER(VP3),
                                                      C.POINTER(I32x3), C.POINTER(F64x3), C.c_int64, C.c_void_p,
                                                      C.POINTER(VP3)]
+        lib.oracle_synth_column.restype = None
+        lib.oracle_synth_column.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_uint64, C.c_int64, C.c_int64, C.c_void_p]
+        lib.oracle_groupby_sum.restype = C.c_int64
+        lib.oracle_groupby_sum.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = lib
     return _lib
 
@@ -74,3 +78,23 @@ def project_filter_impute(key_code, key_valid_words, vals, vals_valid_words, fil
     rows = load().oracle_project_filter_impute(_p(key_code), _p(key_valid_words), C.byref(val), C.byref(vv),
                                                C.byref(dt), C.byref(fl), n, _p(out_code), C.byref(ov))
     return rows, out_code, out_vals
+
+
+def synth_column(seed: int, stream_id: int, kind: int, n: int, row0: int = 0, modulus: int = 1) -> np.ndarray:
+    """pyspark_tf_gke_b200.synth.host_column without nulls (kinds EXACT = 0 and KEY64 = 3), on every host core."""
+    assert kind in (0, 3)
+    out = np.empty(n, dtype=np.float64 if kind == 0 else np.int64)
+    load().oracle_synth_column(seed, stream_id, kind, modulus, row0, n, _p(out))
+    return out
+
+
+def groupby_sum(keys: np.ndarray, vals: np.ndarray, scratch=None):
+    """groupBy(key).agg(count, sum(value)) -> (keys, count, sum), unordered.  `scratch` = three
+    arrays of len(keys) entries to reuse between calls (timing loops)."""
+    n = keys.shape[0]
+    assert keys.dtype == np.int64 and vals.dtype == np.float64 and vals.shape[0] == n
+    ok, oc, os_ = scratch or (np.empty(n, np.int64), np.empty(n, np.int64), np.empty(n, np.float64))
+    g = load().oracle_groupby_sum(_p(keys), _p(vals), n, _p(ok), _p(oc), _p(os_))
+    if g < 0:
+        raise MemoryError("oracle_groupby_sum: out of host memory")
+    return ok[:g], oc[:g], os_[:g]

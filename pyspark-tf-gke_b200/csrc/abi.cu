@@ -71,9 +71,11 @@ int etl_create(int device, etl_handle** out) {
     ETL_CUDA(cudaGetDeviceCount(&count));
     ETL_REQUIRE(device >= 0 && device < count, "etl_create: device %d out of range (%d visible)", device, count);
     ETL_CUDA(cudaSetDevice(device));
+    int sm_count = 0;
+    ETL_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
     Handle* h = new Handle();
     h->device = device;
-    ETL_CUDA(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
+    h->sm_count = sm_count;
     int rc = etl::arena_reserve(h, (size_t)1 << 20);
     if (rc != ETL_OK) {
         delete h;

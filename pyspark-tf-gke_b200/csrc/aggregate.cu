@@ -8,6 +8,12 @@
 // SUM_GRID partials in index order.  No floating-point atomics, so results are
 // bit-reproducible, and exact whenever every partial sum is representable
 // (integer-valued data below 2^53, the reference's default input).
+//
+// etl_column_moments (StandardScaler.fit, north-star item 5) runs the same kernel
+// twice: pass 1 leaves count and mean = sum / count on the device, pass 2
+// (CENTERED) sums (x - mean)^2 - the textbook two-pass variance, as accurate as a
+// Welford / Chan merge and with the same fixed-shape tree; nothing visits the host
+// in between.
 #include "common.cuh"
 
 namespace etl {
@@ -26,6 +32,8 @@ struct SumParams {
     long long* partial_cnt;  // [3][SUM_GRID]
     double* out_sum;
     long long* out_cnt;
+    double* out_mean;        // optional: sum / count (NaN for an empty column)
+    const double* center;    // CENTERED: accumulate (x - center[c])^2 instead of x
     unsigned int* ticket;
 };
 
@@ -37,16 +45,16 @@ __device__ __forceinline__ unsigned nibble_at(const uint32_t* bitmap, int64_t ro
     return nib;
 }
 
-template <int NC>
+template <int NC, bool CENTERED = false>
 __global__ void __launch_bounds__(SUM_THREADS) column_sum_count_kernel(const SumParams p) {
     __shared__ double s_sum[NC][SUM_THREADS / 32];
     __shared__ long long s_cnt[NC][SUM_THREADS / 32];
     __shared__ bool s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    double acc[NC];
+    double acc[NC], ctr[NC];
     long long cnt[NC];
 #pragma unroll
-    for (int c = 0; c < NC; ++c) { acc[c] = 0.0; cnt[c] = 0; }
+    for (int c = 0; c < NC; ++c) { acc[c] = 0.0; cnt[c] = 0; ctr[c] = CENTERED ? p.center[c] : 0.0; }
 
     const int64_t tiles = (p.n + SUM_TILE - 1) / SUM_TILE;
     for (int64_t t = blockIdx.x; t < tiles; t += SUM_GRID) {
@@ -87,7 +95,15 @@ __global__ void __launch_bounds__(SUM_THREADS) column_sum_count_kernel(const Sum
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const bool ok = ((nib >> j) & 1u) && (v[j] == v[j]);
-                if (ok) { acc[c] += v[j]; ++cnt[c]; }
+                if (ok) {
+                    if (CENTERED) {
+                        const double d = __dsub_rn(v[j], ctr[c]);
+                        acc[c] = __dadd_rn(acc[c], __dmul_rn(d, d));
+                    } else {
+                        acc[c] += v[j];
+                    }
+                    ++cnt[c];
+                }
             }
         }
     }
@@ -133,7 +149,11 @@ __global__ void __launch_bounds__(SUM_THREADS) column_sum_count_kernel(const Sum
             s += __shfl_down_sync(0xffffffffu, s, o);
             k += __shfl_down_sync(0xffffffffu, k, o);
         }
-        if (lane == 0) { p.out_sum[c] = s; p.out_cnt[c] = k; }
+        if (lane == 0) {
+            p.out_sum[c] = s;
+            p.out_cnt[c] = k;
+            if (p.out_mean) p.out_mean[c] = k ? s / (double)k : __longlong_as_double(0x7ff8000000000000ll);
+        }
     }
     if (tid == 0) *p.ticket = 0;  // ready for the next launch
 }
@@ -174,22 +194,21 @@ extern "C" int etl_null_count(etl_handle* hh, const uint32_t* valid, int64_t n, 
     return ETL_OK;
 }
 
-extern "C" int etl_column_sum_count(etl_handle* hh, int32_t ncols, const void* const val[],
-                                    const uint32_t* const val_valid[], const int32_t val_dtype[],
-                                    const uint32_t* row_valid, int64_t n, double* d_sum, int64_t* d_count,
-                                    void* stream_) {
-    ETL_REQUIRE(hh && val && val_valid && val_dtype && d_sum && d_count, "column_sum_count: NULL argument");
-    ETL_REQUIRE(ncols >= 1 && ncols <= 3, "column_sum_count: ncols=%d not in 1..3", ncols);
-    ETL_REQUIRE(n >= 0, "column_sum_count: n < 0");
-    ETL_REQUIRE(etl::aligned4(row_valid), "column_sum_count: row_valid misaligned");
+static int launch_sum(etl_handle* hh, const char* who, bool centered, int32_t ncols, const void* const val[],
+                      const uint32_t* const val_valid[], const int32_t val_dtype[], const uint32_t* row_valid, int64_t n,
+                      double* d_sum, int64_t* d_count, double* d_mean, const double* d_center, void* stream_) {
+    ETL_REQUIRE(hh && val && val_valid && val_dtype && d_sum && d_count, "%s: NULL argument", who);
+    ETL_REQUIRE(ncols >= 1 && ncols <= 3, "%s: ncols=%d not in 1..3", who, ncols);
+    ETL_REQUIRE(n >= 0, "%s: n < 0", who);
+    ETL_REQUIRE(etl::aligned4(row_valid), "%s: row_valid misaligned", who);
     Handle* h = reinterpret_cast<Handle*>(hh);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     etl::SumParams p{};
     for (int c = 0; c < ncols; ++c) {
-        ETL_REQUIRE(val[c] != nullptr || n == 0, "column_sum_count: val[%d] is NULL", c);
+        ETL_REQUIRE(val[c] != nullptr || n == 0, "%s: val[%d] is NULL", who, c);
         ETL_REQUIRE(val_dtype[c] == ETL_F64 || val_dtype[c] == ETL_F32 || val_dtype[c] == ETL_I32,
-                    "column_sum_count: val_dtype[%d]=%d unsupported", c, val_dtype[c]);
-        ETL_REQUIRE(etl::aligned16(val[c]) && etl::aligned4(val_valid[c]), "column_sum_count: val[%d] misaligned", c);
+                    "%s: val_dtype[%d]=%d unsupported", who, c, val_dtype[c]);
+        ETL_REQUIRE(etl::aligned16(val[c]) && etl::aligned4(val_valid[c]), "%s: val[%d] misaligned", who, c);
         p.val[c] = val[c];
         p.val_valid[c] = val_valid[c];
         p.val_dtype[c] = val_dtype[c];
@@ -204,12 +223,43 @@ extern "C" int etl_column_sum_count(etl_handle* hh, int32_t ncols, const void* c
     p.partial_cnt = reinterpret_cast<long long*>(p.partial_sum + 3 * etl::SUM_GRID);
     p.out_sum = d_sum;
     p.out_cnt = reinterpret_cast<long long*>(d_count);
+    p.out_mean = d_mean;
+    p.center = d_center;
     p.ticket = h->counters + 0;
-    switch (ncols) {
-        case 1: etl::column_sum_count_kernel<1><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
-        case 2: etl::column_sum_count_kernel<2><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
-        default: etl::column_sum_count_kernel<3><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+    if (centered) {
+        switch (ncols) {
+            case 1: etl::column_sum_count_kernel<1, true><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+            case 2: etl::column_sum_count_kernel<2, true><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+            default: etl::column_sum_count_kernel<3, true><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+        }
+    } else {
+        switch (ncols) {
+            case 1: etl::column_sum_count_kernel<1><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+            case 2: etl::column_sum_count_kernel<2><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+            default: etl::column_sum_count_kernel<3><<<etl::SUM_GRID, etl::SUM_THREADS, 0, stream>>>(p); break;
+        }
     }
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
+}
+
+extern "C" int etl_column_sum_count(etl_handle* hh, int32_t ncols, const void* const val[],
+                                    const uint32_t* const val_valid[], const int32_t val_dtype[],
+                                    const uint32_t* row_valid, int64_t n, double* d_sum, int64_t* d_count,
+                                    void* stream_) {
+    return launch_sum(hh, "column_sum_count", false, ncols, val, val_valid, val_dtype, row_valid, n, d_sum, d_count, nullptr,
+                      nullptr, stream_);
+}
+
+extern "C" int etl_column_moments(etl_handle* hh, int32_t ncols, const void* const val[], const uint32_t* const val_valid[],
+                                  const int32_t val_dtype[], const uint32_t* row_valid, int64_t n, int64_t* d_count,
+                                  double* d_mean, double* d_m2, void* stream_) {
+    ETL_REQUIRE(d_mean && d_m2, "column_moments: NULL argument");
+    // pass 1: count and mean (the sums land in d_m2 and are overwritten by pass 2)
+    int rc = launch_sum(hh, "column_moments", false, ncols, val, val_valid, val_dtype, row_valid, n, d_m2, d_count, d_mean,
+                        nullptr, stream_);
+    if (rc != ETL_OK) return rc;
+    // pass 2: sum of squared deviations from the mean pass 1 left on the device
+    return launch_sum(hh, "column_moments", true, ncols, val, val_valid, val_dtype, row_valid, n, d_m2, d_count, nullptr,
+                      d_mean, stream_);
 }

@@ -32,6 +32,8 @@ struct Handle {
     // cleared whenever the arena is reallocated
     const void* csv_text = nullptr;
     int64_t csv_nbytes = 0;
+    // projection kernel launch state of this device (set on the first projection through this handle)
+    int proj_stages = 0, proj_ctas_per_sm = 0, proj_hints = 3;
     cudaStream_t streams[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t events[12] = {};
 };

@@ -886,7 +886,10 @@ extern "C" int etl_csv_row_offsets(etl_handle* hh, const uint8_t* text, int64_t 
     const int64_t blocks = (nbytes + etl::CSV_BLOCK_BYTES - 1) / etl::CSV_BLOCK_BYTES;
     const size_t need = (size_t)blocks * (sizeof(etl::CsvBlockSummary) + sizeof(etl::CsvBlockStart) +
                                           etl::CSV_THREADS * sizeof(ulonglong2));
-    ETL_REQUIRE(h->scratch_bytes >= need, "csv_row_offsets: call etl_csv_index_rows on the same text first");
+    // the masks pass 1 left in the arena must still be this text's: any call that reserves the arena in between
+    // (sums, partitions, merges ...) clears csv_text
+    ETL_REQUIRE(h->scratch_bytes >= need && h->csv_text == text && h->csv_nbytes == nbytes,
+                "csv_row_offsets: call etl_csv_index_rows on the same text first (nothing that uses the handle's arena in between)");
     auto* sum = static_cast<etl::CsvBlockSummary*>(h->scratch);
     auto* start = reinterpret_cast<etl::CsvBlockStart*>(sum + blocks);
     auto* masks = reinterpret_cast<const ulonglong2*>(start + blocks);   // left there by etl_csv_index_rows

@@ -101,6 +101,7 @@ struct MergeParams {
     const int64_t* fine_base;
     const int64_t* fine_counts;
     int fine;
+    int64_t piece_cap;         // > 0: piece f is slab f (piece_cap records apart) holding min(fine_counts[f], piece_cap) records
     int slots;                 // S, a power of two
     int64_t* out_keys;
     int64_t* out_rows;
@@ -150,7 +151,14 @@ __global__ void __launch_bounds__(MG_THREADS, 2) groupby_merge_kernel(const Merg
     const uint32_t mask = (uint32_t)S - 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int f = blockIdx.x; f < p.fine; f += gridDim.x) {
-        const int64_t lo = p.fine_base[f], cnt = p.fine_counts[f];
+        int64_t lo, cnt;
+        if (p.piece_cap > 0) {
+            lo = (int64_t)f * p.piece_cap;
+            cnt = p.fine_counts[f] < p.piece_cap ? p.fine_counts[f] : p.piece_cap;
+        } else {
+            lo = p.fine_base[f];
+            cnt = p.fine_counts[f];
+        }
         if (cnt == 0) continue;  // the same for every thread of the CTA
         for (int i = threadIdx.x; i < S; i += MG_THREADS) {
             skey[i] = MG_EMPTY;
@@ -249,13 +257,11 @@ extern "C" int etl_hash_subpartition(etl_handle* hh, const int64_t* records, int
     return ETL_OK;
 }
 
-extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* records, int32_t fine,
-                                             const int64_t* d_fine_counts, const int64_t* d_fine_base,
-                                             int32_t smem_slots, int64_t out_capacity, int64_t* out_keys,
-                                             int64_t* out_rows, int64_t* out_count, double* out_sum,
-                                             int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
-                                             void* stream_) {
-    ETL_REQUIRE(hh && d_fine_counts && d_fine_base && d_counters, "groupby_merge_partitioned: NULL argument");
+static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t fine, const int64_t* d_fine_counts,
+                        const int64_t* d_fine_base, int64_t piece_cap, int32_t smem_slots, int64_t out_capacity,
+                        int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum, int64_t* spill_records,
+                        int64_t spill_capacity, int64_t* d_counters, void* stream_) {
+    ETL_REQUIRE(hh && d_fine_counts && (d_fine_base || piece_cap > 0) && d_counters, "groupby_merge_partitioned: NULL argument");
     ETL_REQUIRE(fine >= 1 && fine <= 65536, "groupby_merge_partitioned: fine=%d not in 1..65536", fine);
     ETL_REQUIRE(smem_slots >= 64 && smem_slots <= 8192 && (smem_slots & (smem_slots - 1)) == 0,
                 "groupby_merge_partitioned: smem_slots=%d must be a power of two in 64..8192", smem_slots);
@@ -272,7 +278,7 @@ extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* reco
     if (!records) return ETL_OK;
     etl::MergeParams p{};
     p.rec = reinterpret_cast<const longlong2*>(records);
-    p.fine_base = d_fine_base; p.fine_counts = d_fine_counts; p.fine = fine; p.slots = smem_slots;
+    p.fine_base = d_fine_base; p.fine_counts = d_fine_counts; p.fine = fine; p.slots = smem_slots; p.piece_cap = piece_cap;
     p.out_keys = out_keys; p.out_rows = out_rows; p.out_count = out_count; p.out_sum = out_sum;
     p.out_capacity = out_capacity;
     unsigned long long* ctr = reinterpret_cast<unsigned long long*>(d_counters);
@@ -288,4 +294,25 @@ extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* reco
     etl::groupby_merge_kernel<<<(unsigned)blocks, etl::MG_THREADS, smem, stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
+}
+
+extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* records, int32_t fine,
+                                             const int64_t* d_fine_counts, const int64_t* d_fine_base,
+                                             int32_t smem_slots, int64_t out_capacity, int64_t* out_keys,
+                                             int64_t* out_rows, int64_t* out_count, double* out_sum,
+                                             int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
+                                             void* stream_) {
+    ETL_REQUIRE(d_fine_base != nullptr, "groupby_merge_partitioned: NULL argument");
+    return merge_pieces(hh, records, fine, d_fine_counts, d_fine_base, 0, smem_slots, out_capacity, out_keys, out_rows,
+                        out_count, out_sum, spill_records, spill_capacity, d_counters, stream_);
+}
+
+extern "C" int etl_groupby_merge_slabs(etl_handle* hh, const int64_t* records, int32_t fine, const int64_t* d_cursor,
+                                       int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity,
+                                       int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum,
+                                       int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
+                                       void* stream_) {
+    ETL_REQUIRE(piece_capacity > 0, "groupby_merge_slabs: piece_capacity must be > 0");
+    return merge_pieces(hh, records, fine, d_cursor, nullptr, piece_capacity, smem_slots, out_capacity, out_keys, out_rows,
+                        out_count, out_sum, spill_records, spill_capacity, d_counters, stream_);
 }

@@ -354,16 +354,18 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
     p.n = n;
     p.out_code = out_code;
     p.out_rows = d_out_rows;
-    // persistent grid: every CTA must be resident (a scanner waits for other CTAs' chunk counts)
-    static int s_stages = 0, s_ctas_per_sm = 0;
-    if (s_stages == 0) {
+    // persistent grid: every CTA must be resident (a scanner waits for other CTAs' chunk counts).
+    // The opt-in shared-memory limit and the occupancy belong to the DEVICE, so they are kept per handle
+    // (one handle per GPU); the limit is always raised to the largest ring any path uses, so this path and
+    // the allocation-free entry never undercut each other.
+    if (h->proj_stages == 0) {
         int stages = 3;
         if (const char* e = getenv("ETL_PROJ_STAGES")) stages = atoi(e);
         if (stages < 2) stages = 2;
         if (stages > PROJ_MAX_STAGES) stages = PROJ_MAX_STAGES;
         const size_t dyn = (size_t)stages * sizeof(ProjStage);
         ETL_CUDA(cudaFuncSetAttribute(project_filter_impute_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)dyn));
+                                      (int)(PROJ_MAX_STAGES * sizeof(ProjStage))));
         int occ = 0;
         ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, project_filter_impute_kernel, PROJ_THREADS, dyn));
         if (occ < 1) {
@@ -374,19 +376,17 @@ int launch_project(Handle* h, const int32_t* key_code, const uint32_t* key_valid
             const int want = atoi(e);
             if (want >= 1 && want < occ) occ = want;
         }
-        s_ctas_per_sm = occ;
-        s_stages = stages;
-    }
-    p.stages = s_stages;
-    static int s_hints = -1;
-    if (s_hints < 0) {
         // default 3: evict-first bulk loads + streaming stores.  Measured on config 2: 108.5 us with
         // neither or only one of them, 98.5 us with both (the inputs stop evicting the dirty output
         // lines the L2 is still gathering into full sectors, and vice versa).
         const char* e = getenv("ETL_PROJ_HINTS");
-        s_hints = e ? atoi(e) : 3;
+        h->proj_hints = e ? atoi(e) : 3;
+        h->proj_ctas_per_sm = occ;
+        h->proj_stages = stages;
     }
-    p.hints = s_hints;
+    const int s_stages = h->proj_stages, s_ctas_per_sm = h->proj_ctas_per_sm;
+    p.stages = s_stages;
+    p.hints = h->proj_hints;
     int64_t grid = (int64_t)h->sm_count * s_ctas_per_sm;
     if (grid > tiles) grid = tiles;
     // chunk = unit of dynamic scheduling: ~8+ chunks per CTA, at most 4 tiles (measured best on
@@ -624,9 +624,10 @@ extern "C" int etl_project_filter_impute_host(etl_handle* hh, const int32_t* key
 //     (cudaGetSymbolAddress - in host code the array's name is only a handle,
 //     not a pointer a kernel can use), reads the SM count and sizes the grid.
 //     Make that first call before starting any stream capture;
-//   * every call on a device uses the same words.  Each call re-zeroes the
-//     ticket words and tags the chunk words with a fresh epoch on the caller's
-//     stream, so calls issued one after another on one stream are independent;
+//   * every call on a device uses the same words.  Each call clears the chunk
+//     words it is going to use and the ticket words on the caller's stream (and
+//     tags the chunk words with a fresh epoch), so calls issued one after
+//     another on one stream are independent;
 //     two calls that overlap on the GPU (different streams, no ordering) race
 //     on the scratch and produce garbage.
 // ---------------------------------------------------------------------------
@@ -746,6 +747,9 @@ extern "C" int etl_project_filter_impute_noalloc(const int32_t* key_code, const 
         d->epoch = 0;
     }
     p.epoch = ++d->epoch;
+    // ... and the words this call will use are cleared on the caller's stream as well, so a call's result
+    // never depends on what an earlier call left behind (at most 128 KiB, usually a few KiB)
+    ETL_CUDA(cudaMemsetAsync(d->scratch, 0, (size_t)p.chunks * sizeof(uint64_t), stream));
     ETL_CUDA(cudaMemsetAsync(p.ticket, 0, 2 * sizeof(unsigned int), stream));
     project_filter_impute_kernel<<<(unsigned)grid, PROJ_THREADS, (size_t)NOALLOC_STAGES * sizeof(ProjStage), stream>>>(p);
     ETL_CUDA(cudaGetLastError());

@@ -14,7 +14,17 @@
 //      stay where the bulk copy put them;
 //   4. rows are stored to global memory in sorted order: consecutive threads write consecutive
 //      16-byte records of one destination's run.
-// Shared memory: 2 x 32 KB input + 4 KB permutation + 4 KB counters = 73 KB -> 3 CTAs per SM.
+// Two shapes: 4096-row tiles x 1024 threads (2 x 64 KB input + 8 KB permutation + 5 KB counters = 141 KB,
+// one CTA per SM; the default - a (tile, destination) run is 256 B at 256 destinations) and 2048-row
+// tiles x 256 / 512 threads (74 KB, three CTAs per SM).
+//
+// SLAB mode (template flag): no count pass in front.  Every destination owns a fixed-capacity slab
+// (destination d's records start at slab_origin + d * slab_stride of its buffer, room for dest_cap
+// records) and a cursor that persists across launches, so a table can be scattered chunk by chunk.
+// A run that does not fit its slab is cut at the slab's end and the records beyond it are counted in
+// job.overflow and dropped - the host then repeats the work on the counted path, which sizes every
+// destination exactly.  Segments of a slab-mode input are slabs themselves: segment s holds the
+// records [min(seg_prev[s], seg_cap), min(seg_counts[s], seg_cap)) of slab s.
 #pragma once
 #include "common.cuh"
 
@@ -51,26 +61,44 @@ struct ScatterJob {
     int sub;                    // sub > 0: destination = fine_index(key, fine) - segment * sub
     unsigned fine;
     int parts;                  // destinations per segment (<= PART_MAX)
-    const int64_t* dest_base;   // [segments * parts] first record of every destination
-    unsigned long long* cursor; // [segments * parts] records already claimed, zero at launch
+    const int64_t* dest_base;   // [segments * parts] first record of every destination (counted mode)
+    unsigned long long* cursor; // [segments * parts] records already claimed (counted mode: zero at launch)
+    // ---- slab mode
+    int64_t seg_cap;            // > 0: segment s = slab s of the input (seg_cap records apart), counts clamped to seg_cap
+    const int64_t* seg_prev;    // optional [segments]: records of the segment consumed by earlier launches
+    int shared_dest;            // 1: all segments scatter into the same `parts` destinations (cursor / slabs not per segment)
+    int64_t slab_origin, slab_stride, dest_cap;
+    unsigned long long* overflow;   // [0] += records that found no room in their slab
 };
 
-constexpr size_t SCATTER_SMEM = 2 * PART_TILE * 16 + PART_TILE * 2 + PART_MAX * (4 + 4 + 8) + 16;
+template <int TILE>
+constexpr size_t scatter_smem_bytes() { return 2 * (size_t)TILE * 16 + (size_t)TILE * 2 + PART_MAX * (4 + 4 + 8 + 4) + 16; }
+constexpr size_t SCATTER_SMEM = scatter_smem_bytes<PART_TILE>();
 
-template <bool RECORDS, int THREADS>
-__global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const ScatterJob job, const PartDest dst) {
+template <bool RECORDS, int THREADS, bool SLAB = false, int TILE = PART_TILE>
+__global__ void __launch_bounds__(THREADS, TILE <= 2048 ? 3 : 1) scatter_pipelined_kernel(const ScatterJob job, const PartDest dst) {
     extern __shared__ __align__(128) unsigned char sc_smem[];
-    constexpr int PER = PART_TILE / THREADS;
-    uint16_t* s_src = reinterpret_cast<uint16_t*>(sc_smem + 2 * PART_TILE * 16);
-    unsigned* s_cnt = reinterpret_cast<unsigned*>(s_src + PART_TILE);
+    constexpr int PER = TILE / THREADS;
+    uint16_t* s_src = reinterpret_cast<uint16_t*>(sc_smem + 2 * TILE * 16);
+    unsigned* s_cnt = reinterpret_cast<unsigned*>(s_src + TILE);
     unsigned* s_off = s_cnt + PART_MAX;
-    long long* s_delta = reinterpret_cast<long long*>(s_off + PART_MAX);
+    unsigned* s_lim = s_off + PART_MAX;     // SLAB: sorted positions >= s_lim[d] of destination d found no room
+    long long* s_delta = reinterpret_cast<long long*>(s_lim + PART_MAX);
     uint64_t* bar = reinterpret_cast<uint64_t*>(s_delta + PART_MAX);
     const int seg = blockIdx.y;
-    const int64_t lo = job.seg_base ? job.seg_base[seg] : 0;
-    const int64_t cnt = job.seg_counts ? job.seg_counts[seg] : job.n;
-    const int64_t tiles = (cnt + PART_TILE - 1) / PART_TILE;
-    const size_t d0 = (size_t)seg * job.parts;
+    int64_t lo, cnt;
+    if (SLAB && job.seg_cap > 0) {
+        int64_t prev = job.seg_prev ? job.seg_prev[seg] : 0, cur = job.seg_counts[seg];
+        prev = prev < job.seg_cap ? prev : job.seg_cap;
+        cur = cur < job.seg_cap ? cur : job.seg_cap;
+        lo = (int64_t)seg * job.seg_cap + prev;
+        cnt = cur - prev;
+    } else {
+        lo = job.seg_base ? job.seg_base[seg] : 0;
+        cnt = job.seg_counts ? job.seg_counts[seg] : job.n;
+    }
+    const int64_t tiles = (cnt + TILE - 1) / TILE;
+    const size_t d0 = (SLAB && job.shared_dest) ? 0 : (size_t)seg * job.parts;
     const unsigned sub0 = (unsigned)seg * (unsigned)job.sub;
     const int parts = job.parts;
     if (threadIdx.x == 0) {
@@ -82,24 +110,24 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
 
     // thread 0: start the copy of tile t into buffer `buf`
     auto issue = [&](int64_t t, int buf) {
-        const int64_t left = cnt - t * PART_TILE;
-        const unsigned rows = left < PART_TILE ? (unsigned)left : (unsigned)PART_TILE;
-        unsigned char* in = sc_smem + (size_t)buf * PART_TILE * 16;
+        const int64_t left = cnt - t * TILE;
+        const unsigned rows = left < TILE ? (unsigned)left : (unsigned)TILE;
+        unsigned char* in = sc_smem + (size_t)buf * TILE * 16;
         if (RECORDS) {
             mbar_arrive_expect_tx(bar + buf, rows * 16);
-            bulk_load(in, job.keys + 2 * (lo + t * PART_TILE), rows * 16, bar + buf);
+            bulk_load(in, job.keys + 2 * (lo + t * TILE), rows * 16, bar + buf);
         } else {
-            const int64_t* gk = job.keys + lo + t * PART_TILE;
-            const double* gv = job.vals + lo + t * PART_TILE;
+            const int64_t* gk = job.keys + lo + t * TILE;
+            const double* gv = job.vals + lo + t * TILE;
             const unsigned even = rows & ~1u;  // bulk copies move multiples of 16 bytes
             if (rows & 1u) {                   // an odd last row: by hand, published by the arrive below
                 reinterpret_cast<int64_t*>(in)[even] = gk[even];
-                reinterpret_cast<double*>(in + PART_TILE * 8)[even] = gv[even];
+                reinterpret_cast<double*>(in + TILE * 8)[even] = gv[even];
             }
             mbar_arrive_expect_tx(bar + buf, even * 16);
             if (even) {
                 bulk_load(in, gk, even * 8, bar + buf);
-                bulk_load(in + PART_TILE * 8, gv, even * 8, bar + buf);
+                bulk_load(in + TILE * 8, gv, even * 8, bar + buf);
             }
         }
     };
@@ -118,9 +146,9 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
     for (int it = 0; t < tiles; t += gridDim.x, ++it) {
         const int buf = it & 1;
         mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
-        const int64_t left = cnt - t * PART_TILE;
-        const int rows = left < PART_TILE ? (int)left : PART_TILE;
-        const unsigned char* in = sc_smem + (size_t)buf * PART_TILE * 16;
+        const int64_t left = cnt - t * TILE;
+        const int rows = left < TILE ? (int)left : TILE;
+        const unsigned char* in = sc_smem + (size_t)buf * TILE * 16;
         const int64_t* kin = reinterpret_cast<const int64_t*>(in);
         // 1. destination and rank within (tile, destination), packed: destination << 16 | rank
         unsigned dr[PER];
@@ -137,8 +165,8 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
         if (threadIdx.x == 0 && t + gridDim.x < tiles) issue(t + gridDim.x, buf ^ 1);
         // 2. reserve this tile's run in every destination (atomics in flight while the offsets are scanned)
         unsigned long long gb = 0;
-        if (threadIdx.x < parts && s_cnt[threadIdx.x])
-            gb = atomicAdd(job.cursor + d0 + threadIdx.x, (unsigned long long)s_cnt[threadIdx.x]);
+        const unsigned mycnt = (int)threadIdx.x < parts ? s_cnt[threadIdx.x] : 0u;
+        if (mycnt) gb = atomicAdd(job.cursor + d0 + threadIdx.x, (unsigned long long)mycnt);
         if (parts <= 32) {
             if (threadIdx.x == 0) {
                 unsigned run = 0;
@@ -167,8 +195,18 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
 #pragma unroll
         for (int j = 0; j < PER; ++j)
             if (dr[j] != 0xffffffffu) s_src[s_off[dr[j] >> 16] + (dr[j] & 0xffffu)] = (uint16_t)(j * THREADS + threadIdx.x);
-        if (threadIdx.x < parts)
-            s_delta[threadIdx.x] = (long long)job.dest_base[d0 + threadIdx.x] + (long long)gb - (long long)s_off[threadIdx.x];
+        if ((int)threadIdx.x < parts) {
+            if (SLAB) {
+                long long fit = (long long)job.dest_cap - (long long)gb;      // room left in the slab before this run
+                fit = fit < 0 ? 0 : (fit > (long long)mycnt ? (long long)mycnt : fit);
+                if (fit < (long long)mycnt) atomicAdd(job.overflow, (unsigned long long)((long long)mycnt - fit));
+                s_lim[threadIdx.x] = s_off[threadIdx.x] + (unsigned)fit;
+                s_delta[threadIdx.x] = job.slab_origin + (long long)(d0 + threadIdx.x) * job.slab_stride + (long long)gb -
+                                       (long long)s_off[threadIdx.x];
+            } else {
+                s_delta[threadIdx.x] = (long long)job.dest_base[d0 + threadIdx.x] + (long long)gb - (long long)s_off[threadIdx.x];
+            }
+        }
         __syncthreads();
         // 4. write in sorted order
         for (int i = threadIdx.x; i < rows; i += THREADS) {
@@ -178,36 +216,54 @@ __global__ void __launch_bounds__(THREADS, 3) scatter_pipelined_kernel(const Sca
                 rec = *reinterpret_cast<const longlong2*>(in + (size_t)src * 16);
             } else {
                 rec.x = kin[src];
-                rec.y = kin[PART_TILE + src];
+                rec.y = kin[TILE + src];
             }
             const unsigned d = dest_of((uint64_t)rec.x);
-            *reinterpret_cast<longlong2*>(dst.base[d] + 2 * ((int64_t)s_delta[d] + i)) = rec;
+            if (!SLAB || (unsigned)i < s_lim[d])
+                *reinterpret_cast<longlong2*>(dst.base[d] + 2 * ((int64_t)s_delta[d] + i)) = rec;
         }
     }
 }
 
-// host side: launch over `segments` segments (grid.y) whose largest holds at most max_rows rows
-template <bool RECORDS>
-static inline cudaError_t launch_scatter_pipelined(int sm_count, const ScatterJob& job, const PartDest& dst, int segments,
-                                                   int64_t max_rows, cudaStream_t stream) {
-    // measured (1 B rows, 256 destinations): records 11.8 ms at 256 threads, 11.3 at 512; columns 8.9 / 9.1
-    static const int threads = [] { const char* e = getenv("ETL_PART_THREADS"); return e ? atoi(e) : (RECORDS ? 512 : 256); }();
-    const int64_t tiles = (max_rows + PART_TILE - 1) / PART_TILE;
-    int64_t gx = ((int64_t)sm_count * 3 + segments - 1) / segments;
+// host side: launch over `segments` segments (grid.y) whose largest holds at most max_rows rows.
+// max_ctas > 0 caps the grid (a link-bound exchange scatter leaves SMs to the kernels it overlaps with).
+template <bool RECORDS, int THREADS, bool SLAB, int TILE>
+static inline cudaError_t launch_scatter_variant(int sm_count, const ScatterJob& job, const PartDest& dst, int segments,
+                                                 int64_t max_rows, int max_ctas, cudaStream_t stream) {
+    constexpr size_t smem = scatter_smem_bytes<TILE>();
+    constexpr int per_sm = TILE <= 2048 ? 3 : 1;
+    const int64_t tiles = (max_rows + TILE - 1) / TILE;
+    int64_t total = (int64_t)sm_count * per_sm;
+    if (max_ctas > 0 && max_ctas < total) total = max_ctas;
+    int64_t gx = (total + segments - 1) / segments;
     if (gx > tiles) gx = tiles;
     if (gx < 1) gx = 1;
     const dim3 grid((unsigned)gx, (unsigned)segments);
-    cudaError_t e;
-    if (threads == 512) {
-        e = cudaFuncSetAttribute(scatter_pipelined_kernel<RECORDS, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM);
-        if (e != cudaSuccess) return e;
-        scatter_pipelined_kernel<RECORDS, 512><<<grid, 512, SCATTER_SMEM, stream>>>(job, dst);
-    } else {
-        e = cudaFuncSetAttribute(scatter_pipelined_kernel<RECORDS, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCATTER_SMEM);
-        if (e != cudaSuccess) return e;
-        scatter_pipelined_kernel<RECORDS, 256><<<grid, 256, SCATTER_SMEM, stream>>>(job, dst);
-    }
+    auto kern = scatter_pipelined_kernel<RECORDS, THREADS, SLAB, TILE>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, THREADS, smem, stream>>>(job, dst);
     return cudaGetLastError();
+}
+
+template <bool RECORDS, bool SLAB = false>
+static inline cudaError_t launch_scatter_pipelined(int sm_count, const ScatterJob& job, const PartDest& dst, int segments,
+                                                   int64_t max_rows, cudaStream_t stream, int max_ctas = 0) {
+    // Measured on config 4 (1 B rows, 256 destinations, B200): tile 2048 x 256 / 512 threads 7.45 / 8.33 ms for
+    // level 1 / level 2; tile 4096 x 512 threads 6.77 / 7.45; tile 4096 x 1024 threads 6.13 / 6.76 (twice the run
+    // length per (tile, destination); one 141 KB CTA per SM).  A launch with a CTA cap (max_ctas > 0) is one that
+    // shares the SMs with another scatter (the exchange overlapped with the receiver's first level): it takes the
+    // 2048-row tile, whose 74 KB fit beside a 4096-row CTA.
+    static const int env_threads = [] { const char* e = getenv("ETL_PART_THREADS"); return e ? atoi(e) : 0; }();
+    static const int env_tile = [] { const char* e = getenv("ETL_PART_TILE"); return e ? atoi(e) : 0; }();
+    const int tile = env_tile ? env_tile : (max_ctas > 0 ? 2048 : 4096);
+    const int threads = env_threads ? env_threads : (tile == 4096 ? 1024 : (RECORDS ? 512 : 256));
+    if (tile == 4096) {
+        if (threads == 1024) return launch_scatter_variant<RECORDS, 1024, SLAB, 4096>(sm_count, job, dst, segments, max_rows, max_ctas, stream);
+        return launch_scatter_variant<RECORDS, 512, SLAB, 4096>(sm_count, job, dst, segments, max_rows, max_ctas, stream);
+    }
+    if (threads == 512) return launch_scatter_variant<RECORDS, 512, SLAB, 2048>(sm_count, job, dst, segments, max_rows, max_ctas, stream);
+    return launch_scatter_variant<RECORDS, 256, SLAB, 2048>(sm_count, job, dst, segments, max_rows, max_ctas, stream);
 }
 
 }  // namespace etl

@@ -134,6 +134,99 @@ class PeerExchange:
         return self.buf[:m], m, tot[rank].contiguous(), bucket_start[rank].contiguous()
 
 
+class SlabExchange:
+    """The exchange without a count pass, streamed in chunks and overlapped with the
+    receivers' first partition level.
+
+    Every rank owns a receive buffer in symmetric memory cut into one fixed-capacity
+    slab per SOURCE rank, plus a small table of arrival counts.  A sender scatters a
+    chunk of its rows straight into its slab of every destination's buffer (NVLink
+    peer stores, etl_slab_partition_rows with persistent cursors), publishes its
+    cursors into the receivers' count tables (etl_peer_publish_counts) and joins a
+    symmetric-memory barrier.  After the barrier of chunk c every receiver runs its
+    first partition level over exactly the records that arrived with chunk c
+    (etl_slab_partition_records, segments = sources) on a second stream while chunk
+    c + 1 is crossing NVLink.  Nothing is read back by the host; no all-gather.
+
+    A slab that overflows (skewed keys) only counts the surplus: the result object
+    then repeats the exchange on the counted path (PeerExchange), see
+    Engine.groupby_result."""
+
+    def __init__(self, eng, rows_per_rank: int, groups_hint: int = 0, chunks: int = 4, group=None,
+                 exchange_ctas: Optional[int] = None, level1_ctas: Optional[int] = None):
+        import os
+        import torch.distributed._symmetric_memory as symm
+
+        self.eng = eng
+        self.group = group or dist.group.WORLD
+        self.rank, self.size = dist.get_rank(self.group), dist.get_world_size(self.group)
+        self.rows_per_rank = int(rows_per_rank)
+        total = self.rows_per_rank * self.size
+        g = max(1, min(groups_hint if groups_hint > 0 else total, total))
+        self.rows_per_key = max(1.0, total / g)
+        self.slab = eng.slab_capacity(self.rows_per_rank / self.size, self.rows_per_key)
+        self.chunks = max(1, int(os.environ.get("ETL_EXCHANGE_CHUNKS", chunks)))
+        self.max_chunks = 64
+        self.buf = symm.empty((self.size * self.slab, 2), dtype=torch.int64, device=eng.device)
+        self.handle = symm.rendezvous(self.buf, self.group.group_name)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.counts = symm.empty((self.max_chunks, self.size), dtype=torch.int64, device=eng.device)
+        self.counts_handle = symm.rendezvous(self.counts, self.group.group_name)
+        self.count_ptrs = [int(p) for p in self.counts_handle.buffer_ptrs]
+        self.side = torch.cuda.Stream(device=eng.device)
+        sm = torch.cuda.get_device_properties(eng.device).multi_processor_count
+        # the exchange scatter is NVLink-bound: capped at one 74 KB CTA per SM (a capped launch takes the 2048-row
+        # tile) it leaves room on every SM for the 141 KB CTA of the receiver's level-1 scatter (uncapped: 0)
+        self.exchange_ctas = int(os.environ.get("ETL_EXCHANGE_CTAS", exchange_ctas if exchange_ctas is not None else sm))
+        self.level1_ctas = int(os.environ.get("ETL_LEVEL1_CTAS", level1_ctas if level1_ctas is not None else 0))
+        self._counted: Optional[PeerExchange] = None
+
+    def counted(self) -> "PeerExchange":
+        """The exact-count exchange, created (collectively) the first time an overflow asks for it."""
+        if self._counted is None:
+            self._counted = PeerExchange(self.eng, int(self.rows_per_rank * 1.5) + (1 << 20), group=self.group)
+        return self._counted
+
+    def any_overflow(self, local: int) -> int:
+        t = torch.tensor([int(local)], dtype=torch.int64, device=self.eng.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
+
+    def run(self, chunk_iter, buckets: int, cap1: int, cur1: torch.Tensor, level1: torch.Tensor, overflow: torch.Tensor,
+            mark=None):
+        """chunk_iter yields (keys, vals, n, ready_event or None) device chunks of this
+        rank's rows.  On return (main stream) level1 / cur1 hold this rank's received
+        records cut into `buckets` slabs of cap1 records."""
+        eng, size, rank = self.eng, self.size, self.rank
+        main = torch.cuda.current_stream(eng.device)
+        xcur = torch.zeros(size, dtype=torch.int64, device=eng.device)
+        self.handle.barrier()            # every rank has finished reading the previous exchange's records
+        self.side.wait_stream(main)      # level1 / cur1 / overflow were set up on the main stream
+        c = 0
+        for keys, vals, n, ready in chunk_iter:
+            if c >= self.max_chunks:
+                raise RuntimeError(f"SlabExchange: more than {self.max_chunks} chunks")
+            if ready is not None:
+                main.wait_event(ready)
+            eng.slab_partition_rows(keys, vals, n, size, 1, self.peer_ptrs, rank * self.slab, 0, self.slab, xcur, overflow,
+                                    max_ctas=self.exchange_ctas)
+            eng.peer_publish_counts(xcur, self.count_ptrs, c * size + rank)
+            self.handle.barrier()        # chunk c of every source, and its counts, have landed here
+            arrived = torch.cuda.Event()
+            arrived.record(main)
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(arrived)
+                bound = min(self.slab, -(-n // size) * 2 + 4096)
+                eng.slab_partition_records(self.buf, size, self.slab, self.counts[c], self.counts[c - 1] if c else None, bound,
+                                           buckets, 0, level1, cap1, cur1, overflow, max_ctas=self.level1_ctas)
+            c += 1
+        if mark:
+            mark("exchange")
+        main.wait_stream(self.side)
+        if mark:
+            mark("level1")
+
+
 def peer_layout(matrix: torch.Tensor, rank: int, size: int, buckets: int):
     """Layout of the receive buffers of a bucketed peer exchange.  matrix[s, r * buckets + b]
     = records source s sends to (rank r, bucket b).  A receive buffer holds its buckets one
@@ -158,8 +251,16 @@ def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_
 
 def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
                         buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None,
-                        merge: str = "smem", exchange_buckets: Optional[int] = None):
+                        merge: str = "smem", exchange_buckets: Optional[int] = None, counted: bool = False):
     """Config 4: hash-partition -> all-to-all -> local final merge.
+
+    Default path (merge="smem", groups_hint > 0, one GPU or peer = a SlabExchange):
+    no count passes - every scatter writes into fixed-capacity slabs; at N > 1 the
+    rows cross NVLink in chunks while the receivers already run their first
+    partition level on what has arrived (_slab_shuffle_groupby_sum).  counted=True,
+    peer = a PeerExchange, merge="table" or an unknown group count select the
+    counted path described below, which sizes every destination exactly and is also
+    what a slab overflow falls back to.
 
     Sender: one partition pass groups the rows by destination rank (few
     destinations = long contiguous runs).  The all-to-all moves each rank's range.
@@ -187,6 +288,10 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     mark = mark or (lambda name: None)
     if merge not in ("smem", "table"):
         raise ValueError(f"merge={merge!r}")
+    if merge == "smem" and not counted and groups_hint > 0 and (size == 1 or isinstance(peer, SlabExchange)):
+        return _slab_shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer, mark, group)
+    if isinstance(peer, SlabExchange):
+        peer = peer.counted()
     gt = eng.groupby_new(capacity, 1, minmax=False) if merge == "table" else None
     B = choose_buckets(capacity, 1) if buckets is None else buckets
     mark("init")
@@ -238,3 +343,118 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
             eng.groupby_accumulate_records(gt, by_bucket, starts[b], starts[b] + lengths[b], groups_hint)
     mark("merge")
     return gt
+
+
+def _device_chunks(keys: torch.Tensor, vals: torch.Tensor, chunks: int):
+    n = keys.shape[0]
+    step = max(2048, -(-(-(-n // chunks)) // 2048) * 2048)      # chunk starts stay 16-byte aligned in both columns
+    for lo in range(0, max(n, 1), step):
+        hi = min(n, lo + step)
+        yield keys[lo:hi], vals[lo:hi], hi - lo, None
+
+
+def _slab_shuffle_groupby_sum(eng, keys, vals, capacity: int, groups_hint: int, peer, mark, group, chunk_iter=None,
+                              n_local: Optional[int] = None):
+    """The slab path of shuffle_groupby_sum (see there).  chunk_iter: this rank's rows
+    as device chunks (shuffle_groupby_sum_host feeds them as they arrive from the host)."""
+    rank, size = world()
+    if size == 1:
+        for name in ("init", "partition", "exchange"):
+            mark(name)
+        if chunk_iter is None:
+            pg = eng.groupby_slab_sum(keys, vals, capacity, groups_hint, mark=mark)
+            mark("merge")
+            return pg
+        n = n_local
+        buckets, sub, rpk, cap1, cap2 = eng.slab_plan(n, groups_hint)
+        counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
+        cur1 = torch.zeros(buckets, dtype=torch.int64, device=eng.device)
+        level1 = torch.empty((buckets * cap1, 2), dtype=torch.int64, device=eng.device)
+        main = torch.cuda.current_stream(eng.device)
+        for k, v, m, ready in chunk_iter:
+            if ready is not None:
+                main.wait_event(ready)
+            eng.slab_partition_rows(k, v, m, 1, buckets, [level1.data_ptr()], 0, cap1, cap1, cur1, counters[4:])
+        mark("level1")
+        pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark)
+        mark("merge")
+        return pg
+    n = keys.shape[0] if n_local is None else n_local
+    m = n + n // 8 + (1 << 16)                      # records this rank expects to own (sizes the plan, not the buffers)
+    hint = -(-groups_hint // size) + groups_hint // (8 * size)
+    buckets, sub, rpk, cap1, cap2 = eng.slab_plan(m, hint)
+    counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
+    cur1 = torch.zeros(buckets, dtype=torch.int64, device=eng.device)
+    level1 = torch.empty((buckets * cap1, 2), dtype=torch.int64, device=eng.device)
+    mark("init")
+    mark("partition")
+    peer.run(chunk_iter if chunk_iter is not None else _device_chunks(keys, vals, peer.chunks), buckets, cap1, cur1, level1,
+             counters[4:], mark=mark)
+    pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark)
+    mark("merge")
+    pg.any_overflow = peer.any_overflow
+    if keys is not None:
+        pg.rerun = lambda: shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer=peer.counted(), group=group, counted=True)
+    return pg
+
+
+def shuffle_groupby_sum_host(eng, h_keys: torch.Tensor, h_vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
+                             peer=None, out=None, group=None, chunks: int = 8):
+    """shuffle_groupby_sum for callers whose rows live in HOST memory: `h_keys`
+    int64[n] / `h_vals` float64[n] (pinned for full PCIe speed) are this rank's
+    rows; the rank-local groups come back in host memory as out = (keys int64,
+    count int64, sum float64) arrays of at least `capacity` entries (pinned tensors
+    are filled in place; allocated when None).  Returns the number of groups.  The
+    copies, the exchange and the merge all run inside this call: on the slab path
+    the rows are copied in `chunks` pieces on a copy stream and every piece is
+    scattered (first partition level, or the exchange over NVLink) as soon as it
+    has landed, so the partitioning hides behind the PCIe transfer."""
+    dev = eng.device
+    rank, size = world()
+    n = h_keys.shape[0]
+    main = torch.cuda.current_stream(dev)
+    slab_ok = groups_hint > 0 and n > 0 and (size == 1 or isinstance(peer, SlabExchange))
+    if not slab_ok:
+        d_keys, d_vals = h_keys.to(dev, non_blocking=True), h_vals.to(dev, non_blocking=True)
+        pg = shuffle_groupby_sum(eng, d_keys, d_vals, capacity, groups_hint=groups_hint, peer=peer, group=group)
+    else:
+        d_keys = torch.empty(n, dtype=torch.int64, device=dev)
+        d_vals = torch.empty(n, dtype=torch.float64, device=dev)
+        copy = _copy_stream(dev)
+        copy.wait_stream(main)
+        step = max(2048, -(-(-(-n // chunks)) // 2048) * 2048)
+
+        def arriving():
+            for lo in range(0, n, step):
+                hi = min(n, lo + step)
+                with torch.cuda.stream(copy):
+                    d_keys[lo:hi].copy_(h_keys[lo:hi], non_blocking=True)
+                    d_vals[lo:hi].copy_(h_vals[lo:hi], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(copy)
+                yield d_keys[lo:hi], d_vals[lo:hi], hi - lo, ev
+
+        pg = _slab_shuffle_groupby_sum(eng, None, None, capacity, groups_hint, peer, lambda name: None, group,
+                                       chunk_iter=arriving(), n_local=n)
+        counted_peer = peer.counted if isinstance(peer, SlabExchange) else (lambda: peer)
+        pg.rerun = lambda: shuffle_groupby_sum(eng, d_keys, d_vals, capacity, groups_hint, peer=counted_peer(), group=group,
+                                               counted=True)
+    res = eng.groupby_result(pg, sort=False)
+    g = int(res["keys"].shape[0])
+    if out is None:
+        out = tuple(torch.empty(max(g, 1), dtype=t, pin_memory=True) for t in (torch.int64, torch.int64, torch.float64))
+    out[0][:g].copy_(res["keys"], non_blocking=True)
+    out[1][:g].copy_(res["cols"][0]["count"], non_blocking=True)
+    out[2][:g].copy_(res["cols"][0]["sum"], non_blocking=True)
+    main.synchronize()
+    return g
+
+
+_COPY_STREAMS = {}
+
+
+def _copy_stream(dev) -> "torch.cuda.Stream":
+    key = (dev.type, dev.index)
+    if key not in _COPY_STREAMS:
+        _COPY_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _COPY_STREAMS[key]

@@ -6,7 +6,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 from dataclasses import dataclass
-from typing import List, Optional, Sequence, Tuple
+from typing import Callable, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -89,6 +89,10 @@ class PartitionedGroups:
     spill: torch.Tensor
     capacity: int
     pieces: int
+    # slab path only: counters[4] counts records that found their slab full.  If it (any_overflow: over all
+    # ranks) is non-zero the groups above are incomplete and rerun() repeats the work on the counted path.
+    rerun: Optional[Callable[[], "PartitionedGroups"]] = None
+    any_overflow: Optional[Callable[[int], int]] = None
 
 
 class Engine:
@@ -151,6 +155,33 @@ class Engine:
                                                  n, out_sum.data_ptr(), out_count.data_ptr(), self._stream()))
         self.launches += 1
         return out_sum[:nc], out_count[:nc]
+
+    def column_moments(self, cols: Sequence[Column], row_valid: Optional[torch.Tensor] = None):
+        """StandardScaler.fit's summary of up to 3 columns -> device tensors (count
+        i64[nc], mean f64[nc], m2 f64[nc]): m2 = sum of squared deviations from the
+        mean over the non-null, non-NaN cells (two passes, nothing read back)."""
+        nc, n = len(cols), len(cols[0])
+        count, mean, m2 = self.empty(3, torch.int64), self.empty(3, torch.float64), self.empty(3, torch.float64)
+        val = VP3(*[_ptr(c.data) for c in cols], *([None] * (3 - nc)))
+        vv = VP3(*[_ptr(c.valid) for c in cols], *([None] * (3 - nc)))
+        dt = I32x3(*[c.dtype_code for c in cols], *([0] * (3 - nc)))
+        _lib.check(self.lib.etl_column_moments(self._h, nc, C.byref(val), C.byref(vv), C.byref(dt), _ptr(row_valid), n,
+                                               count.data_ptr(), mean.data_ptr(), m2.data_ptr(), self._stream()))
+        self.launches += 2
+        return count[:nc], mean[:nc], m2[:nc]
+
+    def standard_scaler_fit(self, cols: Sequence[Column], row_valid: Optional[torch.Tensor] = None,
+                            with_mean: bool = False, with_std: bool = True):
+        """Spark ML StandardScaler(withMean, withStd).fit on up to 3 columns ->
+        (shift, scale) lists for assemble_dense / assemble_sparse / pack_tf: shift =
+        mean or 0, scale = 1 / std (unbiased; 0 where std == 0, as Spark does) or 1."""
+        count, mean, m2 = (t.cpu().tolist() for t in self.column_moments(cols, row_valid))
+        shift = [m if with_mean else 0.0 for m in mean]
+        scale = []
+        for k, q in zip(count, m2):
+            std = float(np.sqrt(q / (k - 1))) if k > 1 else 0.0
+            scale.append((1.0 / std if std != 0.0 else 0.0) if with_std else 1.0)
+        return shift, scale
 
     # ------------------------------------------------------------- a3/a5
     def project_filter_impute(self, key: Column, vals: Sequence[Column], fill: Sequence[float],
@@ -352,11 +383,15 @@ class Engine:
             groups_hint, key_range, gt.status.data_ptr(), self._stream()))
         self.launches += 1 if n else 0
 
-    def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None) -> dict:
-        """Dense result sorted by key: keys, rows, per column count/sum/mean[/min/max]
-        (device tensors), plus the null-key group.  Raises if rows were dropped."""
+    def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None, sort: bool = True) -> dict:
+        """Dense result: keys, rows, per column count/sum/mean[/min/max] (device
+        tensors), plus the null-key group.  Raises if rows were dropped.  sort=True
+        orders the groups by key (a radix sort of the key column by torch - a
+        convenience for callers that compare results; Spark's own groupBy output is
+        unordered, and sort=False returns the groups as the kernels left them, with
+        no library kernel on the path)."""
         if isinstance(gt, PartitionedGroups):
-            return self._partitioned_result(gt)
+            return self._partitioned_result(gt, sort)
         cap = gt.capacity if max_groups is None else max_groups
         nc = gt.ncols
         keys = self.empty(cap, torch.int64)
@@ -376,7 +411,7 @@ class Engine:
         g = int(groups.item())
         if g > cap:
             raise _lib.EtlError(-5, f"groupBy: {g} groups exceed the output capacity {cap}")
-        order = torch.argsort(keys[:g])
+        order = torch.argsort(keys[:g]) if sort else slice(None)
         out = {"keys": keys[:g][order], "rows": rows[:g][order], "cols": []}
         for c in range(nc):
             col = {"count": cnt[c, :g][order], "sum": sm[c, :g][order]}
@@ -504,8 +539,111 @@ class Engine:
         self.launches += 1 if n else 0
         return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine)
 
-    def _partitioned_result(self, pg: "PartitionedGroups") -> dict:
-        groups, spilled, _, reserved = pg.counters.cpu().tolist()
+    # ---------------------------------------------- the same, without count passes (slabs)
+    SLAB_SIGMAS = float(os.environ.get("ETL_SLAB_SIGMAS", "6"))
+
+    @classmethod
+    def slab_capacity(cls, expected: float, rows_per_key: float) -> int:
+        """Room for a destination expected to receive `expected` records of keys that
+        carry ~rows_per_key rows each (all rows of a key land together, so the
+        spread is that of a compound Poisson count): mean + SLAB_SIGMAS sigma + 64, a
+        multiple of 8 records."""
+        sigma = float(np.sqrt(max(expected, 1.0) * (max(rows_per_key, 1.0) + 1.0)))
+        return int(-(-(expected + cls.SLAB_SIGMAS * sigma + 64) // 8) * 8)
+
+    def slab_partition_rows(self, keys: torch.Tensor, vals: torch.Tensor, n: int, ranks: int, buckets: int,
+                            dest_ptrs: Sequence[int], slab_origin: int, slab_stride: int, slab_capacity: int,
+                            cursor: torch.Tensor, overflow: torch.Tensor, key_stride: int = 1, val_stride: int = 1,
+                            max_ctas: int = 0) -> None:
+        P = C.c_void_p * ranks
+        _lib.check(self.lib.etl_slab_partition_rows(self._h, _ptr(keys), key_stride, _ptr(vals), val_stride, n, ranks, buckets,
+                                                    P(*dest_ptrs), slab_origin, slab_stride, slab_capacity,
+                                                    cursor.data_ptr(), overflow.data_ptr(), max_ctas, self._stream()))
+        self.launches += 1 if n else 0
+
+    def slab_partition_records(self, records: torch.Tensor, segments: int, seg_capacity: int, seg_counts: torch.Tensor,
+                               seg_prev: Optional[torch.Tensor], max_seg_records: int, buckets: int, sub: int,
+                               out_records: torch.Tensor, slab_capacity: int, cursor: torch.Tensor, overflow: torch.Tensor,
+                               max_ctas: int = 0) -> None:
+        _lib.check(self.lib.etl_slab_partition_records(self._h, records.data_ptr(), segments, seg_capacity,
+                                                       seg_counts.data_ptr(), _ptr(seg_prev), max_seg_records, buckets, sub,
+                                                       out_records.data_ptr(), slab_capacity, cursor.data_ptr(),
+                                                       overflow.data_ptr(), max_ctas, self._stream()))
+        self.launches += 1 if max_seg_records else 0
+
+    def peer_publish_counts(self, cursor: torch.Tensor, table_ptrs: Sequence[int], slot: int) -> None:
+        ranks = len(table_ptrs)
+        P = C.c_void_p * ranks
+        _lib.check(self.lib.etl_peer_publish_counts(self._h, cursor.data_ptr(), ranks, P(*table_ptrs), slot, self._stream()))
+        self.launches += 1
+
+    def slab_plan(self, n: int, groups_hint: int, max_buckets: int = 256):
+        """-> (buckets, sub, rows_per_key, cap1, cap2) for n records holding ~groups_hint distinct keys."""
+        buckets, sub = self.merge_plan(n, groups_hint, max_buckets=max_buckets)
+        g = max(1, min(int(groups_hint) if groups_hint > 0 else n, max(n, 1)))
+        rpk = max(1.0, n / g)
+        cap1 = self.slab_capacity(n / buckets, rpk)
+        cap2 = self.slab_capacity(n / (buckets * sub), rpk) if sub > 1 else cap1
+        return buckets, sub, rpk, cap1, cap2
+
+    def groupby_slab_sum(self, keys: torch.Tensor, vals: torch.Tensor, out_capacity: int, groups_hint: int,
+                         n: Optional[int] = None, key_stride: int = 1, val_stride: int = 1, slots: Optional[int] = None,
+                         mark=None) -> "PartitionedGroups":
+        """groupby_partitioned_sum without the two count passes: both partition levels
+        scatter into fixed-capacity slabs (csrc/slabs.cu).  groups_hint (> 0) sizes the
+        slabs; if a slab overflows (skewed keys, a hint far off) groupby_result repeats
+        the work with groupby_partitioned_sum, so the result is always complete."""
+        n = keys.shape[0] if n is None else n
+        if n == 0 or groups_hint <= 0:
+            return self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride, slots=slots, mark=mark)
+        buckets, sub, rpk, cap1, cap2 = self.slab_plan(n, groups_hint)
+        counters = torch.zeros(5, dtype=torch.int64, device=self.device)
+        cur1 = torch.zeros(buckets, dtype=torch.int64, device=self.device)
+        level1 = torch.empty((buckets * cap1, 2), dtype=torch.int64, device=self.device)
+        self.slab_partition_rows(keys, vals, n, 1, buckets, [level1.data_ptr()], 0, cap1, cap1, cur1, counters[4:], key_stride, val_stride)
+        if mark:
+            mark("level1")
+        pg = self.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, out_capacity, counters, slots=slots, mark=mark)
+        pg.rerun = lambda: self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride, slots=slots)
+        return pg
+
+    def groupby_merge_slab_buckets(self, level1: torch.Tensor, cur1: torch.Tensor, cap1: int, buckets: int, sub: int,
+                                   cap2: int, out_capacity: int, counters: torch.Tensor, slots: Optional[int] = None,
+                                   mark=None) -> "PartitionedGroups":
+        """After the first level (local, or done on what the exchange delivered): the second
+        level into piece slabs and the shared-memory merge.  counters = int64[5], [4] = overflow."""
+        slots = slots or self.MERGE_SLOTS
+        fine, pieces, cur2 = buckets, level1, cur1
+        spill = None
+        if sub > 1:
+            fine = buckets * sub
+            cur2 = torch.zeros(fine, dtype=torch.int64, device=self.device)
+            pieces = torch.empty((fine * cap2, 2), dtype=torch.int64, device=self.device)
+            self.slab_partition_records(level1, buckets, cap1, cur1, None, cap1, buckets, sub, pieces, cap2, cur2, counters[4:])
+            spill = level1             # dead from here on
+        if mark:
+            mark("level2")
+        if spill is None:
+            spill = torch.empty((max(buckets * cap1 // 8, 1 << 16), 2), dtype=torch.int64, device=self.device)
+        out_keys, out_rows = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.int64)
+        out_cnt, out_sum = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.float64)
+        _lib.check(self.lib.etl_groupby_merge_slabs(
+            self._h, pieces.data_ptr(), fine, cur2.data_ptr(), cap2, slots, out_capacity, out_keys.data_ptr(),
+            out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), spill.data_ptr(), spill.shape[0],
+            counters.data_ptr(), self._stream()))
+        self.launches += 1
+        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine)
+
+    def _partitioned_result(self, pg: "PartitionedGroups", sort: bool = True) -> dict:
+        ctr = pg.counters.cpu().tolist()
+        groups, spilled, _, reserved = ctr[:4]
+        overflow = ctr[4] if len(ctr) > 4 else 0
+        if pg.any_overflow is not None:
+            overflow = pg.any_overflow(overflow)       # a collective: every rank of the exchange calls it
+        if overflow:
+            if pg.rerun is None:
+                raise _lib.EtlError(-5, f"groupBy: {overflow} record(s) found their slab full and no counted rerun was given")
+            return self._partitioned_result(pg.rerun(), sort)
         if reserved:
             raise _lib.EtlError(-5, f"groupBy: 0 row(s) dropped (table full), {reserved} row(s) with the reserved key")
         if groups > pg.capacity:
@@ -517,10 +655,10 @@ class Engine:
             cap = 1 << max(4, int(np.ceil(np.log2(2 * spilled))))
             gt = self.groupby_new(cap, 1)
             self.groupby_accumulate_records(gt, pg.spill, 0, spilled, groups_hint=spilled)
-            extra = self.groupby_result(gt, max_groups=spilled)
+            extra = self.groupby_result(gt, max_groups=spilled, sort=False)
             keys, rows = torch.cat([keys, extra["keys"]]), torch.cat([rows, extra["rows"]])
             cnt, sm = torch.cat([cnt, extra["cols"][0]["count"]]), torch.cat([sm, extra["cols"][0]["sum"]])
-        order = torch.argsort(keys)
+        order = torch.argsort(keys) if sort else slice(None)
         col = {"count": cnt[order], "sum": sm[order]}
         col["mean"] = col["sum"] / col["count"].to(torch.float64)
         return {"keys": keys[order], "rows": rows[order], "cols": [col], "null_group_rows": 0, "spilled_records": spilled}

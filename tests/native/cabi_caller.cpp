@@ -108,6 +108,25 @@ int main(int argc, char** argv) {
         ++w;
     }
     if (w != kept) { std::fprintf(stderr, "kept rows: %lld, expected %lld\n", (long long)kept, (long long)w); ++bad; }
+    // the allocation-free entry, with no torch caching allocator in the way: after its set-up call the
+    // driver's free-memory figure must be the same before and after a call, and the result the same rows
+    ETL(etl_project_filter_impute_noalloc(d_code, d_kv, vals, vvs, dts, fill, n, d_out_code, outs, d_rows, nullptr));
+    CK(cudaDeviceSynchronize());
+    for (int rep = 0; rep < 2; ++rep) {
+        size_t free0 = 0, free1 = 0, total = 0;
+        CK(cudaMemGetInfo(&free0, &total));
+        CK(cudaMemset(d_rows, 0xff, 8));
+        ETL(etl_project_filter_impute_noalloc(d_code, d_kv, vals, vvs, dts, fill, n, d_out_code, outs, d_rows, nullptr));
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemGetInfo(&free1, &total));
+        int64_t kept2 = -1;
+        CK(cudaMemcpy(&kept2, d_rows, 8, cudaMemcpyDeviceToHost));
+        if (free0 != free1) { std::fprintf(stderr, "noalloc call changed free device memory: %zu -> %zu\n", free0, free1); ++bad; }
+        if (kept2 != kept) { std::fprintf(stderr, "noalloc kept rows %lld, expected %lld\n", (long long)kept2, (long long)kept); ++bad; }
+    }
+    std::vector<int32_t> again(n);
+    CK(cudaMemcpy(again.data(), d_out_code, n * 4, cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < kept; ++i) if (again[i] != got_code[i]) { ++bad; break; }
     ETL(etl_destroy(h));
     std::printf("cabi_caller: abi %d, %lld rows -> %lld kept, means %.6f %.6f %.6f, mismatches %d\n", etl_abi_version(),
                 (long long)n, (long long)kept, fill[0], fill[1], fill[2], bad);

@@ -1,0 +1,148 @@
+"""The count-free partition path (csrc/slabs.cu): fixed-capacity slabs + persistent
+cursors.  Single-GPU groupBy against the oracle, the overflow -> counted rerun, and
+the chunked exchange on ONE GPU with R local buffers standing in for the R ranks'
+receive buffers (the kernels only see pointers).  Keys, counts exact; sums exact
+(integer-valued data)."""
+import numpy as np
+import pytest
+import torch
+
+import pyspark_tf_gke_b200 as pkg
+import pyspark_tf_gke_b200.dist as D
+import pyspark_tf_gke_b200.synth as S
+from oracle import etl_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = pkg.Engine(0)
+    yield e
+    e.close()
+
+
+def _rows(n, groups, seed=21, row0=0, hot=False):
+    keys, _ = S.host_column(seed, 0, S.KIND_KEY64, n, row0=row0, modulus=groups)
+    vals, _ = S.host_column(seed, 1, S.KIND_EXACT, n, row0=row0)
+    keys = keys - groups // 3
+    if hot:
+        keys[np.arange(n) % 5 < 3] = 7
+    return keys, vals
+
+
+def _same(res, want):
+    assert res["keys"].cpu().numpy().tolist() == want["keys"].tolist()
+    assert res["rows"].cpu().numpy().tolist() == want["rows"].tolist()
+    assert res["cols"][0]["count"].cpu().numpy().tolist() == want["rows"].tolist()
+    assert res["cols"][0]["sum"].cpu().numpy().tobytes() == want["cols"][0]["sum"].tobytes()
+
+
+@pytest.mark.parametrize("n,groups", [(1, 1), (77, 5), (4097, 300), (300_001, 20_000), (2_000_003, 400_000), (3_000_000, 1_500_000)])
+def test_slab_groupby_matches_oracle(eng, n, groups):
+    keys, vals = _rows(n, groups)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    pg = eng.groupby_slab_sum(dk, dv, groups + 1024, groups_hint=groups)
+    assert int(pg.counters[4].item()) == 0                      # uniform keys: nothing overflows at 6 sigma
+    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    # the same rows as {key, value} records (strides 2), as the receiver sees them
+    rec = torch.stack([dk, dv.view(torch.int64)], dim=1).contiguous().view(-1)
+    pg = eng.groupby_slab_sum(rec, rec[1:].view(torch.float64), groups + 1024, groups_hint=groups, n=n, key_stride=2, val_stride=2)
+    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+
+
+def test_slab_overflow_repeats_on_the_counted_path(eng):
+    # one key carries 60 % of the rows: its bucket slab (mean + 6 sigma of a uniform table) overflows, the
+    # overflow is counted, and groupby_result transparently repeats the work with exact counts
+    n, groups = 1_000_000, 200_000
+    keys, vals = _rows(n, groups, hot=True)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    pg = eng.groupby_slab_sum(dk, dv, groups + 1024, groups_hint=groups)
+    assert int(pg.counters[4].item()) > 0
+    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    # through the public entry
+    pg = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups)
+    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+
+
+def test_slab_path_is_the_default_and_counted_path_agrees(eng):
+    n, groups = 1_500_000, 300_000
+    keys, vals = _rows(n, groups)
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    a = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups)
+    b = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups, counted=True)
+    assert a.counters.shape[0] == 5 and b.counters.shape[0] == 4
+    ra, rb = eng.groupby_result(a), eng.groupby_result(b)
+    for x, y in ((ra["keys"], rb["keys"]), (ra["rows"], rb["rows"]), (ra["cols"][0]["sum"], rb["cols"][0]["sum"])):
+        assert torch.equal(x, y)
+    _same(ra, O.groupby_agg_fast(keys, [vals], [None]))
+
+
+def test_host_entry_copies_in_chunks_and_matches_oracle(eng):
+    n, groups = 1_200_007, 100_000
+    keys, vals = _rows(n, groups)
+    hk, hv = torch.from_numpy(keys).pin_memory(), torch.from_numpy(vals).pin_memory()
+    out = tuple(torch.empty(groups + 1024, dtype=t, pin_memory=True) for t in (torch.int64, torch.int64, torch.float64))
+    g = D.shuffle_groupby_sum_host(eng, hk, hv, groups + 1024, groups_hint=groups, out=out, chunks=5)
+    want = O.groupby_agg_fast(keys, [vals], [None])
+    o = np.argsort(out[0][:g].numpy(), kind="stable")
+    assert out[0][:g].numpy()[o].tolist() == want["keys"].tolist()
+    assert out[1][:g].numpy()[o].tolist() == want["rows"].tolist()
+    assert out[2][:g].numpy()[o].tobytes() == want["cols"][0]["sum"].tobytes()
+
+
+@pytest.mark.parametrize("R,chunks", [(2, 1), (4, 3), (8, 4)])
+def test_simulated_chunked_slab_exchange(eng, R, chunks):
+    groups = 50_000
+    sizes = [80_000 + 1013 * s + (s % 2) for s in range(R)]
+    rows = [_rows(sizes[s], groups, row0=s * 1_000_000 // 32 * 32) for s in range(R)]
+    d_rows = [(torch.from_numpy(k).to(eng.device), torch.from_numpy(v).to(eng.device)) for k, v in rows]
+    slab = eng.slab_capacity(max(sizes) / R, 2.0)
+    bufs = [torch.full((R * slab, 2), -1, dtype=torch.int64, device=eng.device) for _ in range(R)]        # per "rank"
+    tables = [torch.zeros((chunks, R), dtype=torch.int64, device=eng.device) for _ in range(R)]
+    overflow = torch.zeros(1, dtype=torch.int64, device=eng.device)
+    # receivers' first level: `buckets` slabs per rank
+    m = max(sizes) + max(sizes) // 4
+    buckets, sub, rpk, cap1, cap2 = eng.slab_plan(m, groups // R + groups // (8 * R), max_buckets=16)
+    level1 = [torch.full((buckets * cap1, 2), -1, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    cur1 = [torch.zeros(buckets, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    xcur = [torch.zeros(R, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    for c in range(chunks):
+        for s in range(R):                 # every source sends its chunk c and publishes its cursors
+            k, v = d_rows[s]
+            step = -(-(-(-sizes[s] // chunks)) // 2048) * 2048
+            lo, hi = min(sizes[s], c * step), min(sizes[s], (c + 1) * step)
+            eng.slab_partition_rows(k[lo:hi], v[lo:hi], hi - lo, R, 1, [b.data_ptr() for b in bufs], s * slab, 0, slab, xcur[s],
+                                    overflow, max_ctas=37)
+            eng.peer_publish_counts(xcur[s], [t.data_ptr() for t in tables], c * R + s)
+        for r in range(R):                 # every receiver partitions what arrived with chunk c
+            eng.slab_partition_records(bufs[r], R, slab, tables[r][c], tables[r][c - 1] if c else None, slab, buckets, 0,
+                                       level1[r], cap1, cur1[r], overflow, max_ctas=50)
+    torch.cuda.synchronize()
+    assert int(overflow.item()) == 0
+    all_k = np.concatenate([k for k, _ in rows])
+    all_v = np.concatenate([v for _, v in rows])
+    dest = O.partition_dest(all_k, R)
+    for r in range(R):
+        # the count table: cumulative records per source after the last chunk = what the oracle sends there
+        want_counts = [int((O.partition_dest(rows[s][0], R) == r).sum()) for s in range(R)]
+        assert tables[r][chunks - 1].cpu().tolist() == want_counts
+        got = bufs[r].cpu().numpy()
+        for s in range(R):                 # source s's slab holds exactly source s's rows for rank r
+            piece = got[s * slab:s * slab + want_counts[s]]
+            sel = O.partition_dest(rows[s][0], R) == r
+            a = np.stack([rows[s][0][sel], rows[s][1][sel].view(np.int64)], axis=1)
+            assert piece[np.lexsort((piece[:, 1], piece[:, 0]))].tobytes() == a[np.lexsort((a[:, 1], a[:, 0]))].tobytes()
+        # level 1: bucket b's slab holds exactly the records whose (rank, bucket) destination is (r, b) of R x buckets
+        own = dest == r
+        fine_dest = O.partition_dest(all_k[own], 1, buckets)
+        l1, counts = level1[r].cpu().numpy(), cur1[r].cpu().tolist()
+        assert counts == np.bincount(fine_dest, minlength=buckets).tolist()
+        for b in range(buckets):
+            piece = l1[b * cap1:b * cap1 + counts[b]]
+            a = np.stack([all_k[own][fine_dest == b], all_v[own][fine_dest == b].view(np.int64)], axis=1)
+            assert piece[np.lexsort((piece[:, 1], piece[:, 0]))].tobytes() == a[np.lexsort((a[:, 1], a[:, 0]))].tobytes()
+        # second level + merge = the oracle's groupBy of the keys this rank owns
+        counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
+        pg = eng.groupby_merge_slab_buckets(level1[r], cur1[r], cap1, buckets, sub, cap2, groups, counters)
+        _same(eng.groupby_result(pg), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))

@@ -51,3 +51,18 @@ def test_no_bitmaps_means_no_nulls():
     assert rows == 1000 and (out_code == code).all()
     for a, b in zip(out_vals, vals):
         assert a.tobytes() == b.tobytes()
+
+
+@pytest.mark.parametrize("n,groups", [(0, 5), (1, 5), (1000, 7), (200_003, 20_000), (300_000, 1)])
+def test_groupby_sum_and_synth_match_numpy(n, groups):
+    # the compiled groupBy (bench.py's CPU arm for config 4) and the compiled generator against NumPy
+    keys = CO.synth_column(3, 0, S.KIND_KEY64, n, row0=96, modulus=groups)
+    vals = CO.synth_column(3, 1, S.KIND_EXACT, n, row0=96)
+    hk, _ = S.host_column(3, 0, S.KIND_KEY64, n, row0=96, modulus=groups)
+    hv, _ = S.host_column(3, 1, S.KIND_EXACT, n, row0=96)
+    assert (keys == hk).all() and vals.tobytes() == hv.tobytes()
+    gk, gc, gs = CO.groupby_sum(keys, vals)
+    want = O.groupby_agg_fast(keys, [vals], [None])
+    order = np.argsort(gk)
+    assert (gk[order] == want["keys"]).all() and (gc[order] == want["rows"]).all()
+    assert gs[order].tobytes() == want["cols"][0]["sum"].tobytes()     # integer-valued data: exact in any order

@@ -58,6 +58,47 @@ def test_noalloc_matches_handle_entry_on_two_calls_in_a_row():
         eng.close()
 
 
+def test_noalloc_leaves_device_memory_untouched():
+    # the property the entry exists for: once the first call on the device has done its one-time set-up,
+    # a call changes neither the driver's free-memory figure (no cudaMalloc / cudaFree anywhere below it)
+    # nor torch's own allocator statistics (the binding allocates nothing either)
+    eng = pkg.Engine(0)
+    try:
+        n, fill = 2_000_003, [1.0, 2.0, 3.0]
+        key, cols = _device_table(eng, n, seed=51)
+        out_code = torch.empty(n, dtype=torch.int32, device=eng.device)
+        out_vals = [torch.empty(n, dtype=torch.float64, device=eng.device) for _ in range(3)]
+        out_rows = torch.zeros(1, dtype=torch.int64, device=eng.device)
+        project_filter_impute_noalloc(key, cols, fill, out_code, out_vals, out_rows)      # warm-up (set-up call)
+        torch.cuda.synchronize()
+        for _ in range(2):                                                               # the 2nd and 3rd calls
+            free0, _ = torch.cuda.mem_get_info(eng.device)
+            reserved0, allocated0 = torch.cuda.memory_reserved(eng.device), torch.cuda.memory_allocated(eng.device)
+            project_filter_impute_noalloc(key, cols, fill, out_code, out_vals, out_rows)
+            torch.cuda.synchronize()
+            free1, _ = torch.cuda.mem_get_info(eng.device)
+            assert free1 == free0
+            assert torch.cuda.memory_reserved(eng.device) == reserved0
+            assert torch.cuda.memory_allocated(eng.device) == allocated0
+        ref_code, ref_vals, ref_rows = eng.project_filter_impute(key, cols, fill)
+        r = int(ref_rows.item())
+        assert int(out_rows.item()) == r and torch.equal(out_code[:r], ref_code[:r])
+    finally:
+        eng.close()
+
+
+def test_noalloc_large_table_uses_more_tiles_per_chunk():
+    # above ~67 M rows the fixed 16,384 chunk words force more than 4 tiles per chunk - the reason the
+    # chunk size is not a constant; 80 M rows, compared with the handle entry bit for bit
+    eng = pkg.Engine(0)
+    try:
+        r = _run_both(eng, 80_000_001, seed=61, fill=[0.5, -0.5, 7.0])
+        assert 0 < r < 80_000_001
+        _run_both(eng, 4_097, seed=62, fill=[0.5, -0.5, 7.0])       # and a small call right after the large one
+    finally:
+        eng.close()
+
+
 def test_noalloc_small_and_empty_inputs():
     eng = pkg.Engine(0)
     try:

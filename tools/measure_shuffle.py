@@ -45,6 +45,8 @@ def main():
     ap.add_argument("--exchange-buckets", type=int, default=0,
                     help="peer + smem: 0 = the exchange also cuts by table bucket; 1 = by rank only, receiver partitions")
     ap.add_argument("--out-capacity", type=int, default=0, help="room for output groups per rank (0 = table capacity)")
+    ap.add_argument("--counted", action="store_true", help="the counted path (exact count passes) instead of the slab path")
+    ap.add_argument("--chunks", type=int, default=4, help="slab exchange: chunks the rows cross NVLink in")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -82,13 +84,19 @@ def main():
     gt = None
     sent = n - n // world if world > 1 else 0  # expected rows leaving this GPU (uniform hash)
     B = D.choose_buckets(cap, 1) if args.buckets < 0 else args.buckets
-    peer = D.PeerExchange(eng, int(n * 1.05) + (1 << 20)) if (world > 1 and args.exchange == "peer") else None
+    peer = None
+    if world > 1 and args.exchange == "peer":
+        peer = (D.PeerExchange(eng, int(n * 1.05) + (1 << 20)) if args.counted
+                else D.SlabExchange(eng, n, groups_hint=args.groups, chunks=args.chunks))
+    from tools.clocks import ClockSampler
+    sampler = ClockSampler(local)
+    sampler.start()
     for it in range(args.warmup + args.steps):
         gt = None
         barrier()
         marks = {"start": ev()}
         gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer, merge=args.merge,
-                                   exchange_buckets=args.exchange_buckets or None,
+                                   exchange_buckets=args.exchange_buckets or None, counted=args.counted,
                                    mark=lambda name: marks.__setitem__(name, ev()))
         torch.cuda.synchronize()
         if it >= args.warmup:
@@ -99,6 +107,7 @@ def main():
             if "level1" in marks:   # inside "merge": the two partition levels of the shared-memory path
                 phases["level1"].append(max_ms(marks["exchange"], marks["level1"]))
                 phases["level2"].append(max_ms(marks["level1"], marks["level2"]))
+    clocks = sampler.stop()
     # ---- checks
     res = eng.groupby_result(gt, max_groups=cap)
     tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
@@ -119,7 +128,8 @@ def main():
                 "buckets_per_rank": B if args.merge == "table" else None, "merge": args.merge, "exchange_buckets": args.exchange_buckets or "auto",
                 "pieces_per_rank": getattr(gt, "pieces", None), "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
                 "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
-                "steps": args.steps}
+                "steps": args.steps, "path": "counted" if args.counted else "slabs", "clocks": clocks,
+                "knobs": {k: v for k, v in os.environ.items() if k.startswith("ETL_")}}
         print(json.dumps(line), flush=True)
     assert ok_rows and ok_sum
     eng.close()
