@@ -393,8 +393,10 @@ ETL_API int etl_hash_partition_scatter_peers(etl_handle* h, const int64_t* keys,
  *      grid.  buckets * sub <= 65536, sub <= 256;
  *   3. etl_groupby_merge_partitioned: one piece at a time per CTA; the groups are
  *      appended (in no particular order) to out_keys / out_rows / out_count /
- *      out_sum [out_capacity]; smem_slots = table size (power of two, 64..8192;
- *      20 bytes of shared memory each).  A record whose key finds no slot within
+ *      out_sum [out_capacity] and, when out_min / out_max are given (both or
+ *      neither; min(value) / max(value) with Spark's ordering: NaN is largest), to
+ *      those; smem_slots = table size (power of two, 64..8192; 20 bytes of shared
+ *      memory each, 36 and at most 4096 slots with min / max).  A record whose key finds no slot within
  *      the probe limit goes to spill_records (int64[2 * spill_capacity], may be
  *      the level-1 buffer, which is dead by then); the caller aggregates those
  *      with etl_groupby_accumulate - a key is never in both outputs.
@@ -409,8 +411,8 @@ ETL_API int etl_hash_subpartition(etl_handle* h, const int64_t* records, int32_t
 ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records, int32_t fine,
                                   const int64_t* d_fine_counts, const int64_t* d_fine_base, int32_t smem_slots,
                                   int64_t out_capacity, int64_t* out_keys, int64_t* out_rows, int64_t* out_count,
-                                  double* out_sum, int64_t* spill_records, int64_t spill_capacity,
-                                  int64_t* d_counters, void* stream);
+                                  double* out_sum, double* out_min, double* out_max, int64_t* spill_records,
+                                  int64_t spill_capacity, int64_t* d_counters, void* stream);
 
 /* The same exchange and the same two partition levels WITHOUT their count passes
  * (the Exchange + final HashAggregate under k_means.py:23-48; north-star item 4;
@@ -436,11 +438,22 @@ ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records,
  *     segments == buckets, segment b is cut into pieces b * sub .. b * sub + sub - 1
  *     of `buckets * sub` (the second level); d_cursor has buckets * sub words.
  *     max_seg_records only sizes the grid.
+ *     sources > 0 (with sub > 0): the input is what a BUCKETED exchange delivered -
+ *     slabs laid out [source][bucket], `buckets` per source; the call cuts buckets
+ *     bucket0 .. bucket0 + segments / sources - 1 (segments = that range x sources),
+ *     all sources of a bucket scattering into that bucket's `sub` pieces.
  *   etl_groupby_merge_slabs: etl_groupby_merge_partitioned over slabs: piece f =
- *     records [f * piece_capacity, + min(d_cursor[f], piece_capacity)).
- *   etl_peer_publish_counts: peer_tables[r][slot] = d_cursor[r] for every rank r
- *     (system-scope release stores; follow with a cross-rank barrier) - how a
- *     receiver learns how much of each source's slab is filled.
+ *     records [f * piece_capacity, + min(d_cursor[f], piece_capacity)), for the
+ *     pieces piece0 .. piece0 + pieces - 1; append != 0 keeps d_counters and appends
+ *     to the groups already in the output (bucket groups merged one after another
+ *     while later ones are still crossing NVLink).
+ *   etl_peer_publish_counts: peer_tables[r][slot + j] = d_cursor[r * per_rank + j]
+ *     for every rank r and j < per_rank (system-scope release stores; follow with a
+ *     cross-rank barrier) - how a receiver learns how much of each source's slabs is
+ *     filled.  ranks * per_rank <= 256.
+ *   etl_copy_async: stream-ordered device-to-device copy (copy engine; dst may be
+ *     a peer's memory) - the bucketed exchange moves whole slabs with it, so the
+ *     SMs stay with the merge of the buckets that have already arrived.
  * Overflow: a record that finds its slab full is counted in *d_overflow (int64,
  * caller-zeroed) and DROPPED.  A non-zero count means the result is incomplete:
  * repeat on the counted path (etl_hash_partition / etl_hash_subpartition), which
@@ -453,14 +466,25 @@ ETL_API int etl_slab_partition_rows(etl_handle* h, const int64_t* keys, int64_t 
                             void* stream);
 ETL_API int etl_slab_partition_records(etl_handle* h, const int64_t* records, int32_t segments, int64_t seg_capacity,
                                const int64_t* d_seg_counts, const int64_t* d_seg_prev, int64_t max_seg_records,
-                               int32_t buckets, int32_t sub, int64_t* out_records, int64_t slab_capacity,
-                               int64_t* d_cursor, int64_t* d_overflow, int32_t max_ctas, void* stream);
-ETL_API int etl_groupby_merge_slabs(etl_handle* h, const int64_t* records, int32_t fine, const int64_t* d_cursor,
-                            int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity, int64_t* out_keys,
-                            int64_t* out_rows, int64_t* out_count, double* out_sum, int64_t* spill_records,
-                            int64_t spill_capacity, int64_t* d_counters, void* stream);
-ETL_API int etl_peer_publish_counts(etl_handle* h, const int64_t* d_cursor, int32_t ranks, int64_t* const* peer_tables,
-                            int64_t slot, void* stream);
+                               int32_t buckets, int32_t sub, int32_t sources, int32_t bucket0, int64_t* out_records,
+                               int64_t slab_capacity, int64_t* d_cursor, int64_t* d_overflow, int32_t max_ctas,
+                               void* stream);
+ETL_API int etl_groupby_merge_slabs(etl_handle* h, const int64_t* records, int32_t piece0, int32_t pieces, int32_t append,
+                            const int64_t* d_cursor, int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity,
+                            int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum, double* out_min,
+                            double* out_max, int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
+                            void* stream);
+ETL_API int etl_peer_publish_counts(etl_handle* h, const int64_t* d_cursor, int32_t ranks, int32_t per_rank,
+                            int64_t* const* peer_tables, int64_t slot, void* stream);
+ETL_API int etl_copy_async(etl_handle* h, void* dst, const void* src, int64_t nbytes, void* stream);
+
+/* Diagnostic, no reference counterpart (tools/nvlink_probe.py): copy nbytes (a
+ * multiple of 16) from src to dst - dst may be a peer GPU's memory mapped here -
+ * with 16-byte stores from registers (mode 0, what the exchange scatter issues) or
+ * with bulk async stores of `chunk` bytes from shared memory (mode 1; TMA engine,
+ * no multicast).  ctas <= 0: four CTAs per SM. */
+ETL_API int etl_peer_write_probe(etl_handle* h, const void* src, void* dst, int64_t nbytes, int32_t mode, int32_t chunk,
+                         int32_t ctas, void* stream);
 
 /* ---- north-star extension: bucketing (no reference site) ------------------ */
 

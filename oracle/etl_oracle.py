@@ -188,7 +188,14 @@ def assemble_features_sparse(index: np.ndarray, num_labels: int, numerics: Seque
 
 def read_csv_columns(text: str) -> Tuple[List[str], Dict[str, List[Optional[str]]]]:
     """CSV text -> {column: [str | None]} with Spark's default null rule for
-    this data: an empty unquoted field is null (nullValue = "").  The parse
+    this data: an empty field is null (nullValue = "").  A QUOTED empty cell
+    (`a,"",b`) is null as well under the reference's default options
+    (spark_workload_to_cloud_k8s.py:48 sets none): Spark 2.4-4.0 hand univocity
+    nullValue = "" for an unquoted empty field and emptyValue = "" (the read-side
+    default) for a quoted one, so both arrive as "", and UnivocityParser
+    .nullSafeDatum turns any datum equal to nullValue into null - for string
+    columns too.  Only a non-default nullValue / emptyValue tells the two apart,
+    which is outside this path.  The parse
     itself is RFC-4180 quoting (quote ", doubled-quote escape), which is what
     both Spark's univocity settings and Python's csv agree on for input that has
     no backslash escapes - the documented input domain."""

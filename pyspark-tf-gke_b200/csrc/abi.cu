@@ -60,7 +60,7 @@ using etl::Handle;
 
 extern "C" {
 
-int etl_abi_version(void) { return 2; }
+int etl_abi_version(void) { return 3; }
 
 const char* etl_last_error(void) { return etl::g_err; }
 

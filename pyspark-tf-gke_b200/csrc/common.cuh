@@ -75,6 +75,17 @@ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     return z ^ (z >> 31);
 }
 
+// doubles as unsigned integers that sort like Spark orders doubles (for integer atomicMin / atomicMax)
+__device__ __forceinline__ uint64_t dbl_sortable(double x) {
+    if (x != x) return 0xfff8000000000000ull;  // every NaN -> one value above +inf (Spark: NaN is largest)
+    const uint64_t b = (uint64_t)__double_as_longlong(x);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dbl_from_sortable(uint64_t e) {
+    const uint64_t b = (e >> 63) ? (e & 0x7fffffffffffffffull) : ~e;
+    return __longlong_as_double((long long)b);
+}
+
 // streaming 128-bit loads: read once, keep out of L1
 __device__ __forceinline__ int4 ld_stream_v4(const void* p) {
     int4 r;

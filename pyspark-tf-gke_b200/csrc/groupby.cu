@@ -46,16 +46,6 @@ struct GroupByParams {
     unsigned long long* status;  // [0] rows that found no global slot (table full), [1] rows with the reserved key
 };
 
-__device__ __forceinline__ uint64_t dbl_sortable(double x) {
-    if (x != x) return 0xfff8000000000000ull;  // every NaN -> one value above +inf (Spark: NaN is largest)
-    const uint64_t b = (uint64_t)__double_as_longlong(x);
-    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
-}
-__device__ __forceinline__ double dbl_from_sortable(uint64_t e) {
-    const uint64_t b = (e >> 63) ? (e & 0x7fffffffffffffffull) : ~e;
-    return __longlong_as_double((long long)b);
-}
-
 __device__ __forceinline__ int64_t gb_load_key(const GroupByParams& p, int64_t i) {
     if (p.key_dtype == ETL_I64) return static_cast<const int64_t*>(p.keys)[i * p.key_stride];
     return (int64_t)static_cast<const int32_t*>(p.keys)[i * p.key_stride];

@@ -95,18 +95,21 @@ __global__ void __launch_bounds__(1024) fine_scan_kernel(const int64_t* __restri
 }
 
 // ---------------------------------------------------------------- merge
-// shared table (dynamic smem): key u64[S] | sum f64[S] | rows u32[S]
+// shared table (dynamic smem): key u64[S] | sum f64[S] | [min u64[S] | max u64[S] (MINMAX, sortable form)] | rows u32[S]
 struct MergeParams {
     const longlong2* rec;
     const int64_t* fine_base;
     const int64_t* fine_counts;
     int fine;
+    int piece0;                // first piece of this launch (pieces piece0 .. piece0 + fine - 1)
     int64_t piece_cap;         // > 0: piece f is slab f (piece_cap records apart) holding min(fine_counts[f], piece_cap) records
     int slots;                 // S, a power of two
     int64_t* out_keys;
     int64_t* out_rows;
     int64_t* out_count;
     double* out_sum;
+    double* out_min;              // MINMAX only
+    double* out_max;
     int64_t out_capacity;
     unsigned long long* groups;   // [0] groups appended (may exceed out_capacity: the caller checks)
     longlong2* spill;
@@ -115,8 +118,9 @@ struct MergeParams {
     unsigned long long* status;   // [1] records with the reserved key
 };
 
-__device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, double* ssum, uint32_t* srows,
-                                          uint32_t mask, const longlong2 r) {
+template <bool MINMAX>
+__device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, double* ssum, uint64_t* smin, uint64_t* smax,
+                                          uint32_t* srows, uint32_t mask, const longlong2 r) {
     const uint64_t key = (uint64_t)r.x;
     if (key == MG_EMPTY) {
         atomicAdd(p.status + 1, 1ull);
@@ -132,6 +136,11 @@ __device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, 
         if (cur == MG_EMPTY || cur == key) {
             atomicAdd(srows + s, 1u);
             atomicAdd(ssum + s, __longlong_as_double(r.y));
+            if (MINMAX) {
+                const unsigned long long e = dbl_sortable(__longlong_as_double(r.y));
+                atomicMin(reinterpret_cast<unsigned long long*>(smin + s), e);
+                atomicMax(reinterpret_cast<unsigned long long*>(smax + s), e);
+            }
             return;
         }
         s = (s + 1) & mask;
@@ -140,17 +149,20 @@ __device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, 
     if ((int64_t)at < p.spill_capacity) p.spill[at] = r;
 }
 
-__global__ void __launch_bounds__(MG_THREADS, 2) groupby_merge_kernel(const MergeParams p) {
+template <bool MINMAX>
+__global__ void __launch_bounds__(MG_THREADS, MINMAX ? 1 : 2) groupby_merge_kernel(const MergeParams p) {
     extern __shared__ __align__(16) unsigned char mg_smem[];
     const int S = p.slots;
     uint64_t* skey = reinterpret_cast<uint64_t*>(mg_smem);
     double* ssum = reinterpret_cast<double*>(skey + S);
-    uint32_t* srows = reinterpret_cast<uint32_t*>(ssum + S);
+    uint64_t* smin = reinterpret_cast<uint64_t*>(ssum + S);
+    uint64_t* smax = smin + (MINMAX ? S : 0);
+    uint32_t* srows = reinterpret_cast<uint32_t*>(smax + (MINMAX ? S : 0));
     __shared__ unsigned s_warp[MG_THREADS / 32];
     __shared__ unsigned long long s_base;
     const uint32_t mask = (uint32_t)S - 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int f = blockIdx.x; f < p.fine; f += gridDim.x) {
+    for (int f = p.piece0 + blockIdx.x; f < p.piece0 + p.fine; f += gridDim.x) {
         int64_t lo, cnt;
         if (p.piece_cap > 0) {
             lo = (int64_t)f * p.piece_cap;
@@ -164,6 +176,7 @@ __global__ void __launch_bounds__(MG_THREADS, 2) groupby_merge_kernel(const Merg
             skey[i] = MG_EMPTY;
             ssum[i] = 0.0;
             srows[i] = 0u;
+            if (MINMAX) { smin[i] = ~0ull; smax[i] = 0ull; }
         }
         __syncthreads();
         const longlong2* rec = p.rec + lo;
@@ -173,9 +186,9 @@ __global__ void __launch_bounds__(MG_THREADS, 2) groupby_merge_kernel(const Merg
 #pragma unroll
             for (int j = 0; j < MG_UNROLL; ++j) r[j] = ld_record(rec + i + j * MG_THREADS);
 #pragma unroll
-            for (int j = 0; j < MG_UNROLL; ++j) merge_one(p, skey, ssum, srows, mask, r[j]);
+            for (int j = 0; j < MG_UNROLL; ++j) merge_one<MINMAX>(p, skey, ssum, smin, smax, srows, mask, r[j]);
         }
-        for (; i < cnt; i += MG_THREADS) merge_one(p, skey, ssum, srows, mask, ld_record(rec + i));
+        for (; i < cnt; i += MG_THREADS) merge_one<MINMAX>(p, skey, ssum, smin, smax, srows, mask, ld_record(rec + i));
         __syncthreads();
         // append the used slots: count per warp, one global atomic per CTA, then warp-ordered writes
         unsigned mine = 0;
@@ -202,6 +215,10 @@ __global__ void __launch_bounds__(MG_THREADS, 2) groupby_merge_kernel(const Merg
                 p.out_rows[g] = rows;
                 p.out_count[g] = rows;   // records carry no nulls: count(value) = rows
                 p.out_sum[g] = ssum[s];
+                if (MINMAX) {
+                    p.out_min[g] = dbl_from_sortable(smin[s]);
+                    p.out_max[g] = dbl_from_sortable(smax[s]);
+                }
             }
             run += __popc(bal);
         }
@@ -257,41 +274,48 @@ extern "C" int etl_hash_subpartition(etl_handle* hh, const int64_t* records, int
     return ETL_OK;
 }
 
-static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t fine, const int64_t* d_fine_counts,
-                        const int64_t* d_fine_base, int64_t piece_cap, int32_t smem_slots, int64_t out_capacity,
-                        int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum, int64_t* spill_records,
-                        int64_t spill_capacity, int64_t* d_counters, void* stream_) {
+static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t piece0, int32_t fine, bool append,
+                        const int64_t* d_fine_counts, const int64_t* d_fine_base, int64_t piece_cap, int32_t smem_slots,
+                        int64_t out_capacity,
+                        int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum, double* out_min,
+                        double* out_max, int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters, void* stream_) {
     ETL_REQUIRE(hh && d_fine_counts && (d_fine_base || piece_cap > 0) && d_counters, "groupby_merge_partitioned: NULL argument");
-    ETL_REQUIRE(fine >= 1 && fine <= 65536, "groupby_merge_partitioned: fine=%d not in 1..65536", fine);
+    ETL_REQUIRE(fine >= 1 && piece0 >= 0 && piece0 + fine <= 65536, "groupby_merge_partitioned: pieces %d..%d not in 0..65536",
+                piece0, piece0 + fine);
     ETL_REQUIRE(smem_slots >= 64 && smem_slots <= 8192 && (smem_slots & (smem_slots - 1)) == 0,
                 "groupby_merge_partitioned: smem_slots=%d must be a power of two in 64..8192", smem_slots);
     ETL_REQUIRE(out_capacity >= 0 && spill_capacity >= 0, "groupby_merge_partitioned: negative capacity");
     ETL_REQUIRE(out_capacity == 0 || (out_keys && out_rows && out_count && out_sum),
                 "groupby_merge_partitioned: NULL output array");
+    ETL_REQUIRE((out_min == nullptr) == (out_max == nullptr), "groupby_merge_partitioned: out_min and out_max go together");
+    const bool minmax = out_min != nullptr;
+    ETL_REQUIRE(!minmax || smem_slots <= 4096, "groupby_merge_partitioned: with min / max at most 4096 slots fit");
     ETL_REQUIRE(spill_capacity == 0 || (spill_records && etl::aligned16(spill_records)),
                 "groupby_merge_partitioned: NULL or misaligned spill buffer");
     Handle* h = reinterpret_cast<Handle*>(hh);
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     ETL_CUDA(cudaSetDevice(h->device));
-    ETL_CUDA(cudaMemsetAsync(d_counters, 0, 4 * sizeof(int64_t), stream));
+    if (!append) ETL_CUDA(cudaMemsetAsync(d_counters, 0, 4 * sizeof(int64_t), stream));
     ETL_REQUIRE(records == nullptr || etl::aligned16(records), "groupby_merge_partitioned: misaligned records");
     if (!records) return ETL_OK;
     etl::MergeParams p{};
     p.rec = reinterpret_cast<const longlong2*>(records);
-    p.fine_base = d_fine_base; p.fine_counts = d_fine_counts; p.fine = fine; p.slots = smem_slots; p.piece_cap = piece_cap;
+    p.fine_base = d_fine_base; p.fine_counts = d_fine_counts; p.fine = fine; p.piece0 = piece0; p.slots = smem_slots; p.piece_cap = piece_cap;
     p.out_keys = out_keys; p.out_rows = out_rows; p.out_count = out_count; p.out_sum = out_sum;
+    p.out_min = out_min; p.out_max = out_max;
     p.out_capacity = out_capacity;
     unsigned long long* ctr = reinterpret_cast<unsigned long long*>(d_counters);
     p.groups = ctr; p.spilled = ctr + 1; p.status = ctr + 2;   // status[1] = ctr[3]: reserved-key records
     p.spill = reinterpret_cast<longlong2*>(spill_records); p.spill_capacity = spill_capacity;
-    const size_t smem = (size_t)smem_slots * 20;
-    ETL_CUDA(cudaFuncSetAttribute(etl::groupby_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = (size_t)smem_slots * (minmax ? 36 : 20);
+    auto kern = minmax ? etl::groupby_merge_kernel<true> : etl::groupby_merge_kernel<false>;
+    ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int occ = 0;
-    ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, etl::groupby_merge_kernel, etl::MG_THREADS, smem));
+    ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, etl::MG_THREADS, smem));
     if (occ < 1) occ = 1;
     int64_t blocks = (int64_t)h->sm_count * occ;
     if (blocks > fine) blocks = fine;
-    etl::groupby_merge_kernel<<<(unsigned)blocks, etl::MG_THREADS, smem, stream>>>(p);
+    kern<<<(unsigned)blocks, etl::MG_THREADS, smem, stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }
@@ -299,20 +323,20 @@ static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t fine, co
 extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* records, int32_t fine,
                                              const int64_t* d_fine_counts, const int64_t* d_fine_base,
                                              int32_t smem_slots, int64_t out_capacity, int64_t* out_keys,
-                                             int64_t* out_rows, int64_t* out_count, double* out_sum,
-                                             int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
-                                             void* stream_) {
+                                             int64_t* out_rows, int64_t* out_count, double* out_sum, double* out_min,
+                                             double* out_max, int64_t* spill_records, int64_t spill_capacity,
+                                             int64_t* d_counters, void* stream_) {
     ETL_REQUIRE(d_fine_base != nullptr, "groupby_merge_partitioned: NULL argument");
-    return merge_pieces(hh, records, fine, d_fine_counts, d_fine_base, 0, smem_slots, out_capacity, out_keys, out_rows,
-                        out_count, out_sum, spill_records, spill_capacity, d_counters, stream_);
+    return merge_pieces(hh, records, 0, fine, false, d_fine_counts, d_fine_base, 0, smem_slots, out_capacity, out_keys, out_rows,
+                        out_count, out_sum, out_min, out_max, spill_records, spill_capacity, d_counters, stream_);
 }
 
-extern "C" int etl_groupby_merge_slabs(etl_handle* hh, const int64_t* records, int32_t fine, const int64_t* d_cursor,
-                                       int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity,
+extern "C" int etl_groupby_merge_slabs(etl_handle* hh, const int64_t* records, int32_t piece0, int32_t pieces, int32_t append,
+                                       const int64_t* d_cursor, int64_t piece_capacity, int32_t smem_slots, int64_t out_capacity,
                                        int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum,
-                                       int64_t* spill_records, int64_t spill_capacity, int64_t* d_counters,
-                                       void* stream_) {
+                                       double* out_min, double* out_max, int64_t* spill_records, int64_t spill_capacity,
+                                       int64_t* d_counters, void* stream_) {
     ETL_REQUIRE(piece_capacity > 0, "groupby_merge_slabs: piece_capacity must be > 0");
-    return merge_pieces(hh, records, fine, d_cursor, nullptr, piece_capacity, smem_slots, out_capacity, out_keys, out_rows,
-                        out_count, out_sum, spill_records, spill_capacity, d_counters, stream_);
+    return merge_pieces(hh, records, piece0, pieces, append != 0, d_cursor, nullptr, piece_capacity, smem_slots, out_capacity, out_keys, out_rows,
+                        out_count, out_sum, out_min, out_max, spill_records, spill_capacity, d_counters, stream_);
 }

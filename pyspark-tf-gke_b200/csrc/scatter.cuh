@@ -67,6 +67,11 @@ struct ScatterJob {
     int64_t seg_cap;            // > 0: segment s = slab s of the input (seg_cap records apart), counts clamped to seg_cap
     const int64_t* seg_prev;    // optional [segments]: records of the segment consumed by earlier launches
     int shared_dest;            // 1: all segments scatter into the same `parts` destinations (cursor / slabs not per segment)
+    // second level over what a bucketed exchange delivered: the input slabs are laid out [source][bucket]
+    // (seg_bucket_stride buckets per source); grid.y walks (bucket, source) pairs: segment y is slab
+    // (y % seg_sources) * seg_bucket_stride + seg_bucket0 + y / seg_sources and belongs to bucket
+    // seg_bucket0 + y / seg_sources, whose `parts` pieces all its sources share.  seg_sources == 0: off.
+    int seg_sources, seg_bucket0, seg_bucket_stride;
     int64_t slab_origin, slab_stride, dest_cap;
     unsigned long long* overflow;   // [0] += records that found no room in their slab
 };
@@ -85,7 +90,12 @@ __global__ void __launch_bounds__(THREADS, TILE <= 2048 ? 3 : 1) scatter_pipelin
     unsigned* s_lim = s_off + PART_MAX;     // SLAB: sorted positions >= s_lim[d] of destination d found no room
     long long* s_delta = reinterpret_cast<long long*>(s_lim + PART_MAX);
     uint64_t* bar = reinterpret_cast<uint64_t*>(s_delta + PART_MAX);
-    const int seg = blockIdx.y;
+    int seg = blockIdx.y;       // input segment (slab) ...
+    int group = seg;            // ... and the destination group it scatters into
+    if (SLAB && job.seg_sources > 0) {
+        group = job.seg_bucket0 + seg / job.seg_sources;
+        seg = (seg % job.seg_sources) * job.seg_bucket_stride + group;
+    }
     int64_t lo, cnt;
     if (SLAB && job.seg_cap > 0) {
         int64_t prev = job.seg_prev ? job.seg_prev[seg] : 0, cur = job.seg_counts[seg];
@@ -98,8 +108,8 @@ __global__ void __launch_bounds__(THREADS, TILE <= 2048 ? 3 : 1) scatter_pipelin
         cnt = job.seg_counts ? job.seg_counts[seg] : job.n;
     }
     const int64_t tiles = (cnt + TILE - 1) / TILE;
-    const size_t d0 = (SLAB && job.shared_dest) ? 0 : (size_t)seg * job.parts;
-    const unsigned sub0 = (unsigned)seg * (unsigned)job.sub;
+    const size_t d0 = (SLAB && job.shared_dest) ? 0 : (size_t)group * job.parts;
+    const unsigned sub0 = (unsigned)group * (unsigned)job.sub;
     const int parts = job.parts;
     if (threadIdx.x == 0) {
         mbar_init(bar, 1);
@@ -235,7 +245,20 @@ static inline cudaError_t launch_scatter_variant(int sm_count, const ScatterJob&
     const int64_t tiles = (max_rows + TILE - 1) / TILE;
     int64_t total = (int64_t)sm_count * per_sm;
     if (max_ctas > 0 && max_ctas < total) total = max_ctas;
+    // CTAs per segment: with several segments (the second level: one per bucket) the grid is segments x gx CTAs
+    // of equal work, so gx is chosen to fill whole waves of the `total` CTAs that are resident at a time - 256
+    // segments x 1 CTA on 148 SMs would run as one full wave and one 73 % empty one
     int64_t gx = (total + segments - 1) / segments;
+    if (segments > 1) {
+        double best = 0.0;
+        const int64_t g0 = gx;
+        for (int64_t g = g0; g <= g0 + 80 && g <= tiles; ++g) {
+            const int64_t ctas = g * segments, waves = (ctas + total - 1) / total;
+            const double eff = (double)ctas / (double)(waves * total);
+            if (eff > best + 1e-9) { best = eff; gx = g; }
+            if (eff > 0.995) break;
+        }
+    }
     if (gx > tiles) gx = tiles;
     if (gx < 1) gx = 1;
     const dim3 grid((unsigned)gx, (unsigned)segments);

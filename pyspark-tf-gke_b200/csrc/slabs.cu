@@ -20,12 +20,61 @@
 
 namespace etl {
 
-__global__ void publish_counts_kernel(const int64_t* __restrict__ cursor, int ranks, PartDest tables, int64_t slot) {
-    const int r = threadIdx.x;
-    if (r < ranks) {
+__global__ void publish_counts_kernel(const int64_t* __restrict__ cursor, int ranks, int per_rank, PartDest tables, int64_t slot) {
+    const int i = threadIdx.x;            // cursor index = rank * per_rank + j  ->  tables[rank][slot + j]
+    if (i < ranks * per_rank) {
         // system-scope release store: ordered after this stream's earlier peer stores by the kernel boundary
-        asm volatile("st.release.sys.global.s64 [%0], %1;" ::"l"(tables.base[r] + slot), "l"(cursor[r]) : "memory");
+        asm volatile("st.release.sys.global.s64 [%0], %1;" ::"l"(tables.base[i / per_rank] + slot + i % per_rank), "l"(cursor[i])
+                     : "memory");
     }
+}
+
+// ---- NVLink write probe (tools/nvlink_probe.py): how fast can one GPU push a buffer into a peer's memory
+//      with (0) 16-byte stores from registers - what the exchange scatter does - or (1) bulk async stores of
+//      `chunk` bytes from shared memory (TMA engine, no tensor map, no multicast)?
+__global__ void __launch_bounds__(256) peer_write_plain_kernel(const longlong2* __restrict__ src, longlong2* dst, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+__device__ __forceinline__ void bulk_store(void* gmem_dst, const void* smem_src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+
+constexpr int PROBE_TILE = 32768;
+__global__ void __launch_bounds__(32) peer_write_bulk_kernel(const unsigned char* __restrict__ src, unsigned char* dst, int64_t nbytes,
+                                                             unsigned chunk) {
+    extern __shared__ __align__(128) unsigned char pb_smem[];
+    __shared__ uint64_t bar[2];
+    if (threadIdx.x != 0) return;
+    mbar_init(bar, 1);
+    mbar_init(bar + 1, 1);
+    mbar_init_fence();
+    const int64_t tiles = (nbytes + PROBE_TILE - 1) / PROBE_TILE;
+    auto issue = [&](int64_t t, int buf) {
+        const int64_t left = nbytes - t * PROBE_TILE;
+        const unsigned bytes = left < PROBE_TILE ? (unsigned)left : (unsigned)PROBE_TILE;
+        mbar_arrive_expect_tx(bar + buf, bytes);
+        bulk_load(pb_smem + buf * PROBE_TILE, src + t * PROBE_TILE, bytes, bar + buf);
+    };
+    int64_t t = blockIdx.x;
+    if (t < tiles) issue(t, 0);
+    for (int it = 0; t < tiles; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        // the other buffer is free once the stores issued from it two iterations ago have read it
+        bulk_wait_read<0>();
+        if (t + gridDim.x < tiles) issue(t + gridDim.x, buf ^ 1);
+        mbar_wait(bar + buf, (unsigned)(it >> 1) & 1u);
+        const int64_t left = nbytes - t * PROBE_TILE;
+        const unsigned bytes = left < PROBE_TILE ? (unsigned)left : (unsigned)PROBE_TILE;
+        for (unsigned o = 0; o < bytes; o += chunk)
+            bulk_store(dst + t * PROBE_TILE + o, pb_smem + buf * PROBE_TILE + o, bytes - o < chunk ? bytes - o : chunk);
+        bulk_commit();
+    }
+    bulk_wait_read<0>();
 }
 
 }  // namespace etl
@@ -69,15 +118,19 @@ extern "C" int etl_slab_partition_rows(etl_handle* hh, const int64_t* keys, int6
 
 extern "C" int etl_slab_partition_records(etl_handle* hh, const int64_t* records, int32_t segments, int64_t seg_capacity,
                                           const int64_t* d_seg_counts, const int64_t* d_seg_prev, int64_t max_seg_records,
-                                          int32_t buckets, int32_t sub, int64_t* out_records, int64_t slab_capacity,
-                                          int64_t* d_cursor, int64_t* d_overflow, int32_t max_ctas, void* stream_) {
+                                          int32_t buckets, int32_t sub, int32_t sources, int32_t bucket0,
+                                          int64_t* out_records, int64_t slab_capacity, int64_t* d_cursor,
+                                          int64_t* d_overflow, int32_t max_ctas, void* stream_) {
     ETL_REQUIRE(hh && d_seg_counts && d_cursor && d_overflow, "slab_partition_records: NULL argument");
     ETL_REQUIRE(segments >= 1 && segments <= 65535 && seg_capacity >= 1 && slab_capacity >= 1 && max_seg_records >= 0,
                 "slab_partition_records: bad segments / capacities");
     ETL_REQUIRE(buckets >= 1 && sub >= 0 && sub <= etl::PART_MAX && (sub > 0 || buckets <= etl::PART_MAX),
                 "slab_partition_records: buckets=%d sub=%d", buckets, sub);
-    ETL_REQUIRE(sub == 0 || (segments == buckets && (int64_t)buckets * sub <= 65536),
-                "slab_partition_records: the second level needs segments == buckets and buckets x sub <= 65536");
+    ETL_REQUIRE(sources >= 0 && bucket0 >= 0, "slab_partition_records: sources / bucket0 < 0");
+    ETL_REQUIRE(sub == 0 || (int64_t)buckets * sub <= 65536, "slab_partition_records: buckets x sub must be <= 65536");
+    ETL_REQUIRE(sub == 0 || (sources == 0 ? segments == buckets : (segments % sources == 0 && bucket0 + segments / sources <= buckets)),
+                "slab_partition_records: the second level needs segments == buckets, or sources x (a range of buckets)");
+    ETL_REQUIRE(sub > 0 || sources == 0, "slab_partition_records: a [source][bucket] input is a second-level input");
     if (max_seg_records == 0) return ETL_OK;
     ETL_REQUIRE(records && out_records && etl::aligned16(records) && etl::aligned16(out_records),
                 "slab_partition_records: NULL or misaligned record buffer");
@@ -93,6 +146,7 @@ extern "C" int etl_slab_partition_records(etl_handle* hh, const int64_t* records
         job.ranks = 1; job.buckets = buckets; job.parts = buckets; job.shared_dest = 1;
     } else {
         job.sub = sub; job.fine = (unsigned)(buckets * sub); job.parts = sub;
+        job.seg_sources = sources; job.seg_bucket0 = bucket0; job.seg_bucket_stride = buckets;
     }
     etl::PartDest dst;
     for (int d = 0; d < etl::PART_MAX; ++d) dst.base[d] = out_records;
@@ -100,10 +154,11 @@ extern "C" int etl_slab_partition_records(etl_handle* hh, const int64_t* records
     return ETL_OK;
 }
 
-extern "C" int etl_peer_publish_counts(etl_handle* hh, const int64_t* d_cursor, int32_t ranks, int64_t* const* peer_tables,
-                                       int64_t slot, void* stream_) {
+extern "C" int etl_peer_publish_counts(etl_handle* hh, const int64_t* d_cursor, int32_t ranks, int32_t per_rank,
+                                       int64_t* const* peer_tables, int64_t slot, void* stream_) {
     ETL_REQUIRE(hh && d_cursor && peer_tables, "peer_publish_counts: NULL argument");
-    ETL_REQUIRE(ranks >= 1 && ranks <= etl::PART_MAX && slot >= 0, "peer_publish_counts: ranks=%d slot=%lld", ranks, (long long)slot);
+    ETL_REQUIRE(ranks >= 1 && per_rank >= 1 && (int64_t)ranks * per_rank <= etl::PART_MAX && slot >= 0,
+                "peer_publish_counts: ranks=%d per_rank=%d slot=%lld", ranks, per_rank, (long long)slot);
     Handle* h = reinterpret_cast<Handle*>(hh);
     etl::PartDest t;
     for (int d = 0; d < etl::PART_MAX; ++d) t.base[d] = nullptr;
@@ -112,7 +167,41 @@ extern "C" int etl_peer_publish_counts(etl_handle* hh, const int64_t* d_cursor, 
         t.base[r] = peer_tables[r];
     }
     ETL_CUDA(cudaSetDevice(h->device));
-    etl::publish_counts_kernel<<<1, etl::PART_MAX, 0, static_cast<cudaStream_t>(stream_)>>>(d_cursor, ranks, t, slot);
+    etl::publish_counts_kernel<<<1, etl::PART_MAX, 0, static_cast<cudaStream_t>(stream_)>>>(d_cursor, ranks, per_rank, t, slot);
     ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+// Diagnostic (no reference counterpart): push nbytes (a multiple of 16) from src (local) to dst (peer or local)
+// with 16-byte register stores (mode 0) or bulk async stores of `chunk` bytes (mode 1; chunk a multiple of 16).
+extern "C" int etl_peer_write_probe(etl_handle* hh, const void* src, void* dst, int64_t nbytes, int32_t mode, int32_t chunk,
+                                    int32_t ctas, void* stream_) {
+    ETL_REQUIRE(hh && src && dst && nbytes >= 0 && (nbytes & 15) == 0 && etl::aligned16(src) && etl::aligned16(dst),
+                "peer_write_probe: bad buffers");
+    ETL_REQUIRE(mode == 0 || (mode == 1 && chunk >= 16 && (chunk & 15) == 0), "peer_write_probe: mode=%d chunk=%d", mode, chunk);
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    ETL_CUDA(cudaSetDevice(h->device));
+    if (nbytes == 0) return ETL_OK;
+    if (ctas <= 0) ctas = h->sm_count * 4;
+    if (mode == 0) {
+        etl::peer_write_plain_kernel<<<ctas, 256, 0, stream>>>(static_cast<const longlong2*>(src), static_cast<longlong2*>(dst),
+                                                                nbytes / 16);
+    } else {
+        ETL_CUDA(cudaFuncSetAttribute(etl::peer_write_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * etl::PROBE_TILE));
+        etl::peer_write_bulk_kernel<<<ctas, 32, 2 * etl::PROBE_TILE, stream>>>(static_cast<const unsigned char*>(src),
+                                                                               static_cast<unsigned char*>(dst), nbytes, (unsigned)chunk);
+    }
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+// Stream-ordered copy (copy engine): how the bucketed exchange moves a rank's slabs into a peer's receive
+// buffer without occupying SMs.  dst may be peer memory mapped into this process.
+extern "C" int etl_copy_async(etl_handle* hh, void* dst, const void* src, int64_t nbytes, void* stream_) {
+    ETL_REQUIRE(hh && nbytes >= 0 && (nbytes == 0 || (dst && src)), "copy_async: bad argument");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    if (nbytes) ETL_CUDA(cudaMemcpyAsync(dst, src, (size_t)nbytes, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream_)));
     return ETL_OK;
 }

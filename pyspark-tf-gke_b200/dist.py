@@ -227,6 +227,138 @@ class SlabExchange:
             mark("level1")
 
 
+class BucketExchange:
+    """The exchange as: partition locally by (destination rank, bucket), move the
+    slabs bucket group by bucket group with the copy engines, merge each group of
+    buckets as soon as it has arrived - NVLink is the only exposed cost.
+
+    Sender: ONE slab scatter (etl_slab_partition_rows, 4096-row tiles, all SMs) cuts
+    this rank's rows into ranks x Bx slabs of a local send buffer, destination-rank
+    major - the receiver's first partition level is done here, at full HBM speed,
+    with no NVLink store in the kernel.  The cursors go to the receivers' count
+    tables (etl_peer_publish_counts).  Then, for each of G groups of buckets, the
+    group's slabs are copied into every receiver's buffer (layout [source][bucket],
+    symmetric memory) with stream-ordered peer copies (etl_copy_async: copy engines,
+    no SMs), followed by a symmetric-memory barrier.
+    Receiver: after the barrier of group g it cuts the group's buckets into pieces
+    (etl_slab_partition_records over the (bucket, source) slabs) and merges them in
+    shared memory (etl_groupby_merge_slabs, append mode) on a compute stream while
+    group g + 1 is still crossing NVLink.  No count pass, no all-gather, nothing
+    read back by the host.
+
+    A slab that overflows (skewed keys) only counts the surplus; the result object
+    then repeats the exchange on the counted path (PeerExchange)."""
+
+    def __init__(self, eng, rows_per_rank: int, groups_hint: int, bucket_groups: int = 8, group=None, copy_streams: int = 4):
+        import os
+        import torch.distributed._symmetric_memory as symm
+
+        self.eng = eng
+        self.group = group or dist.group.WORLD
+        self.rank, self.size = dist.get_rank(self.group), dist.get_world_size(self.group)
+        size = self.size
+        self.rows_per_rank = int(rows_per_rank)
+        total = self.rows_per_rank * size
+        g = max(1, min(groups_hint if groups_hint > 0 else total, total))
+        self.rows_per_key = max(1.0, total / g)
+        hint = -(-g // size) + g // (8 * size)                       # distinct keys this rank may end up owning
+        fine = max(1, -(-hint // eng.MERGE_GROUPS_PER_PIECE))
+        bx = 1
+        while bx * 2 * size <= 256 and bx < fine:
+            bx *= 2
+        self.buckets = bx                                            # Bx buckets per rank (a power of two)
+        self.sub = min(256, max(1, -(-fine // bx)))
+        self.bucket_groups = max(1, min(int(os.environ.get("ETL_BUCKET_GROUPS", bucket_groups)), bx))
+        while bx % self.bucket_groups:
+            self.bucket_groups -= 1
+        self.slab = eng.slab_capacity(self.rows_per_rank / (size * bx), self.rows_per_key)
+        self.cap2 = eng.slab_capacity(self.rows_per_rank / (bx * self.sub), self.rows_per_key)
+        dev = eng.device
+        self.send = torch.empty((size * bx * self.slab, 2), dtype=torch.int64, device=dev)
+        self.recv = symm.empty((size * bx * self.slab, 2), dtype=torch.int64, device=dev)
+        self.handle = symm.rendezvous(self.recv, self.group.group_name)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.counts = symm.empty(size * bx, dtype=torch.int64, device=dev)
+        self.counts_handle = symm.rendezvous(self.counts, self.group.group_name)
+        self.count_ptrs = [int(p) for p in self.counts_handle.buffer_ptrs]
+        self.pieces = torch.empty((bx * self.sub * self.cap2, 2), dtype=torch.int64, device=dev)
+        self.copy_streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, int(os.environ.get("ETL_COPY_STREAMS", copy_streams))))]
+        self.sync_stream = torch.cuda.Stream(device=dev)
+        self.compute = torch.cuda.Stream(device=dev)
+        self._counted: Optional[PeerExchange] = None
+
+    chunks = 1   # device-resident rows need no chunking here (shuffle_groupby_sum_host brings its own chunks)
+
+    def counted(self) -> "PeerExchange":
+        if self._counted is None:
+            self._counted = PeerExchange(self.eng, int(self.rows_per_rank * 1.5) + (1 << 20), group=self.group)
+        return self._counted
+
+    def any_overflow(self, local: int) -> int:
+        t = torch.tensor([int(local)], dtype=torch.int64, device=self.eng.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return int(t.item())
+
+    def shuffle(self, chunk_iter, capacity: int, minmax: bool = False, mark=None):
+        """chunk_iter yields (keys, vals, n, ready_event or None) device chunks of this rank's rows
+        -> PartitionedGroups of the keys this rank owns (enqueued; main stream waits for the merge)."""
+        eng, size, rank, bx, slab = self.eng, self.size, self.rank, self.buckets, self.slab
+        mark = mark or (lambda name: None)
+        main = torch.cuda.current_stream(eng.device)
+        pg = eng.new_partitioned_groups(capacity, max(self.rows_per_rank // 8, 1 << 16), bx * self.sub, minmax=minmax)
+        xcur = torch.zeros(size * bx, dtype=torch.int64, device=eng.device)
+        cur2 = torch.zeros(bx * self.sub, dtype=torch.int64, device=eng.device)
+        mark("init")
+        self.handle.barrier()            # every rank has finished reading the previous exchange's records
+        send_ptr = self.send.data_ptr()
+        for keys, vals, n, ready in chunk_iter:
+            if ready is not None:
+                main.wait_event(ready)
+            eng.slab_partition_rows(keys, vals, n, size, bx, [send_ptr] * size, 0, slab, slab, xcur, pg.counters[4:])
+        eng.peer_publish_counts(xcur, self.count_ptrs, rank * bx, per_rank=bx)
+        partitioned = torch.cuda.Event()
+        partitioned.record(main)
+        mark("partition")
+        for st in self.copy_streams + [self.sync_stream, self.compute]:
+            st.wait_event(partitioned)
+        bpg = bx // self.bucket_groups
+        nbytes = bpg * slab * 16
+        k = 0
+        for g in range(self.bucket_groups):
+            copied = []
+            for i in range(size):
+                r = (rank + 1 + i) % size             # every rank starts with a different peer
+                st = self.copy_streams[k % len(self.copy_streams)]
+                k += 1
+                with torch.cuda.stream(st):
+                    eng.copy_async(self.peer_ptrs[r] + ((rank * bx + g * bpg) * slab) * 16,
+                                   send_ptr + ((r * bx + g * bpg) * slab) * 16, nbytes)
+                    ev = torch.cuda.Event()
+                    ev.record(st)
+                    copied.append(ev)
+            with torch.cuda.stream(self.sync_stream):
+                for ev in copied:
+                    self.sync_stream.wait_event(ev)
+                self.handle.barrier()     # group g of every source (and, the first time, the count tables) has landed here
+                landed = torch.cuda.Event()
+                landed.record(self.sync_stream)
+            with torch.cuda.stream(self.compute):
+                self.compute.wait_event(landed)
+                eng.slab_partition_records(self.recv, bpg * size, slab, self.counts, None, slab, bx, self.sub, self.pieces,
+                                           self.cap2, cur2, pg.counters[4:], sources=size, bucket0=g * bpg)
+                eng.merge_slab_pieces(self.pieces, cur2, self.cap2, g * bpg * self.sub, bpg * self.sub, g > 0, pg)
+        done = torch.cuda.Event()
+        done.record(self.sync_stream)
+        main.wait_event(done)
+        mark("exchange")
+        mark("level1")
+        main.wait_stream(self.compute)
+        mark("level2")
+        mark("merge")
+        pg.any_overflow = self.any_overflow
+        return pg
+
+
 def peer_layout(matrix: torch.Tensor, rank: int, size: int, buckets: int):
     """Layout of the receive buffers of a bucketed peer exchange.  matrix[s, r * buckets + b]
     = records source s sends to (rank r, bucket b).  A receive buffer holds its buckets one
@@ -251,7 +383,8 @@ def choose_buckets(capacity: int, world_size: int, entry_bytes: int = 32, slice_
 
 def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: int, groups_hint: int = 1 << 30,
                         buckets: Optional[int] = None, group=None, mark=None, peer: Optional[PeerExchange] = None,
-                        merge: str = "smem", exchange_buckets: Optional[int] = None, counted: bool = False):
+                        merge: str = "smem", exchange_buckets: Optional[int] = None, counted: bool = False,
+                        minmax: bool = False):
     """Config 4: hash-partition -> all-to-all -> local final merge.
 
     Default path (merge="smem", groups_hint > 0, one GPU or peer = a SlabExchange):
@@ -288,11 +421,11 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     mark = mark or (lambda name: None)
     if merge not in ("smem", "table"):
         raise ValueError(f"merge={merge!r}")
-    if merge == "smem" and not counted and groups_hint > 0 and (size == 1 or isinstance(peer, SlabExchange)):
-        return _slab_shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer, mark, group)
-    if isinstance(peer, SlabExchange):
+    if merge == "smem" and not counted and groups_hint > 0 and (size == 1 or isinstance(peer, (SlabExchange, BucketExchange))):
+        return _slab_shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer, mark, group, minmax=minmax)
+    if isinstance(peer, (SlabExchange, BucketExchange)):
         peer = peer.counted()
-    gt = eng.groupby_new(capacity, 1, minmax=False) if merge == "table" else None
+    gt = eng.groupby_new(capacity, 1, minmax=minmax) if merge == "table" else None
     B = choose_buckets(capacity, 1) if buckets is None else buckets
     mark("init")
     if size > 1:
@@ -309,7 +442,7 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
             mark("level1")
             # the receive buffer is overwritten by the next exchange: spilled records get their own room
             spill = torch.empty((max(m // 8, 1 << 16), 2), dtype=torch.int64, device=eng.device)
-            pg = eng.groupby_merge_buckets(received, bcounts, bbase, B, sub, m, capacity, mark=mark, spill=spill)
+            pg = eng.groupby_merge_buckets(received, bcounts, bbase, B, sub, m, capacity, mark=mark, spill=spill, minmax=minmax)
             mark("merge")
             return pg
         if peer is not None:
@@ -330,7 +463,7 @@ def shuffle_groupby_sum(eng, keys: torch.Tensor, vals: torch.Tensor, capacity: i
     if merge == "smem":
         local_hint = -(-groups_hint // size) + (groups_hint // (8 * size) if size > 1 else 0) if groups_hint > 0 else 0
         pg = eng.groupby_partitioned_sum(rk, rv, capacity, groups_hint=local_hint, n=m, key_stride=stride, val_stride=stride,
-                                         mark=mark)
+                                         mark=mark, minmax=minmax)
         mark("merge")
         return pg
     if B == 1 or m == 0:
@@ -354,7 +487,7 @@ def _device_chunks(keys: torch.Tensor, vals: torch.Tensor, chunks: int):
 
 
 def _slab_shuffle_groupby_sum(eng, keys, vals, capacity: int, groups_hint: int, peer, mark, group, chunk_iter=None,
-                              n_local: Optional[int] = None):
+                              n_local: Optional[int] = None, minmax: bool = False):
     """The slab path of shuffle_groupby_sum (see there).  chunk_iter: this rank's rows
     as device chunks (shuffle_groupby_sum_host feeds them as they arrive from the host)."""
     rank, size = world()
@@ -362,7 +495,7 @@ def _slab_shuffle_groupby_sum(eng, keys, vals, capacity: int, groups_hint: int, 
         for name in ("init", "partition", "exchange"):
             mark(name)
         if chunk_iter is None:
-            pg = eng.groupby_slab_sum(keys, vals, capacity, groups_hint, mark=mark)
+            pg = eng.groupby_slab_sum(keys, vals, capacity, groups_hint, mark=mark, minmax=minmax)
             mark("merge")
             return pg
         n = n_local
@@ -376,8 +509,14 @@ def _slab_shuffle_groupby_sum(eng, keys, vals, capacity: int, groups_hint: int, 
                 main.wait_event(ready)
             eng.slab_partition_rows(k, v, m, 1, buckets, [level1.data_ptr()], 0, cap1, cap1, cur1, counters[4:])
         mark("level1")
-        pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark)
+        pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark, minmax=minmax)
         mark("merge")
+        return pg
+    if isinstance(peer, BucketExchange):
+        pg = peer.shuffle(chunk_iter if chunk_iter is not None else _device_chunks(keys, vals, 1), capacity, minmax=minmax, mark=mark)
+        if keys is not None:
+            pg.rerun = lambda: shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer=peer.counted(), group=group,
+                                                   counted=True, minmax=minmax)
         return pg
     n = keys.shape[0] if n_local is None else n_local
     m = n + n // 8 + (1 << 16)                      # records this rank expects to own (sizes the plan, not the buffers)
@@ -390,11 +529,12 @@ def _slab_shuffle_groupby_sum(eng, keys, vals, capacity: int, groups_hint: int, 
     mark("partition")
     peer.run(chunk_iter if chunk_iter is not None else _device_chunks(keys, vals, peer.chunks), buckets, cap1, cur1, level1,
              counters[4:], mark=mark)
-    pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark)
+    pg = eng.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, capacity, counters, mark=mark, minmax=minmax)
     mark("merge")
     pg.any_overflow = peer.any_overflow
     if keys is not None:
-        pg.rerun = lambda: shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer=peer.counted(), group=group, counted=True)
+        pg.rerun = lambda: shuffle_groupby_sum(eng, keys, vals, capacity, groups_hint, peer=peer.counted(), group=group,
+                                               counted=True, minmax=minmax)
     return pg
 
 
@@ -413,7 +553,7 @@ def shuffle_groupby_sum_host(eng, h_keys: torch.Tensor, h_vals: torch.Tensor, ca
     rank, size = world()
     n = h_keys.shape[0]
     main = torch.cuda.current_stream(dev)
-    slab_ok = groups_hint > 0 and n > 0 and (size == 1 or isinstance(peer, SlabExchange))
+    slab_ok = groups_hint > 0 and n > 0 and (size == 1 or isinstance(peer, (SlabExchange, BucketExchange)))
     if not slab_ok:
         d_keys, d_vals = h_keys.to(dev, non_blocking=True), h_vals.to(dev, non_blocking=True)
         pg = shuffle_groupby_sum(eng, d_keys, d_vals, capacity, groups_hint=groups_hint, peer=peer, group=group)
@@ -436,7 +576,7 @@ def shuffle_groupby_sum_host(eng, h_keys: torch.Tensor, h_vals: torch.Tensor, ca
 
         pg = _slab_shuffle_groupby_sum(eng, None, None, capacity, groups_hint, peer, lambda name: None, group,
                                        chunk_iter=arriving(), n_local=n)
-        counted_peer = peer.counted if isinstance(peer, SlabExchange) else (lambda: peer)
+        counted_peer = peer.counted if isinstance(peer, (SlabExchange, BucketExchange)) else (lambda: peer)
         pg.rerun = lambda: shuffle_groupby_sum(eng, d_keys, d_vals, capacity, groups_hint, peer=counted_peer(), group=group,
                                                counted=True)
     res = eng.groupby_result(pg, sort=False)

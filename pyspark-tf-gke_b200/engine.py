@@ -93,6 +93,8 @@ class PartitionedGroups:
     # ranks) is non-zero the groups above are incomplete and rerun() repeats the work on the counted path.
     rerun: Optional[Callable[[], "PartitionedGroups"]] = None
     any_overflow: Optional[Callable[[int], int]] = None
+    min: Optional[torch.Tensor] = None      # min(value) / max(value) per group when asked for (minmax=True)
+    max: Optional[torch.Tensor] = None
 
 
 class Engine:
@@ -492,7 +494,7 @@ class Engine:
     def groupby_partitioned_sum(self, keys: torch.Tensor, vals: torch.Tensor, out_capacity: int, groups_hint: int = 0,
                                 n: Optional[int] = None, key_stride: int = 1, val_stride: int = 1,
                                 plan: Optional[Tuple[int, int]] = None, slots: Optional[int] = None,
-                                mark=None) -> "PartitionedGroups":
+                                mark=None, minmax: bool = False) -> "PartitionedGroups":
         """groupBy(key).agg(count, sum(value)) of (key int64, value f64) rows through
         two partition levels and a shared-memory merge (csrc/merge.cu).  Everything is
         enqueued on the current stream; nothing is read back until groupby_result."""
@@ -501,11 +503,11 @@ class Engine:
         level1, counts, base = self.hash_partition(keys, vals, 1, buckets, n=n, key_stride=key_stride, val_stride=val_stride)
         if mark:
             mark("level1")
-        return self.groupby_merge_buckets(level1, counts, base, buckets, sub, n, out_capacity, slots=slots, mark=mark)
+        return self.groupby_merge_buckets(level1, counts, base, buckets, sub, n, out_capacity, slots=slots, mark=mark, minmax=minmax)
 
     def groupby_merge_buckets(self, level1: torch.Tensor, counts: torch.Tensor, base: torch.Tensor, buckets: int, sub: int,
                               n: int, out_capacity: int, slots: Optional[int] = None, mark=None,
-                              spill: Optional[torch.Tensor] = None) -> "PartitionedGroups":
+                              spill: Optional[torch.Tensor] = None, minmax: bool = False) -> "PartitionedGroups":
         """The part after the first partition level: `level1` int64[>= n, 2] holds n
         records grouped into `buckets` buckets (device counts / base), as written by
         hash_partition(ranks=1) or by a bucketed peer exchange.  sub > 1 cuts every
@@ -532,12 +534,14 @@ class Engine:
         out_keys, out_rows = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.int64)
         out_cnt, out_sum = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.float64)
         counters = self.empty(4, torch.int64)
+        out_min = self.empty(out_capacity, torch.float64) if minmax else None
+        out_max = self.empty(out_capacity, torch.float64) if minmax else None
         _lib.check(self.lib.etl_groupby_merge_partitioned(
-            self._h, pieces.data_ptr() if n else None, fine, counts.data_ptr(), base.data_ptr(), slots, out_capacity,
-            out_keys.data_ptr(), out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), spill.data_ptr(),
-            spill.shape[0], counters.data_ptr(), self._stream()))
+            self._h, pieces.data_ptr() if n else None, fine, counts.data_ptr(), base.data_ptr(), min(slots, 4096) if minmax else slots,
+            out_capacity, out_keys.data_ptr(), out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), _ptr(out_min),
+            _ptr(out_max), spill.data_ptr(), spill.shape[0], counters.data_ptr(), self._stream()))
         self.launches += 1 if n else 0
-        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine)
+        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine, min=out_min, max=out_max)
 
     # ---------------------------------------------- the same, without count passes (slabs)
     SLAB_SIGMAS = float(os.environ.get("ETL_SLAB_SIGMAS", "6"))
@@ -564,18 +568,48 @@ class Engine:
     def slab_partition_records(self, records: torch.Tensor, segments: int, seg_capacity: int, seg_counts: torch.Tensor,
                                seg_prev: Optional[torch.Tensor], max_seg_records: int, buckets: int, sub: int,
                                out_records: torch.Tensor, slab_capacity: int, cursor: torch.Tensor, overflow: torch.Tensor,
-                               max_ctas: int = 0) -> None:
+                               max_ctas: int = 0, sources: int = 0, bucket0: int = 0) -> None:
         _lib.check(self.lib.etl_slab_partition_records(self._h, records.data_ptr(), segments, seg_capacity,
                                                        seg_counts.data_ptr(), _ptr(seg_prev), max_seg_records, buckets, sub,
-                                                       out_records.data_ptr(), slab_capacity, cursor.data_ptr(),
-                                                       overflow.data_ptr(), max_ctas, self._stream()))
+                                                       sources, bucket0, out_records.data_ptr(), slab_capacity,
+                                                       cursor.data_ptr(), overflow.data_ptr(), max_ctas, self._stream()))
         self.launches += 1 if max_seg_records else 0
 
-    def peer_publish_counts(self, cursor: torch.Tensor, table_ptrs: Sequence[int], slot: int) -> None:
+    def peer_publish_counts(self, cursor: torch.Tensor, table_ptrs: Sequence[int], slot: int, per_rank: int = 1) -> None:
         ranks = len(table_ptrs)
         P = C.c_void_p * ranks
-        _lib.check(self.lib.etl_peer_publish_counts(self._h, cursor.data_ptr(), ranks, P(*table_ptrs), slot, self._stream()))
+        _lib.check(self.lib.etl_peer_publish_counts(self._h, cursor.data_ptr(), ranks, per_rank, P(*table_ptrs), slot,
+                                                    self._stream()))
         self.launches += 1
+
+    def copy_async(self, dst_ptr: int, src_ptr: int, nbytes: int) -> None:
+        """Stream-ordered device-to-device copy on the current stream (copy engine); dst may be peer memory."""
+        _lib.check(self.lib.etl_copy_async(self._h, dst_ptr, src_ptr, nbytes, self._stream()))
+
+    def merge_slab_pieces(self, pieces: torch.Tensor, cursor: torch.Tensor, piece_capacity: int, piece0: int, count: int,
+                          append: bool, pg: "PartitionedGroups", slots: Optional[int] = None) -> None:
+        """Shared-memory merge of the piece slabs piece0 .. piece0 + count - 1 into pg's output columns
+        (append: after the groups earlier calls left there)."""
+        slots = slots or self.MERGE_SLOTS
+        minmax = pg.min is not None
+        _lib.check(self.lib.etl_groupby_merge_slabs(
+            self._h, pieces.data_ptr(), piece0, count, int(append), cursor.data_ptr(), piece_capacity,
+            min(slots, 4096) if minmax else slots, pg.capacity, pg.keys.data_ptr(), pg.rows.data_ptr(), pg.count.data_ptr(),
+            pg.sum.data_ptr(), _ptr(pg.min), _ptr(pg.max), pg.spill.data_ptr(), pg.spill.shape[0], pg.counters.data_ptr(),
+            self._stream()))
+        self.launches += 1
+
+    def new_partitioned_groups(self, out_capacity: int, spill_records: int, pieces: int, minmax: bool = False,
+                               counters: Optional[torch.Tensor] = None) -> "PartitionedGroups":
+        """Empty output of the slab merge: dense columns for out_capacity groups, a spill buffer, counters
+        int64[5] ([4] = slab overflow) zeroed."""
+        e = self.empty
+        counters = torch.zeros(5, dtype=torch.int64, device=self.device) if counters is None else counters
+        spill = torch.empty((max(spill_records, 1), 2), dtype=torch.int64, device=self.device)
+        return PartitionedGroups(e(out_capacity, torch.int64), e(out_capacity, torch.int64), e(out_capacity, torch.int64),
+                                 e(out_capacity, torch.float64), counters, spill, out_capacity, pieces,
+                                 min=e(out_capacity, torch.float64) if minmax else None,
+                                 max=e(out_capacity, torch.float64) if minmax else None)
 
     def slab_plan(self, n: int, groups_hint: int, max_buckets: int = 256):
         """-> (buckets, sub, rows_per_key, cap1, cap2) for n records holding ~groups_hint distinct keys."""
@@ -588,14 +622,15 @@ class Engine:
 
     def groupby_slab_sum(self, keys: torch.Tensor, vals: torch.Tensor, out_capacity: int, groups_hint: int,
                          n: Optional[int] = None, key_stride: int = 1, val_stride: int = 1, slots: Optional[int] = None,
-                         mark=None) -> "PartitionedGroups":
+                         mark=None, minmax: bool = False) -> "PartitionedGroups":
         """groupby_partitioned_sum without the two count passes: both partition levels
         scatter into fixed-capacity slabs (csrc/slabs.cu).  groups_hint (> 0) sizes the
         slabs; if a slab overflows (skewed keys, a hint far off) groupby_result repeats
         the work with groupby_partitioned_sum, so the result is always complete."""
         n = keys.shape[0] if n is None else n
         if n == 0 or groups_hint <= 0:
-            return self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride, slots=slots, mark=mark)
+            return self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride, slots=slots,
+                                                mark=mark, minmax=minmax)
         buckets, sub, rpk, cap1, cap2 = self.slab_plan(n, groups_hint)
         counters = torch.zeros(5, dtype=torch.int64, device=self.device)
         cur1 = torch.zeros(buckets, dtype=torch.int64, device=self.device)
@@ -603,13 +638,15 @@ class Engine:
         self.slab_partition_rows(keys, vals, n, 1, buckets, [level1.data_ptr()], 0, cap1, cap1, cur1, counters[4:], key_stride, val_stride)
         if mark:
             mark("level1")
-        pg = self.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, out_capacity, counters, slots=slots, mark=mark)
-        pg.rerun = lambda: self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride, slots=slots)
+        pg = self.groupby_merge_slab_buckets(level1, cur1, cap1, buckets, sub, cap2, out_capacity, counters, slots=slots, mark=mark,
+                                             minmax=minmax)
+        pg.rerun = lambda: self.groupby_partitioned_sum(keys, vals, out_capacity, groups_hint, n, key_stride, val_stride,
+                                                        slots=slots, minmax=minmax)
         return pg
 
     def groupby_merge_slab_buckets(self, level1: torch.Tensor, cur1: torch.Tensor, cap1: int, buckets: int, sub: int,
                                    cap2: int, out_capacity: int, counters: torch.Tensor, slots: Optional[int] = None,
-                                   mark=None) -> "PartitionedGroups":
+                                   mark=None, minmax: bool = False) -> "PartitionedGroups":
         """After the first level (local, or done on what the exchange delivered): the second
         level into piece slabs and the shared-memory merge.  counters = int64[5], [4] = overflow."""
         slots = slots or self.MERGE_SLOTS
@@ -627,12 +664,14 @@ class Engine:
             spill = torch.empty((max(buckets * cap1 // 8, 1 << 16), 2), dtype=torch.int64, device=self.device)
         out_keys, out_rows = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.int64)
         out_cnt, out_sum = self.empty(out_capacity, torch.int64), self.empty(out_capacity, torch.float64)
+        out_min = self.empty(out_capacity, torch.float64) if minmax else None
+        out_max = self.empty(out_capacity, torch.float64) if minmax else None
         _lib.check(self.lib.etl_groupby_merge_slabs(
-            self._h, pieces.data_ptr(), fine, cur2.data_ptr(), cap2, slots, out_capacity, out_keys.data_ptr(),
-            out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), spill.data_ptr(), spill.shape[0],
-            counters.data_ptr(), self._stream()))
+            self._h, pieces.data_ptr(), 0, fine, 0, cur2.data_ptr(), cap2, min(slots, 4096) if minmax else slots, out_capacity,
+            out_keys.data_ptr(), out_rows.data_ptr(), out_cnt.data_ptr(), out_sum.data_ptr(), _ptr(out_min), _ptr(out_max),
+            spill.data_ptr(), spill.shape[0], counters.data_ptr(), self._stream()))
         self.launches += 1
-        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine)
+        return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine, min=out_min, max=out_max)
 
     def _partitioned_result(self, pg: "PartitionedGroups", sort: bool = True) -> dict:
         ctr = pg.counters.cpu().tolist()
@@ -651,15 +690,21 @@ class Engine:
         if spilled > pg.spill.shape[0]:
             raise _lib.EtlError(-5, f"groupBy: {spilled} spilled records exceed the spill buffer {pg.spill.shape[0]}")
         keys, rows, cnt, sm = pg.keys[:groups], pg.rows[:groups], pg.count[:groups], pg.sum[:groups]
+        minmax = pg.min is not None
+        mn, mx = (pg.min[:groups], pg.max[:groups]) if minmax else (None, None)
         if spilled:   # pieces with more groups than the shared table holds: the global-table path takes them
             cap = 1 << max(4, int(np.ceil(np.log2(2 * spilled))))
-            gt = self.groupby_new(cap, 1)
+            gt = self.groupby_new(cap, 1, minmax=minmax)
             self.groupby_accumulate_records(gt, pg.spill, 0, spilled, groups_hint=spilled)
             extra = self.groupby_result(gt, max_groups=spilled, sort=False)
             keys, rows = torch.cat([keys, extra["keys"]]), torch.cat([rows, extra["rows"]])
             cnt, sm = torch.cat([cnt, extra["cols"][0]["count"]]), torch.cat([sm, extra["cols"][0]["sum"]])
+            if minmax:
+                mn, mx = torch.cat([mn, extra["cols"][0]["min"]]), torch.cat([mx, extra["cols"][0]["max"]])
         order = torch.argsort(keys) if sort else slice(None)
         col = {"count": cnt[order], "sum": sm[order]}
+        if minmax:
+            col["min"], col["max"] = mn[order], mx[order]
         col["mean"] = col["sum"] / col["count"].to(torch.float64)
         return {"keys": keys[order], "rows": rows[order], "cols": [col], "null_group_rows": 0, "spilled_records": spilled}
 

@@ -66,28 +66,98 @@ def _padded(n: int) -> int:
     return (n + 127) // 64 * 64
 
 
+class PinnedRing:
+    """Host side of the bulk ingest (replaces the JDBC / file read of
+    google_health_SQL.py:26-37 and open_text, train_tf_ps.py:53-72): a few
+    page-locked slots that live as long as the engine.  A file (or a bytes object)
+    is cut into slot-sized slices; worker threads fill the slots (readinto / memcpy
+    release the GIL) while earlier slots are already crossing PCIe on a copy
+    stream, so neither a per-call page-lock of the whole input nor a monolithic
+    copy is paid."""
+
+    def __init__(self, device, slots: int = 4, slot_bytes: int = 64 << 20):
+        from concurrent.futures import ThreadPoolExecutor
+
+        self.device = device
+        self.slot_bytes = slot_bytes
+        self.bufs = [torch.empty(slot_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(slots)]
+        self.views = [b.numpy() for b in self.bufs]
+        self.events: List[Optional[torch.cuda.Event]] = [None] * slots
+        self.stream = torch.cuda.Stream(device=device)
+        self.pool = ThreadPoolExecutor(max_workers=slots)
+
+    def upload(self, fill, nbytes: int) -> torch.Tensor:
+        """fill(view: np.ndarray[uint8], offset, length) writes bytes [offset, offset + length) of the
+        input into `view`.  -> device uint8 tensor, zero padded (see _padded)."""
+        dst = torch.empty(_padded(nbytes), dtype=torch.uint8, device=self.device)
+        dst[nbytes:].zero_()
+        main = torch.cuda.current_stream(self.device)
+        self.stream.wait_stream(main)
+        slots, sb = len(self.bufs), self.slot_bytes
+        slices = [(off, min(sb, nbytes - off)) for off in range(0, nbytes, sb)]
+
+        def work(i):
+            slot = i % slots
+            if self.events[slot] is not None:
+                self.events[slot].synchronize()        # the copy that last read this slot has finished
+            off, ln = slices[i]
+            fill(self.views[slot][:ln], off, ln)
+
+        pending = {i: self.pool.submit(work, i) for i in range(min(slots, len(slices)))}
+        for i, (off, ln) in enumerate(slices):
+            pending.pop(i).result()
+            slot = i % slots
+            with torch.cuda.stream(self.stream):
+                dst[off:off + ln].copy_(self.bufs[slot][:ln], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.stream)
+            self.events[slot] = ev
+            if i + slots < len(slices):
+                pending[i + slots] = self.pool.submit(work, i + slots)
+        main.wait_stream(self.stream)
+        return dst
+
+
+def _ring(eng: Engine) -> PinnedRing:
+    ring = getattr(eng, "_pinned_ring", None)
+    if ring is None:
+        ring = eng._pinned_ring = PinnedRing(eng.device)
+    return ring
+
+
 def upload_text(eng: Engine, raw) -> torch.Tensor:
     """File bytes -> device uint8 tensor, zero padded to a multiple of 64 (+64)
     so the decoder's 8- and 16-byte window loads never leave the allocation."""
-    n = len(raw)
-    host = torch.zeros(_padded(n), dtype=torch.uint8).pin_memory()
-    if n:
-        host.numpy()[:n] = np.frombuffer(raw, dtype=np.uint8)
-    return host.to(eng.device, non_blocking=True)
+    src = np.frombuffer(raw, dtype=np.uint8)
+
+    def fill(view, off, ln):
+        view[:] = src[off:off + ln]
+
+    return _ring(eng).upload(fill, len(raw))
 
 
 def upload_file(eng: Engine, path: str):
-    """Local file -> (device tensor, nbytes, pinned host copy): the file is read
-    straight into pinned memory (one host copy) and sent with one async H2D."""
+    """Local file -> (device tensor, nbytes, first bytes of the file for the header):
+    worker threads pread() slices of the file straight into the pinned ring while
+    earlier slices are already on their way to the GPU."""
     import os
 
     n = os.path.getsize(path)
-    host = torch.zeros(_padded(n), dtype=torch.uint8).pin_memory()
-    with open(path, "rb") as fh:
-        got = fh.readinto(memoryview(host.numpy())[:n]) if n else 0
-    if got != n:
-        raise IOError(f"{path}: short read ({got} of {n} bytes)")
-    return host.to(eng.device, non_blocking=True), n, host
+    fd = os.open(path, os.O_RDONLY)
+    try:
+        def fill(view, off, ln):
+            got = 0
+            while got < ln:
+                k = os.preadv(fd, [memoryview(view)[got:ln]], off + got)
+                if k <= 0:
+                    raise IOError(f"{path}: short read at byte {off + got}")
+                got += k
+
+        text = _ring(eng).upload(fill, n)
+        head = os.pread(fd, min(n, 1 << 20), 0)
+    finally:
+        os.close(fd)
+    return text, n, head
 
 
 def _dictionary_labels(text: torch.Tensor, hash_tab: torch.Tensor, rep_tab: torch.Tensor):
@@ -118,9 +188,9 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
     passes cost ~1 ms per GB) and decodes only its contiguous share of the records,
     so quoted newlines need no cross-rank protocol.  device_text: the file already
     on this GPU (as returned by upload_text), to keep the copy out of a timed region."""
-    host = None
+    head = None
     if isinstance(source, str) and not source.startswith(("http://", "https://")) and device_text is None:
-        text, n, host = upload_file(eng, source)          # straight into pinned memory
+        text, n, head = upload_file(eng, source)          # file -> pinned ring -> HBM
     else:
         raw = read_bytes(source)
         n = len(raw)
@@ -131,7 +201,10 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
     row_start = eng.csv_row_offsets(text, n, rows_total)
     # header line -> field positions (DictReader: a repeated name keeps its last position)
     hdr_end = int(row_start[1].item()) if rows_total > 1 else n
-    hdr_bytes = host.numpy()[:hdr_end].tobytes() if host is not None else bytes(raw[:hdr_end])
+    if head is not None:
+        hdr_bytes = head[:hdr_end] if hdr_end <= len(head) else text[:hdr_end].cpu().numpy().tobytes()
+    else:
+        hdr_bytes = bytes(raw[:hdr_end])
     header = next(csv.reader(io.StringIO(hdr_bytes.decode("utf-8"), newline="")))
     pos = {name: j for j, name in enumerate(header)}
     rows = rows_total - 1

@@ -5,8 +5,7 @@ tests/test_gpu_multi.py when the box has >= 2 GPUs, or by hand):
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port P \
         tests/multi_gpu/check_shuffle.py [--rows 2000000 --groups 150000]
 
-Every exchange variant of dist.shuffle_groupby_sum - the chunked slab exchange (the
-default), NCCL all-to-all, the counted fused peer scatter (by rank, and by rank x
+Every exchange variant of dist.shuffle_groupby_sum - the bucketed exchange (the default), the chunked slab exchange, NCCL all-to-all, the counted fused peer scatter (by rank, and by rank x
 bucket), the host-buffer entry - runs on this rank's shard of a seeded
 table; every rank's groups are gathered on rank 0 and compared with
 oracle.groupby_agg_fast on ALL rows: same keys, counts exact, sums bit-exact
@@ -50,7 +49,9 @@ def main():
     cap = args.groups // world * 2 + 4096
     peer = D.PeerExchange(eng, int(n * 1.3) + 4096)
     slab = D.SlabExchange(eng, n, groups_hint=args.groups, chunks=3)
-    variants = {"slab_chunked": dict(peer=slab), "nccl": dict(peer=None, counted=True),
+    bucketed = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=4)
+    variants = {"bucketed": dict(peer=bucketed), "bucketed_minmax": dict(peer=bucketed, minmax=True),
+                "slab_chunked": dict(peer=slab), "nccl": dict(peer=None, counted=True),
                 "peer_by_rank": dict(peer=peer, exchange_buckets=1),
                 "peer_by_rank_and_bucket": dict(peer=peer, exchange_buckets=16), "host_entry": None}
     results = {}
@@ -63,7 +64,7 @@ def main():
         if kw is None:               # pinned host rows in, host group columns out, over the slab exchange
             hk_p, hv_p = torch.from_numpy(hk).pin_memory(), torch.from_numpy(hv).pin_memory()
             out = tuple(torch.empty(cap, dtype=t, pin_memory=True) for t in (torch.int64, torch.int64, torch.float64))
-            g = D.shuffle_groupby_sum_host(eng, hk_p, hv_p, cap, groups_hint=args.groups, peer=slab, out=out, chunks=3)
+            g = D.shuffle_groupby_sum_host(eng, hk_p, hv_p, cap, groups_hint=args.groups, peer=bucketed, out=out, chunks=3)
             mine = tuple(o[:g].numpy().copy() for o in out)
         else:
             for rep in range(2):     # twice: the receive buffer is reused

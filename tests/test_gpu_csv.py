@@ -212,6 +212,22 @@ def test_decoder_on_synthetic_csv_with_quotes_newlines_and_nulls(eng, rows, seed
     assert X.tobytes() == eX.tobytes() and y.tobytes() == ey.tobytes() and vocab == ev
 
 
+def test_quoted_empty_cell_is_null_in_the_decoder_too(eng):
+    # Spark's defaults (nullValue = "" and read-side emptyValue = "") make `""` and an empty field the same
+    # null (oracle.read_csv_columns states the rule): not an empty-string label, not a zero
+    text = 'measure_name,value,lower_ci,upper_ci\n"",1,2,3\n,4,5,6\nx,"",8,9\n"x",10,"",12\n" ",1,1,1\n'
+    table = pkg.read_csv(eng, text.encode(), ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    header, cols = O.read_csv_columns(text)
+    key = table.strings["measure_name"]
+    kv = key.column.valid_host()
+    codes = key.column.data.cpu().numpy()
+    assert [key.labels[c] if ok else None for c, ok in zip(codes, kv)] == cols["measure_name"] == [None, None, "x", "x", " "]
+    for c in ("value", "lower_ci", "upper_ci"):
+        v, vv = O.to_numeric_column(cols[c])
+        assert (table.numeric[c].valid_host() == vv).all()
+        assert table.numeric[c].data.cpu().numpy()[vv].tobytes() == v[vv].tobytes()
+
+
 def test_row_index_across_block_boundaries(eng):
     # quoted fields with newlines and commas straddling the 16 KiB scan blocks
     parts = ["a,b"]
@@ -337,3 +353,27 @@ def test_row_scan_over_index_masks_equals_row_scan_over_text(eng, rows, seed, mo
     eng.reserve(1 << 20)
     cols, status, _ = eng.csv_parse_columns(d_text, n, row_start, 1, total - 1, [3], [0], [None], flags=T.CSV_NAN_IS_NULL | 4)
     assert cols[0].data.cpu().numpy().tobytes() == from_text.numeric["value"].data.cpu().numpy().tobytes()
+
+
+def test_pinned_ring_upload_of_bytes_and_files(eng, tmp_path):
+    import pyspark_tf_gke_b200.table as T
+
+    # the ingest path: bytes / a file cut into slot-sized slices through the engine's pinned ring; small slots so
+    # that a few MB exercise slot reuse, the tail slice and the zero padding
+    from pyspark_tf_gke_b200.table import PinnedRing, _padded
+
+    rng = np.random.default_rng(3)
+    raw = rng.integers(0, 256, 5_000_123, dtype=np.uint8).tobytes()
+    eng._pinned_ring = PinnedRing(eng.device, slots=3, slot_bytes=1 << 20)
+    try:
+        for data in (raw, raw[:1 << 20], raw[:17], b""):
+            d = T.upload_text(eng, data)
+            assert d.shape[0] == _padded(len(data))
+            host = d.cpu().numpy()
+            assert host[:len(data)].tobytes() == data and not host[len(data):].any()
+        path = tmp_path / "blob.bin"
+        path.write_bytes(raw)
+        d, n, head = T.upload_file(eng, str(path))
+        assert n == len(raw) and d.cpu().numpy()[:n].tobytes() == raw and head == raw[:1 << 20]
+    finally:
+        del eng._pinned_ring

@@ -146,3 +146,78 @@ def test_simulated_chunked_slab_exchange(eng, R, chunks):
         counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
         pg = eng.groupby_merge_slab_buckets(level1[r], cur1[r], cap1, buckets, sub, cap2, groups, counters)
         _same(eng.groupby_result(pg), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))
+
+
+@pytest.mark.parametrize("counted", [False, True])
+def test_min_max_on_the_shuffle_path(eng, counted):
+    # north-star item 3 names count / sum / mean / min / max: the shared-memory merge carries min and max of
+    # the value column too (Spark's ordering: NaN is the largest double), on the slab and on the counted path
+    n, groups = 700_003, 60_000
+    keys, _ = _rows(n, groups)
+    vals, _ = S.host_column(23, 1, S.KIND_REAL, n, nan_rate=0.002)
+    vals = vals - 5e4
+    dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
+    pg = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups, minmax=True, counted=counted)
+    res = eng.groupby_result(pg)
+    want = O.groupby_agg(keys, None, [vals], [None])
+    assert res["keys"].cpu().numpy().tolist() == want["keys"].tolist()
+    assert res["rows"].cpu().numpy().tolist() == want["rows"].tolist()
+    col, wcol = res["cols"][0], want["cols"][0]
+    assert np.array_equal(col["min"].cpu().numpy(), wcol["min"], equal_nan=True)
+    assert np.array_equal(col["max"].cpu().numpy(), wcol["max"], equal_nan=True)
+    np.testing.assert_allclose(col["sum"].cpu().numpy(), wcol["sum"], rtol=1e-6, atol=0, equal_nan=True)
+    np.testing.assert_allclose(col["mean"].cpu().numpy(), wcol["mean"], rtol=1e-6, atol=0, equal_nan=True)
+
+
+@pytest.mark.parametrize("R,groups_of_buckets", [(2, 4), (4, 2), (8, 8)])
+def test_simulated_bucketed_exchange(eng, R, groups_of_buckets):
+    # BucketExchange's data path on one GPU: every source partitions its rows into R x Bx slabs of a send buffer,
+    # slabs are copied bucket group by bucket group into the "ranks'" receive buffers ([source][bucket] layout),
+    # cursors go to the count tables, and each receiver cuts + merges one bucket group at a time (append mode)
+    groups = 60_000
+    sizes = [90_000 + 1013 * s + (s % 2) for s in range(R)]
+    rows = [_rows(sizes[s], groups, row0=s * 1_000_000 // 32 * 32) for s in range(R)]
+    bx = 8
+    sub = 3
+    slab = eng.slab_capacity(max(sizes) / (R * bx), 2.0)
+    cap2 = eng.slab_capacity(max(sizes) * 1.3 / (bx * sub), 2.0)
+    recv = [torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    tables = [torch.zeros(R * bx, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    overflow = torch.zeros(1, dtype=torch.int64, device=eng.device)
+    bpg = bx // groups_of_buckets
+    sends = []
+    for s in range(R):
+        k, v = torch.from_numpy(rows[s][0]).to(eng.device), torch.from_numpy(rows[s][1]).to(eng.device)
+        send = torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device)
+        xcur = torch.zeros(R * bx, dtype=torch.int64, device=eng.device)
+        half = sizes[s] // 2 // 2 * 2               # two chunks: the cursors persist
+        for lo, hi in ((0, half), (half, sizes[s])):
+            eng.slab_partition_rows(k[lo:hi], v[lo:hi], hi - lo, R, bx, [send.data_ptr()] * R, 0, slab, slab, xcur, overflow)
+        eng.peer_publish_counts(xcur, [t.data_ptr() for t in tables], s * bx, per_rank=bx)
+        want = np.bincount(O.partition_dest(rows[s][0], R, bx), minlength=R * bx)
+        assert xcur.cpu().tolist() == want.tolist()
+        sends.append(send)
+    all_k = np.concatenate([k for k, _ in rows])
+    all_v = np.concatenate([v for _, v in rows])
+    for r in range(R):
+        pg = eng.new_partitioned_groups(groups, 1 << 16, bx * sub)
+        cur2 = torch.zeros(bx * sub, dtype=torch.int64, device=eng.device)
+        pieces = torch.full((bx * sub * cap2, 2), -1, dtype=torch.int64, device=eng.device)
+        for g in range(groups_of_buckets):
+            for s in range(R):
+                eng.copy_async(recv[r].data_ptr() + ((s * bx + g * bpg) * slab) * 16,
+                               sends[s].data_ptr() + ((r * bx + g * bpg) * slab) * 16, bpg * slab * 16)
+            eng.slab_partition_records(recv[r], bpg * R, slab, tables[r], None, slab, bx, sub, pieces, cap2, cur2, pg.counters[4:],
+                                       sources=R, bucket0=g * bpg)
+            eng.merge_slab_pieces(pieces, cur2, cap2, g * bpg * sub, bpg * sub, g > 0, pg)
+        torch.cuda.synchronize()
+        assert int(pg.counters[4].item()) == 0 and int(overflow.item()) == 0
+        # count table of rank r: [source][bucket] = what the oracle sends there
+        want_counts = [int((O.partition_dest(rows[s][0], R, bx) == r * bx + b).sum()) for s in range(R) for b in range(bx)]
+        assert tables[r].cpu().tolist() == want_counts
+        # piece f of rank r holds exactly the owned records whose fine index is f
+        own = O.partition_dest(all_k, R) == r
+        h = O.mix64(all_k[own].view(np.uint64))
+        fine_idx = (((h & np.uint64(0xFFFFFFFF)) * np.uint64(bx * sub)) >> np.uint64(32)).astype(np.int64)
+        assert cur2.cpu().tolist() == np.bincount(fine_idx, minlength=bx * sub).tolist()
+        _same(eng.groupby_result(pg), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))

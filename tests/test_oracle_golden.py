@@ -105,3 +105,14 @@ def test_bucketize_and_standardize():
     assert m == 2.5 and abs(sd - 1.2909944487358056) < 1e-15
     assert O.standardize(np.array([2.0]), m, sd).tolist() == [2.0 * (1.0 / sd)]
     assert O.standardize(np.array([2.0]), m, 0.0).tolist() == [0.0]
+
+
+def test_quoted_empty_cell_is_null_like_an_unquoted_one():
+    # the rule stated in read_csv_columns: with Spark's default nullValue = "" / emptyValue = "" both forms
+    # reach nullSafeDatum as "" and become null - a quoted empty cell is NOT an empty-string label
+    text = 'measure_name,value,lower_ci,upper_ci\n"",1,2,3\n,4,5,6\nx,"",8,9\n"x",10,"",12\n'
+    header, cols = O.read_csv_columns(text)
+    assert cols["measure_name"] == [None, None, "x", "x"]
+    assert cols["value"] == ["1", "4", None, "10"] and cols["lower_ci"] == ["2", "5", "8", None]
+    out = O.k_means_etl(text, repeats=1)
+    assert out["null_measure_name"] == 2 and out["rows_after_filter"] == 2 and out["labels"] == ["x"]

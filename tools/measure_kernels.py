@@ -37,16 +37,25 @@ def peak():
         return 6650.0, "fallback"
 
 
+LAST_CLOCKS = None   # SM clock / throttle reasons sampled during the most recent timed() region; entry() records them
+
+
 def timed(fn, steps=20, warmup=3):
+    global LAST_CLOCKS
+    from tools.clocks import ClockSampler
+
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
+    sampler = ClockSampler(torch.cuda.current_device())
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    sampler.start()
     ev[0].record()
     for i in range(steps):
         fn()
         ev[i + 1].record()
     torch.cuda.synchronize()
+    LAST_CLOCKS = sampler.stop()
     ts = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
     return sum(ts) / len(ts), min(ts)
 
@@ -66,7 +75,7 @@ def entry(name, rows, alg_bytes, mean_ms, min_ms, cpu=None, note=""):
     gbs = alg_bytes / (mean_ms * 1e-3) / 1e9
     e = {"kernel": name, "rows": rows, "algorithmic_bytes": alg_bytes, "mean_ms": mean_ms, "min_ms": min_ms,
          "rows_per_s": rows / (mean_ms * 1e-3), "achieved_gbs": gbs, "peak_gbs": p, "peak_source": src, "frac": gbs / p,
-         "note": note}
+         "note": note, "clocks": LAST_CLOCKS}
     if cpu:
         e["cpu"] = cpu
     print(json.dumps(e), flush=True)
@@ -168,42 +177,42 @@ def m_partition(eng, args):
 
 
 def m_merge(eng, args):
-    """The shared-memory merge of config 4 stage by stage (csrc/merge.cu)."""
+    """Config 4 on one GPU stage by stage, count-free slab path (csrc/slabs.cu + merge.cu), then the two
+    count passes of the counted path for comparison."""
     from pyspark_tf_gke_b200 import _lib
     cfg = S.CONFIG4
     n = cfg["rows"] if args.full else cfg["rows"] // 4
     groups = cfg["groups"] if args.full else cfg["groups"] // 4
     key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=groups, with_valid=False).data
     val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False).data
-    B, sub = eng.merge_plan(n, groups)
+    B, sub, rpk, cap1, cap2 = eng.slab_plan(n, groups)
     fine = B * sub
     res = []
-    mean, mn = timed(lambda: eng.hash_partition(key, val, 1, B), steps=3, warmup=1)
-    res.append(entry(f"level 1: hash_partition into {B} buckets, {n} rows", n, n * 40, mean, mn, None,
-                     "count pass reads keys (8 B), scatter reads 16 B and writes 16 B per row"))
-    level1, counts, base = eng.hash_partition(key, val, 1, B)
-    fcounts, fbase = eng.empty(fine, torch.int64), eng.empty(fine, torch.int64)
-    pieces = torch.empty((n, 2), dtype=torch.int64, device=eng.device)
+    counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
+    cur1 = torch.zeros(B, dtype=torch.int64, device=eng.device)
+    level1 = torch.empty((B * cap1, 2), dtype=torch.int64, device=eng.device)
 
-    def level2():
-        _lib.check(eng.lib.etl_hash_subpartition(eng._h, level1.data_ptr(), B, sub, counts.data_ptr(), base.data_ptr(), n,
-                                                 fcounts.data_ptr(), fbase.data_ptr(), pieces.data_ptr(), eng._stream()))
+    def l1():
+        cur1.zero_()
+        eng.slab_partition_rows(key, val, n, 1, B, [level1.data_ptr()], 0, cap1, cap1, cur1, counters[4:])
 
-    mean, mn = timed(level2, steps=3, warmup=1)
-    res.append(entry(f"level 2: hash_subpartition {B} x {sub} = {fine} pieces", n, n * 48, mean, mn, None,
-                     "count pass reads the records (16 B), scatter reads 16 B and writes 16 B per row"))
+    mean, mn = timed(l1, steps=3, warmup=1)
+    res.append(entry(f"level 1: scatter_pipelined_kernel<columns, slab> into {B} bucket slabs, {n} rows", n, n * 32, mean, mn, None,
+                     "reads 16 B and writes 16 B per row; no count pass"))
+    cur2 = torch.zeros(fine, dtype=torch.int64, device=eng.device)
+    pieces = torch.empty((fine * cap2, 2), dtype=torch.int64, device=eng.device)
+
+    def l2():
+        cur2.zero_()
+        eng.slab_partition_records(level1, B, cap1, cur1, None, cap1, B, sub, pieces, cap2, cur2, counters[4:])
+
+    mean, mn = timed(l2, steps=3, warmup=1)
+    res.append(entry(f"level 2: scatter_pipelined_kernel<records, slab> {B} x {sub} = {fine} piece slabs", n, n * 32, mean, mn, None,
+                     "reads 16 B and writes 16 B per record; no count pass"))
     cap = groups + groups // 8
-    outs = [eng.empty(cap, torch.int64) for _ in range(3)] + [eng.empty(cap, torch.float64)]
-    counters = eng.empty(4, torch.int64)
-
-    def merge():
-        _lib.check(eng.lib.etl_groupby_merge_partitioned(
-            eng._h, pieces.data_ptr(), fine, fcounts.data_ptr(), fbase.data_ptr(), eng.MERGE_SLOTS, cap, outs[0].data_ptr(),
-            outs[1].data_ptr(), outs[2].data_ptr(), outs[3].data_ptr(), level1.data_ptr(), n, counters.data_ptr(),
-            eng._stream()))
-
-    mean, mn = timed(merge, steps=3, warmup=1)
-    g, spilled = counters.cpu().tolist()[:2]
+    pg = eng.new_partitioned_groups(cap, n // 8, fine, counters=counters)
+    mean, mn = timed(lambda: eng.merge_slab_pieces(pieces, cur2, cap2, 0, fine, False, pg), steps=3, warmup=1)
+    g, spilled, _, _, overflow = counters.cpu().tolist()
     # CPU side of config 4 on a sample that fits the host comfortably: same rows-per-group ratio (10)
     import pyarrow as pa
     m = 20_000_000
@@ -211,10 +220,16 @@ def m_merge(eng, args):
     sv = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, m, with_valid=False).data.cpu().numpy()
     tbl = pa.table({"k": sk, "v": sv})
     t = cpu_time(lambda: tbl.group_by("k").aggregate([("v", "sum"), ("v", "count")]), reps=2)
-    res.append(entry(f"groupby_merge_kernel: {fine} pieces, {g} groups, {spilled} spilled", n, n * 16 + g * 32, mean, mn,
+    res.append(entry(f"groupby_merge_kernel: {fine} pieces, {g} groups, {spilled} spilled, {overflow} slab overflow", n, n * 16 + g * 32,
+                     mean, mn,
                      {"rows_per_s": m / t, "impl": f"pyarrow Table.group_by, {m} rows / {m // 10} groups (whole groupBy, not just the merge)",
                       "cores": pa.cpu_count()},
                      "reads 16 B per record, writes 32 B per group; table updates stay in shared memory"))
+    del level1, pieces, pg
+    # the counted path's passes (exact sizes; what a slab overflow falls back to)
+    mean, mn = timed(lambda: eng.hash_partition(key, val, 1, B), steps=3, warmup=1)
+    res.append(entry(f"counted level 1: partition_count + scatter into {B} buckets, {n} rows", n, n * 40, mean, mn, None,
+                     "count pass reads keys (8 B), scatter reads 16 B and writes 16 B per row"))
     return res
 
 

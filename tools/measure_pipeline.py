@@ -67,12 +67,16 @@ def main():
         return model, F, [ev[i].elapsed_time(ev[i + 1]) for i in range(3)]
 
     run()
+    from tools.clocks import ClockSampler
+    sampler = ClockSampler(local)
+    sampler.start()
     times = []
     for _ in range(args.steps):
         if world > 1:
             dist.barrier()
         model, F, t = run()
         times.append(t)
+    clocks = sampler.stop()
     best = min(times, key=sum)
     tt = torch.tensor(best, dtype=torch.float64, device=eng.device)
     if world > 1:
@@ -90,7 +94,7 @@ def main():
                 "rows_per_s": rows / (total * 1e-3), "text_gb_per_s": nbytes / 1e9 / (total * 1e-3),
                 "features": None if F is None else [int(x) for x in F.shape] + [str(F.dtype)],
                 "h2d_copy_s": h2d_s, "labels": len(model.labels), "means": model.means,
-                "rows_after_filter": model.rows_after_filter, "null_keys": model.null_key_count}
+                "rows_after_filter": model.rows_after_filter, "null_keys": model.null_key_count, "clocks": clocks}
         print(json.dumps(line), flush=True)
     eng.close()
     if world > 1:

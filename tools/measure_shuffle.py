@@ -38,8 +38,11 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--buckets", type=int, default=-1, help="table buckets per rank (-1 = choose from the table size)")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="peer = partition fused with NVLink peer stores; nccl = send buffer + all_to_all_single")
+    ap.add_argument("--exchange", default="bucketed", choices=["bucketed", "peer", "nccl"],
+                    help="bucketed = local (rank, bucket) partition + copy-engine slab copies, merge behind the transfer; "
+                         "peer = partition fused with NVLink peer stores (chunked slabs, or counted with --counted); "
+                         "nccl = send buffer + all_to_all_single")
+    ap.add_argument("--bucket-groups", type=int, default=8)
     ap.add_argument("--merge", default="smem", choices=["smem", "table"],
                     help="smem = two partition levels + shared-memory tables; table = bucket-by-bucket global table")
     ap.add_argument("--exchange-buckets", type=int, default=0,
@@ -85,7 +88,9 @@ def main():
     sent = n - n // world if world > 1 else 0  # expected rows leaving this GPU (uniform hash)
     B = D.choose_buckets(cap, 1) if args.buckets < 0 else args.buckets
     peer = None
-    if world > 1 and args.exchange == "peer":
+    if world > 1 and args.exchange == "bucketed" and not args.counted:
+        peer = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=args.bucket_groups)
+    elif world > 1 and args.exchange in ("peer", "bucketed"):
         peer = (D.PeerExchange(eng, int(n * 1.05) + (1 << 20)) if args.counted
                 else D.SlabExchange(eng, n, groups_hint=args.groups, chunks=args.chunks))
     from tools.clocks import ClockSampler
