@@ -226,7 +226,8 @@ ETL_API int etl_remap_codes(etl_handle* h, int32_t* codes, int64_t n, const int3
 /* The reference reads CSV / JDBC only; Parquet is named by the north star.  The
  * host parses footer and page headers (Thrift compact, a few hundred bytes per
  * MB) and describes the work in two device tables; the row-proportional work is
- * here.  `file` = the whole file in device memory (UNCOMPRESSED column chunks).
+ * here.  `file` = the whole file in device memory (plus, for compressed column
+ * chunks, the region etl_parquet_inflate_pages fills).
  * etl_parquet_expand_streams: d_streams = nstreams records {int64 src_offset;
  *   int32 src_bytes, bit_width; int64 out_offset; int32 max_values, exact; int64
  *   run_offset, run_capacity} - one RLE / bit-packed hybrid stream each
@@ -249,6 +250,26 @@ ETL_API int etl_parquet_gather_pages(etl_handle* h, const uint8_t* file, const v
                              const int32_t* d_levels, const int32_t* d_indices, const void* const* d_dict,
                              const int32_t* d_dict_size, int32_t string_column, void* out, uint32_t* valid,
                              int32_t* d_status, void* stream);
+
+/* Compressed pages and PLAIN strings (same north-star item; no reference site).
+ * etl_parquet_inflate_pages: d_jobs = njobs records {int64 src, src_bytes, dst,
+ *   dst_bytes} (byte offsets in `buffer`): Snappy block format, one warp per page;
+ *   the caller sizes `buffer` as file bytes + a region for the inflated pages and
+ *   describes inflated pages to the other entry points by offsets into that region.
+ *   A bit_width < 0 in a stream record means "read the width byte in front of the
+ *   indices on the device" (the host cannot see into a compressed page).
+ * etl_parquet_plain_strings: d_pages = npages records {int64 val_offset; int32
+ *   val_bytes, max_values; int64 out_offset}: PLAIN BYTE_ARRAY values ([u32
+ *   length][bytes] ...) are entered into a device dictionary (dict_hash / dict_rep:
+ *   zeroed uint64[dict_capacity], a power of two; rep = byte offset << 24 | length)
+ *   and their slot numbers written to d_out[out_offset ...], where
+ *   etl_parquet_gather_pages reads them as dictionary indices.
+ * d_status int32[4]: additionally [0] dictionary full, [3] corrupt Snappy stream. */
+ETL_API int etl_parquet_inflate_pages(etl_handle* h, uint8_t* buffer, const void* d_jobs, int32_t njobs, int32_t* d_status,
+                              void* stream);
+ETL_API int etl_parquet_plain_strings(etl_handle* h, const uint8_t* buffer, const void* d_pages, int32_t npages,
+                              uint64_t* dict_hash, uint64_t* dict_rep, int32_t dict_capacity, int32_t* d_out,
+                              int32_t* d_status, void* stream);
 
 /* ---- a6: StringIndexer.fit's group-by-count ------------------------------ */
 
@@ -451,9 +472,16 @@ ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records,
  *     for every rank r and j < per_rank (system-scope release stores; follow with a
  *     cross-rank barrier) - how a receiver learns how much of each source's slabs is
  *     filled.  ranks * per_rank <= 256.
- *   etl_copy_async: stream-ordered device-to-device copy (copy engine; dst may be
- *     a peer's memory) - the bucketed exchange moves whole slabs with it, so the
- *     SMs stay with the merge of the buckets that have already arrived.
+ *   etl_peer_copy_slabs: the bucketed exchange's data movement.  The send buffer
+ *     holds ranks x buckets slabs, destination-rank major (etl_slab_partition_rows
+ *     with ranks > 1 and ONE local buffer); the filled part of the slabs of
+ *     buckets bucket0 .. bucket0 + nbuckets - 1 of every destination r is stored
+ *     into peer_records[r] at slab (my_rank * buckets + bucket) - the receivers'
+ *     [source][bucket] layout - with 16-byte stores over NVLink (~700 GB/s per GPU
+ *     measured; no shared memory, so it runs beside the merge of earlier groups).
+ *   etl_copy_async: stream-ordered device-to-device copy through a copy engine
+ *     (dst may be a peer's memory); an alternative mover for the same slabs
+ *     (measured slower at 8 GPUs: 330-400 GB/s per GPU).
  * Overflow: a record that finds its slab full is counted in *d_overflow (int64,
  * caller-zeroed) and DROPPED.  A non-zero count means the result is incomplete:
  * repeat on the counted path (etl_hash_partition / etl_hash_subpartition), which
@@ -477,6 +505,9 @@ ETL_API int etl_groupby_merge_slabs(etl_handle* h, const int64_t* records, int32
 ETL_API int etl_peer_publish_counts(etl_handle* h, const int64_t* d_cursor, int32_t ranks, int32_t per_rank,
                             int64_t* const* peer_tables, int64_t slot, void* stream);
 ETL_API int etl_copy_async(etl_handle* h, void* dst, const void* src, int64_t nbytes, void* stream);
+ETL_API int etl_peer_copy_slabs(etl_handle* h, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
+                        int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
+                        const int64_t* d_cursor, int32_t ctas_per_slab, void* stream);
 
 /* Diagnostic, no reference counterpart (tools/nvlink_probe.py): copy nbytes (a
  * multiple of 16) from src to dst - dst may be a peer GPU's memory mapped here -

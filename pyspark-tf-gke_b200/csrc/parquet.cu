@@ -7,6 +7,14 @@
 //        run header speculatively at 32 consecutive byte offsets, a shuffle hop per
 //        run settles which guesses lie on the real chain, and the runs are expanded
 //        at once (no run table);
+//   pq_snappy_kernel         one WARP per compressed page: the Snappy block format (what Spark and Arrow write
+//        by default) is a chain of literal / copy elements that can only be found one after another; the
+//        warp walks the chain in lockstep and all 32 lanes move each element's bytes, into a region behind
+//        the file bytes, so every later kernel addresses inflated pages like any other part of the buffer;
+//   pq_plain_strings_kernel  one WARP per PLAIN BYTE_ARRAY page (a writer's fallback when its dictionary grew
+//        too large): lane 0 walks the [length][bytes] chain 32 values at a time, every lane hashes its value
+//        into a device dictionary (as the CSV decoder does) and the slot numbers take the place of
+//        dictionary indices;
 //   pq_gather_kernel         one CTA per data page: definition levels -> validity
 //        bits (ballot) and, through a block scan, each row's position among the
 //        page's non-null values; PLAIN values are cast to double, dictionary
@@ -121,7 +129,12 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_hybrid_decode_kernel(const uint
     };
     int64_t pos = 0;
     int produced = 0;
-    const int bw = st.bit_width;
+    // bit_width < 0: the page was compressed, so the host could not read the width byte in front of the indices
+    const int bw = st.bit_width >= 0 ? st.bit_width : (int)src[-1];
+    if (bw > 32) {
+        if (lane == 0) atomicAdd(status + 1, 1);
+        return;
+    }
     const int vbytes = (bw + 7) >> 3;
     const uint32_t vmask = vbytes >= 4 ? 0xffffffffu : ((1u << (8 * vbytes)) - 1);
     const uint32_t* sw = reinterpret_cast<const uint32_t*>(s_win);
@@ -219,6 +232,160 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_hybrid_decode_kernel(const uint
         pos += j;
     }
     if (lane == 0 && st.exact && produced < st.max_values) atomicAdd(status + 1, 1);  // stream ended early
+}
+
+// ---------------------------------------------------------------- Snappy
+struct PqInflate { int64_t src, src_bytes, dst, dst_bytes; };   // byte offsets in the buffer
+
+__global__ void __launch_bounds__(PQ_THREADS) pq_snappy_kernel(uint8_t* buf, const PqInflate* __restrict__ jobs, int njobs,
+                                                               int32_t* status) {
+    const int lane = threadIdx.x & 31;
+    const int j = blockIdx.x * PQ_WARPS + (threadIdx.x >> 5);
+    if (j >= njobs) return;
+    const PqInflate job = jobs[j];
+    const uint8_t* in = buf + job.src;      // compressed bytes: read only
+    uint8_t* out = buf + job.dst;           // this warp's output range: written, and read back by copy elements
+    int64_t ip = 0, op = 0;
+    // preamble: the uncompressed length as a varint (every lane runs the same scalar code)
+    uint64_t n = 0;
+    for (int shift = 0; ip < job.src_bytes && shift < 35; shift += 7) {
+        const uint8_t c = __ldg(in + ip++);
+        n |= (uint64_t)(c & 0x7f) << shift;
+        if (!(c & 0x80)) break;
+    }
+    bool bad = (int64_t)n != job.dst_bytes;
+    while (!bad && op < job.dst_bytes && ip < job.src_bytes) {
+        const unsigned tag = __ldg(in + ip++);
+        if ((tag & 3) == 0) {               // literal
+            int64_t len = tag >> 2;
+            if (len >= 60) {
+                const int extra = (int)len - 59;
+                len = 0;
+                for (int k = 0; k < extra; ++k) len |= (int64_t)__ldg(in + ip + k) << (8 * k);
+                ip += extra;
+            }
+            len += 1;
+            if (ip + len > job.src_bytes || op + len > job.dst_bytes) { bad = true; break; }
+            const uint8_t* s = in + ip;
+            uint8_t* d = out + op;
+            // bytes up to 4-byte alignment of the destination, 4-byte words, tail (source words by funnel shift)
+            const int head = (int)((4 - (reinterpret_cast<uintptr_t>(d) & 3)) & 3);
+            const int64_t h = head < len ? head : len;
+            if (lane < h) d[lane] = __ldg(s + lane);
+            const int64_t words = (len - h) >> 2;
+            for (int64_t w = lane; w < words; w += 32) reinterpret_cast<uint32_t*>(d + h)[w] = pq_load_u32(s + h + 4 * w);
+            const int64_t done = h + 4 * words;
+            if (done + lane < len) d[done + lane] = __ldg(s + done + lane);
+            ip += len;
+            op += len;
+        } else {                            // copy of `len` bytes that start `off` bytes back in the output
+            int64_t len, off;
+            if ((tag & 3) == 1) {
+                len = 4 + ((tag >> 2) & 7);
+                off = ((int64_t)(tag >> 5) << 8) | __ldg(in + ip);
+                ip += 1;
+            } else if ((tag & 3) == 2) {
+                len = (tag >> 2) + 1;
+                off = (int64_t)__ldg(in + ip) | ((int64_t)__ldg(in + ip + 1) << 8);
+                ip += 2;
+            } else {
+                len = (tag >> 2) + 1;
+                off = 0;
+                for (int k = 0; k < 4; ++k) off |= (int64_t)__ldg(in + ip + k) << (8 * k);
+                ip += 4;
+            }
+            if (off <= 0 || off > op || op + len > job.dst_bytes || ip > job.src_bytes) { bad = true; break; }
+            // an overlapping copy (off < len) repeats the last `off` bytes: byte i comes from i mod off
+            for (int64_t i = lane; i < len; i += 32) out[op + i] = __ldcg(out + op - off + (i % off));
+            op += len;
+        }
+        __syncwarp();                       // the bytes just written may be the source of the next copy
+    }
+    if (lane == 0 && (bad || op != job.dst_bytes)) atomicAdd(status + 3, 1);
+}
+
+// ---------------------------------------------------------------- PLAIN BYTE_ARRAY pages
+struct PqStringPage {
+    int64_t val_offset;   // byte offset of the page's values: [u32 length][bytes] ...
+    int32_t val_bytes;
+    int32_t max_values;   // at most this many values (the non-null ones; their exact number is in the levels)
+    int64_t out_offset;   // element offset of the page's slot numbers in the int32 output
+};
+
+__device__ __forceinline__ uint64_t pq_string_hash(const uint8_t* p, int len) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (int i = 0; i < len; ++i) h = (h ^ (uint64_t)p[i]) * 0x100000001b3ull;
+    h = mix64(h ^ (uint64_t)len);
+    return h ? h : 1;
+}
+// representative of a slot: offset << 24 | length (the CSV decoder's packing with the "quoted" bit clear, so the
+// host reads the labels back the same way)
+__device__ __forceinline__ int pq_dict_slot(uint64_t* hash_tab, uint64_t* rep_tab, uint32_t mask, const uint8_t* buf,
+                                            const uint8_t* s, int len, uint64_t h) {
+    const uint64_t rep = ((uint64_t)(s - buf) << 24) | (uint64_t)len;
+    uint32_t slot = (uint32_t)(h >> 24) & mask;
+    for (uint32_t probe = 0; probe <= mask; ++probe) {
+        uint64_t cur = ld_relaxed_u64(hash_tab + slot);
+        if (cur == 0) {
+            cur = atomicCAS(reinterpret_cast<unsigned long long*>(hash_tab + slot), 0ull, (unsigned long long)h);
+            if (cur == 0) {
+                st_relaxed_u64(rep_tab + slot, rep);
+                return (int)slot;
+            }
+        }
+        if (cur == h) {
+            uint64_t r;
+            do { r = ld_relaxed_u64(rep_tab + slot); } while (r == 0);
+            const int rl = (int)(r & 0x7fffff);
+            const uint8_t* rp = buf + (r >> 24);
+            bool same = rl == len;
+            for (int i = 0; same && i < len; ++i) same = rp[i] == s[i];
+            if (same) return (int)slot;
+        }
+        slot = (slot + 1) & mask;
+    }
+    return -1;
+}
+
+__global__ void __launch_bounds__(PQ_THREADS) pq_plain_strings_kernel(const uint8_t* __restrict__ buf,
+                                                                      const PqStringPage* __restrict__ pages, int npages,
+                                                                      uint64_t* hash_tab, uint64_t* rep_tab, uint32_t mask,
+                                                                      int32_t* out, int32_t* status) {
+    const int lane = threadIdx.x & 31;
+    const int pi = blockIdx.x * PQ_WARPS + (threadIdx.x >> 5);
+    if (pi >= npages) return;
+    const PqStringPage pg = pages[pi];
+    const uint8_t* base = buf + pg.val_offset;
+    int64_t pos = 0;
+    for (int v0 = 0; v0 < pg.max_values && pos + 4 <= pg.val_bytes; v0 += 32) {
+        // lane 0 walks 32 links of the chain; the others receive their value's position and length
+        int my_pos = -1, my_len = 0;
+        if (lane == 0) my_pos = 0;
+        int64_t p = pos;
+        int count = 0;
+        for (int k = 0; k < 32; ++k) {
+            int len = -1;
+            if (lane == 0 && v0 + k < pg.max_values && p + 4 <= pg.val_bytes) {
+                len = (int)pq_load_u32(base + p);
+                if (len < 0 || len >= (1 << 23) || p + 4 + len > pg.val_bytes) len = -2;
+            }
+            len = __shfl_sync(0xffffffffu, len, 0);
+            if (len == -2) { if (lane == 0) atomicAdd(status + 1, 1); len = -1; }
+            if (len < 0) break;
+            const int64_t at = __shfl_sync(0xffffffffu, p, 0);
+            if (lane == k) { my_pos = (int)(at + 4); my_len = len; }
+            if (lane == 0) p += 4 + len;
+            ++count;
+        }
+        pos = __shfl_sync(0xffffffffu, p, 0);
+        if (lane < count) {
+            const uint8_t* sp = base + my_pos;
+            const int slot = pq_dict_slot(hash_tab, rep_tab, mask, buf, sp, my_len, pq_string_hash(sp, my_len));
+            if (slot < 0) atomicAdd(status + 0, 1);     // dictionary full
+            out[pg.out_offset + v0 + lane] = slot;
+        }
+        if (count < 32) break;
+    }
 }
 
 struct PqGatherParams {
@@ -372,6 +539,40 @@ extern "C" int etl_parquet_gather_pages(etl_handle* hh, const uint8_t* file, con
     p.dict = d_dict; p.dict_size = d_dict_size; p.string_column = string_column; p.out = out; p.valid = valid;
     p.status = d_status;
     etl::pq_gather_kernel<<<(unsigned)npages, etl::PQ_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(p);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_parquet_inflate_pages(etl_handle* hh, uint8_t* buffer, const void* d_jobs, int32_t njobs, int32_t* d_status,
+                                         void* stream_) {
+    ETL_REQUIRE(hh && d_status, "parquet_inflate_pages: NULL argument");
+    ETL_REQUIRE(njobs >= 0, "parquet_inflate_pages: njobs < 0");
+    if (njobs == 0) return ETL_OK;
+    ETL_REQUIRE(buffer && d_jobs, "parquet_inflate_pages: NULL buffer");
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    const unsigned grid = (unsigned)((njobs + etl::PQ_WARPS - 1) / etl::PQ_WARPS);
+    etl::pq_snappy_kernel<<<grid, etl::PQ_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        buffer, static_cast<const etl::PqInflate*>(d_jobs), njobs, d_status);
+    ETL_CUDA(cudaGetLastError());
+    return ETL_OK;
+}
+
+extern "C" int etl_parquet_plain_strings(etl_handle* hh, const uint8_t* buffer, const void* d_pages, int32_t npages,
+                                         uint64_t* dict_hash, uint64_t* dict_rep, int32_t dict_capacity, int32_t* d_out,
+                                         int32_t* d_status, void* stream_) {
+    ETL_REQUIRE(hh && d_status, "parquet_plain_strings: NULL argument");
+    ETL_REQUIRE(npages >= 0, "parquet_plain_strings: npages < 0");
+    if (npages == 0) return ETL_OK;
+    ETL_REQUIRE(buffer && d_pages && dict_hash && dict_rep && d_out, "parquet_plain_strings: NULL buffer");
+    ETL_REQUIRE(dict_capacity >= 2 && (dict_capacity & (dict_capacity - 1)) == 0,
+                "parquet_plain_strings: dict_capacity=%d is not a power of two", dict_capacity);
+    Handle* h = reinterpret_cast<Handle*>(hh);
+    ETL_CUDA(cudaSetDevice(h->device));
+    const unsigned grid = (unsigned)((npages + etl::PQ_WARPS - 1) / etl::PQ_WARPS);
+    etl::pq_plain_strings_kernel<<<grid, etl::PQ_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(
+        buffer, static_cast<const etl::PqStringPage*>(d_pages), npages, dict_hash, dict_rep, (uint32_t)dict_capacity - 1, d_out,
+        d_status);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }

@@ -582,6 +582,15 @@ class Engine:
                                                     self._stream()))
         self.launches += 1
 
+    def peer_copy_slabs(self, send: torch.Tensor, peer_ptrs: Sequence[int], my_rank: int, buckets: int, bucket0: int,
+                        nbuckets: int, slab_capacity: int, cursor: torch.Tensor, ctas_per_slab: int = 0) -> None:
+        """The filled part of this rank's slabs of a bucket group -> every owner's receive buffer (NVLink stores)."""
+        ranks = len(peer_ptrs)
+        P = C.c_void_p * ranks
+        _lib.check(self.lib.etl_peer_copy_slabs(self._h, send.data_ptr(), P(*peer_ptrs), ranks, my_rank, buckets, bucket0, nbuckets,
+                                                slab_capacity, cursor.data_ptr(), ctas_per_slab, self._stream()))
+        self.launches += 1
+
     def copy_async(self, dst_ptr: int, src_ptr: int, nbytes: int) -> None:
         """Stream-ordered device-to-device copy on the current stream (copy engine); dst may be peer memory."""
         _lib.check(self.lib.etl_copy_async(self._h, dst_ptr, src_ptr, nbytes, self._stream()))
@@ -714,34 +723,63 @@ class Engine:
     _PQ_PAGE = np.dtype([("row", "<i8"), ("n", "<i4"), ("kind", "<i4"), ("lvl", "<i8"), ("val", "<i8"), ("dict", "<i4"),
                          ("pad", "<i4")])
 
-    def parquet_decode_columns(self, data: torch.Tensor, rows: int, jobs: Sequence[dict]) -> List[Column]:
-        """Decode several columns of one file (device buffer `data`) from the page
-        tables of parquet.py.  jobs[i] = {"pages": int64[p, 8] (row_start, num_values,
-        def_offset, def_bytes, val_offset, val_bytes, dict_id, bit_width),
-        "kind_plain", "string", "dicts": [device lookup tables]}.  All hybrid streams
-        of all columns (definition levels and dictionary indices) expand in ONE
-        launch into one int32 buffer; then one gather launch per column; the tables
-        reach the device in one copy and the status words are read back once."""
+    _PQ_INFLATE = np.dtype([("src", "<i8"), ("src_bytes", "<i8"), ("dst", "<i8"), ("dst_bytes", "<i8")])
+    _PQ_STRPAGE = np.dtype([("val", "<i8"), ("bytes", "<i4"), ("maxv", "<i4"), ("out", "<i8")])
+
+    def parquet_inflate(self, data: torch.Tensor, jobs: Sequence[Tuple[int, int, int, int]]) -> torch.Tensor:
+        """Snappy pages (src, src_bytes, dst, dst_bytes: byte offsets in `data`) -> inflated
+        in place behind the file bytes.  Returns the int32[4] status words every later
+        Parquet call adds to (read back once, by parquet_decode_columns)."""
+        status = torch.zeros(4, dtype=torch.int32, device=self.device)
+        if jobs:
+            tab = np.zeros(len(jobs), dtype=self._PQ_INFLATE)
+            arr = np.asarray(jobs, dtype=np.int64).reshape(-1, 4)
+            tab["src"], tab["src_bytes"], tab["dst"], tab["dst_bytes"] = arr[:, 0], arr[:, 1], arr[:, 2], arr[:, 3]
+            if int((arr[:, 2] + arr[:, 3]).max()) > data.shape[0]:
+                raise _lib.EtlError(-1, "parquet: the buffer has no room for the inflated pages")
+            d_tab = torch.from_numpy(tab.view(np.uint8)).to(self.device)
+            _lib.check(self.lib.etl_parquet_inflate_pages(self._h, data.data_ptr(), d_tab.data_ptr(), len(jobs),
+                                                          status.data_ptr(), self._stream()))
+            self.launches += 1
+        return status
+
+    def parquet_decode_columns(self, data: torch.Tensor, rows: int, jobs: Sequence[dict], status: Optional[torch.Tensor] = None,
+                               dict_capacity: int = 1 << 16):
+        """Decode several columns of one file (device buffer `data`, compressed pages
+        already inflated by parquet_inflate) from the page tables of parquet.py.
+        jobs[i] = {"pages": int64[p, 8] (row_start, num_values, def_offset, def_bytes,
+        val_offset, val_bytes, dict_id, bit_width; bit_width -1 = read it on the
+        device), "kind_plain", "string", "dictionaries": per row group a label list
+        (strings) or a float64 array (numerics)}.  All hybrid streams of all columns
+        (definition levels and dictionary indices) expand in ONE launch into one int32
+        buffer; PLAIN string pages are entered into a device dictionary; then one
+        gather launch per column.  -> (columns, label lists: sorted labels of the
+        string columns, [] for numeric ones)."""
         if not jobs:
-            return []
-        streams, pages, dict_ptrs, dict_sizes, keep = [], [], [], [], []
-        out_total = run_total = 0
-        page_slices = []
+            return [], []
+        from .table import _dictionary_labels   # (shared with the CSV decoder's dictionary read-back)
+
+        status = torch.zeros(4, dtype=torch.int32, device=self.device) if status is None else status
+        streams, str_pages, out_total, run_total = [], [], 0, 0
+        plans = []
         for job in jobs:
             P = np.asarray(job["pages"], dtype=np.int64).reshape(-1, 8)
             n_pages = P.shape[0]
             row, nv, def_off, def_bytes, val_off, val_bytes, dict_id, bw = (P[:, i] for i in range(8))
             has_def, is_dict = def_off >= 0, dict_id >= 0
+            is_plain_str = (~is_dict) & bool(job["string"])
             if (bw[is_dict] > 32).any():
                 raise _lib.EtlError(-4, f"parquet: dictionary index width {int(bw[is_dict].max())}")
-            # output / run-table offsets: levels of the pages that have them, then the indices of the dictionary pages
+            # output offsets: levels of the pages that have them, then the indices of the dictionary pages and the
+            # dictionary slots of the PLAIN string pages
             span = nv + 8
             lvl_out = np.full(n_pages, -1, dtype=np.int64)
             lvl_out[has_def] = out_total + np.cumsum(span[has_def]) - span[has_def]
             out_total += int(span[has_def].sum())
             idx_out = np.zeros(n_pages, dtype=np.int64)
-            idx_out[is_dict] = out_total + np.cumsum(span[is_dict]) - span[is_dict]
-            out_total += int(span[is_dict].sum())
+            indexed = is_dict | is_plain_str
+            idx_out[indexed] = out_total + np.cumsum(span[indexed]) - span[indexed]
+            out_total += int(span[indexed].sum())
             for mask, src, nbytes, width, out, exact in ((has_def, def_off, def_bytes, np.ones_like(bw), lvl_out, 1),
                                                          (is_dict, val_off + 1, val_bytes - 1, bw, idx_out, 0)):
                 k = int(mask.sum())
@@ -754,54 +792,76 @@ class Engine:
                 st["run"] = run_total + np.cumsum(cap) - cap
                 run_total += int(cap.sum())
                 streams.append(st)
-            pg = np.zeros(n_pages, dtype=self._PQ_PAGE)
-            pg["row"], pg["n"], pg["lvl"] = row, nv, lvl_out
-            pg["kind"] = np.where(is_dict, 4, job["kind_plain"])
-            pg["val"] = np.where(is_dict, idx_out, val_off)
-            pg["dict"] = np.where(is_dict, dict_id + len(dict_ptrs), -1)
-            page_slices.append((sum(x.shape[0] for x in pages), n_pages))
-            pages.append(pg)
-            dict_ptrs += [t.data_ptr() for t in job["dicts"]]
-            dict_sizes += [t.shape[0] for t in job["dicts"]]
-            keep += list(job["dicts"])
-        # one host blob -> one copy: streams | pages | dictionary pointers | dictionary sizes (16-byte aligned parts)
-        parts = [np.concatenate(streams).view(np.uint8) if streams else np.zeros(0, np.uint8),
-                 np.concatenate(pages).view(np.uint8),
-                 np.asarray(dict_ptrs or [0], dtype=np.int64).view(np.uint8),
-                 np.asarray(dict_sizes or [0], dtype=np.int32).view(np.uint8)]
-        offs, total = [], 0
-        for part in parts:
-            offs.append(total)
-            total += (part.nbytes + 15) // 16 * 16
-        blob = np.zeros(total, dtype=np.uint8)
-        for o, part in zip(offs, parts):
-            blob[o:o + part.nbytes] = part
-        d_blob = torch.from_numpy(blob).to(self.device)
-        base = d_blob.data_ptr()
-        status = torch.zeros(4, dtype=torch.int32, device=self.device)
+            sp = None
+            if is_plain_str.any():
+                sp = np.zeros(int(is_plain_str.sum()), dtype=self._PQ_STRPAGE)
+                sp["val"], sp["bytes"], sp["maxv"], sp["out"] = (val_off[is_plain_str], val_bytes[is_plain_str], nv[is_plain_str],
+                                                                 idx_out[is_plain_str])
+            plans.append((P, lvl_out, idx_out, is_dict, is_plain_str, sp))
         decoded = self.empty(max(out_total, 1), torch.int32)
         nstreams = sum(x.shape[0] for x in streams)
         if nstreams:
-            _lib.check(self.lib.etl_parquet_expand_streams(self._h, data.data_ptr(), base + offs[0], nstreams, None,
+            d_streams = torch.from_numpy(np.concatenate(streams).view(np.uint8)).to(self.device)
+            _lib.check(self.lib.etl_parquet_expand_streams(self._h, data.data_ptr(), d_streams.data_ptr(), nstreams, None,
                                                            decoded.data_ptr(), status.data_ptr(), self._stream()))
             self.launches += 1
-        cols = []
-        for job, (first, count) in zip(jobs, page_slices):
+        # PLAIN string pages -> device dictionaries (one per column), read back for their labels
+        device_dicts = []
+        for job, (P, lvl_out, idx_out, is_dict, is_plain_str, sp) in zip(jobs, plans):
+            if sp is None:
+                device_dicts.append(None)
+                continue
+            hash_tab = torch.zeros(dict_capacity, dtype=torch.int64, device=self.device)
+            rep_tab = torch.zeros(dict_capacity, dtype=torch.int64, device=self.device)
+            d_sp = torch.from_numpy(sp.view(np.uint8)).to(self.device)
+            _lib.check(self.lib.etl_parquet_plain_strings(self._h, data.data_ptr(), d_sp.data_ptr(), sp.shape[0],
+                                                          hash_tab.data_ptr(), rep_tab.data_ptr(), dict_capacity,
+                                                          decoded.data_ptr(), status.data_ptr(), self._stream()))
+            self.launches += 1
+            device_dicts.append((hash_tab, rep_tab))
+        cols, label_lists, keep = [], [], []
+        for job, (P, lvl_out, idx_out, is_dict, is_plain_str, sp), dd in zip(jobs, plans, device_dicts):
+            n_pages = P.shape[0]
+            row, nv, val_off, dict_id = P[:, 0], P[:, 1], P[:, 4], P[:, 6]
+            # lookup tables of this column: one per row-group dictionary (+ one for the device dictionary's slots)
+            tables, labels = [], []
+            if job["string"]:
+                used, dev_labels = _dictionary_labels(data, *dd) if dd is not None else (np.zeros(0, np.int64), [])
+                labels = sorted({s for d in job["dictionaries"] for s in d} | set(dev_labels))
+                pos = {s: i for i, s in enumerate(labels)}
+                tables = [torch.tensor([pos[s] for s in d] or [0], dtype=torch.int32, device=self.device) for d in job["dictionaries"]]
+                if dd is not None:
+                    slot_codes = np.full(dict_capacity, -1, dtype=np.int32)
+                    slot_codes[used] = [pos[s] for s in dev_labels]
+                    tables.append(torch.from_numpy(slot_codes).to(self.device))
+            else:
+                tables = [torch.from_numpy(np.ascontiguousarray(d)).to(self.device) for d in job["dictionaries"]]
+            keep += tables
+            pg = np.zeros(n_pages, dtype=self._PQ_PAGE)
+            pg["row"], pg["n"], pg["lvl"] = row, nv, lvl_out
+            indexed = is_dict | is_plain_str
+            pg["kind"] = np.where(indexed, 4, job["kind_plain"])
+            pg["val"] = np.where(indexed, idx_out, val_off)
+            pg["dict"] = np.where(is_dict, dict_id, np.where(is_plain_str, len(tables) - 1, -1))
             out = self.empty(rows, torch.int32 if job["string"] else torch.float64)
             valid = torch.zeros(words_for(rows), dtype=torch.int32, device=self.device)
-            if count:
+            if n_pages:
+                d_pg = torch.from_numpy(pg.view(np.uint8)).to(self.device)
+                d_ptrs = torch.tensor([t.data_ptr() for t in tables] or [0], dtype=torch.int64, device=self.device)
+                d_sizes = torch.tensor([t.shape[0] for t in tables] or [0], dtype=torch.int32, device=self.device)
+                keep += [d_pg, d_ptrs, d_sizes]
                 _lib.check(self.lib.etl_parquet_gather_pages(
-                    self._h, data.data_ptr(), base + offs[1] + first * self._PQ_PAGE.itemsize, count, decoded.data_ptr(),
-                    decoded.data_ptr(), base + offs[2], base + offs[3], int(job["string"]), out.data_ptr(), valid.data_ptr(),
-                    status.data_ptr(), self._stream()))
+                    self._h, data.data_ptr(), d_pg.data_ptr(), n_pages, decoded.data_ptr(), decoded.data_ptr(), d_ptrs.data_ptr(),
+                    d_sizes.data_ptr(), int(job["string"]), out.data_ptr(), valid.data_ptr(), status.data_ptr(), self._stream()))
                 self.launches += 1
             cols.append(Column(out, valid))
+            label_lists.append(labels)
         st = status.cpu().tolist()
-        if st[0] or st[1] or st[2]:
-            raise _lib.EtlError(-4, f"parquet decode: run-table overflow {st[0]}, short streams {st[1]}, "
-                                    f"dictionary indices out of range {st[2]}")
+        if any(st):
+            raise _lib.EtlError(-4, f"parquet decode: string dictionary full {st[0]}, short or malformed streams {st[1]}, "
+                                    f"dictionary indices out of range {st[2]}, corrupt Snappy pages {st[3]}")
         del keep
-        return cols
+        return cols, label_lists
 
     # ------------------------------------------------- KMeans passes (8f rank 2)
     def kmeans_prepare(self, centers: torch.Tensor, num_labels: int, repeats: int):

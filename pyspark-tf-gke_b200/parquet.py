@@ -9,10 +9,16 @@ RLE / bit-packed hybrid streams (definition levels, dictionary indices) are
 expanded, values are gathered to their rows, nulls become validity bits, numeric
 types are cast to double, dictionary indices become label codes.
 
-Supported: flat schemas; UNCOMPRESSED column chunks; data pages v1 and v2; PLAIN
-for DOUBLE / FLOAT / INT32 / INT64; RLE_DICTIONARY / PLAIN_DICTIONARY for
-BYTE_ARRAY (strings) and the numeric types.  Anything else raises
-ParquetUnsupported - never a silent wrong answer."""
+Supported: flat schemas; UNCOMPRESSED and SNAPPY column chunks (what Spark and
+pyarrow write by default - the reference's model.save / pipeline_model.save,
+spark_workload_to_cloud_k8s.py:149-154, produce *.snappy.parquet): compressed data
+pages are inflated on the device (pq_snappy_kernel) into a region behind the file
+bytes; dictionary pages (small) are inflated here; data pages v1 and v2; PLAIN for
+DOUBLE / FLOAT / INT32 / INT64 / BYTE_ARRAY; RLE_DICTIONARY / PLAIN_DICTIONARY
+for BYTE_ARRAY (strings) and the numeric types.  PLAIN string pages (a writer's
+fallback when its dictionary grows too large) go through a device dictionary
+like CSV cells.  Anything else raises ParquetUnsupported - never a silent wrong
+answer."""
 from __future__ import annotations
 
 import struct
@@ -97,6 +103,61 @@ class _Thrift:
             out[fid] = self.value(t)
 
 
+def snappy_decode(buf, pos: int, end: int, limit: Optional[int] = None) -> bytes:
+    """Snappy block format (the raw format Parquet uses), bytes [pos, end) of buf ->
+    the first `limit` uncompressed bytes (all of them when None).  Host side only:
+    dictionary pages and the first bytes of a v1 data page (its definition-level
+    length); the data pages themselves are inflated on the device."""
+    n = shift = 0
+    while True:
+        c = buf[pos]
+        pos += 1
+        n |= (c & 0x7F) << shift
+        if not c & 0x80:
+            break
+        shift += 7
+    want = n if limit is None else min(n, limit)
+    out = bytearray()
+    while len(out) < want and pos < end:
+        tag = buf[pos]
+        pos += 1
+        kind = tag & 3
+        if kind == 0:
+            ln = tag >> 2
+            if ln >= 60:
+                extra = ln - 59
+                ln = int.from_bytes(buf[pos:pos + extra], "little")
+                pos += extra
+            ln += 1
+            out += buf[pos:pos + ln]
+            pos += ln
+            continue
+        if kind == 1:
+            ln = 4 + ((tag >> 2) & 7)
+            off = ((tag >> 5) << 8) | buf[pos]
+            pos += 1
+        elif kind == 2:
+            ln = (tag >> 2) + 1
+            off = buf[pos] | (buf[pos + 1] << 8)
+            pos += 2
+        else:
+            ln = (tag >> 2) + 1
+            off = int.from_bytes(buf[pos:pos + 4], "little")
+            pos += 4
+        if off == 0 or off > len(out):
+            raise ParquetUnsupported("corrupt snappy stream (copy offset outside the output)")
+        start = len(out) - off
+        if off >= ln:
+            out += out[start:start + ln]
+        else:                      # overlapping copy: the last `off` bytes repeat
+            for i in range(ln):
+                out.append(out[start + i])
+    if limit is None and len(out) != n:
+        raise ParquetUnsupported(f"corrupt snappy stream ({len(out)} of {n} bytes)")
+    return bytes(out[:want])
+
+
+CODEC_NONE, CODEC_SNAPPY = 0, 1
 T_BOOLEAN, T_INT32, T_INT64, T_INT96, T_FLOAT, T_DOUBLE, T_BYTE_ARRAY, T_FIXED = range(8)
 ENC_PLAIN, ENC_PLAIN_DICT, ENC_RLE, ENC_BIT_PACKED, ENC_RLE_DICT = 0, 2, 3, 4, 8  # parquet.thrift Encoding
 PAGE_DATA, PAGE_INDEX, PAGE_DICT, PAGE_DATA_V2 = range(4)
@@ -125,6 +186,7 @@ class _ColumnPlan:
     optional: bool
     pages: List[_Page] = field(default_factory=list)
     dictionaries: List[object] = field(default_factory=list)  # list[str] or np.ndarray per row group
+    inflate: List[Tuple[int, int, int, int]] = field(default_factory=list)   # (src, src_bytes, dst, dst_bytes) per compressed page
 
     def page_table(self) -> np.ndarray:
         """int64[pages, 8]: row_start, num_values, def_offset, def_bytes, val_offset, val_bytes,
@@ -144,7 +206,11 @@ def _plain_strings(buf: bytes, n: int) -> List[str]:
     return out
 
 
-def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan]]:
+def _plan(raw: bytes, wanted: Sequence[str], inflated_base: Optional[int] = None) -> Tuple[int, Dict[str, _ColumnPlan], int]:
+    """-> (rows, plans, end of the buffer).  Compressed data pages are given a place
+    in the region that starts at `inflated_base` (default: right behind the padded
+    file bytes) - 64-byte aligned, 64 bytes apart - and every page offset of such a
+    page points there; the third result is where that region ends."""
     if raw[:4] != b"PAR1" or raw[-4:] != b"PAR1":
         raise ParquetUnsupported("not a Parquet file (or an encrypted footer)")
     (flen,) = struct.unpack_from("<I", raw, len(raw) - 8)
@@ -164,6 +230,15 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
         if rep == 2:
             raise ParquetUnsupported(f"column {name}: repeated fields are not supported")
         plans[name] = _ColumnPlan(name, e[1], rep == 1)
+    from .table import _padded
+    cursor = _padded(len(raw)) if inflated_base is None else inflated_base
+
+    def place(nbytes: int) -> int:
+        nonlocal cursor
+        at = cursor
+        cursor += (nbytes + 127) // 64 * 64
+        return at
+
     row0 = 0
     for rg in meta[4]:
         for cc in rg[1]:
@@ -172,9 +247,9 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
             if name not in plans:
                 continue
             plan = plans[name]
-            if cm[4] != 0:
-                raise ParquetUnsupported(f"column {name}: compressed column chunks (codec {cm[4]}) are not supported; "
-                                         "write with compression=NONE")
+            codec = cm[4]
+            if codec not in (CODEC_NONE, CODEC_SNAPPY):
+                raise ParquetUnsupported(f"column {name}: compression codec {codec} is not supported (UNCOMPRESSED and SNAPPY are)")
             starts = [x for x in (cm.get(11), cm.get(9)) if x]  # 0 / absent = no such page
             if not starts:
                 continue
@@ -186,12 +261,12 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
                 th = _Thrift(raw, pos)
                 ph = th.struct()
                 body = th.p
-                size = ph[3]
+                size, usize = ph[3], ph[2]          # compressed / uncompressed size of what follows the header
                 if ph[1] == PAGE_DICT:
                     dh = ph[7]
                     if dh[2] not in (ENC_PLAIN, ENC_PLAIN_DICT):
                         raise ParquetUnsupported(f"column {name}: dictionary page encoding {dh[2]}")
-                    blob = raw[body:body + size]
+                    blob = snappy_decode(raw, body, body + size) if codec == CODEC_SNAPPY else raw[body:body + size]
                     if plan.ptype == T_BYTE_ARRAY:
                         plan.dictionaries.append(_plain_strings(blob, dh[1]))
                     elif plan.ptype in _TYPE_WIDTH:
@@ -203,17 +278,26 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
                 elif ph[1] == PAGE_DATA:
                     dh = ph[5]
                     nv, enc = dh[1], dh[2]
-                    p = body
+                    if plan.optional and dh[3] != ENC_RLE:
+                        raise ParquetUnsupported(f"column {name}: definition-level encoding {dh[3]}")
+                    is_dict = enc in (ENC_PLAIN_DICT, ENC_RLE_DICT)
+                    if codec == CODEC_SNAPPY:
+                        # the whole page body is one Snappy block; it is inflated on the device.  The host only needs
+                        # the 4-byte length of the definition levels in front of it: the block's first bytes
+                        p = place(usize)
+                        plan.inflate.append((body, size, p, usize))
+                        p_end, bw = p + usize, -1
+                        first = snappy_decode(raw, body, body + size, 4) if plan.optional else b""
+                    else:
+                        p, p_end, first = body, body + size, raw[body:body + 4]
                     def_off, def_bytes = -1, 0
                     if plan.optional:
-                        if dh[3] != ENC_RLE:
-                            raise ParquetUnsupported(f"column {name}: definition-level encoding {dh[3]}")
-                        (def_bytes,) = struct.unpack_from("<I", raw, p)
+                        (def_bytes,) = struct.unpack("<I", first)
                         def_off = p + 4
                         p += 4 + def_bytes
-                    is_dict = enc in (ENC_PLAIN_DICT, ENC_RLE_DICT)
-                    plan.pages.append(_Page(row, nv, def_off, def_bytes, p, body + size - p, enc, dict_id if is_dict else -1,
-                                            raw[p] if is_dict and body + size > p else 0))
+                    if codec != CODEC_SNAPPY:
+                        bw = raw[p] if is_dict and p_end > p else 0
+                    plan.pages.append(_Page(row, nv, def_off, def_bytes, p, p_end - p, enc, dict_id if is_dict else -1, bw))
                     row += nv
                 elif ph[1] == PAGE_DATA_V2:
                     dh = ph[8]
@@ -221,11 +305,17 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
                     dl, rl = dh[5], dh[6]
                     if rl:
                         raise ParquetUnsupported(f"column {name}: repetition levels present")
-                    def_off = body if (plan.optional and dl) else -1
+                    def_off = body if (plan.optional and dl) else -1      # v2 levels are never compressed
                     is_dict = enc in (ENC_PLAIN_DICT, ENC_RLE_DICT)
-                    vo = body + dl + rl
-                    plan.pages.append(_Page(row, nv, def_off, dl, vo, size - dl - rl, enc, dict_id if is_dict else -1,
-                                            raw[vo] if is_dict and size > dl + rl else 0))
+                    vo, vbytes = body + dl + rl, size - dl - rl
+                    if codec == CODEC_SNAPPY and dh.get(7, True) and vbytes > 0:
+                        ubytes = usize - dl - rl
+                        at = place(ubytes)
+                        plan.inflate.append((vo, vbytes, at, ubytes))
+                        vo, vbytes, bw = at, ubytes, -1
+                    else:
+                        bw = raw[vo] if is_dict and vbytes > 0 else 0
+                    plan.pages.append(_Page(row, nv, def_off, dl, vo, vbytes, enc, dict_id if is_dict else -1, bw))
                     row += nv
                 else:
                     pass  # index pages carry no values
@@ -233,17 +323,20 @@ def _plan(raw: bytes, wanted: Sequence[str]) -> Tuple[int, Dict[str, _ColumnPlan
             if row - row0 != rg[3]:
                 raise ParquetUnsupported(f"column {name}: page rows {row - row0} != row group rows {rg[3]}")
         row0 += rg[3]
-    return int(meta[3]), plans
+    return int(meta[3]), plans, cursor + 64
 
 
-def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]) -> DeviceTable:
+def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str], dict_capacity: int = 1 << 16) -> DeviceTable:
     """The Parquet counterpart of read_csv: numeric columns -> f64 + validity,
     string columns -> dictionary codes (labels sorted ascending) + validity."""
     raw = read_bytes(source)
-    rows, plans = _plan(raw, list(numeric) + list(strings))
-    data = upload_text(eng, raw)
+    rows, plans, buffer_end = _plan(raw, list(numeric) + list(strings))
+    # the file bytes, then room for the pages the device inflates
+    data = upload_text(eng, raw, extra=max(0, buffer_end - _padded_len(len(raw))))
+    jobs_inflate = [j for plan in plans.values() for j in plan.inflate]
+    status = eng.parquet_inflate(data, jobs_inflate)
     table = DeviceTable(eng, rows, header=list(plans))
-    jobs = []   # (name, want_string, labels, plan): decoded together, one launch for all their streams
+    jobs = []   # (name, want_string, plan): decoded together, one launch for all their streams
     for name in list(numeric) + list(strings):
         want_string = name in strings
         if name not in plans:  # absent column: all null, as read_csv does
@@ -256,20 +349,16 @@ def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[
         plan = plans[name]
         if want_string != (plan.ptype == T_BYTE_ARRAY):
             raise ParquetUnsupported(f"column {name}: physical type {plan.ptype} does not match the requested kind")
-        labels: List[str] = []
-        if want_string:
-            if any(pg.dict_id < 0 for pg in plan.pages):
-                raise ParquetUnsupported(f"column {name}: PLAIN-encoded string pages (dictionary fallback) are not supported")
-            labels = sorted({s for d in plan.dictionaries for s in d})
-        else:
+        if not want_string:
             if plan.ptype not in _TYPE_WIDTH:
                 raise ParquetUnsupported(f"column {name}: physical type {plan.ptype}")
-            for pg in plan.pages:
-                if pg.dict_id < 0 and pg.encoding != ENC_PLAIN:
-                    raise ParquetUnsupported(f"column {name}: value encoding {pg.encoding}")
-        jobs.append((name, want_string, labels, plan))
-    cols = eng.parquet_decode_columns(data, rows, [column_job(eng, plan, want_string, labels) for _, want_string, labels, plan in jobs])
-    for (name, want_string, labels, plan), col in zip(jobs, cols):
+        for pg in plan.pages:
+            if pg.dict_id < 0 and pg.encoding != ENC_PLAIN:
+                raise ParquetUnsupported(f"column {name}: value encoding {pg.encoding}")
+        jobs.append((name, want_string, plan))
+    cols, label_lists = eng.parquet_decode_columns(data, rows, [column_job(plan, want_string) for _, want_string, plan in jobs],
+                                                   status=status, dict_capacity=dict_capacity)
+    for (name, want_string, plan), col, labels in zip(jobs, cols, label_lists):
         if want_string:
             table.strings[name] = StringColumn(col, labels)
         else:
@@ -278,13 +367,13 @@ def read_parquet(eng: Engine, source, numeric: Sequence[str], strings: Sequence[
     return table
 
 
-def column_job(eng: Engine, plan: _ColumnPlan, want_string: bool, labels: Sequence[str]) -> dict:
+def _padded_len(n: int) -> int:
+    from .table import _padded
+    return _padded(n)
+
+
+def column_job(plan: _ColumnPlan, want_string: bool) -> dict:
     """One column's work order for Engine.parquet_decode_columns: the page table, the PLAIN value
-    kind and the per-row-group lookup tables (labels -> sorted codes, or numeric dictionary values)."""
-    if want_string:
-        pos = {s: i for i, s in enumerate(labels)}
-        dicts = [torch.tensor([pos[s] for s in d] or [0], dtype=torch.int32, device=eng.device) for d in plan.dictionaries]
-    else:
-        dicts = [torch.from_numpy(np.ascontiguousarray(d)).to(eng.device) for d in plan.dictionaries]
+    kind and the per-row-group dictionaries (label lists for strings, value arrays for numerics)."""
     kind = {T_DOUBLE: KIND_F64, T_FLOAT: KIND_F32, T_INT32: KIND_I32, T_INT64: KIND_I64}.get(plan.ptype, KIND_DICT)
-    return {"pages": plan.page_table(), "kind_plain": kind, "string": want_string, "dicts": dicts}
+    return {"pages": plan.page_table(), "kind_plain": kind, "string": want_string, "dictionaries": plan.dictionaries}

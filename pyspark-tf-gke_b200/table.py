@@ -86,11 +86,12 @@ class PinnedRing:
         self.stream = torch.cuda.Stream(device=device)
         self.pool = ThreadPoolExecutor(max_workers=slots)
 
-    def upload(self, fill, nbytes: int) -> torch.Tensor:
+    def upload(self, fill, nbytes: int, extra: int = 0) -> torch.Tensor:
         """fill(view: np.ndarray[uint8], offset, length) writes bytes [offset, offset + length) of the
-        input into `view`.  -> device uint8 tensor, zero padded (see _padded)."""
-        dst = torch.empty(_padded(nbytes), dtype=torch.uint8, device=self.device)
-        dst[nbytes:].zero_()
+        input into `view`.  -> device uint8 tensor, zero padded (see _padded), with `extra` more
+        (uninitialised) bytes behind the padding."""
+        dst = torch.empty(_padded(nbytes) + extra, dtype=torch.uint8, device=self.device)
+        dst[nbytes:_padded(nbytes)].zero_()
         main = torch.cuda.current_stream(self.device)
         self.stream.wait_stream(main)
         slots, sb = len(self.bufs), self.slot_bytes
@@ -125,15 +126,16 @@ def _ring(eng: Engine) -> PinnedRing:
     return ring
 
 
-def upload_text(eng: Engine, raw) -> torch.Tensor:
+def upload_text(eng: Engine, raw, extra: int = 0) -> torch.Tensor:
     """File bytes -> device uint8 tensor, zero padded to a multiple of 64 (+64)
-    so the decoder's 8- and 16-byte window loads never leave the allocation."""
+    so the decoder's 8- and 16-byte window loads never leave the allocation;
+    `extra` more bytes behind that (the Parquet reader inflates pages there)."""
     src = np.frombuffer(raw, dtype=np.uint8)
 
     def fill(view, off, ln):
         view[:] = src[off:off + ln]
 
-    return _ring(eng).upload(fill, len(raw))
+    return _ring(eng).upload(fill, len(raw), extra)
 
 
 def upload_file(eng: Engine, path: str):
@@ -181,15 +183,83 @@ def _dictionary_labels(text: torch.Tensor, hash_tab: torch.Tensor, rep_tab: torc
     return used, labels
 
 
+def byte_range_of(path: str, rank: int, world_size: int):
+    """This rank's share of a CSV file when it is split by byte range at record
+    boundaries, the way Spark's CSV source splits a file with its default
+    multiLine=false (every newline ends a record): -> (header line bytes, first
+    byte, end byte) with the range starting after the first newline at or after the
+    nominal cut and ending after the first newline at or after the next cut.  The
+    header line belongs to no range; every rank reads it separately."""
+    import os
+
+    size = os.path.getsize(path)
+    with open(path, "rb") as fh:
+        header = fh.readline()
+
+        def cut(at: int) -> int:       # the first record start at or after byte `at`
+            if at <= len(header):
+                return len(header)
+            if at >= size:
+                return size
+            fh.seek(at - 1)
+            pos = at - 1
+            while True:
+                block = fh.read(1 << 16)
+                if not block:
+                    return size
+                k = block.find(b"\n")
+                if k >= 0:
+                    return pos + k + 1
+                pos += len(block)
+
+        return header, cut(size * rank // world_size), cut(size * (rank + 1) // world_size)
+
+
+def upload_file_range(eng: Engine, path: str, header: bytes, lo: int, hi: int):
+    """header line + bytes [lo, hi) of the file -> device text (what read_csv decodes on this rank)."""
+    import os
+
+    if header and not header.endswith(b"\n"):
+        header += b"\n"
+    hl = len(header)
+    n = hl + (hi - lo)
+    hsrc = np.frombuffer(header, dtype=np.uint8)
+    fd = os.open(path, os.O_RDONLY)
+    try:
+        def fill(view, off, ln):
+            got = 0
+            if off < hl:               # the slice starts inside the header line
+                got = min(ln, hl - off)
+                view[:got] = hsrc[off:off + got]
+            while got < ln:
+                k = os.preadv(fd, [memoryview(view)[got:ln]], lo + off + got - hl)
+                if k <= 0:
+                    raise IOError(f"{path}: short read at byte {lo + off + got - hl}")
+                got += k
+
+        text = _ring(eng).upload(fill, n)
+    finally:
+        os.close(fd)
+    return text, n, header
+
+
 def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str], trim_strings: bool = False,
              nan_is_null: bool = False, dict_capacity: int = 1 << 16, shard: Optional[tuple] = None,
-             device_text: Optional[torch.Tensor] = None) -> DeviceTable:
+             device_text: Optional[torch.Tensor] = None, byte_range: Optional[tuple] = None) -> DeviceTable:
     """shard=(rank, world): every rank indexes the whole text (the two index
     passes cost ~1 ms per GB) and decodes only its contiguous share of the records,
-    so quoted newlines need no cross-rank protocol.  device_text: the file already
-    on this GPU (as returned by upload_text), to keep the copy out of a timed region."""
+    so quoted newlines need no cross-rank protocol.  byte_range=(rank, world) (a
+    local file): this rank reads, uploads and decodes ONLY its byte range of the
+    file, cut at newlines (byte_range_of - Spark's split of a CSV file under its
+    default multiLine=false; a file with newlines inside quoted cells needs `shard`
+    instead).  device_text: the file already on this GPU (as returned by
+    upload_text), to keep the copy out of a timed region."""
     head = None
-    if isinstance(source, str) and not source.startswith(("http://", "https://")) and device_text is None:
+    if byte_range is not None:
+        if not isinstance(source, str) or device_text is not None or shard is not None:
+            raise ValueError("read_csv: byte_range needs a local file path (and neither shard nor device_text)")
+        text, n, head = upload_file_range(eng, source, *byte_range_of(source, *byte_range))
+    elif isinstance(source, str) and not source.startswith(("http://", "https://")) and device_text is None:
         text, n, head = upload_file(eng, source)          # file -> pinned ring -> HBM
     else:
         raw = read_bytes(source)

@@ -377,3 +377,35 @@ def test_pinned_ring_upload_of_bytes_and_files(eng, tmp_path):
         assert n == len(raw) and d.cpu().numpy()[:n].tobytes() == raw and head == raw[:1 << 20]
     finally:
         del eng._pinned_ring
+
+
+def test_byte_range_split_of_a_file_covers_every_record_once(eng, tmp_path):
+    # config 5's input split: each "rank" reads, uploads and decodes only its byte range of the file (cut at
+    # newlines, the header line read by everyone); together the ranges hold every record exactly once, in order
+    import pyspark_tf_gke_b200.table as T
+
+    text = health_text("workloads")
+    path = tmp_path / "health.csv"
+    path.write_text(text)
+    whole = pkg.read_csv(eng, str(path), ["value", "lower_ci", "upper_ci"], ["measure_name"])
+    for world in (1, 3, 8):
+        parts = [pkg.read_csv(eng, str(path), ["value", "lower_ci", "upper_ci"], ["measure_name"], byte_range=(r, world))
+                 for r in range(world)]
+        assert sum(p.rows for p in parts) == whole.rows == 18155
+        ranges = [T.byte_range_of(str(path), r, world) for r in range(world)]
+        assert ranges[0][1] == len(ranges[0][0]) and ranges[-1][2] == len(text.encode())
+        assert all(a[2] == b[1] for a, b in zip(ranges[:-1], ranges[1:]))
+        for c in ("value", "lower_ci", "upper_ci"):
+            got = np.concatenate([p.numeric[c].data.cpu().numpy() for p in parts])
+            ok = np.concatenate([p.numeric[c].valid_host() for p in parts])
+            assert (ok == whole.numeric[c].valid_host()).all()
+            assert got[ok].tobytes() == whole.numeric[c].data.cpu().numpy()[ok].tobytes()
+        labels = np.concatenate([np.array(p.strings["measure_name"].labels, dtype=object)[p.strings["measure_name"].column.data.cpu().numpy()]
+                                 for p in parts if p.rows])
+        want = np.array(whole.strings["measure_name"].labels, dtype=object)[whole.strings["measure_name"].column.data.cpu().numpy()]
+        assert labels.tolist() == want.tolist()
+    # more ranks than records: the surplus ranks get empty tables
+    tiny = tmp_path / "tiny.csv"
+    tiny.write_text("measure_name,value,lower_ci,upper_ci\nx,1,2,3\n")
+    rows = [pkg.read_csv(eng, str(tiny), ["value"], ["measure_name"], byte_range=(r, 4)).rows for r in range(4)]
+    assert sum(rows) == 1

@@ -1,7 +1,8 @@
 """Parquet decode (north-star extension, no reference site): the CUDA page decoder
 against pyarrow's reader on the same file - values bit for bit, nulls exactly,
-string codes through the label table.  Files are written here with pyarrow
-(compression NONE: the supported domain)."""
+string codes through the label table.  Files are written here with pyarrow,
+uncompressed and with Snappy (Spark's and pyarrow's default), dictionary-encoded
+and PLAIN."""
 import io
 
 import numpy as np
@@ -65,10 +66,44 @@ def _check(eng, raw, t, numeric, strings):
 
 @pytest.mark.parametrize("n", [0, 1, 31, 1000, 250_003])
 @pytest.mark.parametrize("version", ["1.0", "2.0"])
-def test_parquet_matches_pyarrow(eng, n, version):
+@pytest.mark.parametrize("codec", ["NONE", "SNAPPY"])
+def test_parquet_matches_pyarrow(eng, n, version, codec):
     t = _table(n, seed=n + 1)
-    raw = _write(t, data_page_version=version, row_group_size=100_000, data_page_size=64 * 1024)
+    raw = _write(t, data_page_version=version, row_group_size=100_000, data_page_size=64 * 1024, compression=codec)
     _check(eng, raw, t, ["value", "lower_ci", "upper_ci", "id"], ["measure_name"])
+
+
+def test_parquet_as_spark_and_pyarrow_write_it_by_default(eng):
+    # no options at all: Snappy, dictionary encoding for every column, 1 MB pages, v1 data pages - and a column
+    # whose dictionary outgrows its limit, so later pages fall back to PLAIN inside a dictionary-encoded chunk
+    n = 600_000
+    t = _table(n, seed=77)
+    rng = np.random.default_rng(78)
+    t = t.append_column("wide", pa.array(rng.random(n) * 1e9, mask=rng.random(n) < 0.05))
+    t = t.append_column("runs", pa.array(np.repeat(np.arange(n // 1000, dtype=np.float64), 1000)))     # compresses to almost nothing
+    buf = io.BytesIO()
+    pq.write_table(t, buf)
+    raw = buf.getvalue()
+    md = pq.ParquetFile(io.BytesIO(raw)).metadata
+    assert md.row_group(0).column(0).compression == "SNAPPY"
+    _check(eng, raw, t, ["value", "lower_ci", "upper_ci", "id", "few", "wide", "runs"], ["measure_name"])
+
+
+@pytest.mark.parametrize("codec", ["NONE", "SNAPPY"])
+def test_parquet_plain_string_pages(eng, codec):
+    # PLAIN BYTE_ARRAY pages (no dictionary, or a writer's fallback when the dictionary grew too large): the
+    # strings go through a device dictionary like CSV cells
+    n = 40_003
+    rng = np.random.default_rng(11)
+    labels = np.array([f"label {i:04d} " + "é" * (i % 7) for i in range(300)] + ["", "x"])
+    t = pa.table({"measure_name": pa.array(rng.choice(labels, n), mask=rng.random(n) < 0.03),
+                  "value": pa.array(rng.random(n), mask=rng.random(n) < 0.07)})
+    raw = _write(t, use_dictionary=False, compression=codec, data_page_size=32 * 1024)
+    _check(eng, raw, t, ["value"], ["measure_name"])
+    # a tiny dictionary page limit: the first pages of each chunk are dictionary-encoded, the rest PLAIN
+    raw = _write(t, use_dictionary=["measure_name"], dictionary_pagesize_limit=1024, compression=codec, data_page_size=8 * 1024,
+                 row_group_size=15_000)
+    _check(eng, raw, t, ["value"], ["measure_name"])
 
 
 def test_parquet_dictionary_encoded_numerics_and_required_columns(eng):
@@ -84,12 +119,20 @@ def test_parquet_dictionary_encoded_numerics_and_required_columns(eng):
 
 def test_parquet_unsupported_inputs_fail_loudly(eng):
     t = _table(1000, seed=9)
-    with pytest.raises(pkg.ParquetUnsupported, match="compressed"):
-        pkg.read_parquet(eng, _write(t, compression="SNAPPY"), ["value"], ["measure_name"])
+    with pytest.raises(pkg.ParquetUnsupported, match="codec"):
+        pkg.read_parquet(eng, _write(t, compression="GZIP"), ["value"], ["measure_name"])
     with pytest.raises(pkg.ParquetUnsupported, match="not a Parquet file"):
         pkg.read_parquet(eng, b"PAR1 nonsense", ["value"], [])
-    with pytest.raises(pkg.ParquetUnsupported, match="PLAIN-encoded string"):
-        pkg.read_parquet(eng, _write(t, use_dictionary=False), [], ["measure_name"])
+    with pytest.raises(pkg.ParquetUnsupported, match="value encoding"):
+        pkg.read_parquet(eng, _write(t, use_dictionary=False, column_encoding={"value": "BYTE_STREAM_SPLIT"}), ["value"], [])
+    # a corrupted Snappy page is reported, not decoded into garbage
+    raw = bytearray(_write(_table(50_000, seed=10), compression="SNAPPY", use_dictionary=False))
+    from pyspark_tf_gke_b200 import parquet as P
+    _, plans, _ = P._plan(bytes(raw), ["value"])
+    src, nbytes, _, _ = plans["value"].inflate[0]
+    raw[src] ^= 0x55                                   # the block's length preamble no longer matches the page header
+    with pytest.raises(pkg.EtlError, match="corrupt Snappy"):
+        pkg.read_parquet(eng, bytes(raw), ["value"], [])
     missing = pkg.read_parquet(eng, _write(t), ["nope"], ["also_nope"])
     assert int(eng.null_count(missing.numeric["nope"]).item()) == 1000
 
@@ -100,7 +143,7 @@ def test_health_parquet_gives_the_same_stage_output_as_health_csv(eng, which, mo
     monkeypatch.setenv("MEASURE_NAME_WEIGHT", "5")
     monkeypatch.setenv("ETL_SKIP_KMEANS", "1")
     arrow = pacsv.read_csv(io.BytesIO(text.encode()), convert_options=pacsv.ConvertOptions(strings_can_be_null=True))
-    raw = _write(arrow)
+    raw = _write(arrow, compression="SNAPPY" if which == "infra" else "NONE")
     cols = (["value", "lower_ci", "upper_ci"], ["measure_name"])
     from_csv, _ = pkg.KMeansWorkload(eng).k_means(pkg.read_csv(eng, text.encode(), *cols))
     from_pq, _ = pkg.KMeansWorkload(eng).k_means(pkg.read_parquet(eng, raw, *cols))

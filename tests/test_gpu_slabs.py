@@ -169,8 +169,8 @@ def test_min_max_on_the_shuffle_path(eng, counted):
     np.testing.assert_allclose(col["mean"].cpu().numpy(), wcol["mean"], rtol=1e-6, atol=0, equal_nan=True)
 
 
-@pytest.mark.parametrize("R,groups_of_buckets", [(2, 4), (4, 2), (8, 8)])
-def test_simulated_bucketed_exchange(eng, R, groups_of_buckets):
+@pytest.mark.parametrize("R,groups_of_buckets,mover", [(2, 4, "sm"), (4, 2, "ce"), (8, 8, "sm"), (8, 1, "ce")])
+def test_simulated_bucketed_exchange(eng, R, groups_of_buckets, mover):
     # BucketExchange's data path on one GPU: every source partitions its rows into R x Bx slabs of a send buffer,
     # slabs are copied bucket group by bucket group into the "ranks'" receive buffers ([source][bucket] layout),
     # cursors go to the count tables, and each receiver cuts + merges one bucket group at a time (append mode)
@@ -185,7 +185,7 @@ def test_simulated_bucketed_exchange(eng, R, groups_of_buckets):
     tables = [torch.zeros(R * bx, dtype=torch.int64, device=eng.device) for _ in range(R)]
     overflow = torch.zeros(1, dtype=torch.int64, device=eng.device)
     bpg = bx // groups_of_buckets
-    sends = []
+    sends, xcurs = [], []
     for s in range(R):
         k, v = torch.from_numpy(rows[s][0]).to(eng.device), torch.from_numpy(rows[s][1]).to(eng.device)
         send = torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device)
@@ -197,6 +197,7 @@ def test_simulated_bucketed_exchange(eng, R, groups_of_buckets):
         want = np.bincount(O.partition_dest(rows[s][0], R, bx), minlength=R * bx)
         assert xcur.cpu().tolist() == want.tolist()
         sends.append(send)
+        xcurs.append(xcur)
     all_k = np.concatenate([k for k, _ in rows])
     all_v = np.concatenate([v for _, v in rows])
     for r in range(R):
@@ -205,8 +206,12 @@ def test_simulated_bucketed_exchange(eng, R, groups_of_buckets):
         pieces = torch.full((bx * sub * cap2, 2), -1, dtype=torch.int64, device=eng.device)
         for g in range(groups_of_buckets):
             for s in range(R):
-                eng.copy_async(recv[r].data_ptr() + ((s * bx + g * bpg) * slab) * 16,
-                               sends[s].data_ptr() + ((r * bx + g * bpg) * slab) * 16, bpg * slab * 16)
+                if mover == "ce":      # whole slabs through a copy engine
+                    eng.copy_async(recv[r].data_ptr() + ((s * bx + g * bpg) * slab) * 16,
+                                   sends[s].data_ptr() + ((r * bx + g * bpg) * slab) * 16, bpg * slab * 16)
+                elif r == 0:           # the store kernel serves every destination at once: the filled parts only
+                    eng.peer_copy_slabs(sends[s], [t.data_ptr() for t in recv], s, bx, g * bpg, bpg, slab, xcurs[s],
+                                        ctas_per_slab=3 if s % 2 else 0)
             eng.slab_partition_records(recv[r], bpg * R, slab, tables[r], None, slab, bx, sub, pieces, cap2, cur2, pg.counters[4:],
                                        sources=R, bucket0=g * bpg)
             eng.merge_slab_pieces(pieces, cur2, cap2, g * bpg * sub, bpg * sub, g > 0, pg)

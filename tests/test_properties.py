@@ -119,7 +119,36 @@ def test_thrift_reader_round_trips_a_pyarrow_footer():
     t = pa.table({"value": pa.array([1.0, None, 3.0]), "measure_name": pa.array(["a", "b", None])})
     buf = io.BytesIO()
     pq.write_table(t, buf, compression="NONE")
-    rows, plans = P._plan(buf.getvalue(), ["value", "measure_name", "absent"])
+    rows, plans, end = P._plan(buf.getvalue(), ["value", "measure_name", "absent"])
     assert rows == 3 and set(plans) == {"value", "measure_name"}
     assert plans["measure_name"].dictionaries == [["a", "b"]]
     assert sum(pg.num_values for pg in plans["value"].pages) == 3 and plans["value"].optional
+    assert not plans["value"].inflate
+    # the same table as Spark / pyarrow write it by default: snappy pages get a place behind the file bytes
+    buf = io.BytesIO()
+    pq.write_table(t, buf, compression="snappy")
+    raw = buf.getvalue()
+    rows, plans, end = P._plan(raw, ["value", "measure_name"])
+    assert rows == 3 and plans["measure_name"].dictionaries == [["a", "b"]]       # dictionary pages are inflated on the host
+    for plan in plans.values():
+        assert len(plan.inflate) == len(plan.pages) == 1
+        src, src_bytes, dst, dst_bytes = plan.inflate[0]
+        assert dst >= len(raw) and dst % 64 == 0 and dst + dst_bytes <= end
+        page = P.snappy_decode(raw, src, src + src_bytes)
+        assert len(page) == dst_bytes
+        pg = plan.pages[0]
+        assert pg.def_offset == dst + 4 and pg.def_bytes == int.from_bytes(page[:4], "little") and pg.bit_width == -1
+        assert pg.val_offset == pg.def_offset + pg.def_bytes and pg.val_offset + pg.val_bytes == dst + dst_bytes
+
+
+def test_snappy_decoder_against_pyarrow():
+    import pyarrow as pa
+
+    from pyspark_tf_gke_b200.parquet import snappy_decode
+
+    rng = np.random.default_rng(0)
+    for data in (b"", b"a", b"abcd" * 1000, bytes(rng.integers(0, 4, 100000, dtype=np.uint8)),
+                 bytes(rng.integers(0, 256, 70000, dtype=np.uint8)), b"\x00" * 100000, b"ab" * 70000 + b"xyz"):
+        c = pa.compress(data, codec="snappy", asbytes=True)
+        assert snappy_decode(c, 0, len(c)) == data
+        assert snappy_decode(c, 0, len(c), 5) == data[:5]
