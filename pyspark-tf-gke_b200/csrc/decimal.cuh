@@ -36,7 +36,7 @@ enum DecStatus : int {
 };
 // bit flags returned through *flags
 constexpr int DEC_FLAG_NONINT = 1;  // had '.', an exponent, or was inf/nan: column is not an integer column
-constexpr int DEC_FLAG_NAN = 2;     // the text was a NaN literal
+constexpr int DEC_FLAG_NAN = 2;     // the text was the bare word nan (any case, no sign)
 
 typedef unsigned __int128 dec_u128;
 
@@ -269,7 +269,9 @@ DEC_HD int dec_parse(const uint8_t* p, int len, double* out, int* flags) {
         if (dec_match_ci(p + i, len - i, "nan", 3)) {
             const uint64_t bits = neg ? 0xfff8000000000000ull : 0x7ff8000000000000ull;
             *out = *reinterpret_cast<const double*>(&bits);
-            *flags |= DEC_FLAG_NAN;
+            // only the bare word is the "missing" marker load_csv tests for (v.lower() == "nan",
+            // train_tf_ps.py:129); "+nan" / "-nan" go through float() and stay NaN values
+            if (i == 0) *flags |= DEC_FLAG_NAN;
             return DEC_OK;
         }
         return DEC_INVALID;

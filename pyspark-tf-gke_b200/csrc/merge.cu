@@ -149,8 +149,10 @@ __device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, 
     if ((int64_t)at < p.spill_capacity) p.spill[at] = r;
 }
 
+// 48 registers: two CTAs take 48 K of the SM's 64 K registers, which leaves room for the exchange's copy CTAs
+// (slabs.cu) to sit beside the merge of the bucket groups that have already landed
 template <bool MINMAX>
-__global__ void __launch_bounds__(MG_THREADS, MINMAX ? 1 : 2) groupby_merge_kernel(const MergeParams p) {
+__global__ void __maxnreg__(48) groupby_merge_kernel(const MergeParams p) {
     extern __shared__ __align__(16) unsigned char mg_smem[];
     const int S = p.slots;
     uint64_t* skey = reinterpret_cast<uint64_t*>(mg_smem);

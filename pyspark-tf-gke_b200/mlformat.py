@@ -92,15 +92,20 @@ def _write_data(path: str, table, spark_schema: dict) -> str:
     return name
 
 
-def _read_data(path: str):
-    import pyarrow as pa
-    import pyarrow.parquet as pq
+def _read_data(path: str) -> dict:
+    """{column: [value per row]} of the part files under <path>/data, through this package's own Parquet
+    reader (parquet.read_nested_small: Snappy, nested lists and structs) - what Spark does on the driver."""
+    from .parquet import read_nested_small
 
     d = os.path.join(path, "data")
     files = sorted(f for f in os.listdir(d) if f.endswith(".parquet"))
     if not files:
         raise FileNotFoundError(f"no parquet part file under {d}")
-    return pa.concat_tables([pq.read_table(os.path.join(d, f)) for f in files])
+    out: dict = {}
+    for f in files:
+        for name, values in read_nested_small(os.path.join(d, f)).items():
+            out.setdefault(name, []).extend(values)
+    return out
 
 
 # ---------------------------------------------------------------- KMeansModel
@@ -140,7 +145,7 @@ def load_kmeans_model(engine, path: str):
     from .kmeans import KMeansModel
 
     meta = _read_metadata(path, KMEANS_CLASS)
-    t = _read_data(path).to_pydict()
+    t = _read_data(path)
     order = np.argsort(np.asarray(t["clusterIdx"]))
     rows = []
     for i in order:
@@ -223,11 +228,11 @@ def load_pipeline_model(engine, path: str):
     classes = [m["class"] for m in metas]
     if classes != [INDEXER_CLASS, ENCODER_CLASS, ASSEMBLER_CLASS]:
         raise ValueError(f"{path}: stages {classes} are not StringIndexerModel -> OneHotEncoderModel -> VectorAssembler")
-    labels_array = _read_data(dirs[0]).to_pydict()["labelsArray"][0]
+    labels_array = _read_data(dirs[0])["labelsArray"][0]
     if len(labels_array) != 1:
         raise ValueError(f"{path}: StringIndexerModel with {len(labels_array)} input columns")
     labels = list(labels_array[0])
-    sizes = _read_data(dirs[1]).to_pydict()["categorySizes"][0]
+    sizes = _read_data(dirs[1])["categorySizes"][0]
     if list(sizes) != [len(labels) + 1]:
         raise ValueError(f"{path}: OneHotEncoder categorySizes {sizes} do not match {len(labels)} labels + 1")
     cols = metas[2]["paramMap"]["inputCols"]

@@ -377,3 +377,242 @@ def column_job(plan: _ColumnPlan, want_string: bool) -> dict:
     kind and the per-row-group dictionaries (label lists for strings, value arrays for numerics)."""
     kind = {T_DOUBLE: KIND_F64, T_FLOAT: KIND_F32, T_INT32: KIND_I32, T_INT64: KIND_I64}.get(plan.ptype, KIND_DICT)
     return {"pages": plan.page_table(), "kind_plain": kind, "string": want_string, "dictionaries": plan.dictionaries}
+
+
+# ---------------------------------------------------------------- small nested files (Spark ML model data)
+# model.save / pipeline_model.save (spark_workload_to_cloud_k8s.py:149-154) write a few hundred bytes of
+# Parquet per model: one row of labelsArray list<list<string>>, one of categorySizes list<int>, k rows of
+# {clusterIdx int, clusterCenter struct<type, size, indices list<int>, values list<double>>}.  Spark reads them
+# on the driver; so does this reader - with the footer / page-header parser, the Snappy decoder and the level
+# decoding of this module (no other Parquet library), assembling records from repetition and definition levels.
+
+def _hybrid_host(buf: bytes, pos: int, end: int, bit_width: int, count: int) -> List[int]:
+    """RLE / bit-packed hybrid stream -> the first `count` values."""
+    out: List[int] = []
+    if bit_width == 0:
+        return [0] * count
+    vbytes = (bit_width + 7) // 8
+    while len(out) < count and pos < end:
+        h = shift = 0
+        while True:
+            c = buf[pos]
+            pos += 1
+            h |= (c & 0x7F) << shift
+            shift += 7
+            if not c & 0x80:
+                break
+        if h & 1:                                   # bit-packed groups of 8
+            n = (h >> 1) * 8
+            nbytes = (h >> 1) * bit_width
+            bits = int.from_bytes(buf[pos:pos + nbytes], "little")
+            mask = (1 << bit_width) - 1
+            out.extend((bits >> (i * bit_width)) & mask for i in range(n))
+            pos += nbytes
+        else:                                       # a run
+            v = int.from_bytes(buf[pos:pos + vbytes], "little")
+            pos += vbytes
+            out.extend([v] * (h >> 1))
+    return out[:count]
+
+
+def _plain_host(ptype: int, buf: bytes, pos: int, n: int) -> list:
+    if ptype == T_BYTE_ARRAY:
+        out = []
+        for _ in range(n):
+            (ln,) = struct.unpack_from("<I", buf, pos)
+            out.append(buf[pos + 4:pos + 4 + ln])
+            pos += 4 + ln
+        return out
+    if ptype == T_BOOLEAN:
+        return [bool((buf[pos + i // 8] >> (i % 8)) & 1) for i in range(n)]
+    fmt = {T_INT32: "<i4", T_INT64: "<i8", T_FLOAT: "<f4", T_DOUBLE: "<f8"}.get(ptype)
+    if fmt is None:
+        raise ParquetUnsupported(f"physical type {ptype}")
+    return np.frombuffer(buf, dtype=fmt, count=n, offset=pos).tolist()
+
+
+@dataclass
+class _Node:
+    name: str
+    repetition: int                 # 0 required, 1 optional, 2 repeated
+    ptype: Optional[int]            # None for groups
+    converted: Optional[int]        # ConvertedType (0 = UTF8, 3 = LIST, 15 INT_8 ...)
+    children: List["_Node"] = field(default_factory=list)
+
+
+def _schema_tree(elements: List[dict]) -> _Node:
+    it = iter(elements)
+
+    def take() -> _Node:
+        e = next(it)
+        node = _Node(e[4].decode(), e.get(3, 0), e.get(1) if not e.get(5) else None, e.get(6))
+        for _ in range(e.get(5, 0) or 0):
+            node.children.append(take())
+        return node
+
+    return take()
+
+
+def _read_leaf(raw: bytes, cm: dict, ptype: int, max_rep: int, max_def: int, string: bool):
+    """One column chunk -> (rep levels, def levels, non-null values), v1 / v2 pages, PLAIN or dictionary."""
+    codec = cm[4]
+    if codec not in (CODEC_NONE, CODEC_SNAPPY):
+        raise ParquetUnsupported(f"compression codec {codec}")
+    starts = [x for x in (cm.get(11), cm.get(9)) if x]
+    pos, end = min(starts), min(starts) + cm[7]
+    reps: List[int] = []
+    defs: List[int] = []
+    vals: list = []
+    dictionary: Optional[list] = None
+    bits = lambda m: max(m, 0).bit_length()       # noqa: E731
+    while pos < end:
+        th = _Thrift(raw, pos)
+        ph = th.struct()
+        body, size = th.p, ph[3]
+        pos = body + size
+        if ph[1] == PAGE_DICT:
+            blob = snappy_decode(raw, body, body + size) if codec == CODEC_SNAPPY else raw[body:body + size]
+            dictionary = _plain_host(ptype, blob, 0, ph[7][1])
+            continue
+        if ph[1] == PAGE_DATA:
+            page = snappy_decode(raw, body, body + size) if codec == CODEC_SNAPPY else raw[body:body + size]
+            nv, enc = ph[5][1], ph[5][2]
+            p = 0
+            r = [0] * nv
+            d = [max_def] * nv
+            if max_rep:
+                (ln,) = struct.unpack_from("<I", page, p)
+                r = _hybrid_host(page, p + 4, p + 4 + ln, bits(max_rep), nv)
+                p += 4 + ln
+            if max_def:
+                (ln,) = struct.unpack_from("<I", page, p)
+                d = _hybrid_host(page, p + 4, p + 4 + ln, bits(max_def), nv)
+                p += 4 + ln
+        elif ph[1] == PAGE_DATA_V2:
+            dh = ph[8]
+            nv, enc, dl, rl = dh[1], dh[4], dh[5], dh[6]
+            r = _hybrid_host(raw, body, body + rl, bits(max_rep), nv) if max_rep else [0] * nv
+            d = _hybrid_host(raw, body + rl, body + rl + dl, bits(max_def), nv) if max_def else [max_def] * nv
+            vb = body + rl + dl
+            page = snappy_decode(raw, vb, body + size) if (codec == CODEC_SNAPPY and dh.get(7, True) and body + size > vb) \
+                else raw[vb:body + size]
+            p = 0
+        else:
+            continue
+        present = sum(1 for x in d if x == max_def)
+        if enc in (ENC_PLAIN_DICT, ENC_RLE_DICT):
+            if dictionary is None:
+                raise ParquetUnsupported("dictionary-encoded page without a dictionary page")
+            idx = _hybrid_host(page, p + 1, len(page), page[p], present) if present else []
+            v = [dictionary[i] for i in idx]
+        elif enc == ENC_PLAIN:
+            v = _plain_host(ptype, page, p, present)
+        else:
+            raise ParquetUnsupported(f"value encoding {enc}")
+        reps += r
+        defs += d
+        vals += [x.decode("utf-8") for x in v] if string else v
+    return reps, defs, vals
+
+
+class _Null:
+    """A null met while descending a leaf's path: `level` = index of the path node that was null."""
+
+    def __init__(self, level: int):
+        self.level = level
+
+
+def _build_leaf(nodes: List[_Node], reps: List[int], defs: List[int], vals: list) -> list:
+    """Record assembly for ONE leaf column: per row, the nested value along the leaf's path - a list per
+    repeated node, _Null(level) where an optional node is null, the leaf value at the bottom.  Groups that
+    are neither null nor repeated are transparent (their fields are zipped by the caller)."""
+    max_def = sum(1 for n in nodes if n.repetition != 0)
+    vidx, k = [], 0
+    for d in defs:
+        vidx.append(k if d == max_def else -1)
+        k += d == max_def
+
+    def build(level: int, lo: int, hi: int, rep_level: int, def_level: int):
+        node = nodes[level]
+        if node.repetition == 1:
+            def_level += 1
+            if defs[lo] < def_level:
+                return _Null(level)
+        elif node.repetition == 2:
+            def_level += 1
+            rep_level += 1
+            if defs[lo] < def_level:
+                return []
+            starts = [lo] + [i for i in range(lo + 1, hi) if reps[i] == rep_level]
+            return [down(level, a, b, rep_level, def_level) for a, b in zip(starts, starts[1:] + [hi])]
+        return down(level, lo, hi, rep_level, def_level)
+
+    def down(level: int, lo: int, hi: int, rep_level: int, def_level: int):
+        if level == len(nodes) - 1:
+            return vals[vidx[lo]]
+        v = build(level + 1, lo, hi, rep_level, def_level)
+        return v
+
+    row_starts = [i for i, r in enumerate(reps) if r == 0] + [len(reps)]
+    return [build(0, a, b, 0, 0) for a, b in zip(row_starts[:-1], row_starts[1:])]
+
+
+def _denull(v):
+    if isinstance(v, _Null):
+        return None
+    if isinstance(v, list):
+        return [_denull(x) for x in v]
+    return v
+
+
+def read_nested_small(source) -> Dict[str, list]:
+    """A (small) Parquet file with nested columns -> {column: [one Python value per row]}: lists for
+    LIST-annotated groups, dicts for structs, None for nulls - what pyarrow's Table.to_pydict() gives.
+    Host-side record assembly from repetition / definition levels; meant for the Spark ML model files, not
+    for bulk data (read_parquet).  Structs inside lists are not supported."""
+    raw = read_bytes(source)
+    if raw[:4] != b"PAR1" or raw[-4:] != b"PAR1":
+        raise ParquetUnsupported("not a Parquet file (or an encrypted footer)")
+    (flen,) = struct.unpack_from("<I", raw, len(raw) - 8)
+    meta = _Thrift(raw, len(raw) - 8 - flen).struct()
+    root = _schema_tree(meta[2])
+    rows_total = int(meta[3])
+
+    def leaves(node: _Node, path, nodes):
+        for ch in node.children:
+            if ch.ptype is None:
+                yield from leaves(ch, path + (ch.name,), nodes + [ch])
+            else:
+                yield path + (ch.name,), nodes + [ch]
+
+    info = dict(leaves(root, (), []))
+    streams: Dict[Tuple[str, ...], list] = {p: [[], [], []] for p in info}
+    for rg in meta[4]:
+        for cc in rg[1]:
+            cm = cc[3]
+            path = tuple(x.decode() for x in cm[3])
+            nodes = info[path]
+            leaf = nodes[-1]
+            max_rep = sum(1 for n in nodes if n.repetition == 2)
+            max_def = sum(1 for n in nodes if n.repetition != 0)
+            r, d, v = _read_leaf(raw, cm, leaf.ptype, max_rep, max_def, leaf.ptype == T_BYTE_ARRAY and leaf.converted in (0, None))
+            for acc, part in zip(streams[path], (r, d, v)):
+                acc += part
+    built = {}
+    for path, (r, d, v) in streams.items():
+        built[path] = _build_leaf(info[path], r, d, v)
+        if len(built[path]) != rows_total:
+            raise ParquetUnsupported(f"column {'.'.join(path)}: {len(built[path])} records for {rows_total} rows")
+
+    def value_of(node: _Node, path, depth: int, row: int):
+        below = [p for p in info if p[:len(path)] == path]
+        if node.ptype is not None or len(below) == 1:
+            return _denull(built[below[0]][row])
+        if any(n.repetition == 2 for p in below for n in info[p][:depth + 1]) or node.repetition == 2:
+            raise ParquetUnsupported(f"column {'.'.join(path)}: a struct inside a list is not supported")
+        states = [built[p][row] for p in below]
+        if all(isinstance(x, _Null) and x.level <= depth for x in states):
+            return None                                    # the struct itself is null
+        return {ch.name: value_of(ch, path + (ch.name,), depth + 1, row) for ch in node.children}
+
+    return {ch.name: [value_of(ch, (ch.name,), 0, row) for row in range(rows_total)] for ch in root.children}

@@ -11,7 +11,14 @@ Same steps, same files (the model is saved as model.npz - the parameter blob and
 layout - instead of a .keras archive).  What cannot be reproduced without TensorFlow:
 its Glorot-uniform draws and its shuffle-buffer draws; both use NumPy generators here
 (seeded), so the loss curve differs from a TF run in the way two TF runs with
-different seeds differ.  The split IS the reference's (NumPy, seed 1337)."""
+different seeds differ.  The split IS the reference's (NumPy, seed 1337).
+
+One deliberate deviation in the batching: the reference batches BEFORE it repeats
+(shuffle().batch(B).repeat(), :664-665), so every pass over the N training rows ends
+in one short batch of N mod B rows that model.fit consumes as an ordinary step; here
+the shuffled index stream is cut into full batches only (a batch may straddle two
+passes), because the epoch kernel takes one batch size per launch.  With the
+reference's defaults that is one step in ~190 whose batch is smaller."""
 from __future__ import annotations
 
 import json

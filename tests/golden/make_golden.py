@@ -76,6 +76,8 @@ CASES = {
     "big_and_small": "subpopulation,value,lower_ci,upper_ci\nA,123456789012345,0.1,1e-5\nB,16777217,3.4e38,1e22\n",
     "inf_text": "subpopulation,value,lower_ci,upper_ci\nA,inf,1,2\nB,-Infinity,1,2\n",
     "blank_lines": "subpopulation,value,lower_ci,upper_ci\n\nA,1,2,3\n\n\nB,4,5,6\n",
+    # only the bare word "nan" drops a row (v.lower() == "nan", train_tf_ps.py:129); a signed one is a NaN VALUE
+    "signed_nan": "subpopulation,value,lower_ci,upper_ci\nA,-nan,2,3\nB,+NaN,2,3\nC,nan,2,3\nD,1,2,3\n",
 }
 
 

@@ -116,3 +116,29 @@ def test_pipeline_model_rejects_other_stage_sequences(tmp_path):
         fh.write(json.dumps(meta) + "\n")
     with pytest.raises((ValueError, FileNotFoundError)):
         M.load_pipeline_model(None, path)
+
+
+def test_own_reader_of_nested_model_files_matches_pyarrow():
+    # the data/*.snappy.parquet files above are read with this package's own Parquet code (footer, Snappy,
+    # repetition / definition levels): the same Python values pyarrow's reader gives, for every page flavour
+    import io
+
+    from pyspark_tf_gke_b200.parquet import read_nested_small
+
+    vec = pa.struct([pa.field("type", pa.int8(), nullable=False), pa.field("size", pa.int32()),
+                     pa.field("indices", pa.list_(pa.field("element", pa.int32(), nullable=False))),
+                     pa.field("values", pa.list_(pa.field("element", pa.float64(), nullable=False)))])
+    rows = [{"type": 1, "size": None, "indices": None, "values": [1.5, 2.5, 3.0]},
+            {"type": 0, "size": 7, "indices": [1, 4], "values": [9.0, -1.0]},
+            None,
+            {"type": 1, "size": None, "indices": None, "values": []}]
+    inner = pa.list_(pa.field("element", pa.string()))
+    t = pa.table({"clusterIdx": pa.array([0, 1, 2, 3], pa.int32()), "clusterCenter": pa.array(rows, vec),
+                  "labelsArray": pa.array([[["a", "b", None], []], None, [], [["é", "zz"]]], pa.list_(pa.field("element", inner))),
+                  "sizes": pa.array([[31], [1, 2, 3], [], None], pa.list_(pa.field("element", pa.int32(), nullable=False))),
+                  "name": pa.array(["x", None, "y", "z"])})
+    for kw in (dict(compression="snappy"), dict(compression="NONE"), dict(compression="snappy", data_page_version="2.0"),
+               dict(compression="snappy", use_dictionary=False), dict(compression="snappy", row_group_size=2)):
+        buf = io.BytesIO()
+        pq.write_table(t, buf, use_compliant_nested_type=True, **kw)
+        assert read_nested_small(buf.getvalue()) == t.to_pydict(), kw
