@@ -9,8 +9,9 @@
 //        at once (no run table);
 //   pq_snappy_kernel         one WARP per compressed page: the Snappy block format (what Spark and Arrow write
 //        by default) is a chain of literal / copy elements that can only be found one after another; the
-//        warp walks the chain in lockstep and all 32 lanes move each element's bytes, into a region behind
-//        the file bytes, so every later kernel addresses inflated pages like any other part of the buffer;
+//        warp walks the chain in lockstep and all 32 lanes move each element's bytes (the most recent output
+//        mirrored in shared memory, so a short-range copy costs no trip to L2), into a region behind the
+//        file bytes, so every later kernel addresses inflated pages like any other part of the buffer;
 //   pq_plain_strings_kernel  one WARP per PLAIN BYTE_ARRAY page (a writer's fallback when its dictionary grew
 //        too large): lane 0 walks the [length][bytes] chain 32 values at a time, every lane hashes its value
 //        into a device dictionary (as the CSV decoder does) and the slot numbers take the place of
@@ -237,11 +238,19 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_hybrid_decode_kernel(const uint
 // ---------------------------------------------------------------- Snappy
 struct PqInflate { int64_t src, src_bytes, dst, dst_bytes; };   // byte offsets in the buffer
 
+// One WARP per page (tried: one CTA per page with every thread walking the chain and all 256 threads moving the
+// bytes - 3x slower on pages of integer-valued doubles, whose zero bytes give ~10-byte elements: the chain, not
+// the copying, is the cost).  The chain is a latency chain, so what matters is the latency of one element: the
+// last PQ_RING output bytes are mirrored in shared memory, and a copy element that reaches no further back than
+// that (offsets of 8 or 16 in columns of doubles) reads the mirror instead of making a round trip to L2.
+constexpr int PQ_RING = 2048;
 __global__ void __launch_bounds__(PQ_THREADS) pq_snappy_kernel(uint8_t* buf, const PqInflate* __restrict__ jobs, int njobs,
                                                                int32_t* status) {
+    __shared__ uint8_t s_ring_all[PQ_WARPS][PQ_RING];
     const int lane = threadIdx.x & 31;
     const int j = blockIdx.x * PQ_WARPS + (threadIdx.x >> 5);
     if (j >= njobs) return;
+    uint8_t* ring = s_ring_all[threadIdx.x >> 5];
     const PqInflate job = jobs[j];
     const uint8_t* in = buf + job.src;      // compressed bytes: read only
     uint8_t* out = buf + job.dst;           // this warp's output range: written, and read back by copy elements
@@ -268,14 +277,33 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_snappy_kernel(uint8_t* buf, con
             if (ip + len > job.src_bytes || op + len > job.dst_bytes) { bad = true; break; }
             const uint8_t* s = in + ip;
             uint8_t* d = out + op;
-            // bytes up to 4-byte alignment of the destination, 4-byte words, tail (source words by funnel shift)
-            const int head = (int)((4 - (reinterpret_cast<uintptr_t>(d) & 3)) & 3);
-            const int64_t h = head < len ? head : len;
-            if (lane < h) d[lane] = __ldg(s + lane);
-            const int64_t words = (len - h) >> 2;
-            for (int64_t w = lane; w < words; w += 32) reinterpret_cast<uint32_t*>(d + h)[w] = pq_load_u32(s + h + 4 * w);
-            const int64_t done = h + 4 * words;
-            if (done + lane < len) d[done + lane] = __ldg(s + done + lane);
+            if (len <= 64) {                // the common short literal: one or two bytes per lane
+                for (int i = lane; i < len; i += 32) {
+                    const uint8_t c = __ldg(s + i);
+                    d[i] = c;
+                    ring[(op + i) & (PQ_RING - 1)] = c;
+                }
+            } else {
+                // bytes up to 4-byte alignment of the destination, 4-byte words, tail (source words by funnel shift)
+                const int head = (int)((4 - (reinterpret_cast<uintptr_t>(d) & 3)) & 3);
+                const int64_t h = head < len ? head : len;
+                if (lane < h) d[lane] = __ldg(s + lane);
+                const int64_t words = (len - h) >> 2;
+                uint32_t* dw = reinterpret_cast<uint32_t*>(d + h);
+                const uint8_t* sw = s + h;
+                int64_t w = lane;
+                for (; w + 96 < words; w += 128) {
+                    const uint32_t a = pq_load_u32(sw + 4 * w), b = pq_load_u32(sw + 4 * (w + 32)), c = pq_load_u32(sw + 4 * (w + 64)),
+                                   e = pq_load_u32(sw + 4 * (w + 96));
+                    dw[w] = a; dw[w + 32] = b; dw[w + 64] = c; dw[w + 96] = e;
+                }
+                for (; w < words; w += 32) dw[w] = pq_load_u32(sw + 4 * w);
+                const int64_t done = h + 4 * words;
+                if (done + lane < len) d[done + lane] = __ldg(s + done + lane);
+                // mirror the literal's last PQ_RING bytes
+                const int64_t m0 = len > PQ_RING ? len - PQ_RING : 0;
+                for (int64_t i = m0 + lane; i < len; i += 32) ring[(op + i) & (PQ_RING - 1)] = __ldg(s + i);
+            }
             ip += len;
             op += len;
         } else {                            // copy of `len` bytes that start `off` bytes back in the output
@@ -295,8 +323,20 @@ __global__ void __launch_bounds__(PQ_THREADS) pq_snappy_kernel(uint8_t* buf, con
                 ip += 4;
             }
             if (off <= 0 || off > op || op + len > job.dst_bytes || ip > job.src_bytes) { bad = true; break; }
-            // an overlapping copy (off < len) repeats the last `off` bytes: byte i comes from i mod off
-            for (int64_t i = lane; i < len; i += 32) out[op + i] = __ldcg(out + op - off + (i % off));
+            // an overlapping copy (off < len) repeats the last `off` bytes: byte i comes from i mod off.  len <= 64.
+            const int64_t from = op - off;
+            uint8_t c0 = 0, c1 = 0;
+            const bool two = lane + 32 < len;
+            if (off <= PQ_RING) {
+                if (lane < len) c0 = ring[(from + (lane % off)) & (PQ_RING - 1)];
+                if (two) c1 = ring[(from + ((lane + 32) % off)) & (PQ_RING - 1)];
+            } else {
+                if (lane < len) c0 = __ldcg(out + from + (lane % off));
+                if (two) c1 = __ldcg(out + from + ((lane + 32) % off));
+            }
+            __syncwarp();                   // every source byte is read before the mirror is overwritten
+            if (lane < len) { out[op + lane] = c0; ring[(op + lane) & (PQ_RING - 1)] = c0; }
+            if (two) { out[op + lane + 32] = c1; ring[(op + lane + 32) & (PQ_RING - 1)] = c1; }
             op += len;
         }
         __syncwarp();                       // the bytes just written may be the source of the next copy
