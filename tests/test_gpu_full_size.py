@@ -1,9 +1,13 @@
-"""BASELINE.json configs at (or near) full size: size-independent properties
-instead of an oracle diff - conservation of rows and of the grand total,
-sortedness / uniqueness of keys, idempotence - as the oracle cannot finish these
-sizes in seconds."""
+"""BASELINE.json configs at (or near) full size: size-independent properties -
+conservation of rows and of the grand total, sortedness / uniqueness of keys,
+idempotence - plus a per-group diff against the oracle on a sample of the keys
+(every row of ~1 % of the keys is pulled to the host and aggregated there), as
+the oracle cannot finish the whole tables in seconds."""
+import numpy as np
 import pytest
 import torch
+
+from oracle import etl_oracle as O
 
 import pyspark_tf_gke_b200 as pkg
 import pyspark_tf_gke_b200.dist as D
@@ -37,6 +41,17 @@ def test_config3_groupby_100m_rows_1k_groups(eng):
         for c in range(3):
             assert int(res["cols"][c]["count"].sum()) == int(counts[c])
             assert float(res["cols"][c]["sum"].sum()) == float(sums[c])   # integer-valued data: exact
+    # per-group diff against the oracle on 1 % of the keys (every row of keys 0..9)
+    idx = torch.nonzero(key.data < 10).flatten()
+    hk = key.data[idx].cpu().numpy()
+    hv = [c.data[idx].cpu().numpy() for c in cols]
+    hvv = [(((c.valid[idx >> 5] >> (idx & 31).to(torch.int32)) & 1) != 0).cpu().numpy() for c in cols]
+    want = O.groupby_agg_fast(hk, hv, hvv)
+    for res in results:
+        assert res["rows"][:10].tolist() == want["rows"].tolist()
+        for c in range(3):
+            assert res["cols"][c]["count"][:10].tolist() == want["cols"][c]["count"].tolist()
+            assert res["cols"][c]["sum"][:10].cpu().numpy().tobytes() == want["cols"][c]["sum"].tobytes()
     for c in range(3):  # the two kernels agree group by group
         assert torch.equal(results[0]["cols"][c]["count"], results[1]["cols"][c]["count"])
         assert torch.equal(results[0]["cols"][c]["sum"], results[1]["cols"][c]["sum"])
@@ -90,6 +105,13 @@ def test_config4_full_size_single_gpu(eng):
     # a key's row count is what a direct count of that key gives (spot check on the busiest group)
     top = int(torch.argmax(res["rows"]))
     assert int((key == k[top]).sum()) == int(res["rows"][top])
+    # per-group diff against the oracle on 1 % of the keys: every row whose key is below G / 100
+    sel = key < G // 100
+    want = O.groupby_agg_fast(key[sel].cpu().numpy(), [val[sel].cpu().numpy()], [None])
+    m = int((k < G // 100).sum())
+    assert k[:m].cpu().numpy().tolist() == want["keys"].tolist()
+    assert res["rows"][:m].cpu().numpy().tolist() == want["rows"].tolist()
+    assert res["cols"][0]["sum"][:m].cpu().numpy().tobytes() == want["cols"][0]["sum"].tobytes()
 
 
 def test_config5_shape_csv_decode_10m_records(eng):
