@@ -578,7 +578,7 @@ def sub_config3(ctx, steps: int):
         state["gt"] = gt
 
     _, per, clocks = timed_steps(ctx, step, steps, 3)
-    res = eng.groupby_result(state["gt"])
+    res = eng.groupby_result(state["gt"], sort=True)
     # oracle diff, group by group, on every row of 10 sampled keys (~1 M rows)
     idx = torch.nonzero(key.data < 10).flatten()
     hk = key.data[idx].cpu().numpy()

@@ -79,7 +79,7 @@ class GroupTable:
 class PartitionedGroups:
     """Result of the shared-memory merge (etl_groupby_merge_partitioned): dense
     columns in no particular order + device counters [groups, spilled, -, reserved]
-    + the spilled records; Engine.groupby_result turns it into the sorted dict."""
+    + the spilled records; Engine.groupby_result turns it into the result dict."""
 
     keys: torch.Tensor
     rows: torch.Tensor
@@ -385,13 +385,13 @@ class Engine:
             groups_hint, key_range, gt.status.data_ptr(), self._stream()))
         self.launches += 1 if n else 0
 
-    def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None, sort: bool = True) -> dict:
+    def groupby_result(self, gt: "GroupTable", max_groups: Optional[int] = None, sort: bool = False) -> dict:
         """Dense result: keys, rows, per column count/sum/mean[/min/max] (device
-        tensors), plus the null-key group.  Raises if rows were dropped.  sort=True
-        orders the groups by key (a radix sort of the key column by torch - a
-        convenience for callers that compare results; Spark's own groupBy output is
-        unordered, and sort=False returns the groups as the kernels left them, with
-        no library kernel on the path)."""
+        tensors), plus the null-key group.  Raises if rows were dropped.  The groups
+        come as the kernels left them - Spark's own groupBy output is unordered too -
+        and no library kernel runs; sort=True orders them by key (a radix sort of the
+        key column by torch: a convenience for callers that compare results, which is
+        what the tests do)."""
         if isinstance(gt, PartitionedGroups):
             return self._partitioned_result(gt, sort)
         cap = gt.capacity if max_groups is None else max_groups
@@ -682,7 +682,7 @@ class Engine:
         self.launches += 1
         return PartitionedGroups(out_keys, out_rows, out_cnt, out_sum, counters, spill, out_capacity, fine, min=out_min, max=out_max)
 
-    def _partitioned_result(self, pg: "PartitionedGroups", sort: bool = True) -> dict:
+    def _partitioned_result(self, pg: "PartitionedGroups", sort: bool = False) -> dict:
         ctr = pg.counters.cpu().tolist()
         groups, spilled, _, reserved = ctr[:4]
         overflow = ctr[4] if len(ctr) > 4 else 0

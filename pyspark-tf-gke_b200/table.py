@@ -286,16 +286,25 @@ def read_csv(eng: Engine, source, numeric: Sequence[str], strings: Sequence[str]
     table = DeviceTable(eng, rows, header=header)
     wanted = [(c, 0) for c in numeric] + [(c, 1) for c in strings]
     present = [(c, k) for c, k in wanted if c in pos]
-    if len(present) > 8:
-        raise ValueError("read_csv: at most 8 columns per call")
     # the index passes above ran on this very text through this engine's handle: the row scan may use their masks
     flags = (CSV_TRIM_STRINGS if trim_strings else 0) | (CSV_NAN_IS_NULL if nan_is_null else 0) | CSV_USE_INDEX_MASKS
     dicts = [None if k == 0 else (torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device),
                                   torch.zeros(dict_capacity, dtype=torch.int64, device=eng.device)) for _, k in present]
     if present and rows:
-        cols, status, first_bad = eng.csv_parse_columns(text, n, row_start, first, rows, [pos[c] for c, _ in present],
-                                                        [k for _, k in present], dicts, flags)
-        st = status.cpu().numpy()
+        # the parse kernel takes up to 8 columns per launch: wider selections go in groups of 8 over the same row index
+        # (the masks of the index passes stay valid: parsing does not touch the handle's arena)
+        cols, type_bits, st = [], 0, np.zeros(4, dtype=np.int64)
+        for g0 in range(0, len(present), 8):
+            part = present[g0:g0 + 8]
+            pcols, status, first_bad = eng.csv_parse_columns(text, n, row_start, first, rows, [pos[c] for c, _ in part],
+                                                             [k for _, k in part], dicts[g0:g0 + 8], flags)
+            pst = status.cpu().numpy().astype(np.int64)
+            cols += pcols
+            type_bits |= int(pst[2]) << g0
+            st[:2] += pst[:2]
+            if pst[0] or pst[1]:
+                break
+        st[2] = type_bits
         if st[0]:
             raise EtlError(-4, f"{int(st[0])} numeral(s) outside the exactly-converted domain (more than 60 significant "
                                f"digits); first at CSV record {int(first_bad.item())}")

@@ -409,3 +409,28 @@ def test_byte_range_split_of_a_file_covers_every_record_once(eng, tmp_path):
     tiny.write_text("measure_name,value,lower_ci,upper_ci\nx,1,2,3\n")
     rows = [pkg.read_csv(eng, str(tiny), ["value"], ["measure_name"], byte_range=(r, 4)).rows for r in range(4)]
     assert sum(rows) == 1
+
+
+def test_read_csv_more_than_eight_columns(eng):
+    # the parse kernel takes 8 columns per launch; a wider selection is decoded in groups over one row index
+    rng = np.random.default_rng(2)
+    names = [f"c{i}" for i in range(13)]
+    rows = 3001
+    data = rng.integers(-1000, 1000, (rows, 11))
+    lines = [",".join(names)]
+    for r in range(rows):
+        cells = [str(v) if (r + i) % 17 else "" for i, v in enumerate(data[r])]
+        cells[3] = f"{data[r][3]}.5"                    # a double column among the integer ones
+        lines.append(",".join(cells + [f"lab{r % 5}", f'"q,{r % 3}"']))
+    text = "\n".join(lines) + "\n"
+    table = pkg.read_csv(eng, text.encode(), names[:11], names[11:])
+    header, cols = O.read_csv_columns(text)
+    for i, name in enumerate(names[:11]):
+        v, vv = O.to_numeric_column(cols[name])
+        assert (table.numeric[name].valid_host() == vv).all()
+        assert table.numeric[name].data.cpu().numpy()[vv].tobytes() == v[vv].tobytes()
+        assert table.inferred_types[name] == ("double" if i == 3 else "int")
+    for name in names[11:]:
+        sc = table.strings[name]
+        codes = sc.column.data.cpu().numpy()
+        assert [sc.labels[c] for c in codes] == cols[name]

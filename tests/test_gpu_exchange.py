@@ -97,7 +97,7 @@ def test_simulated_peer_exchange_matches_oracle(eng, R, B):
         flat = bufs[r].view(-1)
         pg = eng.groupby_partitioned_sum(flat, flat[1:].view(torch.float64), 1 << 15, groups_hint=groups // R, n=m,
                                          key_stride=2, val_stride=2)
-        res = eng.groupby_result(pg)
+        res = eng.groupby_result(pg, sort=True)
         want = O.groupby_agg_fast(all_k[own], [all_v[own]], [None])
         assert res["keys"].cpu().numpy().tolist() == want["keys"].tolist()
         assert res["rows"].cpu().numpy().tolist() == want["rows"].tolist()

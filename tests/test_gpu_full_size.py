@@ -33,7 +33,7 @@ def test_config3_groupby_100m_rows_1k_groups(eng):
         gt = eng.groupby_new(4096, 3)
         eng.groupby_accumulate(gt, key.data, None, [c.data for c in cols], [c.valid for c in cols], groups_hint=G,
                                key_range=key_range)
-        results.append(eng.groupby_result(gt))
+        results.append(eng.groupby_result(gt, sort=True))
     sums, counts = eng.sum_count(cols)
     for res in results:
         assert res["keys"].tolist() == list(range(G))           # every key present, once, sorted
@@ -67,11 +67,11 @@ def test_config4_shape_groupby_quarter_size_single_gpu(eng):
     direct = eng.groupby_new(cap, 1)
     eng.groupby_accumulate(direct, key, None, [val], groups_hint=G)
     pieces = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G)     # two partition levels + shared-memory merge
-    b = eng.groupby_result(pieces)
+    b = eng.groupby_result(pieces, sort=True)
     assert b["spilled_records"] == 0
     del pieces
     bucketed = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G, merge="table")   # bucket-by-bucket table merge
-    a, c = eng.groupby_result(direct, max_groups=G), eng.groupby_result(bucketed, max_groups=G)
+    a, c = eng.groupby_result(direct, max_groups=G, sort=True), eng.groupby_result(bucketed, max_groups=G, sort=True)
     assert torch.equal(a["keys"], c["keys"]) and torch.equal(a["rows"], c["rows"])
     assert torch.equal(a["cols"][0]["sum"], c["cols"][0]["sum"])
     del c, bucketed
@@ -93,7 +93,7 @@ def test_config4_full_size_single_gpu(eng):
     key = eng.synth_column(cfg["seed"], 0, S.KIND_KEY64, n, modulus=G, with_valid=False).data
     val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, with_valid=False).data
     pieces = D.shuffle_groupby_sum(eng, key, val, G + G // 8, groups_hint=G)
-    res = eng.groupby_result(pieces)
+    res = eng.groupby_result(pieces, sort=True)
     del pieces
     s, _ = eng.sum_count([pkg.Column(val)])
     k = res["keys"]

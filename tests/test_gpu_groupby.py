@@ -53,7 +53,7 @@ def test_groupby_matches_oracle(eng, n, groups, hint, key_dtype):
     kcol = pkg.Column.from_host(keys, kv, eng.device)
     cols = [pkg.Column.from_host(v, vv, eng.device) for v, vv in zip(vals, valid)]
     eng.groupby_accumulate(gt, kcol.data, kcol.valid, [c.data for c in cols], [c.valid for c in cols], groups_hint=hint)
-    res = eng.groupby_result(gt)
+    res = eng.groupby_result(gt, sort=True)
     exp = O.groupby_agg(keys, kv, vals, valid)
     _check(res, exp, exact_sums=False, minmax=True)
 
@@ -72,7 +72,7 @@ def test_groupby_exact_sums_on_integer_valued_data_in_batches(eng):
         k = pkg.Column.from_host(keys[lo:hi], None, eng.device)
         cols = [pkg.Column.from_host(v[lo:hi], vv[lo:hi], eng.device) for v, vv in zip(vals, valid)]
         eng.groupby_accumulate(gt, k.data, None, [c.data for c in cols], [c.valid for c in cols], groups_hint=groups)
-    res = eng.groupby_result(gt)
+    res = eng.groupby_result(gt, sort=True)
     exp = O.groupby_agg(keys, None, vals, valid)
     _check(res, exp, exact_sums=True, minmax=False)
 
@@ -96,7 +96,7 @@ def test_groupby_direct_indexed_path(eng, ncols):
     cols = [pkg.Column.from_host(v, vv, eng.device) for v, vv in zip(vals, valid)]
     eng.groupby_accumulate(gt, k.data, k.valid, [c.data for c in cols], [c.valid for c in cols], groups_hint=groups,
                            key_range=groups)
-    res = eng.groupby_result(gt)
+    res = eng.groupby_result(gt, sort=True)
     exp = O.groupby_agg(keys, kv, vals, valid)
     _check(res, exp, exact_sums=True, minmax=False)
 
@@ -108,7 +108,7 @@ def test_groupby_all_null_group_and_full_table(eng):
     gt = eng.groupby_new(8, 1, minmax=True)
     c = pkg.Column.from_host(v, vv, eng.device)
     eng.groupby_accumulate(gt, torch.from_numpy(keys).to(eng.device), None, [c.data], [c.valid])
-    res = eng.groupby_result(gt)
+    res = eng.groupby_result(gt, sort=True)
     assert res["keys"].cpu().tolist() == [1, 2, 3] and res["rows"].cpu().tolist() == [2, 1, 1]
     col = res["cols"][0]
     assert col["count"].cpu().tolist() == [2, 0, 1] and col["sum"].cpu().tolist() == [3.0, 0.0, 7.0]
@@ -118,7 +118,7 @@ def test_groupby_all_null_group_and_full_table(eng):
     gt = eng.groupby_new(8, 0)
     eng.groupby_accumulate(gt, torch.arange(100, dtype=torch.int64, device=eng.device), None, [], groups_hint=4096)
     with pytest.raises(pkg.EtlError, match="dropped"):
-        eng.groupby_result(gt)
+        eng.groupby_result(gt, sort=True)
 
 
 @pytest.mark.parametrize("ranks,buckets", [(1, 1), (2, 1), (8, 1), (1, 16), (8, 32)])
@@ -158,7 +158,7 @@ def test_partition_then_strided_merge_equals_direct_groupby(eng, buckets):
         for k in range(buckets):
             d = r * buckets + k
             eng.groupby_accumulate_records(gt, rec, b[d], b[d + 1], groups)
-        res = eng.groupby_result(gt)
+        res = eng.groupby_result(gt, sort=True)
         all_keys.append(res["keys"]); all_sums.append(res["cols"][0]["sum"]); all_rows.append(res["rows"])
     k = torch.cat(all_keys).cpu().numpy()
     order = np.argsort(k)
@@ -178,7 +178,7 @@ def test_bucketed_single_gpu_shuffle_path(eng):
     exp = O.groupby_agg_fast(keys, [vals], [None])
     for buckets, merge in ((1, "table"), (16, "table"), (None, "smem")):
         gt = D.shuffle_groupby_sum(eng, dk, dv, 1 << 18, groups_hint=groups, buckets=buckets, merge=merge)
-        res = eng.groupby_result(gt)
+        res = eng.groupby_result(gt, sort=True)
         assert res["keys"].cpu().numpy().tolist() == exp["keys"].tolist()
         assert res["cols"][0]["sum"].cpu().numpy().tobytes() == exp["cols"][0]["sum"].tobytes()
     assert D.choose_buckets(1 << 28, 1) == 256 and D.choose_buckets(1 << 25, 8) == 32 and D.choose_buckets(1 << 10, 8) == 1
@@ -201,7 +201,7 @@ def test_smem_merge_matches_oracle(eng, n, groups, plan, slots):
     vals, _ = S.host_column(21, 1, S.KIND_EXACT, n)
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     pg = eng.groupby_partitioned_sum(dk, dv, max(n, 1), groups_hint=groups, plan=plan, slots=slots)
-    res = eng.groupby_result(pg)
+    res = eng.groupby_result(pg, sort=True)
     exp = O.groupby_agg_fast(keys, [vals], [None])
     _check(res, exp, exact_sums=True, minmax=False)
     if plan in ((3, 5), (7, 1)):
@@ -221,7 +221,7 @@ def test_smem_merge_skew_real_values_and_strided_records(eng):
     rec = torch.from_numpy(np.stack([keys, vals.view(np.int64)], axis=1)).to(eng.device)
     flat = rec.view(-1)
     pg = eng.groupby_partitioned_sum(flat, flat[1:].view(torch.float64), n, groups_hint=groups, n=n, key_stride=2, val_stride=2)
-    res = eng.groupby_result(pg)
+    res = eng.groupby_result(pg, sort=True)
     _check(res, O.groupby_agg_fast(keys, [vals], [None]), exact_sums=False, minmax=False)
 
 
@@ -230,10 +230,10 @@ def test_smem_merge_reports_reserved_key_and_small_output(eng):
     vals = np.ones(1000)
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     with pytest.raises(pkg.EtlError, match="exceed the output capacity"):
-        eng.groupby_result(eng.groupby_partitioned_sum(dk, dv, 999, groups_hint=1000))
+        eng.groupby_result(eng.groupby_partitioned_sum(dk, dv, 999, groups_hint=1000), sort=True)
     keys[17] = np.iinfo(np.int64).min
     with pytest.raises(pkg.EtlError, match="reserved key"):
-        eng.groupby_result(eng.groupby_partitioned_sum(torch.from_numpy(keys).to(eng.device), dv, 1000, groups_hint=1000))
+        eng.groupby_result(eng.groupby_partitioned_sum(torch.from_numpy(keys).to(eng.device), dv, 1000, groups_hint=1000), sort=True)
     assert pkg.Engine.merge_plan(10**9, 10**8) == (256, 255) and pkg.Engine.merge_plan(1000, 0) == (1, 1)
     assert pkg.Engine.merge_plan(125_000_000, 14_000_000) == (96, 95)
 

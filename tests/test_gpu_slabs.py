@@ -44,11 +44,11 @@ def test_slab_groupby_matches_oracle(eng, n, groups):
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     pg = eng.groupby_slab_sum(dk, dv, groups + 1024, groups_hint=groups)
     assert int(pg.counters[4].item()) == 0                      # uniform keys: nothing overflows at 6 sigma
-    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(keys, [vals], [None]))
     # the same rows as {key, value} records (strides 2), as the receiver sees them
     rec = torch.stack([dk, dv.view(torch.int64)], dim=1).contiguous().view(-1)
     pg = eng.groupby_slab_sum(rec, rec[1:].view(torch.float64), groups + 1024, groups_hint=groups, n=n, key_stride=2, val_stride=2)
-    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(keys, [vals], [None]))
 
 
 def test_slab_overflow_repeats_on_the_counted_path(eng):
@@ -59,10 +59,10 @@ def test_slab_overflow_repeats_on_the_counted_path(eng):
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     pg = eng.groupby_slab_sum(dk, dv, groups + 1024, groups_hint=groups)
     assert int(pg.counters[4].item()) > 0
-    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(keys, [vals], [None]))
     # through the public entry
     pg = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups)
-    _same(eng.groupby_result(pg), O.groupby_agg_fast(keys, [vals], [None]))
+    _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(keys, [vals], [None]))
 
 
 def test_slab_path_is_the_default_and_counted_path_agrees(eng):
@@ -72,7 +72,7 @@ def test_slab_path_is_the_default_and_counted_path_agrees(eng):
     a = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups)
     b = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups, counted=True)
     assert a.counters.shape[0] == 5 and b.counters.shape[0] == 4
-    ra, rb = eng.groupby_result(a), eng.groupby_result(b)
+    ra, rb = eng.groupby_result(a, sort=True), eng.groupby_result(b, sort=True)
     for x, y in ((ra["keys"], rb["keys"]), (ra["rows"], rb["rows"]), (ra["cols"][0]["sum"], rb["cols"][0]["sum"])):
         assert torch.equal(x, y)
     _same(ra, O.groupby_agg_fast(keys, [vals], [None]))
@@ -145,7 +145,7 @@ def test_simulated_chunked_slab_exchange(eng, R, chunks):
         # second level + merge = the oracle's groupBy of the keys this rank owns
         counters = torch.zeros(5, dtype=torch.int64, device=eng.device)
         pg = eng.groupby_merge_slab_buckets(level1[r], cur1[r], cap1, buckets, sub, cap2, groups, counters)
-        _same(eng.groupby_result(pg), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))
+        _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))
 
 
 @pytest.mark.parametrize("counted", [False, True])
@@ -158,7 +158,7 @@ def test_min_max_on_the_shuffle_path(eng, counted):
     vals = vals - 5e4
     dk, dv = torch.from_numpy(keys).to(eng.device), torch.from_numpy(vals).to(eng.device)
     pg = D.shuffle_groupby_sum(eng, dk, dv, groups + 1024, groups_hint=groups, minmax=True, counted=counted)
-    res = eng.groupby_result(pg)
+    res = eng.groupby_result(pg, sort=True)
     want = O.groupby_agg(keys, None, [vals], [None])
     assert res["keys"].cpu().numpy().tolist() == want["keys"].tolist()
     assert res["rows"].cpu().numpy().tolist() == want["rows"].tolist()
@@ -225,4 +225,4 @@ def test_simulated_bucketed_exchange(eng, R, groups_of_buckets, mover):
         h = O.mix64(all_k[own].view(np.uint64))
         fine_idx = (((h & np.uint64(0xFFFFFFFF)) * np.uint64(bx * sub)) >> np.uint64(32)).astype(np.int64)
         assert cur2.cpu().tolist() == np.bincount(fine_idx, minlength=bx * sub).tolist()
-        _same(eng.groupby_result(pg), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))
+        _same(eng.groupby_result(pg, sort=True), O.groupby_agg_fast(all_k[own], [all_v[own]], [None]))

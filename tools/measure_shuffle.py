@@ -43,6 +43,7 @@ def main():
                          "peer = partition fused with NVLink peer stores (chunked slabs, or counted with --counted); "
                          "nccl = send buffer + all_to_all_single")
     ap.add_argument("--bucket-groups", type=int, default=8)
+    ap.add_argument("--out", default=None, help="append the JSON line to this file as well (rank 0)")
     ap.add_argument("--merge", default="smem", choices=["smem", "table"],
                     help="smem = two partition levels + shared-memory tables; table = bucket-by-bucket global table")
     ap.add_argument("--exchange-buckets", type=int, default=0,
@@ -114,7 +115,7 @@ def main():
                 phases["level2"].append(max_ms(marks["level1"], marks["level2"]))
     clocks = sampler.stop()
     # ---- checks
-    res = eng.groupby_result(gt, max_groups=cap)
+    res = eng.groupby_result(gt, max_groups=cap, sort=True)
     tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
     gsum = res["cols"][0]["sum"].sum().reshape(1)
     s, c = eng.sum_count([pkg.Column(val)])
@@ -136,6 +137,9 @@ def main():
                 "steps": args.steps, "path": "counted" if args.counted else "slabs", "clocks": clocks,
                 "knobs": {k: v for k, v in os.environ.items() if k.startswith("ETL_")}}
         print(json.dumps(line), flush=True)
+        if args.out:
+            with open(args.out, "a") as fh:
+                fh.write(json.dumps(line) + "\n")
     assert ok_rows and ok_sum
     eng.close()
     if world > 1:
