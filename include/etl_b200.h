@@ -590,12 +590,20 @@ ETL_API int etl_kmeans_silhouette(etl_handle* h, const int32_t* index, const dou
  * trains on rows d_order[s * batch .. + batch); d_params / d_adam_m / d_adam_v are
  * updated in place; step0 = optimiser steps already taken (Adam bias correction);
  * d_loss[s] / d_acc[s] = mean loss / accuracy of step s's batch before its update.
+ * etl_mlp_train_steps_ragged: the same with d_step_rows[s] (1..batch, device
+ *   int32[steps]; NULL = batch) rows of step s counting - batch() before repeat()
+ *   ends every pass over the data with one short batch (train_tf_ps.py:664-665),
+ *   which model.fit consumes as an ordinary step; d_order stays [steps][batch].
  * etl_mlp_evaluate: forward only - per-sample loss (needs y) and / or arg-max class. */
 ETL_API int etl_mlp_param_count(int32_t classes);
 ETL_API int etl_mlp_train_steps(etl_handle* h, const float* X, const int32_t* y, int64_t n, const int32_t* d_order,
                         int32_t batch, int32_t steps, int32_t classes, float* d_params, float* d_adam_m,
                         float* d_adam_v, int64_t step0, float lr, float beta1, float beta2, float eps,
                         float* d_loss, float* d_acc, void* stream);
+ETL_API int etl_mlp_train_steps_ragged(etl_handle* h, const float* X, const int32_t* y, int64_t n, const int32_t* d_order,
+                               const int32_t* d_step_rows, int32_t batch, int32_t steps, int32_t classes, float* d_params,
+                               float* d_adam_m, float* d_adam_v, int64_t step0, float lr, float beta1, float beta2,
+                               float eps, float* d_loss, float* d_acc, void* stream);
 ETL_API int etl_mlp_evaluate(etl_handle* h, const float* X, const int32_t* y, int64_t n, const float* d_params,
                      int32_t classes, float* d_loss, int32_t* d_pred, void* stream);
 

@@ -44,6 +44,7 @@ struct MlpTrainParams {
     const float* X;        // [N][3]
     const int32_t* y;      // [N]
     const int32_t* order;  // [steps][batch] row indices
+    const int32_t* step_rows;  // optional [steps]: rows of step s that count (1..batch): the short batch that ends a pass
     float* params;         // [P] in / out
     float* adam_m;         // [P] in / out
     float* adam_v;         // [P] in / out
@@ -136,13 +137,14 @@ __global__ void __launch_bounds__(MLP_TRAIN_THREADS) mlp_train_kernel(const MlpT
     __shared__ int s_hit[MLP_CHUNK];
     for (int i = threadIdx.x; i < P; i += blockDim.x) { w[i] = p.params[i]; am[i] = p.adam_m[i]; av[i] = p.adam_v[i]; }
     __syncthreads();
-    const float inv_b = 1.f / (float)p.batch;
     for (int step = 0; step < p.steps; ++step) {
+        const int bs = p.step_rows ? p.step_rows[step] : p.batch;     // the same for every thread
+        const float inv_b = 1.f / (float)bs;
         for (int i = threadIdx.x; i < P; i += blockDim.x) g[i] = 0.f;
         float loss_sum = 0.f;  // thread 0 only
         int hits = 0;
-        for (int c0 = 0; c0 < p.batch; c0 += MLP_CHUNK) {
-            const int n = p.batch - c0 < MLP_CHUNK ? p.batch - c0 : MLP_CHUNK;
+        for (int c0 = 0; c0 < bs; c0 += MLP_CHUNK) {
+            const int n = bs - c0 < MLP_CHUNK ? bs - c0 : MLP_CHUNK;
             __syncthreads();
             for (int t = threadIdx.x; t < n; t += blockDim.x) {
                 const int32_t r = p.order[(int64_t)step * p.batch + c0 + t];
@@ -269,6 +271,14 @@ extern "C" int etl_mlp_train_steps(etl_handle* hh, const float* X, const int32_t
                                    int32_t batch, int32_t steps, int32_t classes, float* d_params, float* d_adam_m,
                                    float* d_adam_v, int64_t step0, float lr, float beta1, float beta2, float eps,
                                    float* d_loss, float* d_acc, void* stream_) {
+    return etl_mlp_train_steps_ragged(hh, X, y, n, d_order, nullptr, batch, steps, classes, d_params, d_adam_m, d_adam_v, step0,
+                                      lr, beta1, beta2, eps, d_loss, d_acc, stream_);
+}
+
+extern "C" int etl_mlp_train_steps_ragged(etl_handle* hh, const float* X, const int32_t* y, int64_t n, const int32_t* d_order,
+                                          const int32_t* d_step_rows, int32_t batch, int32_t steps, int32_t classes,
+                                          float* d_params, float* d_adam_m, float* d_adam_v, int64_t step0, float lr,
+                                          float beta1, float beta2, float eps, float* d_loss, float* d_acc, void* stream_) {
     ETL_REQUIRE(hh && X && y && d_order && d_params && d_adam_m && d_adam_v && d_loss && d_acc, "mlp_train_steps: NULL argument");
     ETL_REQUIRE(n >= 1 && batch >= 1 && steps >= 0 && classes >= 2 && classes <= etl::MLP_MAX_CLASSES,
                 "mlp_train_steps: n=%lld batch=%d steps=%d classes=%d", (long long)n, batch, steps, classes);
@@ -276,7 +286,7 @@ extern "C" int etl_mlp_train_steps(etl_handle* hh, const float* X, const int32_t
     Handle* h = reinterpret_cast<Handle*>(hh);
     ETL_CUDA(cudaSetDevice(h->device));
     etl::MlpTrainParams p{};
-    p.X = X; p.y = y; p.order = d_order; p.params = d_params; p.adam_m = d_adam_m; p.adam_v = d_adam_v;
+    p.X = X; p.y = y; p.order = d_order; p.step_rows = d_step_rows; p.params = d_params; p.adam_m = d_adam_m; p.adam_v = d_adam_v;
     p.classes = classes; p.batch = batch; p.steps = steps; p.step0 = step0;
     p.lr = lr; p.beta1 = beta1; p.beta2 = beta2; p.eps = eps; p.loss = d_loss; p.acc = d_acc;
     const int P = etl::mlp_param_count(classes);

@@ -937,16 +937,18 @@ class Engine:
 
     def mlp_train_steps(self, X: torch.Tensor, y: torch.Tensor, order: torch.Tensor, batch: int, classes: int,
                         params: torch.Tensor, adam_m: torch.Tensor, adam_v: torch.Tensor, step0: int = 0,
-                        lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-7):
+                        lr: float = 1e-3, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-7,
+                        step_rows: Optional[torch.Tensor] = None):
         """`order` int32[steps * batch] row indices -> (loss f32[steps], acc f32[steps]);
-        params / moments are updated in place."""
+        params / moments are updated in place.  step_rows int32[steps] (optional): how
+        many of a step's `batch` slots count - the short batch at the end of a pass."""
         steps = order.numel() // batch
         loss = self.empty(max(steps, 1), torch.float32)
         acc = self.empty(max(steps, 1), torch.float32)
-        _lib.check(self.lib.etl_mlp_train_steps(self._h, X.data_ptr(), y.data_ptr(), X.shape[0], order.data_ptr(), batch,
-                                                steps, classes, params.data_ptr(), adam_m.data_ptr(), adam_v.data_ptr(),
-                                                step0, lr, beta1, beta2, eps, loss.data_ptr(), acc.data_ptr(),
-                                                self._stream()))
+        _lib.check(self.lib.etl_mlp_train_steps_ragged(self._h, X.data_ptr(), y.data_ptr(), X.shape[0], order.data_ptr(),
+                                                       _ptr(step_rows), batch, steps, classes, params.data_ptr(),
+                                                       adam_m.data_ptr(), adam_v.data_ptr(), step0, lr, beta1, beta2, eps,
+                                                       loss.data_ptr(), acc.data_ptr(), self._stream()))
         self.launches += 1 if steps else 0
         return loss[:steps], acc[:steps]
 

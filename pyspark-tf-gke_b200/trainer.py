@@ -13,12 +13,13 @@ its Glorot-uniform draws and its shuffle-buffer draws; both use NumPy generators
 (seeded), so the loss curve differs from a TF run in the way two TF runs with
 different seeds differ.  The split IS the reference's (NumPy, seed 1337).
 
-One deliberate deviation in the batching: the reference batches BEFORE it repeats
-(shuffle().batch(B).repeat(), :664-665), so every pass over the N training rows ends
-in one short batch of N mod B rows that model.fit consumes as an ordinary step; here
-the shuffled index stream is cut into full batches only (a batch may straddle two
-passes), because the epoch kernel takes one batch size per launch.  With the
-reference's defaults that is one step in ~190 whose batch is smaller."""
+The batching is the reference's: it batches BEFORE it repeats (shuffle().batch(B)
+.repeat(), :664-665), so every pass over the N training rows ends in one short batch
+of N mod B rows that model.fit consumes as an ordinary step, and an epoch is the next
+N // B batches of that endless stream (epochs do not line up with passes).  The epoch
+kernel takes the number of rows of each step (etl_mlp_train_steps_ragged); the
+epoch's loss / accuracy are the per-batch means weighted by batch size, as Keras'
+metric accumulators do."""
 from __future__ import annotations
 
 import json
@@ -46,10 +47,31 @@ def glorot_uniform_params(classes: int, rng: np.random.Generator) -> np.ndarray:
     return np.concatenate(parts)
 
 
+def batch_stream(n: int, buffer_size: int, batch: int, steps: int, rng: np.random.Generator):
+    """The first `steps` batches of Dataset.range(n).shuffle(buffer_size).batch(batch).repeat()
+    -> (order int32[steps, batch] padded with row 0, rows int32[steps]): every pass over the
+    n rows is reshuffled and cut into ceil(n / batch) batches, the last one short."""
+    per_pass = -(-n // batch)
+    passes = -(-steps // per_pass)
+    order = np.zeros((steps, batch), dtype=np.int32)
+    rows = np.zeros(steps, dtype=np.int32)
+    s = 0
+    for _ in range(passes):
+        idx = shuffle_buffer_order(n, buffer_size, n, rng)
+        for lo in range(0, n, batch):
+            if s == steps:
+                break
+            part = idx[lo:lo + batch]
+            order[s, :part.shape[0]] = part
+            rows[s] = part.shape[0]
+            s += 1
+    return order, rows
+
+
 def shuffle_buffer_order(n: int, buffer_size: int, count: int, rng: np.random.Generator) -> np.ndarray:
     """Indices produced by Dataset.range(n).shuffle(buffer_size).repeat() - tf.data's
     shuffle-buffer semantics (fill a buffer, emit a random slot, refill it with the
-    next element; repeat() follows shuffle(), so each epoch drains its own buffer)."""
+    next element; each pass drains its own buffer)."""
     out = np.empty(count, dtype=np.int32)
     k = 0
     while k < count:
@@ -98,18 +120,21 @@ def fit(eng: Engine, X: torch.Tensor, y: torch.Tensor, classes: int, epochs: int
     rng = np.random.default_rng(seed)
     params = torch.from_numpy(glorot_uniform_params(classes, rng)).to(eng.device)
     m, v = torch.zeros_like(params), torch.zeros_like(params)
-    order = shuffle_buffer_order(n, min(3000, n), epochs * steps * batch_size, np.random.default_rng(seed + 1))
-    d_order = torch.from_numpy(order).to(eng.device)
+    order, step_rows = batch_stream(n, min(3000, n), batch_size, epochs * steps, np.random.default_rng(seed + 1))
+    d_order = torch.from_numpy(order.reshape(-1)).to(eng.device)
+    d_rows = torch.from_numpy(step_rows).to(eng.device)
+    weight = d_rows.to(torch.float32)
     hist: Dict[str, List[float]] = {"loss": [], "accuracy": []}
     if X_val is not None:
         hist.update({"val_loss": [], "val_accuracy": []})
     model = DeepModel(eng, classes, params, hist)
     per = steps * batch_size
     for e in range(epochs):
+        w = weight[e * steps:(e + 1) * steps]
         loss, acc = eng.mlp_train_steps(X, y, d_order[e * per:(e + 1) * per], batch_size, classes, params, m, v, step0=e * steps,
-                                        lr=lr)
-        hist["loss"].append(float(loss.mean()))
-        hist["accuracy"].append(float(acc.mean()))
+                                        lr=lr, step_rows=d_rows[e * steps:(e + 1) * steps])
+        hist["loss"].append(float((loss * w).sum() / w.sum()))
+        hist["accuracy"].append(float((acc * w).sum() / w.sum()))
         if X_val is not None:
             vl, va = model.evaluate(X_val, y_val)
             hist["val_loss"].append(vl)

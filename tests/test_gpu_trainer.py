@@ -33,19 +33,19 @@ def _split(params, C):
     return out
 
 
-def _torch_reference(X, y, order, B, C, params, steps, lr=1e-3, b1=0.9, b2=0.999, eps=1e-7):
+def _torch_reference(X, y, order, B, C, params, steps, lr=1e-3, b1=0.9, b2=0.999, eps=1e-7, step_rows=None):
     p = params.clone().requires_grad_(True)
     m, v = torch.zeros_like(p), torch.zeros_like(p)
     losses, accs = [], []
     for s in range(steps):
-        rows = order[s * B:(s + 1) * B].long()
+        rows = order[s * B:s * B + (B if step_rows is None else int(step_rows[s]))].long()
         W1, c1, W2, c2, W3, c3, W4, c4 = _split(p, C)
         h = torch.relu(X[rows] @ W1 + c1)
         h = torch.relu(h @ W2 + c2)
         h = torch.relu(h @ W3 + c3)
         logits = h @ W4 + c4
         prob = torch.softmax(logits, dim=1)
-        pl = prob[torch.arange(B), y[rows].long()]
+        pl = prob[torch.arange(rows.shape[0]), y[rows].long()]
         loss = -torch.log(torch.clamp(pl, min=1e-7)).mean()
         (g,) = torch.autograd.grad(loss, p)
         with torch.no_grad():
@@ -84,6 +84,27 @@ def test_train_steps_match_torch_fp32_reference(eng, B, C, steps):
     ref_l = torch.nn.functional.cross_entropy(logits, y.long(), reduction="none")
     np.testing.assert_allclose(ev_loss.cpu().numpy(), ref_l.cpu().numpy(), rtol=1e-4, atol=1e-5)
     assert float((pred == logits.argmax(1)).float().mean()) > 0.999
+
+
+def test_ragged_steps_match_torch_fp32_reference(eng):
+    # batch() before repeat(): every pass ends in a short batch that is an ordinary optimiser step (train_tf_ps.py:664-665)
+    rng = np.random.default_rng(99)
+    n, B, C = 300, 64, 4                                  # passes of 64, 64, 64, 64, 44 rows
+    X = torch.from_numpy((rng.random((n, 3)) * 4 - 2).astype(np.float32)).to(eng.device)
+    y = torch.from_numpy(rng.integers(0, C, n).astype(np.int32)).to(eng.device)
+    params0 = torch.from_numpy(T.glorot_uniform_params(C, rng)).to(eng.device)
+    steps = 12
+    order_np, rows_np = T.batch_stream(n, min(3000, n), B, steps, np.random.default_rng(5))
+    assert rows_np.tolist() == [64, 64, 64, 64, 44, 64, 64, 64, 64, 44, 64, 64]
+    assert sorted(np.concatenate([order_np[i, :rows_np[i]] for i in range(5)]).tolist()) == list(range(n))   # a pass = a permutation
+    order = torch.from_numpy(order_np.reshape(-1)).to(eng.device)
+    params = params0.clone()
+    m, v = torch.zeros_like(params), torch.zeros_like(params)
+    loss, acc = eng.mlp_train_steps(X, y, order, B, C, params, m, v, step_rows=torch.from_numpy(rows_np).to(eng.device))
+    ref_p, ref_loss, ref_acc = _torch_reference(X, y, order, B, C, params0, steps, step_rows=rows_np)
+    np.testing.assert_allclose(loss.cpu().numpy(), np.array(ref_loss), rtol=TOL_LOSS)
+    np.testing.assert_allclose(acc.cpu().numpy(), np.array(ref_acc), atol=1.5 / 44)
+    np.testing.assert_allclose(params.cpu().numpy(), ref_p.cpu().numpy(), atol=TOL_PARAM)
 
 
 def test_shuffle_buffer_order_semantics():
