@@ -220,7 +220,7 @@ class KMeans:
         if distinct.shape[0] <= k:
             return distinct
         cluster, _ = eng.kmeans_assign(index, nums, torch.from_numpy(distinct).to(eng.device), L, repeats)
-        weights = self._all_sum(torch.bincount(cluster.to(torch.int64), minlength=distinct.shape[0]))
+        weights = self._all_sum(eng.code_histogram(Column(cluster), distinct.shape[0])[0])     # rows per candidate
         return local_kmeans_pp(np.random.default_rng(self.seed), distinct, weights.cpu().numpy().astype(np.float64), k)
 
     def fit(self, dataset) -> KMeansModel:
