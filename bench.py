@@ -333,6 +333,8 @@ def run_config4(ctx, args):
     val = eng.synth_column(cfg["seed"], 1, S.KIND_EXACT, n, row0=row0, with_valid=False).data
     cap = G // world + G // (world * 8) + 4096
     peer = D.BucketExchange(eng, n, groups_hint=G) if world > 1 else None
+    if peer is not None:
+        peer.timing = True               # events around the NVLink transfer of every step (first copy starts .. last group landed)
     state = {}
 
     def step():
@@ -347,6 +349,8 @@ def run_config4(ctx, args):
         state["pg"] = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=G, peer=peer, mark=mark)
         state["marks"] = marks
         state.setdefault("all_marks", []).append(marks)
+        if peer is not None:
+            state.setdefault("windows", []).append(peer.window)
 
     total_ms, per_step, clocks = timed_steps(ctx, step, args.steps, args.warmup)
     launches = ctx.sum_over_ranks(ctx.launches)
@@ -359,6 +363,9 @@ def run_config4(ctx, args):
             phase_ms[b] = ctx.max_over_ranks(statistics.mean(vals_ms))
     ms_per_step = total_ms / args.steps
     value = rows_total / (ms_per_step * 1e-3)
+    transfer_ms = None
+    if peer is not None:
+        transfer_ms = ctx.max_over_ranks(statistics.mean(a.elapsed_time(b) for a, b in state["windows"][-args.steps:]))
 
     # ---- checks (not timed): the last step's output against the oracle
     res = eng.groupby_result(state["pg"], sort=False)
@@ -430,7 +437,8 @@ def run_config4(ctx, args):
             del h_key, h_val, h_out
         except Exception as exc:   # e.g. the host cannot pin 16 GB
             e2e = {"value": None, "unit": UNIT, "error": f"{type(exc).__name__}: {exc}"}
-    slab_bytes_moved = 16.0 * peer.slab * peer.buckets * (world - 1) if world > 1 else 0.0
+    slab_bytes_moved = 16.0 * sum(peer.slabs) * peer.buckets * (world - 1) if world > 1 else 0.0
+    waves = peer.waves if world > 1 else 0
     del key, val, peer
 
     line = None
@@ -445,9 +453,11 @@ def run_config4(ctx, args):
         design = {"level1": 32.0 * n, "level2": 32.0 * n, "merge": 16.0 * n + 32.0 * g_local}
         if world > 1:
             # N > 1 (dist.BucketExchange): "partition" = the local (rank, bucket) scatter - the first level, done by the
-            # sender; "exchange" = the slab copies over NVLink (send buffer read, receive buffer written) with the
-            # second level and the merge of the bucket groups that have landed running behind them; what is left of
-            # those after the last group has landed shows up as the (small) level2 / merge phases.
+            # sender, wave by wave (the slabs of wave w already cross NVLink while wave w + 1 is being cut, so this
+            # phase overlaps the transfer); "exchange" = what is left of the slab copies over NVLink (send buffer
+            # read, receive buffer written) after the last wave has been cut, with the second level and the merge
+            # of the bucket groups that have landed running behind them; what is left of those after the last group
+            # has landed shows up as the (small) level2 / merge phases.  nvlink.transfer_ms is the whole transfer.
             design = {"partition": 32.0 * n, "exchange": 32.0 * n + 32.0 * n + 16.0 * n + 32.0 * g_local}
         phases = {}
         for name, ms in phase_ms.items():
@@ -471,19 +481,23 @@ def run_config4(ctx, args):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": dict(config4_workload(rows_total, G), rows_per_gpu=n,
                            l2=f"no flush: {16 * n / 1e9:.1f} GB of input per GPU per step >> 126 MB L2",
-                           parallelism=(f"rows split over {world} GPUs; each rank partitions its rows by (owner rank, bucket), "
-                                        "copies the slabs into the owners' symmetric-memory buffers over NVLink bucket group "
-                                        "by bucket group (copy engines) and merges every group as soon as it has landed")
+                           parallelism=(f"rows split over {world} GPUs; each rank partitions its rows by (owner rank, bucket) in "
+                                        f"{waves} waves, stores the slabs of a wave into the owners' symmetric-memory buffers "
+                                        "over NVLink bucket group by bucket group while the next wave is being cut, and "
+                                        "merges every group as soon as its last wave has landed")
                            if world > 1 else "one GPU, no exchange"),
             "roofline": roof, "checks": checks, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
-        if world > 1 and phase_ms.get("exchange"):
+        if world > 1 and transfer_ms:
             sent = 16.0 * (n - n / world)
-            gbs = sent / (phase_ms["exchange"] * 1e-3) / 1e9
-            line["nvlink"] = {"bound": "nvlink", "sent_bytes_per_gpu": sent, "exchange_ms": phase_ms["exchange"],
+            gbs = sent / (transfer_ms * 1e-3) / 1e9
+            line["nvlink"] = {"bound": "nvlink", "sent_bytes_per_gpu": sent, "transfer_ms": transfer_ms,
+                              "exchange_ms": phase_ms.get("exchange"), "waves": waves,
                               "achieved": gbs, "peak": NVLINK_GBS, "unit": "GB/s", "frac": gbs / NVLINK_GBS,
-                              "moved_bytes_per_gpu": slab_bytes_moved,
-                              "note": "sent = payload records leaving the GPU; moved = whole slabs (payload + the 6-sigma slack)"}
+                              "slab_room_bytes_per_gpu": slab_bytes_moved,
+                              "note": "sent = payload records leaving the GPU (only the filled part of a slab moves); transfer_ms = "
+                                      "first copy kernel of the first wave starts .. last bucket group of the last wave has landed "
+                                      "on every rank (CUDA events, mean over the timed steps, max over ranks)"}
     return line
 
 

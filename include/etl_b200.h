@@ -479,6 +479,10 @@ ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records,
  *     into peer_records[r] at slab (my_rank * buckets + bucket) - the receivers'
  *     [source][bucket] layout - with 16-byte stores over NVLink (~700 GB/s per GPU
  *     measured; no shared memory, so it runs beside the merge of earlier groups).
+ *   etl_peer_copy_slabs_bulk: the same movement, same arguments, through the TMA
+ *     engine: one thread per CTA streams its share of a slab through a 48 KB ring
+ *     of shared memory (bulk async load from the send buffer, bulk async store into
+ *     the owner's buffer; no tensor map).  ctas_per_slab 0 = about one CTA per SM.
  *   etl_copy_async: stream-ordered device-to-device copy through a copy engine
  *     (dst may be a peer's memory); an alternative mover for the same slabs
  *     (measured slower at 8 GPUs: 330-400 GB/s per GPU).
@@ -508,6 +512,9 @@ ETL_API int etl_copy_async(etl_handle* h, void* dst, const void* src, int64_t nb
 ETL_API int etl_peer_copy_slabs(etl_handle* h, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
                         int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
                         const int64_t* d_cursor, int32_t ctas_per_slab, void* stream);
+ETL_API int etl_peer_copy_slabs_bulk(etl_handle* h, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
+                             int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
+                             const int64_t* d_cursor, int32_t ctas_per_slab, void* stream);
 
 /* Diagnostic, no reference counterpart (tools/nvlink_probe.py): copy nbytes (a
  * multiple of 16) from src to dst - dst may be a peer GPU's memory mapped here -

@@ -92,6 +92,8 @@ _PROTOS = {
                                              C.c_void_p, C.c_int32, C.c_void_p]),
     "etl_peer_copy_slabs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                       C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
+    "etl_peer_copy_slabs_bulk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                           C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
     "etl_copy_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "etl_groupby_merge_slabs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64,
                                           C.c_int32, C.c_int64,

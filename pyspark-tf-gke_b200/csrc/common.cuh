@@ -7,6 +7,7 @@
 #include <stdarg.h>
 #include <string.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "../../include/etl_b200.h"
 
@@ -169,6 +170,17 @@ __device__ __forceinline__ unsigned lanemask_lt() {
     unsigned m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
+}
+
+// ETL_SMEM_CARVEOUT=<percent>: preferred shared-memory carve-out of the partition and merge kernels (unset = the
+// driver's choice, the smallest configuration that holds the resident CTAs).  A larger carve-out leaves room for
+// another kernel's shared memory on the same SM (the TMA slab mover beside the merge).
+inline int smem_carveout_percent() {
+    static const int v = [] {
+        const char* e = getenv("ETL_SMEM_CARVEOUT");
+        return e && *e ? atoi(e) : -1;
+    }();
+    return v;
 }
 
 // Tile-state word: [63:42] epoch (22 bits) | [41:40] flag | [39:0] value.

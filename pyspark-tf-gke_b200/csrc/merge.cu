@@ -312,6 +312,8 @@ static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t piece0, 
     const size_t smem = (size_t)smem_slots * (minmax ? 36 : 20);
     auto kern = minmax ? etl::groupby_merge_kernel<true> : etl::groupby_merge_kernel<false>;
     ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (const int carve = etl::smem_carveout_percent(); carve >= 0)
+        ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     int occ = 0;
     ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, etl::MG_THREADS, smem));
     if (occ < 1) occ = 1;

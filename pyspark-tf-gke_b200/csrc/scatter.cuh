@@ -265,6 +265,10 @@ static inline cudaError_t launch_scatter_variant(int sm_count, const ScatterJob&
     auto kern = scatter_pipelined_kernel<RECORDS, THREADS, SLAB, TILE>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    if (const int carve = smem_carveout_percent(); carve >= 0) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        if (e != cudaSuccess) return e;
+    }
     kern<<<grid, THREADS, smem, stream>>>(job, dst);
     return cudaGetLastError();
 }

@@ -120,6 +120,58 @@ __global__ void __launch_bounds__(32) peer_write_bulk_kernel(const unsigned char
     bulk_wait_read<0>();
 }
 
+// ---- the same movement through the TMA engine: one thread per CTA streams its share of a slab through a ring of
+//      shared-memory stages - bulk async load from this GPU's send buffer, bulk async store into the owner's receive
+//      buffer (no tensor map, no multicast: TMA multicast loads here read only this GPU's memory, and this kernel
+//      uses none).  The bytes in flight are the ring (48 KB per CTA) instead of eight registers per thread, so the
+//      transfer keeps its rate when the partition and merge kernels load HBM beside it, and it takes no issue slots
+//      from them.
+constexpr int BULK_CHUNK = 8192;
+constexpr int BULK_STAGES = 6;
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__global__ void __launch_bounds__(32) peer_copy_slabs_bulk_kernel(const SlabCopyJob job, const PartDest peers) {
+    extern __shared__ __align__(128) unsigned char cb_smem[];
+    __shared__ uint64_t bar[BULK_STAGES];
+    if (threadIdx.x != 0) return;
+    const int r = blockIdx.y / job.nbuckets, b = job.bucket0 + blockIdx.y % job.nbuckets;
+    int64_t n = job.cursor[r * job.buckets + b];
+    n = n < job.slab ? n : job.slab;
+    const int64_t nbytes = n * 16;
+    const unsigned char* src = reinterpret_cast<const unsigned char*>(job.send + ((int64_t)r * job.buckets + b) * job.slab);
+    unsigned char* dst = reinterpret_cast<unsigned char*>(reinterpret_cast<longlong2*>(peers.base[r]) +
+                                                          ((int64_t)job.my_rank * job.buckets + b) * job.slab);
+    const int64_t chunks = (nbytes + BULK_CHUNK - 1) / BULK_CHUNK;
+    const int64_t mine = chunks > blockIdx.x ? (chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;   // chunks x, x + grid, ...
+    if (mine == 0) return;
+    for (int s = 0; s < BULK_STAGES; ++s) mbar_init(bar + s, 1);
+    mbar_init_fence();
+    auto bytes_of = [&](int64_t c) {
+        const int64_t left = nbytes - c * BULK_CHUNK;
+        return left < BULK_CHUNK ? (unsigned)left : (unsigned)BULK_CHUNK;
+    };
+    auto issue = [&](int64_t j) {
+        const int s = (int)(j % BULK_STAGES);
+        const int64_t c = blockIdx.x + j * gridDim.x;
+        const unsigned bytes = bytes_of(c);
+        mbar_arrive_expect_tx(bar + s, bytes);
+        bulk_load(cb_smem + s * BULK_CHUNK, src + c * BULK_CHUNK, bytes, bar + s);
+    };
+    for (int64_t j = 0; j < BULK_STAGES - 1 && j < mine; ++j) issue(j);
+    for (int64_t j = 0; j < mine; ++j) {
+        const int s = (int)(j % BULK_STAGES);
+        const int64_t c = blockIdx.x + j * gridDim.x;
+        mbar_wait(bar + s, (unsigned)(j / BULK_STAGES) & 1u);
+        bulk_store(dst + c * BULK_CHUNK, cb_smem + s * BULK_CHUNK, bytes_of(c));
+        bulk_commit();
+        if (j + BULK_STAGES - 1 < mine) {
+            bulk_wait_read<1>();      // every store but the one just issued has read its stage: the stage of chunk j - 1 is free
+            issue(j + BULK_STAGES - 1);
+        }
+    }
+    bulk_wait_all();
+}
+
 }  // namespace etl
 
 using etl::Handle;
@@ -249,9 +301,9 @@ extern "C" int etl_copy_async(etl_handle* hh, void* dst, const void* src, int64_
     return ETL_OK;
 }
 
-extern "C" int etl_peer_copy_slabs(etl_handle* hh, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
-                                   int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
-                                   const int64_t* d_cursor, int32_t ctas_per_slab, void* stream_) {
+static int peer_copy_slabs(bool bulk, etl_handle* hh, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
+                           int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
+                           const int64_t* d_cursor, int32_t ctas_per_slab, void* stream_) {
     ETL_REQUIRE(hh && send_records && peer_records && d_cursor, "peer_copy_slabs: NULL argument");
     ETL_REQUIRE(ranks >= 1 && buckets >= 1 && (int64_t)ranks * buckets <= etl::PART_MAX && my_rank >= 0 && my_rank < ranks,
                 "peer_copy_slabs: ranks=%d buckets=%d my_rank=%d", ranks, buckets, my_rank);
@@ -270,11 +322,36 @@ extern "C" int etl_peer_copy_slabs(etl_handle* hh, const int64_t* send_records, 
     job.send = reinterpret_cast<const longlong2*>(send_records); job.cursor = d_cursor; job.ranks = ranks; job.my_rank = my_rank;
     job.buckets = buckets; job.bucket0 = bucket0; job.nbuckets = nbuckets; job.slab = slab_capacity;
     const int pairs = ranks * nbuckets;
-    int gx = ctas_per_slab > 0 ? ctas_per_slab : (h->sm_count / 2 + pairs - 1) / pairs;     // about one small CTA per two SMs
-    const int64_t want = (slab_capacity + etl::COPY_THREADS * etl::COPY_UNROLL - 1) / (etl::COPY_THREADS * etl::COPY_UNROLL);
-    if (gx > want) gx = (int)want;
-    if (gx < 1) gx = 1;
-    etl::peer_copy_slabs_kernel<<<dim3((unsigned)gx, (unsigned)pairs), etl::COPY_THREADS, 0, static_cast<cudaStream_t>(stream_)>>>(job, peers);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (bulk) {
+        int gx = ctas_per_slab > 0 ? ctas_per_slab : (h->sm_count + pairs - 1) / pairs;     // about one one-warp CTA per SM
+        const int64_t want = (slab_capacity * 16 + etl::BULK_CHUNK - 1) / etl::BULK_CHUNK;
+        if (gx > want) gx = (int)want;
+        if (gx < 1) gx = 1;
+        const int smem = etl::BULK_STAGES * etl::BULK_CHUNK;
+        ETL_CUDA(cudaFuncSetAttribute(etl::peer_copy_slabs_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        etl::peer_copy_slabs_bulk_kernel<<<dim3((unsigned)gx, (unsigned)pairs), 32, smem, stream>>>(job, peers);
+    } else {
+        int gx = ctas_per_slab > 0 ? ctas_per_slab : (h->sm_count / 2 + pairs - 1) / pairs;     // about one small CTA per two SMs
+        const int64_t want = (slab_capacity + etl::COPY_THREADS * etl::COPY_UNROLL - 1) / (etl::COPY_THREADS * etl::COPY_UNROLL);
+        if (gx > want) gx = (int)want;
+        if (gx < 1) gx = 1;
+        etl::peer_copy_slabs_kernel<<<dim3((unsigned)gx, (unsigned)pairs), etl::COPY_THREADS, 0, stream>>>(job, peers);
+    }
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
+}
+
+extern "C" int etl_peer_copy_slabs(etl_handle* hh, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
+                                   int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
+                                   const int64_t* d_cursor, int32_t ctas_per_slab, void* stream_) {
+    return peer_copy_slabs(false, hh, send_records, peer_records, ranks, my_rank, buckets, bucket0, nbuckets, slab_capacity, d_cursor,
+                           ctas_per_slab, stream_);
+}
+
+extern "C" int etl_peer_copy_slabs_bulk(etl_handle* hh, const int64_t* send_records, int64_t* const* peer_records, int32_t ranks,
+                                        int32_t my_rank, int32_t buckets, int32_t bucket0, int32_t nbuckets, int64_t slab_capacity,
+                                        const int64_t* d_cursor, int32_t ctas_per_slab, void* stream_) {
+    return peer_copy_slabs(true, hh, send_records, peer_records, ranks, my_rank, buckets, bucket0, nbuckets, slab_capacity, d_cursor,
+                           ctas_per_slab, stream_);
 }

@@ -250,7 +250,8 @@ class BucketExchange:
     A slab that overflows (skewed keys) only counts the surplus; the result object
     then repeats the exchange on the counted path (PeerExchange)."""
 
-    def __init__(self, eng, rows_per_rank: int, groups_hint: int, bucket_groups: int = 8, group=None, copy_streams: int = 4):
+    def __init__(self, eng, rows_per_rank: int, groups_hint: int, bucket_groups: int = 8, group=None, copy_streams: int = 4,
+                 waves: Optional[int] = None, mover: Optional[str] = None):
         import os
         import torch.distributed._symmetric_memory as symm
 
@@ -272,24 +273,64 @@ class BucketExchange:
         self.bucket_groups = max(1, min(int(os.environ.get("ETL_BUCKET_GROUPS", bucket_groups)), bx))
         while bx % self.bucket_groups:
             self.bucket_groups -= 1
-        self.slab = eng.slab_capacity(self.rows_per_rank / (size * bx), self.rows_per_key)
+        # The rows can go in `waves` parts, each with its own slabs: wave w crosses NVLink while wave w + 1 is still being
+        # cut, so only the cut of the first wave is exposed.  The merge of a bucket group needs every wave's records of
+        # the group, so the LAST wave is the large one (1 - head of the rows: its groups are sent one by one with the
+        # merges right behind them) and every earlier wave is `head` of what follows it - just enough transfer to cover
+        # the next cut (cut : transfer is about 1 : 4 on NVLink 5, hence head = 1/4).  Measured on config 4: two waves
+        # 13.1 -> 12.5 ms at 2 GPUs, but 4.63 -> 4.74 ms at 8 (the cut and the transfer slow each other down by as much
+        # as the overlap gains: DESIGN.md section 6), so the default is two waves on 2 GPUs and one otherwise.
+        default_waves = os.environ.get("ETL_EXCHANGE_WAVES", "2" if size == 2 else "1")
+        W = self.waves = max(1, min(int(default_waves) if waves is None else int(waves), 6))
+        head = min(0.5, max(0.01, float(os.environ.get("ETL_EXCHANGE_HEAD", "0.25"))))
+        fracs = [head ** (W - 1 - w) * (1.0 - head if w else 1.0) for w in range(W)] if W > 1 else [1.0]
+        fracs = [f / sum(fracs) for f in fracs]
+        bounds, acc = [0], 0.0
+        for w in range(W):
+            acc += fracs[w]
+            end = self.rows_per_rank if w == W - 1 else min(self.rows_per_rank, -(-int(acc * self.rows_per_rank) // 4096) * 4096)
+            bounds.append(max(end, bounds[-1]))
+        self.wave_bounds = bounds                                      # wave w = rows [bounds[w], bounds[w + 1]) of this rank
+        self.slabs = [eng.slab_capacity(max(bounds[w + 1] - bounds[w], 1) / (size * bx), self.rows_per_key) for w in range(W)]
+        self.wave_groups = []
+        for w in range(W):                                           # bucket groups a wave is sent in (powers of two divide bx)
+            want = self.bucket_groups if w == W - 1 else max(1, int(self.bucket_groups * fracs[w] + 0.5))
+            gw = 1
+            while gw * 2 <= want and bx % (gw * 2) == 0:
+                gw *= 2
+            self.wave_groups.append(self.bucket_groups if w == W - 1 else gw)
         self.cap2 = eng.slab_capacity(self.rows_per_rank / (bx * self.sub), self.rows_per_key)
         dev = eng.device
-        self.send = torch.empty((size * bx * self.slab, 2), dtype=torch.int64, device=dev)
-        self.recv = symm.empty((size * bx * self.slab, 2), dtype=torch.int64, device=dev)
-        self.handle = symm.rendezvous(self.recv, self.group.group_name)
-        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
-        self.counts = symm.empty(size * bx, dtype=torch.int64, device=dev)
-        self.counts_handle = symm.rendezvous(self.counts, self.group.group_name)
-        self.count_ptrs = [int(p) for p in self.counts_handle.buffer_ptrs]
+        starts = [0]
+        for w in range(W):
+            starts.append(starts[-1] + size * bx * self.slabs[w])    # records of a wave's slabs, [rank or source][bucket]
+        self.send_all = torch.empty((starts[-1], 2), dtype=torch.int64, device=dev)
+        self.recv_all = symm.empty((starts[-1], 2), dtype=torch.int64, device=dev)
+        self.handle = symm.rendezvous(self.recv_all, self.group.group_name)
+        self.send = [self.send_all[starts[w]:starts[w + 1]] for w in range(W)]
+        self.recv = [self.recv_all[starts[w]:starts[w + 1]] for w in range(W)]
+        self.peer_ptrs = [[int(p) + starts[w] * 16 for p in self.handle.buffer_ptrs] for w in range(W)]
+        self.counts_all = symm.empty(W * size * bx, dtype=torch.int64, device=dev)
+        self.counts_handle = symm.rendezvous(self.counts_all, self.group.group_name)
+        self.counts = self.counts_all.view(W, size * bx)
+        self.count_ptrs = [[int(p) + w * size * bx * 8 for p in self.counts_handle.buffer_ptrs] for w in range(W)]
         self.pieces = torch.empty((bx * self.sub * self.cap2, 2), dtype=torch.int64, device=dev)
         self.copy_streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, int(os.environ.get("ETL_COPY_STREAMS", copy_streams))))]
         self.sync_stream = torch.cuda.Stream(device=dev)
         self.compute = torch.cuda.Stream(device=dev)
-        # how the slabs cross NVLink: "sm" = etl_peer_copy_slabs (16-byte stores, ~700 GB/s per GPU measured, runs beside
-        # the merge kernels), "ce" = stream-ordered peer copies through the copy engines (330-400 GB/s at 8 GPUs)
-        self.mover = os.environ.get("ETL_EXCHANGE_MOVER", "sm")
+        # how the slabs cross NVLink: "sm" = etl_peer_copy_slabs (16-byte stores from registers, runs beside the merge
+        # kernels), "tma" = etl_peer_copy_slabs_bulk (bulk async copies through a shared-memory ring, one thread per CTA),
+        # "ce" = stream-ordered peer copies through the copy engines (330-400 GB/s at 8 GPUs)
+        self.mover = mover or os.environ.get("ETL_EXCHANGE_MOVER", "sm")
+        if self.mover not in ("sm", "tma", "ce"):
+            raise ValueError(f"BucketExchange: mover={self.mover!r}")
         self.copy_ctas = int(os.environ.get("ETL_COPY_CTAS", "0"))
+        # measurement only (tools/measure_shuffle.py --skip; the result is then wrong): "copy" = leave the transfer out
+        # (the receive buffers keep the previous exchange's records), "compute" = leave the receivers' second level and
+        # merge out - what each side costs on its own
+        self.skip = ""
+        self.timing = False            # True: every shuffle leaves (first copy starts, last group landed) events in .window
+        self.window = None
         self._counted: Optional[PeerExchange] = None
 
     chunks = 1   # device-resident rows need no chunking here (shuffle_groupby_sum_host brings its own chunks)
@@ -307,66 +348,93 @@ class BucketExchange:
     def shuffle(self, chunk_iter, capacity: int, minmax: bool = False, mark=None):
         """chunk_iter yields (keys, vals, n, ready_event or None) device chunks of this rank's rows
         -> PartitionedGroups of the keys this rank owns (enqueued; main stream waits for the merge)."""
-        eng, size, rank, bx, slab = self.eng, self.size, self.rank, self.buckets, self.slab
+        eng, size, rank, bx, W = self.eng, self.size, self.rank, self.buckets, self.waves
         mark = mark or (lambda name: None)
         main = torch.cuda.current_stream(eng.device)
         pg = eng.new_partitioned_groups(capacity, max(self.rows_per_rank // 8, 1 << 16), bx * self.sub, minmax=minmax)
-        xcur = torch.zeros(size * bx, dtype=torch.int64, device=eng.device)
+        xcur = torch.zeros((W, size * bx), dtype=torch.int64, device=eng.device)
         cur2 = torch.zeros(bx * self.sub, dtype=torch.int64, device=eng.device)
         mark("init")
         self.handle.barrier()            # every rank has finished reading the previous exchange's records
-        send_ptr = self.send.data_ptr()
+        state = {"k": 0, "first": None, "landed": None}
+
+        def send_wave(w):
+            """Wave w has been cut into its slabs on the main stream: publish the counts, move the slabs group by group,
+            and let the compute stream take every group as soon as it has landed."""
+            slab, groups = self.slabs[w], self.wave_groups[w]
+            bpg = bx // groups
+            nbytes = bpg * slab * 16
+            eng.peer_publish_counts(xcur[w], self.count_ptrs[w], rank * bx, per_rank=bx)
+            cut = torch.cuda.Event()
+            cut.record(main)
+            movers = self.copy_streams if self.mover == "ce" else self.copy_streams[:1]
+            for st in movers:
+                st.wait_event(cut)
+            if self.timing and state["first"] is None:
+                state["first"] = torch.cuda.Event(enable_timing=True)
+                state["first"].record(movers[0])
+            send_ptr = self.send[w].data_ptr()
+            for g in range(groups):
+                copied = []
+                if self.mover != "ce" and self.skip != "copy":    # one kernel per group over NVLink, only the filled part of the slabs
+                    st = movers[0]
+                    with torch.cuda.stream(st):
+                        eng.peer_copy_slabs(self.send[w], self.peer_ptrs[w], rank, bx, g * bpg, bpg, slab, xcur[w], self.copy_ctas,
+                                            bulk=self.mover == "tma")
+                        ev = torch.cuda.Event()
+                        ev.record(st)
+                        copied.append(ev)
+                for i in range(size if self.mover == "ce" else 0):
+                    r = (rank + 1 + i) % size             # every rank starts with a different peer
+                    st = movers[state["k"] % len(movers)]
+                    state["k"] += 1
+                    with torch.cuda.stream(st):
+                        eng.copy_async(self.peer_ptrs[w][r] + ((rank * bx + g * bpg) * slab) * 16,
+                                       send_ptr + ((r * bx + g * bpg) * slab) * 16, nbytes)
+                        ev = torch.cuda.Event()
+                        ev.record(st)
+                        copied.append(ev)
+                with torch.cuda.stream(self.sync_stream):
+                    for ev in copied:
+                        self.sync_stream.wait_event(ev)
+                    self.handle.barrier()     # group g of every source (and the wave's count tables) has landed here
+                    landed = torch.cuda.Event(enable_timing=self.timing)
+                    landed.record(self.sync_stream)
+                    state["landed"] = landed
+                with torch.cuda.stream(self.compute):
+                    self.compute.wait_event(landed)
+                    if self.skip == "compute":
+                        continue
+                    eng.slab_partition_records(self.recv[w], bpg * size, slab, self.counts[w], None, slab, bx, self.sub, self.pieces,
+                                               self.cap2, cur2, pg.counters[4:], sources=size, bucket0=g * bpg)
+                    if w == W - 1:        # every wave's records of this group are in the pieces now
+                        eng.merge_slab_pieces(self.pieces, cur2, self.cap2, g * bpg * self.sub, bpg * self.sub, g > 0, pg)
+
+        w, pos = 0, 0
         for keys, vals, n, ready in chunk_iter:
             if ready is not None:
                 main.wait_event(ready)
-            eng.slab_partition_rows(keys, vals, n, size, bx, [send_ptr] * size, 0, slab, slab, xcur, pg.counters[4:])
-        eng.peer_publish_counts(xcur, self.count_ptrs, rank * bx, per_rank=bx)
-        partitioned = torch.cuda.Event()
-        partitioned.record(main)
+            a = 0
+            while a < n:
+                while w < W - 1 and pos >= self.wave_bounds[w + 1]:
+                    send_wave(w)
+                    w += 1
+                take = n - a if w == W - 1 else min(n - a, self.wave_bounds[w + 1] - pos)
+                eng.slab_partition_rows(keys[a:a + take], vals[a:a + take], take, size, bx, [self.send[w].data_ptr()] * size, 0,
+                                        self.slabs[w], self.slabs[w], xcur[w], pg.counters[4:])
+                a += take
+                pos += take
         mark("partition")
-        for st in self.copy_streams + [self.sync_stream, self.compute]:
-            st.wait_event(partitioned)
-        bpg = bx // self.bucket_groups
-        nbytes = bpg * slab * 16
-        k = 0
-        for g in range(self.bucket_groups):
-            copied = []
-            if self.mover == "sm":        # one kernel per group: 16-byte stores over NVLink, only the filled part of the slabs
-                st = self.copy_streams[0]
-                with torch.cuda.stream(st):
-                    eng.peer_copy_slabs(self.send, self.peer_ptrs, rank, bx, g * bpg, bpg, slab, xcur, self.copy_ctas)
-                    ev = torch.cuda.Event()
-                    ev.record(st)
-                    copied.append(ev)
-            for i in range(size if self.mover == "ce" else 0):
-                r = (rank + 1 + i) % size             # every rank starts with a different peer
-                st = self.copy_streams[k % len(self.copy_streams)]
-                k += 1
-                with torch.cuda.stream(st):
-                    eng.copy_async(self.peer_ptrs[r] + ((rank * bx + g * bpg) * slab) * 16,
-                                   send_ptr + ((r * bx + g * bpg) * slab) * 16, nbytes)
-                    ev = torch.cuda.Event()
-                    ev.record(st)
-                    copied.append(ev)
-            with torch.cuda.stream(self.sync_stream):
-                for ev in copied:
-                    self.sync_stream.wait_event(ev)
-                self.handle.barrier()     # group g of every source (and, the first time, the count tables) has landed here
-                landed = torch.cuda.Event()
-                landed.record(self.sync_stream)
-            with torch.cuda.stream(self.compute):
-                self.compute.wait_event(landed)
-                eng.slab_partition_records(self.recv, bpg * size, slab, self.counts, None, slab, bx, self.sub, self.pieces,
-                                           self.cap2, cur2, pg.counters[4:], sources=size, bucket0=g * bpg)
-                eng.merge_slab_pieces(self.pieces, cur2, self.cap2, g * bpg * self.sub, bpg * self.sub, g > 0, pg)
-        done = torch.cuda.Event()
-        done.record(self.sync_stream)
-        main.wait_event(done)
+        while w < W:                     # the last wave, and empty ones if this rank had fewer rows: every rank runs every barrier
+            send_wave(w)
+            w += 1
+        main.wait_event(state["landed"])
         mark("exchange")
         mark("level1")
         main.wait_stream(self.compute)
         mark("level2")
         mark("merge")
+        self.window = (state["first"], state["landed"]) if self.timing else None
         pg.any_overflow = self.any_overflow
         return pg
 

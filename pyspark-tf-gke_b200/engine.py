@@ -583,12 +583,14 @@ class Engine:
         self.launches += 1
 
     def peer_copy_slabs(self, send: torch.Tensor, peer_ptrs: Sequence[int], my_rank: int, buckets: int, bucket0: int,
-                        nbuckets: int, slab_capacity: int, cursor: torch.Tensor, ctas_per_slab: int = 0) -> None:
-        """The filled part of this rank's slabs of a bucket group -> every owner's receive buffer (NVLink stores)."""
+                        nbuckets: int, slab_capacity: int, cursor: torch.Tensor, ctas_per_slab: int = 0, bulk: bool = False) -> None:
+        """The filled part of this rank's slabs of a bucket group -> every owner's receive buffer over NVLink:
+        16-byte stores from registers, or (bulk) TMA bulk copies through a shared-memory ring."""
         ranks = len(peer_ptrs)
         P = C.c_void_p * ranks
-        _lib.check(self.lib.etl_peer_copy_slabs(self._h, send.data_ptr(), P(*peer_ptrs), ranks, my_rank, buckets, bucket0, nbuckets,
-                                                slab_capacity, cursor.data_ptr(), ctas_per_slab, self._stream()))
+        fn = self.lib.etl_peer_copy_slabs_bulk if bulk else self.lib.etl_peer_copy_slabs
+        _lib.check(fn(self._h, send.data_ptr(), P(*peer_ptrs), ranks, my_rank, buckets, bucket0, nbuckets,
+                      slab_capacity, cursor.data_ptr(), ctas_per_slab, self._stream()))
         self.launches += 1
 
     def copy_async(self, dst_ptr: int, src_ptr: int, nbytes: int) -> None:

@@ -50,7 +50,10 @@ def main():
     peer = D.PeerExchange(eng, int(n * 1.3) + 4096)
     slab = D.SlabExchange(eng, n, groups_hint=args.groups, chunks=3)
     bucketed = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=4)
+    one_wave = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=2, waves=1)
+    three_waves = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=8, waves=3, mover="tma")
     variants = {"bucketed": dict(peer=bucketed), "bucketed_minmax": dict(peer=bucketed, minmax=True),
+                "bucketed_one_wave": dict(peer=one_wave), "bucketed_three_waves_tma": dict(peer=three_waves),
                 "slab_chunked": dict(peer=slab), "nccl": dict(peer=None, counted=True),
                 "peer_by_rank": dict(peer=peer, exchange_buckets=1),
                 "peer_by_rank_and_bucket": dict(peer=peer, exchange_buckets=16), "host_entry": None}

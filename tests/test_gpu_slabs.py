@@ -169,57 +169,65 @@ def test_min_max_on_the_shuffle_path(eng, counted):
     np.testing.assert_allclose(col["mean"].cpu().numpy(), wcol["mean"], rtol=1e-6, atol=0, equal_nan=True)
 
 
-@pytest.mark.parametrize("R,groups_of_buckets,mover", [(2, 4, "sm"), (4, 2, "ce"), (8, 8, "sm"), (8, 1, "ce")])
-def test_simulated_bucketed_exchange(eng, R, groups_of_buckets, mover):
-    # BucketExchange's data path on one GPU: every source partitions its rows into R x Bx slabs of a send buffer,
-    # slabs are copied bucket group by bucket group into the "ranks'" receive buffers ([source][bucket] layout),
-    # cursors go to the count tables, and each receiver cuts + merges one bucket group at a time (append mode)
+@pytest.mark.parametrize("R,groups_of_buckets,mover,waves", [(2, 4, "sm", 1), (4, 2, "ce", 2), (8, 8, "sm", 2), (8, 1, "ce", 1),
+                                                              (2, 2, "sm", 3), (4, 4, "tma", 2), (8, 2, "tma", 1)])
+def test_simulated_bucketed_exchange(eng, R, groups_of_buckets, mover, waves):
+    # BucketExchange's data path on one GPU: every source partitions its rows, wave by wave, into R x Bx slabs of the
+    # wave's send buffer, slabs are copied bucket group by bucket group into the "ranks'" receive buffers ([source][bucket]
+    # layout, one set per wave), cursors go to the count tables, and each receiver cuts every group of every wave into
+    # the same pieces and merges a group once its last wave is in (append mode)
     groups = 60_000
     sizes = [90_000 + 1013 * s + (s % 2) for s in range(R)]
     rows = [_rows(sizes[s], groups, row0=s * 1_000_000 // 32 * 32) for s in range(R)]
     bx = 8
     sub = 3
-    slab = eng.slab_capacity(max(sizes) / (R * bx), 2.0)
+    W = waves
+    wave_rows = -(-max(sizes) // (W * 4096)) * 4096
+    slab = eng.slab_capacity(wave_rows / (R * bx), 2.0)
     cap2 = eng.slab_capacity(max(sizes) * 1.3 / (bx * sub), 2.0)
-    recv = [torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device) for _ in range(R)]
-    tables = [torch.zeros(R * bx, dtype=torch.int64, device=eng.device) for _ in range(R)]
+    recv = [[torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device) for _ in range(R)] for _ in range(W)]
+    tables = [[torch.zeros(R * bx, dtype=torch.int64, device=eng.device) for _ in range(R)] for _ in range(W)]
     overflow = torch.zeros(1, dtype=torch.int64, device=eng.device)
     bpg = bx // groups_of_buckets
-    sends, xcurs = [], []
+    sends, xcurs = [[] for _ in range(W)], [[] for _ in range(W)]
     for s in range(R):
         k, v = torch.from_numpy(rows[s][0]).to(eng.device), torch.from_numpy(rows[s][1]).to(eng.device)
-        send = torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device)
-        xcur = torch.zeros(R * bx, dtype=torch.int64, device=eng.device)
-        half = sizes[s] // 2 // 2 * 2               # two chunks: the cursors persist
-        for lo, hi in ((0, half), (half, sizes[s])):
-            eng.slab_partition_rows(k[lo:hi], v[lo:hi], hi - lo, R, bx, [send.data_ptr()] * R, 0, slab, slab, xcur, overflow)
-        eng.peer_publish_counts(xcur, [t.data_ptr() for t in tables], s * bx, per_rank=bx)
-        want = np.bincount(O.partition_dest(rows[s][0], R, bx), minlength=R * bx)
-        assert xcur.cpu().tolist() == want.tolist()
-        sends.append(send)
-        xcurs.append(xcur)
+        for w in range(W):
+            send = torch.full((R * bx * slab, 2), -1, dtype=torch.int64, device=eng.device)
+            xcur = torch.zeros(R * bx, dtype=torch.int64, device=eng.device)
+            w_lo, w_hi = min(sizes[s], w * wave_rows), min(sizes[s], (w + 1) * wave_rows) if w < W - 1 else sizes[s]
+            half = w_lo + (w_hi - w_lo) // 2 // 2 * 2               # two chunks per wave: the cursors persist
+            for lo, hi in ((w_lo, half), (half, w_hi)):
+                eng.slab_partition_rows(k[lo:hi], v[lo:hi], hi - lo, R, bx, [send.data_ptr()] * R, 0, slab, slab, xcur, overflow)
+            eng.peer_publish_counts(xcur, [t.data_ptr() for t in tables[w]], s * bx, per_rank=bx)
+            want = np.bincount(O.partition_dest(rows[s][0][w_lo:w_hi], R, bx), minlength=R * bx)
+            assert xcur.cpu().tolist() == want.tolist()
+            sends[w].append(send)
+            xcurs[w].append(xcur)
     all_k = np.concatenate([k for k, _ in rows])
     all_v = np.concatenate([v for _, v in rows])
     for r in range(R):
         pg = eng.new_partitioned_groups(groups, 1 << 16, bx * sub)
         cur2 = torch.zeros(bx * sub, dtype=torch.int64, device=eng.device)
         pieces = torch.full((bx * sub * cap2, 2), -1, dtype=torch.int64, device=eng.device)
-        for g in range(groups_of_buckets):
-            for s in range(R):
-                if mover == "ce":      # whole slabs through a copy engine
-                    eng.copy_async(recv[r].data_ptr() + ((s * bx + g * bpg) * slab) * 16,
-                                   sends[s].data_ptr() + ((r * bx + g * bpg) * slab) * 16, bpg * slab * 16)
-                elif r == 0:           # the store kernel serves every destination at once: the filled parts only
-                    eng.peer_copy_slabs(sends[s], [t.data_ptr() for t in recv], s, bx, g * bpg, bpg, slab, xcurs[s],
-                                        ctas_per_slab=3 if s % 2 else 0)
-            eng.slab_partition_records(recv[r], bpg * R, slab, tables[r], None, slab, bx, sub, pieces, cap2, cur2, pg.counters[4:],
-                                       sources=R, bucket0=g * bpg)
-            eng.merge_slab_pieces(pieces, cur2, cap2, g * bpg * sub, bpg * sub, g > 0, pg)
+        for w in range(W):
+            for g in range(groups_of_buckets):
+                for s in range(R):
+                    if mover == "ce":      # whole slabs through a copy engine
+                        eng.copy_async(recv[w][r].data_ptr() + ((s * bx + g * bpg) * slab) * 16,
+                                       sends[w][s].data_ptr() + ((r * bx + g * bpg) * slab) * 16, bpg * slab * 16)
+                    elif r == 0:           # the store kernel serves every destination at once: the filled parts only
+                        eng.peer_copy_slabs(sends[w][s], [t.data_ptr() for t in recv[w]], s, bx, g * bpg, bpg, slab, xcurs[w][s],
+                                            ctas_per_slab=3 if s % 2 else 0, bulk=mover == "tma")
+                eng.slab_partition_records(recv[w][r], bpg * R, slab, tables[w][r], None, slab, bx, sub, pieces, cap2, cur2,
+                                           pg.counters[4:], sources=R, bucket0=g * bpg)
+                if w == W - 1:
+                    eng.merge_slab_pieces(pieces, cur2, cap2, g * bpg * sub, bpg * sub, g > 0, pg)
         torch.cuda.synchronize()
         assert int(pg.counters[4].item()) == 0 and int(overflow.item()) == 0
-        # count table of rank r: [source][bucket] = what the oracle sends there
+        # count tables of rank r: [source][bucket] = what the oracle sends there, summed over the waves
         want_counts = [int((O.partition_dest(rows[s][0], R, bx) == r * bx + b).sum()) for s in range(R) for b in range(bx)]
-        assert tables[r].cpu().tolist() == want_counts
+        assert sum(tables[w][r] for w in range(W)).cpu().tolist() == want_counts
         # piece f of rank r holds exactly the owned records whose fine index is f
         own = O.partition_dest(all_k, R) == r
         h = O.mix64(all_k[own].view(np.uint64))

@@ -43,6 +43,10 @@ def main():
                          "peer = partition fused with NVLink peer stores (chunked slabs, or counted with --counted); "
                          "nccl = send buffer + all_to_all_single")
     ap.add_argument("--bucket-groups", type=int, default=8)
+    ap.add_argument("--waves", type=int, default=None, help="bucketed exchange: parts the rows are cut and sent in (default 2)")
+    ap.add_argument("--skip", default="", choices=["", "copy", "compute"],
+                    help="bucketed exchange, timed steps only: leave out the NVLink transfer or the receivers' work, to time "
+                         "the other side alone (the result is then wrong by design: no checks)")
     ap.add_argument("--out", default=None, help="append the JSON line to this file as well (rank 0)")
     ap.add_argument("--merge", default="smem", choices=["smem", "table"],
                     help="smem = two partition levels + shared-memory tables; table = bucket-by-bucket global table")
@@ -90,15 +94,20 @@ def main():
     B = D.choose_buckets(cap, 1) if args.buckets < 0 else args.buckets
     peer = None
     if world > 1 and args.exchange == "bucketed" and not args.counted:
-        peer = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=args.bucket_groups)
+        peer = D.BucketExchange(eng, n, groups_hint=args.groups, bucket_groups=args.bucket_groups, waves=args.waves)
     elif world > 1 and args.exchange in ("peer", "bucketed"):
         peer = (D.PeerExchange(eng, int(n * 1.05) + (1 << 20)) if args.counted
                 else D.SlabExchange(eng, n, groups_hint=args.groups, chunks=args.chunks))
     from tools.clocks import ClockSampler
     sampler = ClockSampler(local)
     sampler.start()
+    transfer = []
+    if isinstance(peer, D.BucketExchange):
+        peer.timing = True
     for it in range(args.warmup + args.steps):
         gt = None
+        if it == args.warmup and args.skip:
+            peer.skip = args.skip
         barrier()
         marks = {"start": ev()}
         gt = D.shuffle_groupby_sum(eng, key, val, cap, groups_hint=args.groups, buckets=B, peer=peer, merge=args.merge,
@@ -110,12 +119,18 @@ def main():
             for a, b in zip(order[:-1], order[1:]):
                 phases[b].append(max_ms(marks[a], marks[b]))
             phases["total"].append(max_ms(marks["start"], marks["merge"]))
+            if getattr(peer, "window", None):   # first copy kernel starts .. last bucket group landed
+                transfer.append(max_ms(*peer.window))
             if "level1" in marks:   # inside "merge": the two partition levels of the shared-memory path
                 phases["level1"].append(max_ms(marks["exchange"], marks["level1"]))
                 phases["level2"].append(max_ms(marks["level1"], marks["level2"]))
     clocks = sampler.stop()
     # ---- checks
-    res = eng.groupby_result(gt, max_groups=cap, sort=True)
+    if args.skip:                    # a timing-only run: there is no result to check
+        res = {"rows": torch.zeros(1, dtype=torch.int64, device=eng.device), "keys": torch.zeros(0, device=eng.device),
+               "cols": [{"sum": torch.zeros(1, dtype=torch.float64, device=eng.device)}]}
+    else:
+        res = eng.groupby_result(gt, max_groups=cap, sort=True)
     tot = torch.stack([res["rows"].sum(), torch.tensor(res["keys"].shape[0], device=eng.device)])
     gsum = res["cols"][0]["sum"].sum().reshape(1)
     s, c = eng.sum_count([pkg.Column(val)])
@@ -128,19 +143,22 @@ def main():
     ok_sum = float(gsum.item()) == float(direct.item())  # integer-valued data: exact
     if rank == 0:
         mean = {k: float(np.mean(v)) for k, v in phases.items() if v}
+        if transfer:
+            mean["transfer"] = float(np.mean(transfer))
         line = {"workload": "config4 shuffle+aggregate", "n_gpus": world, "rows_total": n * world, "groups": args.groups,
                 "distinct_keys_found": int(tot[1].item()), "rows_conserved": ok_rows, "sum_matches_column_sum": ok_sum,
                 "ms": mean, "rows_per_s": n * world / (mean["total"] * 1e-3),
                 "buckets_per_rank": B if args.merge == "table" else None, "merge": args.merge, "exchange_buckets": args.exchange_buckets or "auto",
                 "pieces_per_rank": getattr(gt, "pieces", None), "exchange": args.exchange if world > 1 else "none", "nvlink_sent_gb_per_gpu": sent * 16 / 1e9,
-                "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean["exchange"] * 1e-3) if mean["exchange"] > 0 else None,
+                "nvlink_gbs_per_gpu": (sent * 16 / 1e9) / (mean.get("transfer", mean["exchange"]) * 1e-3) if mean["exchange"] > 0 else None,
+                "waves": getattr(peer, "waves", None), "skip": args.skip,
                 "steps": args.steps, "path": "counted" if args.counted else "slabs", "clocks": clocks,
                 "knobs": {k: v for k, v in os.environ.items() if k.startswith("ETL_")}}
         print(json.dumps(line), flush=True)
         if args.out:
             with open(args.out, "a") as fh:
                 fh.write(json.dumps(line) + "\n")
-    assert ok_rows and ok_sum
+    assert args.skip or (ok_rows and ok_sum)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
