@@ -229,8 +229,8 @@ class SlabExchange:
 
 class BucketExchange:
     """The exchange as: partition locally by (destination rank, bucket), move the
-    slabs bucket group by bucket group with the copy engines, merge each group of
-    buckets as soon as it has arrived - NVLink is the only exposed cost.
+    slabs bucket group by bucket group over NVLink, merge each group of buckets as
+    soon as it has arrived - the transfer is what stays exposed.
 
     Sender: ONE slab scatter (etl_slab_partition_rows, 4096-row tiles, all SMs) cuts
     this rank's rows into ranks x Bx slabs of a local send buffer, destination-rank
@@ -246,6 +246,11 @@ class BucketExchange:
     shared memory (etl_groupby_merge_slabs, append mode) on a compute stream while
     group g + 1 is still crossing NVLink.  No count pass, no all-gather, nothing
     read back by the host.
+    Waves (optional; the default on 2 GPUs): the rows are cut in W parts with their
+    own slabs, so that part w crosses NVLink while part w + 1 is being cut; a bucket
+    group is merged once its last wave has landed (see __init__).
+    Movers: "sm" (default, the store kernel above), "tma" (etl_peer_copy_slabs_bulk),
+    "ce" (copy engines).
 
     A slab that overflows (skewed keys) only counts the surplus; the result object
     then repeats the exchange on the counted path (PeerExchange)."""
