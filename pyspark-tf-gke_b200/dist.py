@@ -282,10 +282,10 @@ class BucketExchange:
         # cut, so only the cut of the first wave is exposed.  The merge of a bucket group needs every wave's records of
         # the group, so the LAST wave is the large one (1 - head of the rows: its groups are sent one by one with the
         # merges right behind them) and every earlier wave is `head` of what follows it - just enough transfer to cover
-        # the next cut (cut : transfer is about 1 : 4 on NVLink 5, hence head = 1/4).  Measured on config 4: two waves
-        # 13.1 -> 12.5 ms at 2 GPUs, but 4.63 -> 4.74 ms at 8 (the cut and the transfer slow each other down by as much
-        # as the overlap gains: DESIGN.md section 6), so the default is two waves on 2 GPUs and one otherwise.
-        default_waves = os.environ.get("ETL_EXCHANGE_WAVES", "2" if size == 2 else "1")
+        # the next cut (cut : transfer is about 1 : 4 on NVLink 5, hence head = 1/4).  Measured on config 4 (bench.py):
+        # two waves 13.4 -> 12.4 ms at 2 GPUs, 7.85 -> 7.24 at 4, 4.60 -> 4.45 at 8 - less than the cut it hides, because
+        # the cut and the transfer slow each other down; three waves gain nothing over two.
+        default_waves = os.environ.get("ETL_EXCHANGE_WAVES", "2")
         W = self.waves = max(1, min(int(default_waves) if waves is None else int(waves), 6))
         head = min(0.5, max(0.01, float(os.environ.get("ETL_EXCHANGE_HEAD", "0.25"))))
         fracs = [head ** (W - 1 - w) * (1.0 - head if w else 1.0) for w in range(W)] if W > 1 else [1.0]
