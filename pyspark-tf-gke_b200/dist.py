@@ -227,6 +227,25 @@ class SlabExchange:
             mark("level1")
 
 
+def plan_waves(rows: int, waves: int, head: float = 0.25):
+    """How BucketExchange cuts a rank's `rows` into `waves` parts: the last wave holds 1 - head of
+    the rows, and the rows up to and including wave w are `head` of the rows up to and including
+    wave w + 1 (so every wave is at least `head` of the next one).  -> (fractions, bounds) with wave w
+    = rows [bounds[w], bounds[w + 1]); inner bounds are multiples of 4096 rows (the scatter tile,
+    and 16-byte aligned in both columns), bounds[-1] = rows; a wave may be empty when rows is small."""
+    waves = max(1, int(waves))
+    head = min(0.5, max(0.01, float(head)))
+    fracs = [head ** (waves - 1 - w) * (1.0 - head if w else 1.0) for w in range(waves)] if waves > 1 else [1.0]
+    total = sum(fracs)
+    fracs = [f / total for f in fracs]
+    bounds, acc = [0], 0.0
+    for w in range(waves):
+        acc += fracs[w]
+        end = rows if w == waves - 1 else min(rows, -(-int(acc * rows) // 4096) * 4096)
+        bounds.append(max(end, bounds[-1]))
+    return fracs, bounds
+
+
 class BucketExchange:
     """The exchange as: partition locally by (destination rank, bucket), move the
     slabs bucket group by bucket group over NVLink, merge each group of buckets as
@@ -281,20 +300,15 @@ class BucketExchange:
         # The rows can go in `waves` parts, each with its own slabs: wave w crosses NVLink while wave w + 1 is still being
         # cut, so only the cut of the first wave is exposed.  The merge of a bucket group needs every wave's records of
         # the group, so the LAST wave is the large one (1 - head of the rows: its groups are sent one by one with the
-        # merges right behind them) and every earlier wave is `head` of what follows it - just enough transfer to cover
+        # merges right behind them) and everything before a wave is `head` of everything up to and including it, so every
+        # wave is at least `head` of the next one - enough transfer to cover
         # the next cut (cut : transfer is about 1 : 4 on NVLink 5, hence head = 1/4).  Measured on config 4 (bench.py):
         # two waves 13.4 -> 12.4 ms at 2 GPUs, 7.85 -> 7.24 at 4, 4.60 -> 4.45 at 8 - less than the cut it hides, because
         # the cut and the transfer slow each other down; three waves gain nothing over two.
         default_waves = os.environ.get("ETL_EXCHANGE_WAVES", "2")
         W = self.waves = max(1, min(int(default_waves) if waves is None else int(waves), 6))
-        head = min(0.5, max(0.01, float(os.environ.get("ETL_EXCHANGE_HEAD", "0.25"))))
-        fracs = [head ** (W - 1 - w) * (1.0 - head if w else 1.0) for w in range(W)] if W > 1 else [1.0]
-        fracs = [f / sum(fracs) for f in fracs]
-        bounds, acc = [0], 0.0
-        for w in range(W):
-            acc += fracs[w]
-            end = self.rows_per_rank if w == W - 1 else min(self.rows_per_rank, -(-int(acc * self.rows_per_rank) // 4096) * 4096)
-            bounds.append(max(end, bounds[-1]))
+        head = float(os.environ.get("ETL_EXCHANGE_HEAD", "0.25"))
+        fracs, bounds = plan_waves(self.rows_per_rank, W, head)
         self.wave_bounds = bounds                                      # wave w = rows [bounds[w], bounds[w + 1]) of this rank
         self.slabs = [eng.slab_capacity(max(bounds[w + 1] - bounds[w], 1) / (size * bx), self.rows_per_key) for w in range(W)]
         self.wave_groups = []

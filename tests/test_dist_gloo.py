@@ -102,3 +102,23 @@ def test_peer_layout_places_every_run_exactly_once():
                 assert first == pos
                 pos += length
             assert pos == int(m.reshape(size, size, buckets)[:, r, :].sum())
+
+
+def test_plan_waves_covers_every_row_once_with_aligned_cuts():
+    # BucketExchange's wave plan: contiguous, aligned, last wave the large one, tiny shards leave later waves empty
+    for rows in (0, 1, 1000, 4096, 4097, 1_000_003, 125_000_000, 500_000_000):
+        for waves in (1, 2, 3, 6):
+            for head in (0.25, 0.1, 0.5):
+                fracs, bounds = D.plan_waves(rows, waves, head)
+                assert len(fracs) == waves and abs(sum(fracs) - 1.0) < 1e-12
+                assert len(bounds) == waves + 1 and bounds[0] == 0 and bounds[-1] == rows
+                assert all(a <= b for a, b in zip(bounds, bounds[1:]))
+                assert all(b % 4096 == 0 or b == rows for b in bounds[1:-1])
+                if waves > 1:
+                    assert fracs[-1] == max(fracs) and abs(fracs[-1] - (1.0 - head)) < 1e-12
+                    # the rows up to and including wave w are `head` of the rows up to and including wave w + 1
+                    assert all(abs(sum(fracs[:w + 1]) - head * sum(fracs[:w + 2])) < 1e-12 for w in range(waves - 1))
+    fr, b = D.plan_waves(125_000_000, 2)
+    assert fr == [0.25, 0.75] and b == [0, 31_252_480, 125_000_000]
+    assert D.plan_waves(1000, 3)[1] == [0, 1000, 1000, 1000]
+    assert D.plan_waves(10, 0)[1] == [0, 10] and D.plan_waves(10, 2, head=7.0)[0] == [0.5, 0.5]
