@@ -97,9 +97,14 @@ class KMeansWorkload:
     pipeline_model = None
     kmeans_model = None
 
-    def __init__(self, engine: Optional[Engine] = None):
+    def __init__(self, engine: Optional[Engine] = None, repeats: Optional[int] = None, fit_kmeans: Optional[bool] = None):
+        """repeats / fit_kmeans: explicit settings for callers inside this package (the CSV twin takes the
+        one-hot block once and fits its own KMeans); None = what the reference reads from the environment
+        (MEASURE_NAME_WEIGHT, k_means.py:56-61) / ETL_SKIP_KMEANS."""
         self.logger = logging.getLogger("KMeansWorkload")
         self.engine = engine
+        self.repeats = repeats
+        self.fit_kmeans = fit_kmeans
 
     def k_means(self, input_df: DeviceTable):
         try:
@@ -132,7 +137,7 @@ class KMeansWorkload:
             means = [s / c if c else None for s, c in zip(sums, counts)]
 
             try:
-                repeats = int(os.environ.get("MEASURE_NAME_WEIGHT", "5"))                 # k_means.py:56-61
+                repeats = int(os.environ.get("MEASURE_NAME_WEIGHT", "5")) if self.repeats is None else int(self.repeats)  # k_means.py:56-61
             except Exception:
                 repeats = 5
             if repeats < 1:
@@ -160,7 +165,9 @@ class KMeansWorkload:
             eng.remap_codes(code, model._index_table(key.labels), len(labels))
             model.index, model.numerics = code, nums
             model.features_dim = repeats * len(labels) + 3
-            if os.environ.get("ETL_SKIP_KMEANS", "").lower() in ("1", "true", "yes", "y"):
+            skip = os.environ.get("ETL_SKIP_KMEANS", "").lower() in ("1", "true", "yes", "y") if self.fit_kmeans is None \
+                else not self.fit_kmeans
+            if skip:
                 return model, None
             # K-Means Model Training (k_means.py:83-87)
             from .kmeans import KMeans

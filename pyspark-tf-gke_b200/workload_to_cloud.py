@@ -33,18 +33,9 @@ def run(source, model_dir: Optional[str] = None, engine: Optional[Engine] = None
         print(f" |-- {name}: {kind} (nullable = true)")
     print(f"Total number of rows: {health_df.rows}")
     # the stage itself is k_means.py's, with the one-hot block used once (feature_cols = [vec] + numerics, :98)
-    saved = os.environ.get("MEASURE_NAME_WEIGHT"), os.environ.get("ETL_SKIP_KMEANS")
-    os.environ["MEASURE_NAME_WEIGHT"], os.environ["ETL_SKIP_KMEANS"] = "1", "1"
-    try:
-        print("Checking for missing values in 'measure_name'...")
-        wl = KMeansWorkload(eng)
-        pipeline_model, _ = wl.k_means(health_df)
-    finally:
-        for key, val in zip(("MEASURE_NAME_WEIGHT", "ETL_SKIP_KMEANS"), saved):
-            if val is None:
-                os.environ.pop(key, None)
-            else:
-                os.environ[key] = val
+    print("Checking for missing values in 'measure_name'...")
+    wl = KMeansWorkload(eng, repeats=1, fit_kmeans=False)
+    pipeline_model, _ = wl.k_means(health_df)
     print(f"Column 'measure_name' has {pipeline_model.null_key_count} missing values")
     print(f"Rows after filtering out missing 'measure_name' values: {pipeline_model.rows_after_filter}")
     print("Applying feature engineering pipeline...")
