@@ -39,7 +39,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--buckets", type=int, default=-1, help="table buckets per rank (-1 = choose from the table size)")
     ap.add_argument("--exchange", default="bucketed", choices=["bucketed", "peer", "nccl"],
-                    help="bucketed = local (rank, bucket) partition + copy-engine slab copies, merge behind the transfer; "
+                    help="bucketed = local (rank, bucket) partition in waves + slab copies over NVLink, merge behind the transfer; "
                          "peer = partition fused with NVLink peer stores (chunked slabs, or counted with --counted); "
                          "nccl = send buffer + all_to_all_single")
     ap.add_argument("--bucket-groups", type=int, default=8)
