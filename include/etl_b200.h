@@ -465,9 +465,12 @@ ETL_API int etl_groupby_merge_partitioned(etl_handle* h, const int64_t* records,
  *     all sources of a bucket scattering into that bucket's `sub` pieces.
  *   etl_groupby_merge_slabs: etl_groupby_merge_partitioned over slabs: piece f =
  *     records [f * piece_capacity, + min(d_cursor[f], piece_capacity)), for the
- *     pieces piece0 .. piece0 + pieces - 1; append != 0 keeps d_counters and appends
- *     to the groups already in the output (bucket groups merged one after another
- *     while later ones are still crossing NVLink).
+ *     pieces piece0 .. piece0 + pieces - 1; `append` is a flag word: bit 0 keeps
+ *     d_counters and appends to the groups already in the output (bucket groups
+ *     merged one after another while later ones are still crossing NVLink); bit 1
+ *     says the launch shares the SMs with a concurrent transfer kernel
+ *     (etl_peer_copy_slabs): it then runs 512-thread CTAs, which leave registers
+ *     for the copy CTAs, instead of the 640-thread CTAs a launch on its own gets.
  *   etl_peer_publish_counts: peer_tables[r][slot + j] = d_cursor[r * per_rank + j]
  *     for every rank r and j < per_rank (system-scope release stores; follow with a
  *     cross-rank barrier) - how a receiver learns how much of each source's slabs is

@@ -31,7 +31,8 @@ constexpr uint64_t MG_EMPTY = 0x8000000000000000ull;  // same reserved key as th
 constexpr int SUB_TILE = 2048;
 constexpr int SUB_THREADS = 256;
 constexpr int SUB_MAX = 256;         // pieces per level-A bucket
-constexpr int MG_THREADS = 512;
+constexpr int MG_THREADS = 640;         // a launch that has the SMs to itself: 2 x 640 threads x 48 registers = 60 K of 64 K
+constexpr int MG_THREADS_SHARED = 512;  // a launch beside the exchange's copy kernel: 48 K, room for the copy CTAs (slabs.cu)
 constexpr int MG_MAX_PROBES = 48;
 constexpr int MG_UNROLL = 4;
 
@@ -149,9 +150,11 @@ __device__ __forceinline__ void merge_one(const MergeParams& p, uint64_t* skey, 
     if ((int64_t)at < p.spill_capacity) p.spill[at] = r;
 }
 
-// 48 registers: two CTAs take 48 K of the SM's 64 K registers, which leaves room for the exchange's copy CTAs
-// (slabs.cu) to sit beside the merge of the bucket groups that have already landed
-template <bool MINMAX>
+// 48 registers, two CTAs per SM.  THREADS = 512: 48 K of the SM's 64 K registers, which leaves room for the exchange's
+// copy CTAs (slabs.cu) to sit beside the merge of the bucket groups that have already landed (measured at 2 GPUs:
+// 12.5 ms, against 13.1 with the 640-thread CTAs that keep the copy kernel off the SM).  THREADS = 640: 40 warps per SM
+// instead of 32 for the shared-memory atomics' latency - config 4 on one GPU 7.9 -> 7.4 ms.
+template <bool MINMAX, int THREADS>
 __global__ void __maxnreg__(48) groupby_merge_kernel(const MergeParams p) {
     extern __shared__ __align__(16) unsigned char mg_smem[];
     const int S = p.slots;
@@ -160,7 +163,7 @@ __global__ void __maxnreg__(48) groupby_merge_kernel(const MergeParams p) {
     uint64_t* smin = reinterpret_cast<uint64_t*>(ssum + S);
     uint64_t* smax = smin + (MINMAX ? S : 0);
     uint32_t* srows = reinterpret_cast<uint32_t*>(smax + (MINMAX ? S : 0));
-    __shared__ unsigned s_warp[MG_THREADS / 32];
+    __shared__ unsigned s_warp[THREADS / 32];
     __shared__ unsigned long long s_base;
     const uint32_t mask = (uint32_t)S - 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -174,7 +177,7 @@ __global__ void __maxnreg__(48) groupby_merge_kernel(const MergeParams p) {
             cnt = p.fine_counts[f];
         }
         if (cnt == 0) continue;  // the same for every thread of the CTA
-        for (int i = threadIdx.x; i < S; i += MG_THREADS) {
+        for (int i = threadIdx.x; i < S; i += THREADS) {
             skey[i] = MG_EMPTY;
             ssum[i] = 0.0;
             srows[i] = 0u;
@@ -183,30 +186,30 @@ __global__ void __maxnreg__(48) groupby_merge_kernel(const MergeParams p) {
         __syncthreads();
         const longlong2* rec = p.rec + lo;
         int64_t i = threadIdx.x;
-        for (; i + (MG_UNROLL - 1) * MG_THREADS < cnt; i += MG_UNROLL * MG_THREADS) {
+        for (; i + (MG_UNROLL - 1) * THREADS < cnt; i += MG_UNROLL * THREADS) {
             longlong2 r[MG_UNROLL];
 #pragma unroll
-            for (int j = 0; j < MG_UNROLL; ++j) r[j] = ld_record(rec + i + j * MG_THREADS);
+            for (int j = 0; j < MG_UNROLL; ++j) r[j] = ld_record(rec + i + j * THREADS);
 #pragma unroll
             for (int j = 0; j < MG_UNROLL; ++j) merge_one<MINMAX>(p, skey, ssum, smin, smax, srows, mask, r[j]);
         }
-        for (; i < cnt; i += MG_THREADS) merge_one<MINMAX>(p, skey, ssum, smin, smax, srows, mask, ld_record(rec + i));
+        for (; i < cnt; i += THREADS) merge_one<MINMAX>(p, skey, ssum, smin, smax, srows, mask, ld_record(rec + i));
         __syncthreads();
         // append the used slots: count per warp, one global atomic per CTA, then warp-ordered writes
         unsigned mine = 0;
-        for (int s = threadIdx.x; s < S; s += MG_THREADS) mine += skey[s] != MG_EMPTY;
+        for (int s = threadIdx.x; s < S; s += THREADS) mine += skey[s] != MG_EMPTY;
         mine = __reduce_add_sync(0xffffffffu, mine);
         if (lane == 0) s_warp[warp] = mine;
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned run = 0;
 #pragma unroll
-            for (int w = 0; w < MG_THREADS / 32; ++w) { const unsigned c = s_warp[w]; s_warp[w] = run; run += c; }
+            for (int w = 0; w < THREADS / 32; ++w) { const unsigned c = s_warp[w]; s_warp[w] = run; run += c; }
             s_base = run ? atomicAdd(p.groups, (unsigned long long)run) : 0ull;
         }
         __syncthreads();
         int64_t run = (int64_t)s_base + s_warp[warp];
-        for (int s = threadIdx.x; s < S; s += MG_THREADS) {
+        for (int s = threadIdx.x; s < S; s += THREADS) {
             const uint64_t key = skey[s];
             const bool used = key != MG_EMPTY;
             const unsigned bal = __ballot_sync(0xffffffffu, used);
@@ -276,7 +279,7 @@ extern "C" int etl_hash_subpartition(etl_handle* hh, const int64_t* records, int
     return ETL_OK;
 }
 
-static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t piece0, int32_t fine, bool append,
+static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t piece0, int32_t fine, bool append, bool shared_sms,
                         const int64_t* d_fine_counts, const int64_t* d_fine_base, int64_t piece_cap, int32_t smem_slots,
                         int64_t out_capacity,
                         int64_t* out_keys, int64_t* out_rows, int64_t* out_count, double* out_sum, double* out_min,
@@ -310,16 +313,21 @@ static int merge_pieces(etl_handle* hh, const int64_t* records, int32_t piece0, 
     p.groups = ctr; p.spilled = ctr + 1; p.status = ctr + 2;   // status[1] = ctr[3]: reserved-key records
     p.spill = reinterpret_cast<longlong2*>(spill_records); p.spill_capacity = spill_capacity;
     const size_t smem = (size_t)smem_slots * (minmax ? 36 : 20);
-    auto kern = minmax ? etl::groupby_merge_kernel<true> : etl::groupby_merge_kernel<false>;
+    static const int env_threads = [] { const char* e = getenv("ETL_MERGE_THREADS"); return e && *e ? atoi(e) : 0; }();
+    const int threads = env_threads == etl::MG_THREADS || env_threads == etl::MG_THREADS_SHARED
+                            ? env_threads : (shared_sms ? etl::MG_THREADS_SHARED : etl::MG_THREADS);
+    const bool wide = threads == etl::MG_THREADS;
+    auto kern = minmax ? (wide ? etl::groupby_merge_kernel<true, etl::MG_THREADS> : etl::groupby_merge_kernel<true, etl::MG_THREADS_SHARED>)
+                       : (wide ? etl::groupby_merge_kernel<false, etl::MG_THREADS> : etl::groupby_merge_kernel<false, etl::MG_THREADS_SHARED>);
     ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (const int carve = etl::smem_carveout_percent(); carve >= 0)
         ETL_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     int occ = 0;
-    ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, etl::MG_THREADS, smem));
+    ETL_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
     if (occ < 1) occ = 1;
     int64_t blocks = (int64_t)h->sm_count * occ;
     if (blocks > fine) blocks = fine;
-    kern<<<(unsigned)blocks, etl::MG_THREADS, smem, stream>>>(p);
+    kern<<<(unsigned)blocks, threads, smem, stream>>>(p);
     ETL_CUDA(cudaGetLastError());
     return ETL_OK;
 }
@@ -331,7 +339,7 @@ extern "C" int etl_groupby_merge_partitioned(etl_handle* hh, const int64_t* reco
                                              double* out_max, int64_t* spill_records, int64_t spill_capacity,
                                              int64_t* d_counters, void* stream_) {
     ETL_REQUIRE(d_fine_base != nullptr, "groupby_merge_partitioned: NULL argument");
-    return merge_pieces(hh, records, 0, fine, false, d_fine_counts, d_fine_base, 0, smem_slots, out_capacity, out_keys, out_rows,
+    return merge_pieces(hh, records, 0, fine, false, false, d_fine_counts, d_fine_base, 0, smem_slots, out_capacity, out_keys, out_rows,
                         out_count, out_sum, out_min, out_max, spill_records, spill_capacity, d_counters, stream_);
 }
 
@@ -341,6 +349,6 @@ extern "C" int etl_groupby_merge_slabs(etl_handle* hh, const int64_t* records, i
                                        double* out_min, double* out_max, int64_t* spill_records, int64_t spill_capacity,
                                        int64_t* d_counters, void* stream_) {
     ETL_REQUIRE(piece_capacity > 0, "groupby_merge_slabs: piece_capacity must be > 0");
-    return merge_pieces(hh, records, piece0, pieces, append != 0, d_cursor, nullptr, piece_capacity, smem_slots, out_capacity, out_keys, out_rows,
+    return merge_pieces(hh, records, piece0, pieces, (append & 1) != 0, (append & 2) != 0, d_cursor, nullptr, piece_capacity, smem_slots, out_capacity, out_keys, out_rows,
                         out_count, out_sum, out_min, out_max, spill_records, spill_capacity, d_counters, stream_);
 }

@@ -427,7 +427,8 @@ class BucketExchange:
                     eng.slab_partition_records(self.recv[w], bpg * size, slab, self.counts[w], None, slab, bx, self.sub, self.pieces,
                                                self.cap2, cur2, pg.counters[4:], sources=size, bucket0=g * bpg)
                     if w == W - 1:        # every wave's records of this group are in the pieces now
-                        eng.merge_slab_pieces(self.pieces, cur2, self.cap2, g * bpg * self.sub, bpg * self.sub, g > 0, pg)
+                        eng.merge_slab_pieces(self.pieces, cur2, self.cap2, g * bpg * self.sub, bpg * self.sub, g > 0, pg,
+                                              shared_sms=True)
 
         w, pos = 0, 0
         for keys, vals, n, ready in chunk_iter:

@@ -598,13 +598,14 @@ class Engine:
         _lib.check(self.lib.etl_copy_async(self._h, dst_ptr, src_ptr, nbytes, self._stream()))
 
     def merge_slab_pieces(self, pieces: torch.Tensor, cursor: torch.Tensor, piece_capacity: int, piece0: int, count: int,
-                          append: bool, pg: "PartitionedGroups", slots: Optional[int] = None) -> None:
+                          append: bool, pg: "PartitionedGroups", slots: Optional[int] = None, shared_sms: bool = False) -> None:
         """Shared-memory merge of the piece slabs piece0 .. piece0 + count - 1 into pg's output columns
-        (append: after the groups earlier calls left there)."""
+        (append: after the groups earlier calls left there; shared_sms: the launch runs beside the exchange's
+        copy kernel and keeps to 512-thread CTAs so that the copy CTAs fit on the same SMs)."""
         slots = slots or self.MERGE_SLOTS
         minmax = pg.min is not None
         _lib.check(self.lib.etl_groupby_merge_slabs(
-            self._h, pieces.data_ptr(), piece0, count, int(append), cursor.data_ptr(), piece_capacity,
+            self._h, pieces.data_ptr(), piece0, count, int(bool(append)) | (2 if shared_sms else 0), cursor.data_ptr(), piece_capacity,
             min(slots, 4096) if minmax else slots, pg.capacity, pg.keys.data_ptr(), pg.rows.data_ptr(), pg.count.data_ptr(),
             pg.sum.data_ptr(), _ptr(pg.min), _ptr(pg.max), pg.spill.data_ptr(), pg.spill.shape[0], pg.counters.data_ptr(),
             self._stream()))
