@@ -48,3 +48,34 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     lib = pkg._lib.load()
     assert lib.etl_reserve(None, 0) == -1
     assert b"NULL" in lib.etl_last_error()
+
+
+def _declared_params():
+    """name -> list of parameter declarations, from the header text."""
+    with open(os.path.join(ROOT, "include", "etl_b200.h")) as fh:
+        text = re.sub(r"/\*.*?\*/", " ", fh.read(), flags=re.S)
+    out = {}
+    for m in re.finditer(r"ETL_API\s+[\w\s\*]+?\b(etl_\w+)\s*\(([^;]*?)\)\s*;", text, flags=re.S):
+        params = [p.strip() for p in m.group(2).split(",")]
+        out[m.group(1)] = [] if params == ["void"] or params == [""] else params
+    return out
+
+
+def test_binding_prototypes_match_the_header():
+    # every ctypes prototype has as many arguments as the declaration, pointers where the header has pointers /
+    # arrays, and 64-bit integers where the header says int64_t (a drifted prototype corrupts a call silently)
+    decl = _declared_params()
+    assert sorted(decl) == _declared()
+    for name, (_, args) in pkg._lib._PROTOS.items():
+        params = decl[name]
+        assert len(args) == len(params), f"{name}: {len(args)} ctypes arguments, {len(params)} in etl_b200.h"
+        for a, p in zip(args, params):
+            is_ptr = "*" in p or "[" in p
+            if is_ptr:
+                assert a in (ctypes.c_void_p, ctypes.c_char_p) or issubclass(a, (ctypes._Pointer, ctypes.Array)), (name, p, a)
+            elif re.match(r"^(const\s+)?int64_t\b", p):
+                assert a is ctypes.c_int64, (name, p, a)
+            elif re.match(r"^(const\s+)?int32_t\b", p) or re.match(r"^(const\s+)?int\b", p):
+                assert a in (ctypes.c_int32, ctypes.c_int), (name, p, a)
+            elif re.match(r"^(const\s+)?double\b", p):
+                assert a is ctypes.c_double, (name, p, a)
