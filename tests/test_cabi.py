@@ -79,3 +79,21 @@ def test_binding_prototypes_match_the_header():
                 assert a in (ctypes.c_int32, ctypes.c_int), (name, p, a)
             elif re.match(r"^(const\s+)?double\b", p):
                 assert a is ctypes.c_double, (name, p, a)
+
+
+def test_header_is_plain_c_and_cxx(tmp_path):
+    # the boundary is a C ABI: the header must compile as C99 and as C++17 with nothing but the standard headers,
+    # and the torch-free native caller must compile against it (it is built and RUN by tests/test_gpu_native_caller.py)
+    import shutil
+    import subprocess
+
+    hdr = os.path.join(ROOT, "include", "etl_b200.h")
+    if shutil.which("gcc"):
+        subprocess.run(["gcc", "-fsyntax-only", "-x", "c", "-std=c99", "-Wall", "-Werror", hdr], check=True)
+    if shutil.which("g++"):
+        subprocess.run(["g++", "-fsyntax-only", "-x", "c++", "-std=c++17", "-Wall", "-Werror", hdr], check=True)
+        caller = os.path.join(ROOT, "tests", "native", "cabi_caller.cpp")
+        cuda_inc = "/usr/local/cuda/include"
+        if os.path.isdir(cuda_inc):
+            subprocess.run(["g++", "-fsyntax-only", "-std=c++17", "-I", os.path.join(ROOT, "include"), "-I", cuda_inc, caller],
+                           check=True)
