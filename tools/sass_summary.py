@@ -5,7 +5,7 @@
 (the fp64 add loop), ATOMS.POPC / ATOMS.ADD = native 32-bit shared atomics, REDG / ATOMG = global reductions / atomics,
 VOTE / MATCH / REDUX / SHFL = warp collectives, LDL / STL = local memory (spills).
 
-    python tools/sass_summary.py > profiles/r02_sass_mnemonics.txt
+    python tools/sass_summary.py > profiles/r02_sass_mnemonics.txt      (round 1: profiles/r01_sass_mnemonics.txt, counts only)
 """
 import collections
 import os
